@@ -1,0 +1,134 @@
+/*
+ * nbody_b200.h -- C ABI of the B200-native force-evaluation + Velocity-Verlet engine.
+ *
+ * This is the drop-in boundary for LessUp/n-body's hot path: every entry point replaces one
+ * reference interface (cited as file:line, paths relative to the reference checkout).  Plain C:
+ * raw device/host pointers, sizes, scalars and an opaque stream handle (cudaStream_t passed as
+ * void*; NULL = legacy default stream, which is what the reference uses everywhere).  No C++
+ * types and no exceptions cross this boundary; include/nbody/ *.hpp wraps it in the reference's
+ * class names and turns return codes back into the reference's exception types.
+ *
+ * Return value: 0 on success; > 0 is a cudaError_t; < 0 is one of NB_ERR_*.  nb_last_error()
+ * gives the message of the calling thread's last failure.
+ *
+ * There is no CPU fallback: every compute entry point needs a CUDA device of compute capability
+ * 10.x and fails with NB_ERR_NO_DEVICE otherwise.
+ */
+#ifndef NBODY_B200_H
+#define NBODY_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NB_OK 0
+#define NB_ERR_INVALID (-1)     /* bad argument (maps to nbody::ValidationException)                 */
+#define NB_ERR_NO_DEVICE (-2)   /* no sm_100 device / library built without a usable kernel image     */
+#define NB_ERR_RESOURCE (-3)    /* allocation failed (maps to nbody::ResourceException)               */
+#define NB_ERR_GRID_TOO_LARGE (-4) /* spatial hash > 1e8 cells: src/cuda/force_spatial_hash.cu:252-254 (std::runtime_error) */
+#define NB_ERR_NCCL (-5)        /* NCCL failure in the multi-GPU path                                  */
+#define NB_ERR_INTERNAL (-6)
+
+typedef struct nb_context nb_context; /* one per device; owns all scratch; NOT thread-safe
+                                         (same contract as include/nbody/force_calculator.hpp:8-20) */
+typedef void* nb_stream;              /* cudaStream_t */
+
+/* Same layout as nbody::ParticleData (include/nbody/types.hpp:234-276): 13 float* then count,
+ * 112 bytes, so a `ParticleData*` can be passed as `nb_particles*` unchanged.  The 13 arrays are
+ * caller-owned, separately allocated, and never freed or reallocated by this library. */
+typedef struct nb_particles {
+  float *pos_x, *pos_y, *pos_z;
+  float *vel_x, *vel_y, *vel_z;
+  float *acc_x, *acc_y, *acc_z;
+  float *acc_old_x, *acc_old_y, *acc_old_z;
+  float* mass;
+  size_t count;
+} nb_particles;
+
+/* ---- library / context ------------------------------------------------------------------- */
+int nb_version(void);
+const char* nb_last_error(void);
+/* device query used by validateResourceRequirements (src/utils/error_handling.cpp:25-44) */
+int nb_device_info(int device, int* sm_count, int* cc_major, int* cc_minor, size_t* total_mem, int* clock_khz);
+int nb_context_create(int device, size_t max_bodies_hint, nb_context** out);
+int nb_context_destroy(nb_context* ctx);
+int nb_context_sm_count(const nb_context* ctx);
+int nb_synchronize(nb_context* ctx, nb_stream stream);
+/* number of this library's kernels launched through ctx since creation (bench.py gpu_launches) */
+uint64_t nb_launch_count(const nb_context* ctx);
+
+/* ---- ParticleDataManager (src/cuda/particle_init.cu:143-283) ------------------------------ */
+int nb_particles_alloc_device(nb_particles* d, size_t count); /* :143-168, acc/acc_old zeroed   */
+int nb_particles_free_device(nb_particles* d);                /* :170-198                        */
+int nb_particles_upload(nb_context* ctx, nb_particles* d, const nb_particles* h, nb_stream s);   /* :257-269: pos, vel, acc, mass (acc_old not copied) */
+int nb_particles_download(nb_context* ctx, nb_particles* h, const nb_particles* d, nb_stream s); /* :271-283 */
+
+/* ---- direct N^2: DirectForceCalculator::computeForces -> launchDirectForceKernel
+ *      (src/cuda/force_direct.cu:103-106, 88-98, 10-85).  Overwrites acc_x/y/z only. --------- */
+int nb_direct_forces(nb_context* ctx, const nb_particles* d, float G, float eps2, nb_stream s);
+
+/* ---- Integrator (src/cuda/integrator.cu) --------------------------------------------------- */
+int nb_store_accelerations(nb_context* ctx, const nb_particles* d, nb_stream s);   /* :248-250, :39-48 */
+int nb_update_positions(nb_context* ctx, const nb_particles* d, float dt, nb_stream s);  /* :240-242, :11-21 */
+int nb_update_velocities(nb_context* ctx, const nb_particles* d, float dt, nb_stream s); /* :244-246, :24-36 */
+/* Integrator::integrate with a DirectForceCalculator, fused (:224-238): store+drift+pack, force,
+ * reduce+kick.  Post-state identical to the 4-call sequence. */
+int nb_step_direct(nb_context* ctx, const nb_particles* d, float dt, float G, float eps2, nb_stream s);
+/* Integrator::compute{Kinetic,Potential}Energy (:252-289), fp64 accumulation; synchronises. */
+int nb_kinetic_energy(nb_context* ctx, const nb_particles* d, double* ke, nb_stream s);
+int nb_potential_energy(nb_context* ctx, const nb_particles* d, float G, float eps, double* pe, nb_stream s);
+
+/* ---- host-buffer entry points (what bench.py's e2e times): host SoA in, host SoA out, H2D and
+ *      D2H inside the call.  Equivalent to ParticleSystem::setState -> update x steps -> getState
+ *      (src/core/particle_system.cpp:240-292, 115-127, 213-238) without re-allocation. ---------- */
+int nb_host_direct_forces(nb_context* ctx, const nb_particles* h, float G, float eps2);
+int nb_host_step_direct(nb_context* ctx, nb_particles* h, float dt, float G, float eps2, int steps,
+                        int recompute_initial_forces);
+
+/* ---- Barnes-Hut: BarnesHutTree::build / computeForces (src/cuda/force_barnes_hut.cu:282-289,
+ *      488-498), BarnesHutCalculator::computeForces (:526-532).  Tree rebuilt on the GPU. ------- */
+int nb_bh_build(nb_context* ctx, const nb_particles* d, nb_stream s);
+int nb_bh_forces(nb_context* ctx, const nb_particles* d, float theta, float G, float eps, nb_stream s);
+/* exports for parity tests / getTree(): host buffers, may be NULL to skip.  keys/perm = sorted
+ * Morton keys and sort permutation (n each); left/right/prefix = n-1 internal nodes; parent and
+ * node_com (x,y,z,m) = 2n-1 nodes; bbox = {minx,miny,minz,maxx,maxy,maxz}. */
+int nb_bh_export(nb_context* ctx, uint32_t* keys, int32_t* perm, int32_t* left, int32_t* right,
+                 int32_t* parent, int32_t* prefix, float* node_com, float* bbox);
+int nb_bh_stats(nb_context* ctx, uint64_t* interactions, int* node_count);
+
+/* ---- spatial hash: SpatialHashGrid::build / computeForces (src/cuda/force_spatial_hash.cu:235-316),
+ *      SpatialHashCalculator::computeForces (:370-377). ------------------------------------------ */
+int nb_sh_build(nb_context* ctx, const nb_particles* d, float cell_size, nb_stream s);
+int nb_sh_forces(nb_context* ctx, const nb_particles* d, float cutoff, float G, float eps, nb_stream s);
+/* copyCellDataToHost (:318-335) + getGridDims/getTotalCells; NULL to skip. */
+int nb_sh_export(nb_context* ctx, int32_t dims[3], float bbox_padded[6], int32_t* particle_cell,
+                 int32_t* cell_start, int32_t* cell_end, int32_t* sorted_indices);
+int nb_sh_total_cells(nb_context* ctx, int* total_cells);
+
+/* ---- stand-alone primitives (exported for tests and reuse) ---------------------------------- */
+/* stable LSD radix sort of (u32 key, i32 value) pairs on device; replaces thrust::sort_by_key
+ * (src/cuda/force_barnes_hut.cu:276-280).  end_bit <= 32, begin_bit = 0. */
+int nb_sort_pairs(nb_context* ctx, uint32_t* d_keys, int32_t* d_vals, size_t n, int end_bit, nb_stream s);
+/* bbox kernel (src/cuda/force_barnes_hut.cu:218-258); out = 6 host floats; synchronises. */
+int nb_bounding_box(nb_context* ctx, const nb_particles* d, float out[6], nb_stream s);
+
+/* ---- multi-GPU direct N^2 (no counterpart in the reference; target-sharded) ---
+ * The caller (one process per GPU) provides the exchange: `gathered_src` is this rank's replicated
+ * packed source buffer.  Flow per step: nb_mgpu_pack_local -> (all-gather of the local slice, any
+ * transport, on comm stream) -> nb_mgpu_forces_local (own slice as sources, overlaps the gather) ->
+ * nb_mgpu_forces_remote (all other slices, after the gather) -> nb_mgpu_finish (reduce [+kick]). */
+int nb_mgpu_layout(nb_context* ctx, size_t n_total, int rank, int nranks, size_t* slice_begin,
+                   size_t* slice_count, size_t* padded_slice, size_t* packed_bytes_total);
+int nb_mgpu_pack_local(nb_context* ctx, const nb_particles* d_local, float* gathered_src, float dt,
+                       float G, int do_drift, nb_stream s);
+int nb_mgpu_forces_local(nb_context* ctx, const float* gathered_src, float eps2, nb_stream s);
+int nb_mgpu_forces_remote(nb_context* ctx, const float* gathered_src, float eps2, nb_stream s);
+int nb_mgpu_finish(nb_context* ctx, const nb_particles* d_local, float dt, int do_kick, nb_stream s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NBODY_B200_H */

@@ -1,0 +1,17 @@
+"""nbody_b200 -- B200-native force-evaluation + Velocity-Verlet path behind LessUp/n-body's
+ForceCalculator / ParticleSystem / SimulationConfig API.
+
+Layout:  csrc/        hand-written CUDA for sm_100a + the C ABI (include/nbody_b200.h)
+         _lib.py      ctypes loader (fails loudly when libnbody_b200.so is missing)
+         api.py       Python mirror of the reference's classes over the C ABI
+         ics.py       synthetic initial conditions (Plummer, uniform sphere/box, disk)
+         dist.py      one-process-per-GPU target sharding for direct N^2 (torch.distributed)
+"""
+from .api import (  # noqa: F401
+    BarnesHutCalculator, Context, CudaException, DirectForceCalculator, ForceCalculator, ForceMethod,
+    InitDistribution, Integrator, ParticleData, ParticleDataManager, ParticleSystem, ResourceException,
+    SimulationConfig, SimulationState, SpatialHashCalculator, ValidationException, createForceCalculator,
+    get_context, validateSimulationConfig,
+)
+
+__version__ = "0.1.0"

@@ -1,0 +1,359 @@
+// c_api.cu -- the extern "C" boundary declared in include/nbody_b200.h: context, error plumbing,
+// ParticleDataManager equivalents, and the direct / integrator / host-buffer / multi-GPU entry
+// points.  Barnes-Hut, spatial hash, sort and bbox entry points live next to their kernels.
+#include <cstdarg>
+#include <cstring>
+#include <new>
+
+#include "common.cuh"
+
+namespace nb {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof g_err, fmt, ap);
+  va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
+  set_error("CUDA Error: %s (%s) at %s:%d", cudaGetErrorString(e), what, file, line);
+  cudaGetLastError();  // clear sticky-free errors
+  return (int)e;
+}
+
+int DevBuf::ensure(size_t bytes) {
+  if (bytes <= cap) return NB_OK;
+  if (p) {
+    cudaError_t e = cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFree", __FILE__, __LINE__);
+  }
+  size_t want = bytes + bytes / 8 + 256;
+  cudaError_t e = cudaMalloc(&p, want);
+  if (e != cudaSuccess) {
+    p = nullptr;
+    set_error("Insufficient GPU memory - Required: %zu bytes", want);
+    cudaGetLastError();
+    return NB_ERR_RESOURCE;
+  }
+  cap = want;
+  return NB_OK;
+}
+
+void DevBuf::release() {
+  if (p) cudaFree(p);
+  p = nullptr;
+  cap = 0;
+}
+
+// implemented in the kernel files
+int direct_run(nb_context* ctx, const nb_particles* d, float dt, float G, float eps2, bool step, cudaStream_t st);
+int launch_store_acc(nb_context* ctx, const nb_particles* d, cudaStream_t st);
+int launch_drift(nb_context* ctx, const nb_particles* d, float dt, cudaStream_t st);
+int launch_kick(nb_context* ctx, const nb_particles* d, float dt, cudaStream_t st);
+int kinetic_energy(nb_context* ctx, const nb_particles* d, double* ke, cudaStream_t st);
+int potential_energy(nb_context* ctx, const nb_particles* d, float G, float eps, double* pe, cudaStream_t st);
+void bh_destroy(nb_context* ctx);
+void sh_destroy(nb_context* ctx);
+
+static int check_ctx(nb_context* ctx) {
+  if (!ctx) {
+    set_error("null context");
+    return NB_ERR_INVALID;
+  }
+  cudaError_t e = cudaSetDevice(ctx->device);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaSetDevice", __FILE__, __LINE__);
+  return NB_OK;
+}
+
+static int check_particles(const nb_particles* d, bool need_vel) {
+  if (!d) {
+    set_error("null particle data");
+    return NB_ERR_INVALID;
+  }
+  if (d->count == 0) return NB_OK;
+  if (!d->pos_x || !d->pos_y || !d->pos_z || !d->mass || !d->acc_x || !d->acc_y || !d->acc_z) {
+    set_error("particle data has null position/mass/acceleration arrays");
+    return NB_ERR_INVALID;
+  }
+  if (need_vel && (!d->vel_x || !d->vel_y || !d->vel_z || !d->acc_old_x || !d->acc_old_y || !d->acc_old_z)) {
+    set_error("particle data has null velocity/acc_old arrays");
+    return NB_ERR_INVALID;
+  }
+  return NB_OK;
+}
+
+}  // namespace nb
+
+using namespace nb;
+
+#define NB_ENTER(ctx)                       \
+  do {                                      \
+    if (int rc__ = check_ctx(ctx)) return rc__; \
+  } while (0)
+
+extern "C" {
+
+int nb_version(void) { return 100; }  // 0.1.0
+
+const char* nb_last_error(void) { return g_err; }
+
+int nb_device_info(int device, int* sm_count, int* cc_major, int* cc_minor, size_t* total_mem, int* clock_khz) {
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    cudaGetLastError();
+    set_error("no CUDA device available (%s); this library has no CPU fallback",
+              e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
+    return NB_ERR_NO_DEVICE;
+  }
+  cudaDeviceProp pr;
+  NB_CUDA(cudaGetDeviceProperties(&pr, device));
+  int clk = 0;
+  cudaDeviceGetAttribute(&clk, cudaDevAttrClockRate, device);
+  if (sm_count) *sm_count = pr.multiProcessorCount;
+  if (cc_major) *cc_major = pr.major;
+  if (cc_minor) *cc_minor = pr.minor;
+  if (total_mem) *total_mem = pr.totalGlobalMem;
+  if (clock_khz) *clock_khz = clk;
+  return NB_OK;
+}
+
+int nb_context_create(int device, size_t max_bodies_hint, nb_context** out) {
+  if (!out) {
+    set_error("null out pointer");
+    return NB_ERR_INVALID;
+  }
+  *out = nullptr;
+  int sms = 0, maj = 0, min = 0;
+  if (int rc = nb_device_info(device, &sms, &maj, &min, nullptr, nullptr)) return rc;
+  if (maj != 10) {
+    set_error("device %d is sm_%d%d; this library ships sm_100a code only and has no fallback", device, maj, min);
+    return NB_ERR_NO_DEVICE;
+  }
+  NB_CUDA(cudaSetDevice(device));
+  nb_context* ctx = new (std::nothrow) nb_context();
+  if (!ctx) {
+    set_error("out of host memory");
+    return NB_ERR_RESOURCE;
+  }
+  ctx->device = device;
+  ctx->sm_count = sms;
+  ctx->cc_major = maj;
+  ctx->cc_minor = min;
+  (void)max_bodies_hint;
+  *out = ctx;
+  return NB_OK;
+}
+
+int nb_context_destroy(nb_context* ctx) {
+  if (!ctx) return NB_OK;
+  cudaSetDevice(ctx->device);
+  cudaDeviceSynchronize();
+  bh_destroy(ctx);
+  sh_destroy(ctx);
+  ctx->src.release();
+  ctx->partial.release();
+  ctx->red.release();
+  ctx->sort_keys2.release();
+  ctx->sort_vals2.release();
+  ctx->sort_hist.release();
+  ctx->bbox_dev.release();
+  if (ctx->h_red) cudaFreeHost(ctx->h_red);
+  if (ctx->h_bbox) cudaFreeHost(ctx->h_bbox);
+  if (ctx->stage_cap) nb_particles_free_device(&ctx->stage);
+  if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
+  delete ctx;
+  return NB_OK;
+}
+
+int nb_context_sm_count(const nb_context* ctx) { return ctx ? ctx->sm_count : 0; }
+uint64_t nb_launch_count(const nb_context* ctx) { return ctx ? ctx->launches : 0; }
+
+int nb_synchronize(nb_context* ctx, nb_stream stream) {
+  NB_ENTER(ctx);
+  NB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  return NB_OK;
+}
+
+// ---- ParticleDataManager ---------------------------------------------------------------------
+static float** field_ptrs(nb_particles* d, float** out[13]) {
+  float** f[13] = {&d->pos_x, &d->pos_y, &d->pos_z, &d->vel_x, &d->vel_y, &d->vel_z, &d->acc_x,
+                   &d->acc_y, &d->acc_z, &d->acc_old_x, &d->acc_old_y, &d->acc_old_z, &d->mass};
+  for (int k = 0; k < 13; k++) out[k] = f[k];
+  return nullptr;
+}
+
+int nb_particles_alloc_device(nb_particles* d, size_t count) {
+  if (!d) {
+    set_error("null particle data");
+    return NB_ERR_INVALID;
+  }
+  float** f[13];
+  field_ptrs(d, f);
+  for (int k = 0; k < 13; k++) *f[k] = nullptr;
+  d->count = count;
+  const size_t bytes = (count ? count : 1) * sizeof(float);
+  for (int k = 0; k < 13; k++) {
+    cudaError_t e = cudaMalloc((void**)f[k], bytes);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      for (int j = 0; j < k; j++) cudaFree(*f[j]);
+      for (int j = 0; j < 13; j++) *f[j] = nullptr;
+      d->count = 0;
+      set_error("Insufficient GPU memory - Required: %zu bytes", bytes * 13);
+      return NB_ERR_RESOURCE;
+    }
+  }
+  for (int k = 6; k < 12; k++) NB_CUDA(cudaMemset(*f[k], 0, bytes));  // acc, acc_old (particle_init.cu:161-167)
+  return NB_OK;
+}
+
+int nb_particles_free_device(nb_particles* d) {
+  if (!d) return NB_OK;
+  float** f[13];
+  field_ptrs(d, f);
+  for (int k = 0; k < 13; k++) {
+    if (*f[k]) cudaFree(*f[k]);
+    *f[k] = nullptr;
+  }
+  d->count = 0;
+  return NB_OK;
+}
+
+static int copy_fields(nb_particles* dst, const nb_particles* src, const int* which, int nwhich, size_t n,
+                       cudaMemcpyKind kind, cudaStream_t st) {
+  float** fd[13];
+  float** fs[13];
+  field_ptrs(dst, fd);
+  field_ptrs(const_cast<nb_particles*>(src), fs);
+  for (int k = 0; k < nwhich; k++) {
+    const int w = which[k];
+    if (!*fd[w] || !*fs[w]) continue;
+    NB_CUDA(cudaMemcpyAsync(*fd[w], *fs[w], n * sizeof(float), kind, st));
+  }
+  return NB_OK;
+}
+
+int nb_particles_upload(nb_context* ctx, nb_particles* d, const nb_particles* h, nb_stream s) {
+  NB_ENTER(ctx);
+  if (!d || !h || h->count > d->count) {
+    set_error("upload: bad particle data (host count exceeds device count)");
+    return NB_ERR_INVALID;
+  }
+  static const int which[10] = {0, 1, 2, 3, 4, 5, 6, 7, 8, 12};  // particle_init.cu:257-269
+  return copy_fields(d, h, which, 10, h->count, cudaMemcpyHostToDevice, (cudaStream_t)s);
+}
+
+int nb_particles_download(nb_context* ctx, nb_particles* h, const nb_particles* d, nb_stream s) {
+  NB_ENTER(ctx);
+  if (!d || !h || d->count > h->count) {
+    set_error("download: bad particle data (device count exceeds host count)");
+    return NB_ERR_INVALID;
+  }
+  static const int which[10] = {0, 1, 2, 3, 4, 5, 6, 7, 8, 12};  // particle_init.cu:271-283
+  if (int rc = copy_fields(h, d, which, 10, d->count, cudaMemcpyDeviceToHost, (cudaStream_t)s)) return rc;
+  NB_CUDA(cudaStreamSynchronize((cudaStream_t)s));
+  return NB_OK;
+}
+
+// ---- direct / integrator ---------------------------------------------------------------------
+int nb_direct_forces(nb_context* ctx, const nb_particles* d, float G, float eps2, nb_stream s) {
+  NB_ENTER(ctx);
+  if (int rc = check_particles(d, false)) return rc;
+  return direct_run(ctx, d, 0.f, G, eps2, false, (cudaStream_t)s);
+}
+
+int nb_store_accelerations(nb_context* ctx, const nb_particles* d, nb_stream s) {
+  NB_ENTER(ctx);
+  if (int rc = check_particles(d, true)) return rc;
+  return launch_store_acc(ctx, d, (cudaStream_t)s);
+}
+int nb_update_positions(nb_context* ctx, const nb_particles* d, float dt, nb_stream s) {
+  NB_ENTER(ctx);
+  if (int rc = check_particles(d, true)) return rc;
+  return launch_drift(ctx, d, dt, (cudaStream_t)s);
+}
+int nb_update_velocities(nb_context* ctx, const nb_particles* d, float dt, nb_stream s) {
+  NB_ENTER(ctx);
+  if (int rc = check_particles(d, true)) return rc;
+  return launch_kick(ctx, d, dt, (cudaStream_t)s);
+}
+
+int nb_step_direct(nb_context* ctx, const nb_particles* d, float dt, float G, float eps2, nb_stream s) {
+  NB_ENTER(ctx);
+  if (int rc = check_particles(d, true)) return rc;
+  return direct_run(ctx, d, dt, G, eps2, true, (cudaStream_t)s);
+}
+
+int nb_kinetic_energy(nb_context* ctx, const nb_particles* d, double* ke, nb_stream s) {
+  NB_ENTER(ctx);
+  if (!ke || !d || (d->count && (!d->vel_x || !d->vel_y || !d->vel_z || !d->mass))) {
+    set_error("kinetic energy: null argument");
+    return NB_ERR_INVALID;
+  }
+  return kinetic_energy(ctx, d, ke, (cudaStream_t)s);
+}
+
+int nb_potential_energy(nb_context* ctx, const nb_particles* d, float G, float eps, double* pe, nb_stream s) {
+  NB_ENTER(ctx);
+  if (!pe || !d || (d->count && (!d->pos_x || !d->pos_y || !d->pos_z || !d->mass))) {
+    set_error("potential energy: null argument");
+    return NB_ERR_INVALID;
+  }
+  return potential_energy(ctx, d, G, eps, pe, (cudaStream_t)s);
+}
+
+// ---- host-buffer entry points ------------------------------------------------------------------
+static int ensure_stage(nb_context* ctx, size_t n) {
+  if (!ctx->own_stream) NB_CUDA(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
+  if (n <= ctx->stage_cap) {
+    ctx->stage.count = n;
+    return NB_OK;
+  }
+  if (ctx->stage_cap) nb_particles_free_device(&ctx->stage);
+  ctx->stage_cap = 0;
+  if (int rc = nb_particles_alloc_device(&ctx->stage, n)) return rc;
+  ctx->stage_cap = n;
+  return NB_OK;
+}
+
+int nb_host_direct_forces(nb_context* ctx, const nb_particles* h, float G, float eps2) {
+  NB_ENTER(ctx);
+  if (int rc = check_particles(h, false)) return rc;
+  const size_t n = h->count;
+  if (int rc = ensure_stage(ctx, n)) return rc;
+  cudaStream_t st = ctx->own_stream;
+  static const int in[4] = {0, 1, 2, 12};
+  static const int out[3] = {6, 7, 8};
+  if (int rc = copy_fields(&ctx->stage, h, in, 4, n, cudaMemcpyHostToDevice, st)) return rc;
+  if (int rc = direct_run(ctx, &ctx->stage, 0.f, G, eps2, false, st)) return rc;
+  if (int rc = copy_fields(const_cast<nb_particles*>(h), &ctx->stage, out, 3, n, cudaMemcpyDeviceToHost, st)) return rc;
+  NB_CUDA(cudaStreamSynchronize(st));
+  return NB_OK;
+}
+
+int nb_host_step_direct(nb_context* ctx, nb_particles* h, float dt, float G, float eps2, int steps,
+                        int recompute_initial_forces) {
+  NB_ENTER(ctx);
+  if (int rc = check_particles(h, true)) return rc;
+  const size_t n = h->count;
+  if (int rc = ensure_stage(ctx, n)) return rc;
+  cudaStream_t st = ctx->own_stream;
+  static const int in[10] = {0, 1, 2, 3, 4, 5, 6, 7, 8, 12};
+  static const int out[12] = {0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11};
+  if (int rc = copy_fields(&ctx->stage, h, in, 10, n, cudaMemcpyHostToDevice, st)) return rc;
+  if (recompute_initial_forces)  // ParticleSystem::setState recomputes a(0): particle_system.cpp:283
+    if (int rc = direct_run(ctx, &ctx->stage, 0.f, G, eps2, false, st)) return rc;
+  for (int k = 0; k < steps; k++)
+    if (int rc = direct_run(ctx, &ctx->stage, dt, G, eps2, true, st)) return rc;
+  if (int rc = copy_fields(h, &ctx->stage, out, 12, n, cudaMemcpyDeviceToHost, st)) return rc;
+  NB_CUDA(cudaStreamSynchronize(st));
+  return NB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,173 @@
+// common.cuh -- shared device helpers (packed f32x2 math, mbarrier/TMA bulk copy) and the
+// context definition.  sm_100a only.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+
+#include "../../include/nbody_b200.h"
+
+namespace nb {
+
+// ---- error plumbing -----------------------------------------------------------------------
+void set_error(const char* fmt, ...);
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
+
+#define NB_CUDA(call)                                                       \
+  do {                                                                      \
+    cudaError_t e__ = (call);                                               \
+    if (e__ != cudaSuccess) return nb::cuda_fail(e__, #call, __FILE__, __LINE__); \
+  } while (0)
+// launch check: cudaGetLastError only (async), like CUDA_CHECK_KERNEL in Release builds
+// (include/nbody/error_handling.hpp:116-123).
+#define NB_LAUNCH_CHECK(ctx)                                                \
+  do {                                                                      \
+    (ctx)->launches++;                                                      \
+    cudaError_t e__ = cudaGetLastError();                                   \
+    if (e__ != cudaSuccess) return nb::cuda_fail(e__, "kernel launch", __FILE__, __LINE__); \
+  } while (0)
+
+// ---- packed fp32x2 (Blackwell FFMA2 / FADD2 / FMUL2) -----------------------------------------
+typedef unsigned long long f2;  // two fp32 in one 64-bit register pair {lo, hi}
+
+__device__ __forceinline__ f2 pk(float lo, float hi) {
+  f2 r;
+  asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void upk(f2 v, float& lo, float& hi) {
+  asm("mov.b64 {%0,%1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) {
+  f2 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ f2 add2(f2 a, f2 b) {
+  f2 d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ f2 sub2(f2 a, f2 b) {
+  f2 d;
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ f2 mul2(f2 a, f2 b) {
+  f2 d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+// single MUFU.RSQ, no denormal fix-up code (the reference's rsqrtf adds an FSETP/FMUL guard,
+// SURVEY.md A.4).  Max relative error 2^-22.
+__device__ __forceinline__ float rsq(float x) {
+  float r;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
+// ---- mbarrier + 1-D TMA bulk copy (cp.async.bulk, SASS UBLKCP) --------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+// global -> shared bulk copy; bytes % 16 == 0, both addresses 16-B aligned.
+__device__ __forceinline__ void tma_load_1d(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+          smem_u32(smem_dst)),
+      "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+
+__device__ __forceinline__ float warp_min(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// ---- device buffer that only grows ---------------------------------------------------------
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  int ensure(size_t bytes);
+  void release();
+  template <typename T>
+  T* as() const { return static_cast<T*>(p); }
+};
+
+}  // namespace nb
+
+// One stream-K pass of the direct kernel (see direct.cu).
+struct nb_pass {
+  long long U;      // work units = n_itiles * UJ
+  int UJ;           // source tiles per target tile
+  int G;            // CTAs the units are split over (== gridDim.x of that launch)
+  int n_itiles;
+  size_t slot_base; // first partial slot of this pass
+};
+
+struct nb_context {
+  int device = 0;
+  int sm_count = 0;
+  int cc_major = 0, cc_minor = 0;
+  uint64_t launches = 0;
+  // direct N^2
+  nb::DevBuf src;       // packed float4 (x,y,z,G*m), tile padded
+  nb::DevBuf partial;   // stream-K partial accelerations
+  nb_pass pass[2];
+  int n_pass = 0;
+  int direct_occ[4] = {0, 0, 0, 0};  // resident CTAs/SM per kernel config (lazy)
+  // energy
+  nb::DevBuf red;       // per-CTA fp64 partials
+  double* h_red = nullptr;  // pinned
+  // host-buffer entry points
+  nb_particles stage{};  // device mirror for nb_host_*
+  size_t stage_cap = 0;
+  cudaStream_t own_stream = nullptr;
+  // Barnes-Hut
+  struct BH* bh = nullptr;
+  // spatial hash
+  struct SH* sh = nullptr;
+  // radix sort scratch
+  nb::DevBuf sort_keys2, sort_vals2, sort_hist;
+  // bbox scratch (6 ordered ints) + pinned readback
+  nb::DevBuf bbox_dev;
+  float* h_bbox = nullptr;
+  // multi-GPU
+  size_t mg_n_total = 0, mg_begin = 0, mg_count = 0, mg_padded = 0;
+  int mg_rank = 0, mg_nranks = 1;
+};

@@ -1,0 +1,20 @@
+// direct.cuh -- host-side interface of direct.cu shared with mgpu.cu.
+#pragma once
+#include "common.cuh"
+
+namespace nb {
+
+struct DirectCfg {
+  int T, I, JT;  // threads per CTA, targets per thread, sources per shared-memory tile
+  int IT() const { return T * I; }
+};
+
+const DirectCfg& direct_cfg(size_t n_total_sources);
+int launch_pack(nb_context* ctx, const nb_particles* d, float4* src, size_t n, size_t n_pad, float G, float dt,
+                bool drift, cudaStream_t st);
+int launch_direct_pass(nb_context* ctx, const DirectCfg& cfg, const float4* src, const float4* tgt, int n_itiles,
+                       int ja0, int na, int jb0, int nbt, float eps2, int pass_index, cudaStream_t st);
+int launch_reduce(nb_context* ctx, const DirectCfg& cfg, const nb_particles* d, size_t n, float dt, bool kick,
+                  cudaStream_t st);
+
+}  // namespace nb

@@ -1,0 +1,174 @@
+/*
+ * oracle/lbvh.c -- sequential restatement of the binary radix tree (Karras, "Maximizing
+ * Parallelism in the Construction of BVHs, Octrees, and k-d Trees", HPG 2012, sec. 4) that the
+ * GPU path builds from the reference's sorted Morton keys
+ * (src/cuda/force_barnes_hut.cu:113-127, :276-280), plus the bottom-up centres of mass and the
+ * group ("warp-cooperative") traversal.  The opening test and the monopole formula are the
+ * reference's (src/cuda/force_barnes_hut.cu:160-183).  TEST INFRASTRUCTURE ONLY (see oracle.h).
+ */
+#include "oracle.h"
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+static inline int clz32(uint32_t v) { return v ? __builtin_clz(v) : 32; }
+
+/* delta(i,j): length of the common prefix of keys i and j; equal keys fall back to the
+ * positions (Karras 2012, sec. 4, "duplicate keys"). Out of range -> -1. */
+static inline int delta(const uint32_t* k, int n, int i, int j) {
+  if (j < 0 || j >= n) return -1;
+  uint32_t a = k[i], b = k[j];
+  if (a == b) return 32 + clz32((uint32_t)i ^ (uint32_t)j);
+  return clz32(a ^ b);
+}
+
+void orc_lbvh_build(int n, const uint32_t* k, int32_t* left, int32_t* right, int32_t* parent,
+                    int32_t* prefix, int32_t* range_first, int32_t* range_last) {
+  if (n <= 0) return;
+  parent[0] = -1;
+  if (n == 1) return; /* single leaf = node 0, no internal nodes */
+  const int leaf0 = n - 1;
+  for (int i = 0; i < n - 1; i++) {
+    int d = (delta(k, n, i, i + 1) - delta(k, n, i, i - 1)) >= 0 ? 1 : -1;
+    int dmin = delta(k, n, i, i - d);
+    int lmax = 2;
+    while (delta(k, n, i, i + lmax * d) > dmin) lmax *= 2;
+    int l = 0;
+    for (int t = lmax / 2; t >= 1; t /= 2)
+      if (delta(k, n, i, i + (l + t) * d) > dmin) l += t;
+    int j = i + l * d;
+    int dnode = delta(k, n, i, j);
+    int s = 0, t = l;
+    do {
+      t = (t + 1) / 2;
+      if (delta(k, n, i, i + (s + t) * d) > dnode) s += t;
+    } while (t > 1);
+    int gamma = i + s * d + (d < 0 ? d : 0);
+    int lo = i < j ? i : j, hi = i < j ? j : i;
+    int lc = (lo == gamma) ? leaf0 + gamma : gamma;
+    int rc = (hi == gamma + 1) ? leaf0 + gamma + 1 : gamma + 1;
+    left[i] = lc;
+    right[i] = rc;
+    parent[lc] = i;
+    parent[rc] = i;
+    /* key bits start at bit 29: prefix in key bits = clz - 2, capped at 30 (equal keys) */
+    int p = dnode - 2;
+    prefix[i] = p > 30 ? 30 : p;
+    if (range_first) range_first[i] = lo;
+    if (range_last) range_last[i] = hi;
+  }
+}
+
+/* node ordering guarantees nothing about child > parent, so do an explicit post-order walk. */
+void orc_lbvh_com(int n, const int32_t* left, const int32_t* right, const float* sx, const float* sy,
+                  const float* sz, const float* sm, float* node_com) {
+  if (n <= 0) return;
+  const int leaf0 = n - 1;
+  for (int k = 0; k < n; k++) {
+    float* c = node_com + 4 * (size_t)(leaf0 + k);
+    c[0] = sx[k]; c[1] = sy[k]; c[2] = sz[k]; c[3] = sm[k];
+  }
+  if (n == 1) return;
+  /* iterative post-order */
+  int32_t* stack = (int32_t*)malloc(sizeof(int32_t) * 2 * (size_t)n);
+  uint8_t* done = (uint8_t*)calloc((size_t)n, 1);
+  int sp = 0;
+  stack[sp++] = 0;
+  while (sp > 0) {
+    int i = stack[sp - 1];
+    int l = left[i], r = right[i];
+    int need = 0;
+    if (l < leaf0 && !done[l]) { stack[sp++] = l; need = 1; }
+    if (r < leaf0 && !done[r]) { stack[sp++] = r; need = 1; }
+    if (need) continue;
+    sp--;
+    const float* a = node_com + 4 * (size_t)l;
+    const float* b = node_com + 4 * (size_t)r;
+    float* c = node_com + 4 * (size_t)i;
+    /* same operation order as the GPU kernel (nbody_b200/csrc/lbvh.cu: bh_com_kernel):
+     * m = ma + mb; c = (ca*ma + cb*mb) / m with separately rounded mul, add, div. */
+    float m = a[3] + b[3];
+    if (m > 0.0f) {
+      c[0] = (a[0] * a[3] + b[0] * b[3]) / m;
+      c[1] = (a[1] * a[3] + b[1] * b[3]) / m;
+      c[2] = (a[2] * a[3] + b[2] * b[3]) / m;
+    } else {
+      c[0] = a[0]; c[1] = a[1]; c[2] = a[2];
+    }
+    c[3] = m;
+    done[i] = 1;
+  }
+  free(stack);
+  free(done);
+}
+
+/* Side of the Morton cell a node with common-prefix length L lives in: the key grid splits
+ * x first, then y, then z (x is bit 2 of each triple, src/cuda/force_barnes_hut.cu:37), each
+ * axis normalised by its own extent + 0.001f (:265-267); the opening test uses the largest
+ * side, which reduces to the reference's octree cell side 2*half_size (:164) at L = 3k for a
+ * cubic box. */
+float orc_lbvh_cell_size(int L, const float bbox[6]) {
+  if (L > 30) L = 30;
+  if (L < 0) L = 0;
+  const float sx = bbox[3] - bbox[0] + 0.001f, sy = bbox[4] - bbox[1] + 0.001f, sz = bbox[5] - bbox[2] + 0.001f;
+  float ex = ldexpf(sx, -((L + 2) / 3)), ey = ldexpf(sy, -((L + 1) / 3)), ez = ldexpf(sz, -(L / 3));
+  return fmaxf(ex, fmaxf(ey, ez));
+}
+
+void orc_lbvh_forces(int n, const int32_t* left, const int32_t* right, const int32_t* prefix,
+                     const float* node_com, const float* sx, const float* sy, const float* sz,
+                     const float bbox[6], float theta, float G, float eps, int group, float* ax, float* ay,
+                     float* az, uint64_t* interactions) {
+  const float theta2 = theta * theta, eps2 = eps * eps;
+  const int leaf0 = n - 1;
+  float size2_of[31];
+  for (int L = 0; L <= 30; L++) {
+    float s = orc_lbvh_cell_size(L, bbox);
+    size2_of[L] = s * s;
+  }
+  uint64_t total = 0;
+  const int ngroups = (n + group - 1) / group;
+#pragma omp parallel for schedule(dynamic, 16) reduction(+ : total)
+  for (int g = 0; g < ngroups; g++) {
+    const int k0 = g * group, k1 = (k0 + group < n) ? k0 + group : n, cnt = k1 - k0;
+    float accx[64], accy[64], accz[64], dxs[64], dys[64], dzs[64], d2s[64];
+    for (int t = 0; t < cnt; t++) accx[t] = accy[t] = accz[t] = 0.0f;
+    int32_t stack[192];
+    int sp = 0;
+    stack[sp++] = 0;
+    while (sp > 0) {
+      const int ni = stack[--sp];
+      const float* c = node_com + 4 * (size_t)ni;
+      if (c[3] == 0.0f) continue; /* src/cuda/force_barnes_hut.cu:157-158 */
+      const int is_leaf = ni >= leaf0;
+      const float size2 = is_leaf ? 0.0f : size2_of[prefix[ni]];
+      int all_accept = 1;
+      for (int t = 0; t < cnt; t++) {
+        const int k = k0 + t;
+        float dx = c[0] - sx[k], dy = c[1] - sy[k], dz = c[2] - sz[k];
+        float d2 = fmaf(dz, dz, fmaf(dy, dy, fmaf(dx, dx, eps2)));
+        dxs[t] = dx; dys[t] = dy; dzs[t] = dz; d2s[t] = d2;
+        /* reference test: size2 / dist2 < theta2 (:167); evaluated as size2 < theta2*dist2 */
+        if (!(is_leaf || size2 < theta2 * d2)) all_accept = 0;
+      }
+      if (all_accept) {
+        for (int t = 0; t < cnt; t++) {
+          if (is_leaf && ni == leaf0 + k0 + t) continue; /* own leaf, :174 */
+          float inv = 1.0f / sqrtf(d2s[t]);
+          float f = (G * c[3]) * (inv * inv * inv);
+          accx[t] = fmaf(f, dxs[t], accx[t]);
+          accy[t] = fmaf(f, dys[t], accy[t]);
+          accz[t] = fmaf(f, dzs[t], accz[t]);
+        }
+        total += (uint64_t)cnt;
+      } else {
+        stack[sp++] = right[ni];
+        stack[sp++] = left[ni];
+      }
+    }
+    for (int t = 0; t < cnt; t++) {
+      ax[k0 + t] = accx[t]; ay[k0 + t] = accy[t]; az[k0 + t] = accz[t];
+    }
+  }
+  if (interactions) *interactions = total;
+}

@@ -1,0 +1,209 @@
+"""GPU parity: direct N^2 + Velocity Verlet + energy through the C ABI vs the CPU oracle."""
+import numpy as np
+import pytest
+
+from tests.conftest import rel_err
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-5  # BASELINE.json north_star: max relative acceleration error, fp32 direct N^2
+
+
+def _device_data(state):
+    import nbody_b200 as nb
+    h = nb.ParticleDataManager.fromState(state)
+    d = nb.ParticleData()
+    nb.ParticleDataManager.allocateDevice(d, h.count)
+    nb.ParticleDataManager.copyToDevice(d, h)
+    return d
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 31, 257, 1000, 4096, 5000, 40000])
+def test_direct_vs_oracle_f64(orc, n):
+    import nbody_b200 as nb
+    from nbody_b200 import ics
+    st = ics.plummer(n, seed=7) if n > 3 else ics.uniform_box(n, -1, 1, seed=3)
+    d = _device_data(st)
+    calc = nb.DirectForceCalculator()
+    calc.setSofteningParameter(0.01)
+    calc.computeForces(d)
+    out = d.numpy()
+    ref = orc.direct_f64(st["pos_x"], st["pos_y"], st["pos_z"], st["mass"], 1.0, 1e-4)
+    if n == 1:
+        assert out["acc_x"][0] == 0 and out["acc_y"][0] == 0 and out["acc_z"][0] == 0
+        return
+    e = rel_err((out["acc_x"], out["acc_y"], out["acc_z"]), ref)
+    assert e.max() <= TOL, f"n={n} max rel err {e.max():.3e}"
+
+
+def test_direct_two_body_anchor():
+    """tests/test_force_calculation.cpp:13-30: |F| = 1 at r = 1, eps = 0, G = m = 1."""
+    import nbody_b200 as nb
+    from nbody_b200 import ics
+    st = ics.empty_state(2)
+    st["pos_x"][:] = [0.0, 1.0]
+    st["mass"][:] = 1.0
+    d = _device_data(st)
+    calc = nb.DirectForceCalculator()
+    calc.setSofteningParameter(0.0)
+    calc.computeForces(d)
+    out = d.numpy()
+    assert abs(out["acc_x"][0] - 1.0) < 1e-6 and abs(out["acc_x"][1] + 1.0) < 1e-6
+    assert out["acc_y"][0] == 0 and out["acc_z"][0] == 0
+
+
+def test_direct_eps0_coincident_and_zero_mass():
+    import nbody_b200 as nb
+    from nbody_b200 import ics
+    st = ics.uniform_box(300, -1, 1, seed=5)
+    st["mass"][::3] = 0.0
+    d = _device_data(st)
+    calc = nb.DirectForceCalculator()
+    calc.setSofteningParameter(0.0)
+    calc.computeForces(d)
+    out = d.numpy()
+    assert np.isfinite(out["acc_x"]).all()
+    ref = __import__("oracle.bindings", fromlist=["x"]).direct_f64(st["pos_x"], st["pos_y"], st["pos_z"], st["mass"],
+                                                                   1.0, 0.0)
+    assert rel_err((out["acc_x"], out["acc_y"], out["acc_z"]), ref).max() <= TOL
+
+
+def test_direct_G_and_eps(orc):
+    import nbody_b200 as nb
+    from nbody_b200 import ics
+    st = ics.uniform_sphere(3000, 10.0, seed=11)
+    d = _device_data(st)
+    calc = nb.DirectForceCalculator()
+    calc.setGravitationalConstant(6.5)
+    calc.setSofteningParameter(0.1)
+    calc.computeForces(d)
+    out = d.numpy()
+    ref = orc.direct_f64(st["pos_x"], st["pos_y"], st["pos_z"], st["mass"], 6.5, np.float32(0.1) ** 2)
+    assert rel_err((out["acc_x"], out["acc_y"], out["acc_z"]), ref).max() <= TOL
+
+
+@pytest.mark.parametrize("fuse", [True, False])
+def test_verlet_steps_vs_oracle(orc, fuse):
+    """10 steps, fused and 4-call paths, against the fp32 oracle step (integrator.cu:224-238)."""
+    import nbody_b200 as nb
+    from nbody_b200 import ics
+    n = 2048
+    st = ics.plummer(n, seed=42)
+    d = _device_data(st)
+    calc = nb.DirectForceCalculator()
+    calc.setSofteningParameter(0.01)
+    calc.computeForces(d)
+    integ = nb.Integrator()
+    integ.fuse = fuse
+    ref = {k: v.copy() for k, v in st.items()}
+    a0 = orc.direct_f32(ref["pos_x"], ref["pos_y"], ref["pos_z"], ref["mass"], 1.0, 1e-4)
+    ref["acc_x"], ref["acc_y"], ref["acc_z"] = a0
+    for _ in range(10):
+        integ.integrate(d, calc, 1e-3)
+    orc.run_direct(ref, 1e-3, 1.0, 1e-4, 10)
+    out = d.numpy()
+    for k in ("pos_x", "pos_y", "pos_z", "vel_x", "vel_y", "vel_z"):
+        np.testing.assert_allclose(out[k], ref[k], rtol=2e-5, atol=2e-6, err_msg=k)
+    e = rel_err((out["acc_x"], out["acc_y"], out["acc_z"]), (ref["acc_x"], ref["acc_y"], ref["acc_z"]))
+    assert e.max() < 1e-4  # both sides fp32 here
+    # acc_old = a(t) of the last step start: equal to previous acc; check it is populated
+    assert np.abs(out["acc_old_x"]).max() > 0
+
+
+def test_drift_kick_bit_exact(orc):
+    """The integrator kernels reproduce the reference's rounding sequence bit for bit."""
+    import nbody_b200 as nb
+    from nbody_b200 import ics
+    n = 10007
+    rng = np.random.default_rng(1)
+    st = ics.uniform_box(n, -10, 10, seed=2)
+    for k in ("vel_x", "vel_y", "vel_z", "acc_x", "acc_y", "acc_z", "acc_old_x", "acc_old_y", "acc_old_z"):
+        st[k] = rng.standard_normal(n).astype(np.float32)
+    h = nb.ParticleDataManager.fromState(st)
+    d = nb.ParticleData()
+    nb.ParticleDataManager.allocateDevice(d, n)
+    nb.ParticleDataManager.copyToDevice(d, h)
+    integ = nb.Integrator()
+    ref = {k: v.copy() for k, v in st.items()}
+    integ.storeOldAccelerations(d)
+    integ.updatePositions(d, 0.0123)
+    integ.updateVelocities(d, 0.0123)
+    orc.store_acc(ref)
+    orc.drift(ref, np.float32(0.0123))
+    orc.kick(ref, np.float32(0.0123))
+    out = d.numpy()
+    for k in ("pos_x", "pos_y", "pos_z", "vel_x", "vel_y", "vel_z", "acc_old_x", "acc_old_y", "acc_old_z"):
+        assert np.array_equal(out[k], ref[k]), k
+
+
+def test_integrator_anchors():
+    """tests/test_integrator.cpp:15-49 (x = 0.1 after dt = 0.1, v = 1) and :51-84 (KE = 4.5)."""
+    import nbody_b200 as nb
+    from nbody_b200 import ics
+    st = ics.empty_state(1)
+    st["vel_x"][:] = 1.0
+    st["mass"][:] = 1.0
+    d = _device_data(st)
+    integ = nb.Integrator()
+    integ.updatePositions(d, 0.1)
+    assert abs(d.numpy()["pos_x"][0] - 0.1) < 1e-6
+    st = ics.empty_state(2)
+    st["mass"][:] = [1.0, 2.0]
+    st["vel_x"][:] = [1.0, 2.0]
+    d = _device_data(st)
+    assert abs(integ.computeKineticEnergy(d) - 4.5) < 1e-6
+
+
+def test_energy_vs_oracle(orc):
+    import nbody_b200 as nb
+    from nbody_b200 import ics
+    for n in (2, 777, 6000):
+        st = ics.plummer(n, seed=9)
+        d = _device_data(st)
+        integ = nb.Integrator()
+        ke = integ.computeKineticEnergy(d)
+        pe = integ.computePotentialEnergy(d, 1.0, 0.01)
+        ke_ref = orc.kinetic(st["vel_x"], st["vel_y"], st["vel_z"], st["mass"])
+        pe_ref = orc.potential(st["pos_x"], st["pos_y"], st["pos_z"], st["mass"], 1.0, np.float32(0.01))
+        assert abs(ke - ke_ref) <= 1e-9 * abs(ke_ref) + 1e-15
+        assert abs(pe - pe_ref) <= 2e-6 * abs(pe_ref)
+
+
+def test_two_body_energy_drift():
+    """tests/test_integrator.cpp:90-162: circular orbit r=5, eps=0.01, dt=1e-3, 100 steps, drift < 1 %."""
+    import nbody_b200 as nb
+    from nbody_b200 import ics
+    st = ics.empty_state(2)
+    st["mass"][:] = 1.0
+    st["pos_x"][:] = [-2.5, 2.5]
+    v = np.sqrt(1.0 / (4 * 2.5))
+    st["vel_y"][:] = [-v, v]
+    d = _device_data(st)
+    calc = nb.DirectForceCalculator()
+    calc.setSofteningParameter(0.01)
+    calc.computeForces(d)
+    integ = nb.Integrator()
+    e0 = integ.computeTotalEnergy(d, 1.0, 0.01)
+    for _ in range(100):
+        integ.integrate(d, calc, 1e-3)
+    e1 = integ.computeTotalEnergy(d, 1.0, 0.01)
+    assert abs(e1 - e0) / abs(e0) < 0.01
+
+
+def test_host_entry_points(orc):
+    import ctypes as C
+    import nbody_b200 as nb
+    from nbody_b200 import _lib, ics
+    n = 3000
+    st = ics.plummer(n, seed=4)
+    h = nb.ParticleDataManager.fromState(st, pinned=True)
+    ctx = nb.get_context()
+    _lib.check(_lib.lib().nb_host_direct_forces(ctx.handle, C.byref(h.c), 1.0, 1e-4))
+    ref = orc.direct_f64(st["pos_x"], st["pos_y"], st["pos_z"], st["mass"], 1.0, 1e-4)
+    assert rel_err((h.acc_x, h.acc_y, h.acc_z), ref).max() <= TOL
+    _lib.check(_lib.lib().nb_host_step_direct(ctx.handle, C.byref(h.c), 1e-3, 1.0, 1e-4, 3, 0))
+    ref = {k: v.copy() for k, v in st.items()}
+    ref["acc_x"], ref["acc_y"], ref["acc_z"] = orc.direct_f32(st["pos_x"], st["pos_y"], st["pos_z"], st["mass"], 1.0, 1e-4)
+    orc.run_direct(ref, 1e-3, 1.0, 1e-4, 3)
+    for k in ("pos_x", "vel_x", "pos_z", "vel_z"):
+        np.testing.assert_allclose(h.arrays[k], ref[k], rtol=2e-5, atol=2e-6, err_msg=k)
