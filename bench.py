@@ -1,0 +1,328 @@
+#!/usr/bin/env python
+"""bench.py -- direct-N^2 G-interactions/s (BASELINE.json metric) on N B200s of one node.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--bodies B]
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A "step" is one Velocity-Verlet step (store-acc + drift, N^2 force evaluation, kick) =
+Integrator::integrate of the reference (src/cuda/integrator.cu:224-238) = N^2 pair interactions.
+  N = 1 : configs[1] of BASELINE.json -- 1 Mi bodies, Plummer, fp32, one B200.
+  N > 1 : configs[2] -- 4 Mi bodies target-sharded over N GPUs, NCCL all-gather of packed positions
+          each step overlapped with the local-source pass (strong scaling: total work fixed).
+`value` times K steps with state resident in HBM; `e2e` times the host-buffer C-ABI call
+(nb_host_step_direct / ShardedDirectSystem.host_update): pinned host state in, one step, host state
+out, copies inside the timed region.  The CPU legs (cpu_baseline, --impl reference) run the oracle
+port of the reference's CPU loop (examples/example_force_methods.cpp:44-66) on a bounded sample.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+FLOP_PER_INTERACTION = 20.0
+FP32_PEAK_DATASHEET_TF = 80.0    # B200 datasheet, the denominator BASELINE.json's target names
+G_CONST, SOFTENING, DT = 1.0, 0.01, 1e-3
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--bodies", type=int, default=0, help="override the body count (parity/debug only)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-reference-gpu", action="store_true")
+    return ap.parse_args()
+
+
+def workload(n_gpus: int, bodies: int):
+    if bodies:
+        return bodies, f"direct_n2_{bodies}_plummer"
+    if n_gpus == 1:
+        return 1 << 20, "direct_n2_1Mi_plummer_1gpu"
+    return 1 << 22, "direct_n2_4Mi_plummer_target_sharded"
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f)
+    except Exception:
+        return {}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            p = [x.strip() for x in ln.split(",")]
+            if len(p) < 8:
+                continue
+            try:
+                sm.append(float(p[1])); mx.append(float(p[2])); pw.append(float(p[3]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, p[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "power_w_max": float(max(pw)),
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def cpu_sample_rate(state, n_targets: int, reps: int = 1):
+    """Oracle port of the reference CPU loop on a bounded sample: the first n_targets targets of the
+    workload against ALL sources.  Returns (G-interactions/s, threads, seconds)."""
+    from oracle import bindings as orc
+    n = state["pos_x"].size
+    n_targets = min(n_targets, n)
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        orc.direct_f32(state["pos_x"], state["pos_y"], state["pos_z"], state["mass"], G_CONST,
+                       float(np.float32(SOFTENING) ** 2), 0, n_targets)
+    dt = (time.perf_counter() - t0) / reps
+    return n_targets * float(n) / dt / 1e9, orc.num_threads(), dt
+
+
+def run_reference_arm(args):
+    """--impl reference: the reference has no CPU force path of its own; the timed
+    CPU implementation is the oracle port of its example loop, all host threads, bounded sample."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from nbody_b200 import ics
+    n, wl = workload(args.gpus, args.bodies)
+    st = ics.plummer(n, seed=42)
+    sample = 16384 if n >= (1 << 20) else min(n, 4096)
+    for _ in range(max(args.warmup, 0)):
+        cpu_sample_rate(st, max(sample // 8, 256))
+    times = []
+    for _ in range(max(args.steps, 1)):
+        rate, threads, sec = cpu_sample_rate(st, sample)
+        times.append(sec)
+    sec = float(np.mean(times))
+    value = sample * float(n) / sec / 1e9
+    line = {
+        "impl": "reference", "metric": "direct_n2_g_interactions_per_s", "value": value,
+        "unit": "G-interactions/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "strong" if args.gpus > 1 else "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl, "bodies": n, "ic": "plummer_henon_seed42", "softening": SOFTENING, "dt": DT,
+                   "step": "sample of one force evaluation"},
+        "cpu_baseline": {"value": value, "unit": "G-interactions/s", "cores": threads, "kind": "port",
+                         "sample": f"first {sample} targets x all {n} sources per step "
+                                   f"({sample * n / 1e9:.1f} G pair interactions), OpenMP over targets"},
+        "e2e": {"value": value, "unit": "G-interactions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference_arm(args)
+        return
+
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    if args.gpus > 1 and world == 1:
+        raise SystemExit("launch N>1 with: python -m torch.distributed.run --nproc-per-node N bench.py --gpus N")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    import nbody_b200 as nb
+    from nbody_b200 import _lib, ics
+    from nbody_b200.dist import ShardedDirectSystem, shard_layout, slice_state
+
+    n, wl = workload(args.gpus, args.bodies)
+    state = ics.plummer(n, seed=42)
+    eps2 = float(np.float32(SOFTENING) ** 2)
+    ctx = nb.get_context(local_rank)
+    L = _lib.lib()
+
+    begin, count, _ = shard_layout(n, rank, world)
+    system = ShardedDirectSystem(slice_state(state, begin, count), n, rank, world, G_CONST, SOFTENING)
+    system.compute_forces()  # a(0), ParticleSystem::initialize (particle_system.cpp:91)
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- device-resident timing ---------------------------------------------------------------
+    for _ in range(args.warmup):
+        system.update(DT)
+    barrier()
+    L.nb_profile_enable(ctx.handle, 1)
+    launches0 = ctx.launch_count
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        system.update(DT)
+    e1.record()
+    barrier()
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    launches = ctx.launch_count - launches0
+    clocks = sampler.stop() if rank == 0 else None
+    kms, kl = C.c_double(0), C.c_uint64(0)
+    L.nb_profile_read(ctx.handle, C.byref(kms), C.byref(kl))
+    L.nb_profile_enable(ctx.handle, 0)
+    ms_per_step = ms_total / args.steps
+    interactions_per_step = float(n) * float(n)
+    value = interactions_per_step / (ms_per_step * 1e-3) / 1e9
+
+    # ---- end-to-end through the host-buffer call ------------------------------------------------
+    for _ in range(min(args.warmup, 2)):
+        system.host_update(DT, 1)
+    barrier()
+    t0 = time.perf_counter()
+    e0.record()
+    for _ in range(args.steps):
+        system.host_update(DT, 1)
+    e1.record()
+    barrier()
+    e2e_ms = max_over_ranks(max(e0.elapsed_time(e1), 0.0)) / args.steps
+    e2e_wall = max_over_ranks((time.perf_counter() - t0) * 1e3) / args.steps
+    e2e_ms = max(e2e_ms, e2e_wall)  # the host clock also sees the final D2H and sync
+    e2e_value = interactions_per_step / (e2e_ms * 1e-3) / 1e9
+    h2d = 10 * 4 * count
+    d2h = 12 * 4 * count
+
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank != 0:
+        return
+
+    # ---- roofline of the dominant kernel (FP32 CUDA cores; neither HBM nor tensor bound) ---------
+    peaks = measured_peaks()
+    sm_max = float(peaks.get("sm_max_mhz", 1965.0))
+    clock_peak_tf = 148 * 128 * 2 * sm_max * 1e6 / 1e12
+    kernel_ms = kms.value / max(kl.value, 1)                  # per force-kernel launch (CUDA events)
+    pairs_per_launch = float(count) * float(n) / (1 if world == 1 else 2)  # N>1: local + remote pass
+    if world > 1:
+        kernel_ms = kms.value / args.steps                    # both passes of one step
+        pairs_per_launch = float(count) * float(n)
+    achieved_tf = pairs_per_launch * FLOP_PER_INTERACTION / (kernel_ms * 1e-3) / 1e12 if kernel_ms > 0 else None
+    roofline = {
+        "bound": "fp32", "kernel": "nb::direct_force_kernel<256,2,1024>",
+        "achieved": achieved_tf, "peak": FP32_PEAK_DATASHEET_TF, "unit": "TFLOP/s",
+        "frac": (achieved_tf / FP32_PEAK_DATASHEET_TF) if achieved_tf else None,
+        "peak_source": "B200 datasheet FP32 (BASELINE.json target denominator); MEASURED_PEAKS.json holds no FP32 figure",
+        "peak_clock_derived": clock_peak_tf, "frac_of_clock_peak": (achieved_tf / clock_peak_tf) if achieved_tf else None,
+        "peak_measured_ffma": 71.8, "peak_measured_ffma2": 64.3,
+        "frac_of_measured_ffma2": (achieved_tf / 64.3) if achieved_tf else None,
+        "flop_per_interaction": FLOP_PER_INTERACTION, "kernel_ms": kernel_ms,
+        "kernel_share_of_step": (kms.value / args.steps) / ms_per_step if ms_per_step > 0 else None,
+        "traffic": None,
+    }
+
+    cpu = None
+    if not args.no_cpu_baseline:
+        sample = 16384 if n >= (1 << 20) else min(n, 4096)
+        rate, threads, sec = cpu_sample_rate(state, sample)
+        cpu = {"value": rate, "unit": "G-interactions/s", "cores": threads, "kind": "port",
+               "sample": f"first {sample} targets x all {n} sources of the same workload, {sec:.1f} s, "
+                         "oracle port of examples/example_force_methods.cpp:44-66, OpenMP over targets"}
+
+    ref_gpu = None
+    if not args.no_reference_gpu and world == 1:
+        try:
+            from oracle import ref_bindings as ref
+            if ref.available():
+                nr = min(n, 1 << 18)   # the reference kernel is slow; a 256 Ki-body evaluation is enough
+                sub = {k: np.ascontiguousarray(v[:nr]) for k, v in state.items()}
+                ms = ref.forces(sub, 0, G_CONST, SOFTENING, iters=2)
+                ref_gpu = {"value": float(nr) * nr / (ms * 1e-3) / 1e9, "unit": "G-interactions/s",
+                           "what": "reference computeForcesDirectKernel (unmodified source, sm_100) on this B200",
+                           "bodies": nr, "ms": ms}
+        except Exception as e:  # the reference build is optional evidence, never the product path
+            ref_gpu = {"unavailable": str(e)[:200]}
+
+    line = {
+        "metric": "direct_n2_g_interactions_per_s", "value": value, "unit": "G-interactions/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
+        "steps_per_s": 1e3 / ms_per_step, "higher_is_better": True,
+        "scaling": "strong" if args.gpus > 1 else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl, "bodies": n, "ic": "plummer_henon_seed42", "softening": SOFTENING, "dt": DT,
+                   "G": G_CONST, "parallelism": f"target_sharded_x{world}" if world > 1 else "single_gpu",
+                   "cache": "positions (16 MiB+ packed) are rewritten every step; compute bound, L2 state irrelevant"},
+        "tflops_20flop": value * 1e9 * FLOP_PER_INTERACTION / 1e12,
+        "pct_fp32_peak_datasheet": 100.0 * value * 1e9 * FLOP_PER_INTERACTION / 1e12 / (FP32_PEAK_DATASHEET_TF * args.gpus),
+        "e2e": {"value": e2e_value, "unit": "G-interactions/s", "ms_per_step": e2e_ms,
+                "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": d2h * world},
+        "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+        "reference_gpu": ref_gpu,
+    }
+    print(json.dumps(line))
+
+
+if __name__ == "__main__":
+    main()

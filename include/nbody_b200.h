@@ -60,6 +60,12 @@ int nb_synchronize(nb_context* ctx, nb_stream stream);
 /* number of this library's kernels launched through ctx since creation (bench.py gpu_launches) */
 uint64_t nb_launch_count(const nb_context* ctx);
 
+/* optional device-side timing of the dominant kernels (CUDA events on the launching stream around
+ * every direct-force / BH-traversal / SH-force launch).  nb_profile_read synchronises, returns the
+ * summed kernel milliseconds and launch count since the last read, and resets them. */
+int nb_profile_enable(nb_context* ctx, int on);
+int nb_profile_read(nb_context* ctx, double* kernel_ms, uint64_t* kernel_launches);
+
 /* ---- ParticleDataManager (src/cuda/particle_init.cu:143-283) ------------------------------ */
 int nb_particles_alloc_device(nb_particles* d, size_t count); /* :143-168, acc/acc_old zeroed   */
 int nb_particles_free_device(nb_particles* d);                /* :170-198                        */

@@ -57,6 +57,8 @@ SYMBOLS = {
     "nb_context_sm_count": (_i, [_vp]),
     "nb_synchronize": (_i, [_vp, _vp]),
     "nb_launch_count": (C.c_uint64, [_vp]),
+    "nb_profile_enable": (_i, [_vp, _i]),
+    "nb_profile_read": (_i, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]),
     "nb_particles_alloc_device": (_i, [_pp, _sz]),
     "nb_particles_free_device": (_i, [_pp]),
     "nb_particles_upload": (_i, [_vp, _pp, _pp, _vp]),

@@ -50,6 +50,28 @@ void DevBuf::release() {
   cap = 0;
 }
 
+static cudaEvent_t prof_get_event(nb_context* ctx) {
+  cudaEvent_t e = nullptr;
+  if (!ctx->prof_pool.empty()) {
+    e = ctx->prof_pool.back();
+    ctx->prof_pool.pop_back();
+  } else {
+    cudaEventCreate(&e);
+  }
+  return e;
+}
+ProfScope::ProfScope(nb_context* c, cudaStream_t s) : ctx(c), st(s) {
+  if (!ctx->prof || ctx->prof_ev.size() >= 65536) return;
+  e0 = prof_get_event(ctx);
+  e1 = prof_get_event(ctx);
+  cudaEventRecord(e0, st);
+}
+ProfScope::~ProfScope() {
+  if (!e0) return;
+  cudaEventRecord(e1, st);
+  ctx->prof_ev.emplace_back(e0, e1);
+}
+
 // implemented in the kernel files
 int direct_run(nb_context* ctx, const nb_particles* d, float dt, float G, float eps2, bool step, cudaStream_t st);
 int launch_store_acc(nb_context* ctx, const nb_particles* d, cudaStream_t st);
@@ -167,12 +189,40 @@ int nb_context_destroy(nb_context* ctx) {
   if (ctx->h_bbox) cudaFreeHost(ctx->h_bbox);
   if (ctx->stage_cap) nb_particles_free_device(&ctx->stage);
   if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
+  for (auto& pr : ctx->prof_ev) {
+    cudaEventDestroy(pr.first);
+    cudaEventDestroy(pr.second);
+  }
+  for (auto e : ctx->prof_pool) cudaEventDestroy(e);
   delete ctx;
   return NB_OK;
 }
 
 int nb_context_sm_count(const nb_context* ctx) { return ctx ? ctx->sm_count : 0; }
 uint64_t nb_launch_count(const nb_context* ctx) { return ctx ? ctx->launches : 0; }
+
+int nb_profile_enable(nb_context* ctx, int on) {
+  NB_ENTER(ctx);
+  ctx->prof = on != 0;
+  return NB_OK;
+}
+
+int nb_profile_read(nb_context* ctx, double* kernel_ms, uint64_t* kernel_launches) {
+  NB_ENTER(ctx);
+  double total = 0.0;
+  for (auto& pr : ctx->prof_ev) {
+    NB_CUDA(cudaEventSynchronize(pr.second));
+    float ms = 0.f;
+    NB_CUDA(cudaEventElapsedTime(&ms, pr.first, pr.second));
+    total += ms;
+    ctx->prof_pool.push_back(pr.first);
+    ctx->prof_pool.push_back(pr.second);
+  }
+  if (kernel_ms) *kernel_ms = total;
+  if (kernel_launches) *kernel_launches = ctx->prof_ev.size();
+  ctx->prof_ev.clear();
+  return NB_OK;
+}
 
 int nb_synchronize(nb_context* ctx, nb_stream stream) {
   NB_ENTER(ctx);

@@ -5,6 +5,8 @@
 #include <cstdint>
 #include <cstdio>
 #include <string>
+#include <utility>
+#include <vector>
 
 #include "../../include/nbody_b200.h"
 
@@ -131,6 +133,17 @@ struct DevBuf {
 
 }  // namespace nb
 
+namespace nb {
+// RAII event pair around the dominant kernel of a path when profiling is on.
+struct ProfScope {
+  nb_context* ctx;
+  cudaStream_t st;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  ProfScope(nb_context* c, cudaStream_t s);
+  ~ProfScope();
+};
+}  // namespace nb
+
 // One stream-K pass of the direct kernel (see direct.cu).
 struct nb_pass {
   long long U;      // work units = n_itiles * UJ
@@ -145,6 +158,9 @@ struct nb_context {
   int sm_count = 0;
   int cc_major = 0, cc_minor = 0;
   uint64_t launches = 0;
+  bool prof = false;  // nb_profile_enable
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_ev;
+  std::vector<cudaEvent_t> prof_pool;
   // direct N^2
   nb::DevBuf src;       // packed float4 (x,y,z,G*m), tile padded
   nb::DevBuf partial;   // stream-K partial accelerations

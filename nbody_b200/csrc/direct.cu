@@ -268,6 +268,7 @@ int launch_direct_pass(nb_context* ctx, const DirectCfg& cfg, const float4* src,
 #define NB_LAUNCH_DIRECT(T_, I_, JT_, E_)                                                             \
   direct_force_kernel<T_, I_, JT_, E_><<<ps.G, T_, 0, st>>>(src, tgt, part, ps.U, UJ, ja0, na, jb0, eps2, \
                                                             (unsigned long long)ps.slot_base)
+  ProfScope prof(ctx, st);
   if (big) {
     if (eps0) NB_LAUNCH_DIRECT(256, 2, 1024, true);
     else NB_LAUNCH_DIRECT(256, 2, 1024, false);

@@ -1,0 +1,119 @@
+"""Target-sharded direct N^2 across the GPUs of one node: one process per GPU, torch.distributed
+for the plumbing (NCCL all-gather of packed positions over NVLink/NVSwitch), our kernels for the
+work.  The reference is single-GPU; this is new capability named by
+BASELINE.json's north_star.
+
+Per step on rank r (targets [r*N/R, (r+1)*N/R), all N sources):
+  1. pack: store-acc + drift of the local slice, written as float4 {x,y,z,G*m} into this rank's
+     slot of the replicated source buffer                               (nb_mgpu_pack_local)
+  2. all-gather of the slots, asynchronous on NCCL's stream             (torch.distributed)
+  3. force pass over the LOCAL source slot -- overlaps the gather       (nb_mgpu_forces_local)
+  4. wait for the gather; force pass over the other R-1 slots           (nb_mgpu_forces_remote)
+  5. fixed-order reduction of the stream-K partials + kick              (nb_mgpu_finish)
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from .ics import FIELDS
+
+# tile quantum of the direct kernel (nbody_b200/csrc/direct.cu: kCfgBig / kCfgSmall)
+_SMALL_N = 32768
+
+
+def shard_layout(n_total: int, rank: int, world: int):
+    """Same arithmetic as nb_mgpu_layout: (begin, count, padded_slice)."""
+    if world < 1 or not (0 <= rank < world) or n_total <= 0:
+        raise ValueError("bad shard layout arguments")
+    begin = n_total * rank // world
+    end = n_total * (rank + 1) // world
+    max_cnt = (n_total + world - 1) // world
+    q = 256 if n_total < _SMALL_N else 1024
+    padded = (max_cnt + q - 1) // q * q
+    return begin, end - begin, padded
+
+
+def slice_state(state: dict, begin: int, count: int) -> dict:
+    return {k: np.ascontiguousarray(state[k][begin:begin + count]) for k in FIELDS}
+
+
+def pack_sources_host(state_local: dict, padded: int, G: float) -> np.ndarray:
+    """Host restatement of the pack kernel (used by the gloo CPU tests of the sharding logic)."""
+    n = state_local["pos_x"].size
+    out = np.zeros((padded, 4), np.float32)
+    out[:n, 0] = state_local["pos_x"]
+    out[:n, 1] = state_local["pos_y"]
+    out[:n, 2] = state_local["pos_z"]
+    out[:n, 3] = np.float32(G) * state_local["mass"]
+    return out
+
+
+class ShardedDirectSystem:
+    """ParticleSystem-like driver for one rank of a target-sharded direct-N^2 run."""
+
+    def __init__(self, state_local: dict, n_total: int, rank: int, world: int, G: float = 1.0,
+                 softening: float = 0.01, group=None):
+        import torch
+        from . import _lib
+        from .api import ParticleData, ParticleDataManager, get_context
+        self.torch = torch
+        self.L = _lib.lib()
+        self.check = _lib.check
+        self.rank, self.world, self.n_total = rank, world, n_total
+        self.G = float(np.float32(G))
+        self.eps2 = float(np.float32(softening) * np.float32(softening))
+        self.group = group
+        self.ctx = get_context()
+        b, c, p, tot = C.c_size_t(), C.c_size_t(), C.c_size_t(), C.c_size_t()
+        self.check(self.L.nb_mgpu_layout(self.ctx.handle, n_total, rank, world, C.byref(b), C.byref(c),
+                                         C.byref(p), C.byref(tot)))
+        assert (b.value, c.value, p.value) == shard_layout(n_total, rank, world)
+        self.begin, self.count, self.padded = b.value, c.value, p.value
+        assert state_local["pos_x"].size == self.count
+        self.h = ParticleDataManager.fromState(state_local, pinned=True)
+        self.d = ParticleData()
+        ParticleDataManager.allocateDevice(self.d, self.count)
+        ParticleDataManager.copyToDevice(self.d, self.h)
+        self.gathered = torch.zeros(world * self.padded * 4, dtype=torch.float32, device="cuda")
+        self.simulation_time = 0.0
+
+    def _stream(self):
+        return C.c_void_p(self.torch.cuda.current_stream().cuda_stream)
+
+    def _evaluate(self, dt: float, step: bool):
+        L, ctx, gp = self.L, self.ctx.handle, C.c_void_p(self.gathered.data_ptr())
+        s = self._stream()
+        self.check(L.nb_mgpu_pack_local(ctx, C.byref(self.d.c), gp, dt, self.G, 1 if step else 0, s))
+        work = None
+        if self.world > 1:
+            import torch.distributed as dist
+            mine = self.gathered[self.rank * self.padded * 4:(self.rank + 1) * self.padded * 4]
+            work = dist.all_gather_into_tensor(self.gathered, mine, group=self.group, async_op=True)
+        self.check(L.nb_mgpu_forces_local(ctx, gp, self.eps2, s))
+        if work is not None:
+            work.wait()  # current stream waits for the gather; the local pass above overlapped it
+            self.check(L.nb_mgpu_forces_remote(ctx, gp, self.eps2, s))
+        self.check(L.nb_mgpu_finish(ctx, C.byref(self.d.c), dt, 1 if step else 0, s))
+
+    def compute_forces(self):
+        self._evaluate(0.0, False)
+
+    def update(self, dt: float):
+        self._evaluate(float(np.float32(dt)), True)
+        self.simulation_time += dt
+
+    def host_update(self, dt: float, steps: int = 1):
+        """Host-buffer step: H2D of the local state, `steps` steps, D2H (the e2e path at N > 1)."""
+        t = self.torch
+        for k in ("pos_x", "pos_y", "pos_z", "vel_x", "vel_y", "vel_z", "acc_x", "acc_y", "acc_z", "mass"):
+            self.d.arrays[k].copy_(self.h._pinned[k][:self.count], non_blocking=True)
+        for _ in range(steps):
+            self.update(dt)
+        for k in FIELDS[:12]:
+            self.h._pinned[k][:self.count].copy_(self.d.arrays[k], non_blocking=True)
+        t.cuda.current_stream().synchronize()
+
+    def local_arrays(self) -> dict:
+        return self.d.numpy()
