@@ -15,6 +15,8 @@
 //   * accumulation is two-level: plain fp32 inside a source tile, Kahan-compensated across tiles.
 #include "direct.cuh"
 
+#include <cstdlib>
+
 namespace nb {
 
 // ---------------------------------------------------------------------------------------------
@@ -257,7 +259,12 @@ int launch_direct_pass(nb_context* ctx, const DirectCfg& cfg, const float4* src,
   const bool eps0 = !(eps2 > 0.f);
   int& occ = ctx->direct_occ[(big ? 0 : 2) + (eps0 ? 1 : 0)];
   if (occ == 0) occ = big ? occupancy<256, 2, 1024>(eps0) : occupancy<128, 2, 256>(eps0);
-  long long g = (long long)occ * ctx->sm_count;
+  int use_occ = occ;
+  if (const char* e = getenv("NB_DIRECT_OCC")) {  // tuning knob: resident CTAs per SM
+    const int v = atoi(e);
+    if (v > 0 && v < occ) use_occ = v;
+  }
+  long long g = (long long)use_occ * ctx->sm_count;
   if (g > ps.U) g = ps.U;
   ps.G = (int)g;
   // pass 0 reserves room for a second pass too: the buffer must not move while pass 0 runs

@@ -126,6 +126,35 @@ __global__ void k_mix2(float* out, float a, float b, int iters) {
   out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
+// FFMA2 : FFMA mixes -- does scalar FFMA fill what FFMA2 leaves of the FP32 pipe?
+template <int R2, int R1>
+__global__ void k_mixfs(float* out, float a, float b, int iters) {
+  uint64_t v[R2 > 0 ? R2 : 1];
+  float w[R1 > 0 ? R1 : 1];
+  uint64_t a2 = pk(a, a * 1.0001f), b2 = pk(b, b * 1.0001f);
+#pragma unroll
+  for (int c = 0; c < R2; c++) v[c] = pk(threadIdx.x * 1e-3f + c, threadIdx.x * 2e-3f + c);
+#pragma unroll
+  for (int c = 0; c < R1; c++) w[c] = threadIdx.x * 3e-3f + c;
+  for (int it = 0; it < iters; it++) {
+#pragma unroll
+    for (int c = 0; c < (R2 > R1 ? R2 : R1); c++) {
+      if (c < R2) v[c] = fma2(v[c], a2, b2);
+      if (c < R1) w[c] = fmaf(w[c], a, b);
+    }
+  }
+  float s = 0;
+#pragma unroll
+  for (int c = 0; c < R2; c++) {
+    float x, y;
+    upk(v[c], x, y);
+    s += x + y;
+  }
+#pragma unroll
+  for (int c = 0; c < R1; c++) s += w[c];
+  out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
 // ---- direct pair body variants ----------------------------------------------
 // I targets per thread, T threads, tile of T sources (float4) per sync.
 template <int I, int T>
@@ -277,6 +306,16 @@ int main() {
     }
   }
 
+#define RUN_MIX(R2, R1)                                                                                   \
+  {                                                                                                       \
+    float ms = time_ms([&] { k_mixfs<R2, R1><<<sms * 4, 256>>>(out, 1.0001f, 0.5f, iters); }, 5);        \
+    double fl = (4.0 * R2 + 2.0 * R1) * iters * 256.0 * sms * 4;                                          \
+    printf("MIX %2d FFMA2 : %2d FFMA  %.3f ms  %.2f TFLOP/s  (%.1f FMA lanes/clk/SM)\n", R2, R1, ms,     \
+           fl / ms / 1e9, fl / 2 / (ms * 1e-3) / sms / (clk_khz * 1e3));                                  \
+  }
+  RUN_MIX(8, 0) RUN_MIX(8, 2) RUN_MIX(8, 4) RUN_MIX(8, 8) RUN_MIX(4, 8) RUN_MIX(2, 8) RUN_MIX(0, 8) RUN_MIX(0, 16)
+  RUN_MIX(12, 4) RUN_MIX(6, 6)
+  if (getenv("UBENCH_PIPES_ONLY")) return 0;
   // direct variants
   const int n = sms * 2048;  // 303104 on 148 SMs
   std::vector<float4> h(n);
