@@ -1,0 +1,385 @@
+// bh.cu -- Barnes-Hut on the GPU, rebuilt every step: bbox -> Morton keys -> radix sort ->
+// Karras LBVH -> bottom-up centres of mass -> warp-cooperative traversal.
+//
+// Replaces BarnesHutTree::build / computeForces (reference src/cuda/force_barnes_hut.cu:282-289,
+// 488-498).  The reference copies everything to the host, inserts bodies one by one into an octree
+// on one CPU thread (and, as shipped, never splits a leaf: SURVEY.md sec. 0) and traverses it with a
+// per-thread 1 KiB local-memory stack.  Here the integer front half (bbox, keys, stable sort) is
+// bit-exact with the reference's arithmetic (:23-38, :113-127, :260-280), the tree is a binary radix
+// tree over those keys (Karras 2012), and the traversal keeps the reference's acceptance test
+// (is-leaf or size^2/(d^2+eps^2) < theta^2, :167) and monopole formula (:175-181), with "size" the
+// side of the Morton cell the node lives in (== the reference's octree cell 2*half_size at every
+// third level for a cubic box).  32 Morton-consecutive bodies walk the tree together: a node is
+// used only if every lane accepts it (__all_sync), so each body's force is at least as accurate as
+// with its own per-body test.
+#include <cstring>
+
+#include "common.cuh"
+
+namespace nb {
+
+int bbox_device(nb_context* ctx, const nb_particles* d, cudaStream_t st);
+int sort_pairs(nb_context* ctx, uint32_t* d_keys, int32_t* d_vals, size_t n, int end_bit, cudaStream_t st);
+
+}  // namespace nb
+
+struct BH {
+  size_t n = 0;
+  nb::DevBuf keys, perm, node_com, meta, parent, flags, misc;  // misc: size2 table[32] + counter + bbox floats
+  float h_bbox[6] = {0, 0, 0, 0, 0, 0};
+  bool built = false;
+};
+
+namespace nb {
+
+__device__ __forceinline__ float ord2f_dev(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); }
+
+// src/cuda/force_barnes_hut.cu:23-29
+__device__ __forceinline__ unsigned expand_bits(unsigned v) {
+  v = (v * 0x00010001u) & 0xFF0000FFu;
+  v = (v * 0x00000101u) & 0x0F00F00Fu;
+  v = (v * 0x00000011u) & 0xC30C30C3u;
+  v = (v * 0x00000005u) & 0x49249249u;
+  return v;
+}
+
+// misc layout (floats): [0..31] size2 table by prefix length, [32..37] bbox, [40..41] u64 counter
+__global__ void bh_prepare_kernel(const int* __restrict__ bb_ord, float* __restrict__ misc) {
+  const int t = threadIdx.x;
+  __shared__ float bb[6];
+  if (t < 6) {
+    bb[t] = ord2f_dev(bb_ord[t]);
+    misc[32 + t] = bb[t];
+  }
+  if (t == 6) *reinterpret_cast<unsigned long long*>(misc + 40) = 0ull;
+  __syncthreads();
+  if (t <= 30) {
+    // side of the Morton cell at prefix length L: x is split first, then y, then z
+    // (x is bit 2 of each key triple, :37); extents as in :265-267
+    const float sx = __fadd_rn(__fsub_rn(bb[3], bb[0]), 0.001f), sy = __fadd_rn(__fsub_rn(bb[4], bb[1]), 0.001f),
+                sz = __fadd_rn(__fsub_rn(bb[5], bb[2]), 0.001f);
+    const float ex = ldexpf(sx, -((t + 2) / 3)), ey = ldexpf(sy, -((t + 1) / 3)), ez = ldexpf(sz, -(t / 3));
+    const float s = fmaxf(ex, fmaxf(ey, ez));
+    misc[t] = __fmul_rn(s, s);
+  }
+  if (t == 31) misc[31] = 0.f;
+}
+
+// :260-274 (host part: size = max-min+0.001f, inv = 1.0f/size) and :113-127 (device part)
+__global__ void __launch_bounds__(256) bh_morton_kernel(const float* __restrict__ px, const float* __restrict__ py,
+                                                        const float* __restrict__ pz, size_t n,
+                                                        const float* __restrict__ misc, uint32_t* __restrict__ keys,
+                                                        int32_t* __restrict__ perm) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float mnx = misc[32], mny = misc[33], mnz = misc[34];
+  const float ix = __fdiv_rn(1.0f, __fadd_rn(__fsub_rn(misc[35], mnx), 0.001f));
+  const float iy = __fdiv_rn(1.0f, __fadd_rn(__fsub_rn(misc[36], mny), 0.001f));
+  const float iz = __fdiv_rn(1.0f, __fadd_rn(__fsub_rn(misc[37], mnz), 0.001f));
+  const float nx = __fmul_rn(__fsub_rn(px[i], mnx), ix);
+  const float ny = __fmul_rn(__fsub_rn(py[i], mny), iy);
+  const float nz = __fmul_rn(__fsub_rn(pz[i], mnz), iz);
+  // static_cast<unsigned>(x * 1024.0f) clamped to [0, 1023] (:31-35); cvt.rzi.u32.f32 saturates
+  const unsigned ux = min(__float2uint_rz(__fmul_rn(nx, 1024.0f)), 1023u);
+  const unsigned uy = min(__float2uint_rz(__fmul_rn(ny, 1024.0f)), 1023u);
+  const unsigned uz = min(__float2uint_rz(__fmul_rn(nz, 1024.0f)), 1023u);
+  keys[i] = (expand_bits(ux) << 2) | (expand_bits(uy) << 1) | expand_bits(uz);
+  perm[i] = (int32_t)i;
+}
+
+// leaves of the tree = bodies in sorted order, packed {x,y,z,m}
+__global__ void __launch_bounds__(256) bh_gather_kernel(nb_particles d, size_t n, const int32_t* __restrict__ perm,
+                                                        float4* __restrict__ leaves) {
+  const size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int i = perm[k];
+  leaves[k] = make_float4(d.pos_x[i], d.pos_y[i], d.pos_z[i], d.mass[i]);
+}
+
+__device__ __forceinline__ int bh_delta(const uint32_t* __restrict__ k, int n, int i, int j) {
+  if (j < 0 || j >= n) return -1;
+  const uint32_t a = k[i], b = k[j];
+  if (a == b) return 32 + __clz((unsigned)i ^ (unsigned)j);
+  return __clz(a ^ b);
+}
+
+// Karras 2012, sec. 4: one thread per internal node.  meta[i] = {left, right, prefix, 0}.
+__global__ void __launch_bounds__(256) bh_karras_kernel(const uint32_t* __restrict__ keys, int n,
+                                                        int4* __restrict__ meta, int32_t* __restrict__ parent) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n - 1) return;
+  const int leaf0 = n - 1;
+  const int d = (bh_delta(keys, n, i, i + 1) - bh_delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+  const int dmin = bh_delta(keys, n, i, i - d);
+  int lmax = 2;
+  while (bh_delta(keys, n, i, i + lmax * d) > dmin) lmax <<= 1;
+  int l = 0;
+  for (int t = lmax >> 1; t >= 1; t >>= 1)
+    if (bh_delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+  const int j = i + l * d;
+  const int dnode = bh_delta(keys, n, i, j);
+  int s = 0, t = l;
+  do {
+    t = (t + 1) >> 1;
+    if (bh_delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+  } while (t > 1);
+  const int gamma = i + s * d + (d < 0 ? d : 0);
+  const int lo = min(i, j), hi = max(i, j);
+  const int lc = (lo == gamma) ? leaf0 + gamma : gamma;
+  const int rc = (hi == gamma + 1) ? leaf0 + gamma + 1 : gamma + 1;
+  int p = dnode - 2;
+  if (p > 30) p = 30;
+  meta[i] = make_int4(lc, rc, p, 0);
+  parent[lc] = i;
+  parent[rc] = i;
+  if (i == 0) parent[0] = -1;
+}
+
+// bottom-up centres of mass: the second thread to reach a node combines its two children.
+// c = (ca*ma + cb*mb) / (ma+mb), a = left child, b = right child: order-independent of arrival.
+__global__ void __launch_bounds__(256) bh_com_kernel(int n, const int4* __restrict__ meta,
+                                                     const int32_t* __restrict__ parent, int* __restrict__ flags,
+                                                     float4* node_com) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  int p = parent[n - 1 + k];
+  while (p >= 0) {
+    __threadfence();
+    if (atomicAdd(&flags[p], 1) == 0) return;
+    const int4 m = meta[p];
+    const float4 a = __ldcg(node_com + m.x), b = __ldcg(node_com + m.y);
+    const float ms = __fadd_rn(a.w, b.w);
+    float4 c;
+    if (ms > 0.f) {
+      c.x = __fdiv_rn(__fadd_rn(__fmul_rn(a.x, a.w), __fmul_rn(b.x, b.w)), ms);
+      c.y = __fdiv_rn(__fadd_rn(__fmul_rn(a.y, a.w), __fmul_rn(b.y, b.w)), ms);
+      c.z = __fdiv_rn(__fadd_rn(__fmul_rn(a.z, a.w), __fmul_rn(b.z, b.w)), ms);
+    } else {
+      c.x = a.x; c.y = a.y; c.z = a.z;
+    }
+    c.w = ms;
+    __stcg(node_com + p, c);
+    p = parent[p];
+  }
+}
+
+// ---- traversal ---------------------------------------------------------------------------------------
+constexpr int BH_WARPS = 8;
+constexpr int BH_STACK = 96;
+
+__global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const float4* __restrict__ node_com,
+                                                                  const int4* __restrict__ meta,
+                                                                  const int32_t* __restrict__ perm,
+                                                                  const float* __restrict__ misc, float theta2, float G,
+                                                                  float eps2, float* __restrict__ ax,
+                                                                  float* __restrict__ ay, float* __restrict__ az,
+                                                                  unsigned long long* __restrict__ counter) {
+  __shared__ int stack[BH_WARPS][BH_STACK];
+  __shared__ float size2_tab[32];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (threadIdx.x < 32) size2_tab[threadIdx.x] = misc[threadIdx.x];
+  __syncthreads();
+  const int leaf0 = n - 1;
+  const long long group = (long long)blockIdx.x * BH_WARPS + w;
+  const long long k = group * 32 + lane;
+  if (group * 32 >= n) return;
+  const bool live = k < n;
+  const float4 me = live ? node_com[leaf0 + k] : make_float4(0.f, 0.f, 0.f, 0.f);
+  float sx = 0.f, sy = 0.f, sz = 0.f;
+  unsigned visits = 0;
+  int* st = stack[w];
+  int sp = 0;
+  int ni = 0;
+  for (;;) {
+    const float4 c = node_com[ni];  // same address in every lane: one broadcast load
+    bool descend = false;
+    if (c.w != 0.f) {  // total_mass == 0 -> skip (:157-158)
+      const float dx = c.x - me.x, dy = c.y - me.y, dz = c.z - me.z;
+      const float d2 = fmaf(dz, dz, fmaf(dy, dy, fmaf(dx, dx, eps2)));
+      const bool is_leaf = ni >= leaf0;
+      int4 m = make_int4(0, 0, 31, 0);
+      if (!is_leaf) m = meta[ni];
+      const float size2 = size2_tab[m.z];
+      const bool accept = !live || is_leaf || (size2 < theta2 * d2);  // size2/dist2 < theta2 (:167)
+      if (__all_sync(0xffffffffu, accept)) {
+        if (live && !(is_leaf && ni == leaf0 + (int)k)) {  // own leaf skipped (:174)
+          const float inv = rsq(d2);
+          const float f = (G * c.w) * (inv * inv * inv);
+          sx = fmaf(f, dx, sx);
+          sy = fmaf(f, dy, sy);
+          sz = fmaf(f, dz, sz);
+        }
+        visits++;
+      } else {
+        descend = true;
+        if (lane == 0) st[sp] = m.y;  // right child waits, left child is next
+        sp++;
+        ni = m.x;
+        __syncwarp();
+      }
+    }
+    if (!descend) {
+      if (sp == 0) break;
+      ni = st[--sp];
+    }
+  }
+  if (live) {
+    const int i = perm[k];
+    ax[i] = sx;
+    ay[i] = sy;
+    az[i] = sz;
+  }
+  if (lane == 0) {
+    const int cnt = (int)min((long long)32, (long long)n - group * 32);
+    atomicAdd(counter, (unsigned long long)visits * cnt);
+  }
+}
+
+static BH* bh_get(nb_context* ctx) {
+  if (!ctx->bh) ctx->bh = new BH();
+  return ctx->bh;
+}
+
+void bh_destroy(nb_context* ctx) {
+  if (!ctx->bh) return;
+  BH* b = ctx->bh;
+  b->keys.release(); b->perm.release(); b->node_com.release(); b->meta.release();
+  b->parent.release(); b->flags.release(); b->misc.release();
+  delete b;
+  ctx->bh = nullptr;
+}
+
+int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
+  BH* b = bh_get(ctx);
+  const size_t n = d->count;
+  b->built = false;
+  if (n == 0) return NB_OK;
+  if (n > 0x3fffffffull) {
+    set_error("Barnes-Hut: particle count %zu too large", n);
+    return NB_ERR_INVALID;
+  }
+  b->n = n;
+  if (int rc = b->keys.ensure(n * 4)) return rc;
+  if (int rc = b->perm.ensure(n * 4)) return rc;
+  if (int rc = b->node_com.ensure((2 * n) * sizeof(float4))) return rc;
+  if (int rc = b->meta.ensure(n * sizeof(int4))) return rc;
+  if (int rc = b->parent.ensure(2 * n * 4)) return rc;
+  if (int rc = b->flags.ensure(n * 4)) return rc;
+  if (int rc = b->misc.ensure(64 * 4)) return rc;
+  float* misc = b->misc.as<float>();
+  if (int rc = bbox_device(ctx, d, st)) return rc;
+  bh_prepare_kernel<<<1, 32, 0, st>>>(ctx->bbox_dev.as<int>(), misc);
+  NB_LAUNCH_CHECK(ctx);
+  const unsigned gn = (unsigned)((n + 255) / 256);
+  bh_morton_kernel<<<gn, 256, 0, st>>>(d->pos_x, d->pos_y, d->pos_z, n, misc, b->keys.as<uint32_t>(),
+                                       b->perm.as<int32_t>());
+  NB_LAUNCH_CHECK(ctx);
+  if (int rc = sort_pairs(ctx, b->keys.as<uint32_t>(), b->perm.as<int32_t>(), n, 30, st)) return rc;
+  float4* com = b->node_com.as<float4>();
+  bh_gather_kernel<<<gn, 256, 0, st>>>(*d, n, b->perm.as<int32_t>(), com + (n - 1));
+  NB_LAUNCH_CHECK(ctx);
+  NB_CUDA(cudaMemsetAsync(b->parent.p, 0xff, sizeof(int32_t), st));  // parent[0] = -1 (also when n == 1)
+  if (n > 1) {
+    NB_CUDA(cudaMemsetAsync(b->flags.p, 0, (n - 1) * 4, st));
+    const unsigned gi = (unsigned)((n - 1 + 255) / 256);
+    bh_karras_kernel<<<gi, 256, 0, st>>>(b->keys.as<uint32_t>(), (int)n, b->meta.as<int4>(), b->parent.as<int32_t>());
+    NB_LAUNCH_CHECK(ctx);
+    bh_com_kernel<<<gn, 256, 0, st>>>((int)n, b->meta.as<int4>(), b->parent.as<int32_t>(), b->flags.as<int>(), com);
+    NB_LAUNCH_CHECK(ctx);
+  }
+  b->built = true;
+  return NB_OK;
+}
+
+int bh_forces(nb_context* ctx, const nb_particles* d, float theta, float G, float eps, cudaStream_t st) {
+  BH* b = bh_get(ctx);
+  const size_t n = d->count;
+  if (n == 0) return NB_OK;
+  if (!b->built || b->n != n) {
+    set_error("Barnes-Hut: forces requested without a tree built for these particles");
+    return NB_ERR_INVALID;
+  }
+  float* misc = b->misc.as<float>();
+  const long long groups = ((long long)n + 31) / 32;
+  const unsigned grid = (unsigned)((groups + BH_WARPS - 1) / BH_WARPS);
+  ProfScope prof(ctx, st);
+  bh_force_kernel<<<grid, BH_WARPS * 32, 0, st>>>((int)n, b->node_com.as<float4>(), b->meta.as<int4>(),
+                                                  b->perm.as<int32_t>(), misc, theta * theta, G, eps * eps, d->acc_x,
+                                                  d->acc_y, d->acc_z, reinterpret_cast<unsigned long long*>(misc + 40));
+  NB_LAUNCH_CHECK(ctx);
+  return NB_OK;
+}
+
+}  // namespace nb
+
+using namespace nb;
+
+extern "C" {
+
+int nb_bh_build(nb_context* ctx, const nb_particles* d, nb_stream s) {
+  if (!ctx || !d || (d->count && (!d->pos_x || !d->pos_y || !d->pos_z || !d->mass))) {
+    set_error("Barnes-Hut build: null argument");
+    return NB_ERR_INVALID;
+  }
+  NB_CUDA(cudaSetDevice(ctx->device));
+  return bh_build(ctx, d, (cudaStream_t)s);
+}
+
+int nb_bh_forces(nb_context* ctx, const nb_particles* d, float theta, float G, float eps, nb_stream s) {
+  if (!ctx || !d || (d->count && (!d->acc_x || !d->acc_y || !d->acc_z))) {
+    set_error("Barnes-Hut forces: null argument");
+    return NB_ERR_INVALID;
+  }
+  NB_CUDA(cudaSetDevice(ctx->device));
+  return bh_forces(ctx, d, theta, G, eps, (cudaStream_t)s);
+}
+
+int nb_bh_export(nb_context* ctx, uint32_t* keys, int32_t* perm, int32_t* left, int32_t* right, int32_t* parent,
+                 int32_t* prefix, float* node_com, float* bbox) {
+  if (!ctx || !ctx->bh || !ctx->bh->built) {
+    set_error("Barnes-Hut export: no tree built");
+    return NB_ERR_INVALID;
+  }
+  NB_CUDA(cudaSetDevice(ctx->device));
+  NB_CUDA(cudaDeviceSynchronize());
+  BH* b = ctx->bh;
+  const size_t n = b->n;
+  if (keys) NB_CUDA(cudaMemcpy(keys, b->keys.p, n * 4, cudaMemcpyDeviceToHost));
+  if (perm) NB_CUDA(cudaMemcpy(perm, b->perm.p, n * 4, cudaMemcpyDeviceToHost));
+  if (parent) NB_CUDA(cudaMemcpy(parent, b->parent.p, (2 * n - 1) * 4, cudaMemcpyDeviceToHost));
+  if (node_com) NB_CUDA(cudaMemcpy(node_com, b->node_com.p, (2 * n - 1) * sizeof(float4), cudaMemcpyDeviceToHost));
+  if ((left || right || prefix) && n > 1) {
+    int4* h = (int4*)malloc((n - 1) * sizeof(int4));
+    if (!h) {
+      set_error("out of host memory");
+      return NB_ERR_RESOURCE;
+    }
+    cudaError_t e = cudaMemcpy(h, b->meta.p, (n - 1) * sizeof(int4), cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) {
+      free(h);
+      return cuda_fail(e, "cudaMemcpy", __FILE__, __LINE__);
+    }
+    for (size_t i = 0; i + 1 < n; i++) {
+      if (left) left[i] = h[i].x;
+      if (right) right[i] = h[i].y;
+      if (prefix) prefix[i] = h[i].z;
+    }
+    free(h);
+  }
+  if (bbox) NB_CUDA(cudaMemcpy(bbox, b->misc.as<float>() + 32, 6 * 4, cudaMemcpyDeviceToHost));
+  return NB_OK;
+}
+
+int nb_bh_stats(nb_context* ctx, uint64_t* interactions, int* node_count) {
+  if (!ctx || !ctx->bh || !ctx->bh->built) {
+    set_error("Barnes-Hut stats: no tree built");
+    return NB_ERR_INVALID;
+  }
+  NB_CUDA(cudaSetDevice(ctx->device));
+  NB_CUDA(cudaDeviceSynchronize());
+  if (interactions) NB_CUDA(cudaMemcpy(interactions, ctx->bh->misc.as<float>() + 40, 8, cudaMemcpyDeviceToHost));
+  if (node_count) *node_count = (int)(2 * ctx->bh->n - 1);
+  return NB_OK;
+}
+
+}  // extern "C"

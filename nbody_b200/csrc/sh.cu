@@ -1,0 +1,300 @@
+// sh.cu -- spatial-hash (uniform grid) short-range forces.
+//
+// Replaces SpatialHashGrid::build / computeForces (reference src/cuda/force_spatial_hash.cu:235-316):
+// the reference counts with N global atomics, scans with Thrust, scatters with N more atomics (so
+// the order inside a cell is racy) and gathers neighbours through an index indirection.  Here the
+// cell ids -- same arithmetic, bit-exact (:28-49, :226-246) -- are the keys of the stable radix
+// sort (sort.cu), cell_start/cell_end are read off the sorted keys (identical to the reference's
+// exclusive scan, empty cells included), bodies are physically reordered into cell order as packed
+// float4, and the 27-cell sweep (:83-152) walks 9 contiguous x-runs of that array.  Order inside a
+// cell is ascending body index, so results are reproducible.
+#include <cmath>
+#include <cstring>
+
+#include "common.cuh"
+
+namespace nb {
+int bbox_device(nb_context* ctx, const nb_particles* d, cudaStream_t st);
+int sort_pairs(nb_context* ctx, uint32_t* d_keys, int32_t* d_vals, size_t n, int end_bit, cudaStream_t st);
+}  // namespace nb
+
+struct SHMisc {  // device + pinned host mirror
+  float bbox[6];  // padded
+  int dims[3];
+  int too_large;
+  long long total;
+  unsigned long long pairs;
+};
+
+struct SH {
+  size_t n = 0;
+  float cell_size = 0.f;
+  int total_cells = 0;
+  int dims[3] = {0, 0, 0};
+  float bbox[6] = {0, 0, 0, 0, 0, 0};
+  nb::DevBuf particle_cell, keys, sorted_idx, spos, cell_start, cell_end, misc;
+  SHMisc* h_misc = nullptr;
+  bool built = false;
+};
+
+namespace nb {
+
+__device__ __forceinline__ float sh_ord2f(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); }
+
+// :226-232 pad, :244-246 dims = (int)ceilf((max-min)/cell)+1, :249-254 limit
+__global__ void sh_prepare_kernel(const int* __restrict__ bb_ord, float cell, SHMisc* __restrict__ m) {
+  if (threadIdx.x != 0) return;
+  float bb[6];
+  for (int a = 0; a < 3; a++) {
+    bb[a] = __fsub_rn(sh_ord2f(bb_ord[a]), 0.001f);
+    bb[3 + a] = __fadd_rn(sh_ord2f(bb_ord[3 + a]), 0.001f);
+  }
+  long long total = 1;
+  for (int a = 0; a < 3; a++) {
+    m->bbox[a] = bb[a];
+    m->bbox[3 + a] = bb[3 + a];
+    const int dgrid = (int)ceilf(__fdiv_rn(__fsub_rn(bb[3 + a], bb[a]), cell)) + 1;
+    m->dims[a] = dgrid;
+    total *= (long long)dgrid;
+  }
+  m->total = total;
+  m->too_large = total > 100000000LL ? 1 : 0;
+  m->pairs = 0ull;
+}
+
+// :28-49
+__global__ void __launch_bounds__(256) sh_assign_kernel(const float* __restrict__ px, const float* __restrict__ py,
+                                                        const float* __restrict__ pz, size_t n, float cell,
+                                                        const SHMisc* __restrict__ m, int32_t* __restrict__ pcell,
+                                                        uint32_t* __restrict__ keys, int32_t* __restrict__ vals) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int nx = m->dims[0], ny = m->dims[1], nz = m->dims[2];
+  const float x = __fsub_rn(px[i], m->bbox[0]), y = __fsub_rn(py[i], m->bbox[1]), z = __fsub_rn(pz[i], m->bbox[2]);
+  int cx = (int)floorf(__fdiv_rn(x, cell)), cy = (int)floorf(__fdiv_rn(y, cell)), cz = (int)floorf(__fdiv_rn(z, cell));
+  cx = max(0, min(cx, nx - 1));
+  cy = max(0, min(cy, ny - 1));
+  cz = max(0, min(cz, nz - 1));
+  const int c = cx + cy * nx + cz * nx * ny;
+  pcell[i] = c;
+  keys[i] = (uint32_t)c;
+  vals[i] = (int32_t)i;
+}
+
+// cell_start[c] = #bodies with cell < c ; cell_end[c] = #bodies with cell <= c  (:285-288, :61-68)
+__global__ void __launch_bounds__(256) sh_ranges_kernel(const uint32_t* __restrict__ keys, size_t n, int total_cells,
+                                                        int32_t* __restrict__ cell_start,
+                                                        int32_t* __restrict__ cell_end) {
+  const size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k > n) return;
+  const long long prev = (k == 0) ? -1 : (long long)keys[k - 1];
+  const long long cur = (k == n) ? (long long)total_cells : (long long)keys[k];
+  // cells prev+1 .. cur start at k; cells prev .. cur-1 end at k
+  for (long long c = prev + 1; c <= cur && c < total_cells; c++) cell_start[c] = (int32_t)k;
+  for (long long c = (prev < 0 ? 0 : prev); c < cur; c++) cell_end[c] = (int32_t)k;
+}
+
+__global__ void __launch_bounds__(256) sh_gather_kernel(nb_particles d, size_t n, const int32_t* __restrict__ sidx,
+                                                        float4* __restrict__ spos) {
+  const size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int i = sidx[k];
+  spos[k] = make_float4(d.pos_x[i], d.pos_y[i], d.pos_z[i], d.mass[i]);
+}
+
+// :83-152.  One thread per body in cell order; neighbours read as contiguous float4 runs.
+__global__ void __launch_bounds__(128) sh_force_kernel(size_t n, const float4* __restrict__ spos,
+                                                       const int32_t* __restrict__ sidx,
+                                                       const int32_t* __restrict__ cell_start,
+                                                       const int32_t* __restrict__ cell_end,
+                                                       const SHMisc* __restrict__ m, float cell, float cutoff2, float G,
+                                                       float eps2, float* __restrict__ ax, float* __restrict__ ay,
+                                                       float* __restrict__ az, unsigned long long* __restrict__ pairs) {
+  const size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  unsigned cnt = 0;
+  if (k < n) {
+    const int nx = m->dims[0], ny = m->dims[1], nz = m->dims[2];
+    const float4 me = spos[k];
+    // own cell recomputed WITHOUT clamp (:100-102)
+    const int cx = (int)floorf(__fdiv_rn(__fsub_rn(me.x, m->bbox[0]), cell));
+    const int cy = (int)floorf(__fdiv_rn(__fsub_rn(me.y, m->bbox[1]), cell));
+    const int cz = (int)floorf(__fdiv_rn(__fsub_rn(me.z, m->bbox[2]), cell));
+    float sx = 0.f, sy = 0.f, sz = 0.f;
+    for (int dz = -1; dz <= 1; dz++) {
+      const int z = cz + dz;
+      if (z < 0 || z >= nz) continue;
+      for (int dy = -1; dy <= 1; dy++) {
+        const int y = cy + dy;
+        if (y < 0 || y >= ny) continue;
+        // the in-grid part of x-1..x+1 is one contiguous run of the cell-ordered array
+        const int x0 = max(cx - 1, 0), x1 = min(cx + 1, nx - 1);
+        if (x0 > x1) continue;
+        const int row = y * nx + z * nx * ny;
+        const int j0 = cell_start[row + x0], j1 = cell_end[row + x1];
+        for (int j = j0; j < j1; j++) {
+          if (j == (int)k) continue;  // j == i (:125-126)
+          const float4 p = spos[j];
+          const float ddx = p.x - me.x, ddy = p.y - me.y, ddz = p.z - me.z;
+          float dist2 = __fadd_rn(__fadd_rn(__fmul_rn(ddx, ddx), __fmul_rn(ddy, ddy)), __fmul_rn(ddz, ddz));
+          if (dist2 < cutoff2) {  // un-softened test (:131-135)
+            dist2 = __fadd_rn(dist2, eps2);
+            const float inv = rsq(dist2);
+            const float f = (G * p.w) * (inv * inv * inv);
+            sx = fmaf(f, ddx, sx);
+            sy = fmaf(f, ddy, sy);
+            sz = fmaf(f, ddz, sz);
+            cnt++;
+          }
+        }
+      }
+    }
+    const int i = sidx[k];
+    ax[i] = sx;
+    ay[i] = sy;
+    az[i] = sz;
+  }
+  // one atomic per warp
+  unsigned long long c = cnt;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  if ((threadIdx.x & 31) == 0 && c) atomicAdd(pairs, c);
+}
+
+static SH* sh_get(nb_context* ctx) {
+  if (!ctx->sh) ctx->sh = new SH();
+  return ctx->sh;
+}
+
+void sh_destroy(nb_context* ctx) {
+  if (!ctx->sh) return;
+  SH* s = ctx->sh;
+  s->particle_cell.release(); s->keys.release(); s->sorted_idx.release(); s->spos.release();
+  s->cell_start.release(); s->cell_end.release(); s->misc.release();
+  if (s->h_misc) cudaFreeHost(s->h_misc);
+  delete s;
+  ctx->sh = nullptr;
+}
+
+int sh_build(nb_context* ctx, const nb_particles* d, float cell, cudaStream_t st) {
+  SH* s = sh_get(ctx);
+  const size_t n = d->count;
+  s->built = false;
+  if (!(cell > 0.f) || std::isnan(cell) || std::isinf(cell)) {
+    set_error("Spatial hash cell size must be positive and finite");
+    return NB_ERR_INVALID;
+  }
+  if (n == 0) return NB_OK;
+  if (n > 0x7ffffff0ull) {
+    set_error("spatial hash: particle count %zu too large", n);
+    return NB_ERR_INVALID;
+  }
+  s->n = n;
+  s->cell_size = cell;
+  if (int rc = s->particle_cell.ensure(n * 4)) return rc;
+  if (int rc = s->keys.ensure(n * 4)) return rc;
+  if (int rc = s->sorted_idx.ensure(n * 4)) return rc;
+  if (int rc = s->spos.ensure(n * sizeof(float4))) return rc;
+  if (int rc = s->misc.ensure(sizeof(SHMisc))) return rc;
+  if (!s->h_misc) NB_CUDA(cudaMallocHost(&s->h_misc, sizeof(SHMisc)));
+  SHMisc* misc = s->misc.as<SHMisc>();
+  if (int rc = bbox_device(ctx, d, st)) return rc;
+  sh_prepare_kernel<<<1, 32, 0, st>>>(ctx->bbox_dev.as<int>(), cell, misc);
+  NB_LAUNCH_CHECK(ctx);
+  // the grid size decides the allocation: one small readback (the reference does 12 here)
+  NB_CUDA(cudaMemcpyAsync(s->h_misc, misc, sizeof(SHMisc), cudaMemcpyDeviceToHost, st));
+  NB_CUDA(cudaStreamSynchronize(st));
+  if (s->h_misc->too_large) {
+    set_error("Spatial hash grid too large: reduce cell_size or bounding box");  // :252-254
+    return NB_ERR_GRID_TOO_LARGE;
+  }
+  s->total_cells = (int)s->h_misc->total;
+  memcpy(s->dims, s->h_misc->dims, sizeof s->dims);
+  memcpy(s->bbox, s->h_misc->bbox, sizeof s->bbox);
+  if (int rc = s->cell_start.ensure((size_t)s->total_cells * 4)) return rc;
+  if (int rc = s->cell_end.ensure((size_t)s->total_cells * 4)) return rc;
+  const unsigned gn = (unsigned)((n + 255) / 256);
+  sh_assign_kernel<<<gn, 256, 0, st>>>(d->pos_x, d->pos_y, d->pos_z, n, cell, misc, s->particle_cell.as<int32_t>(),
+                                       s->keys.as<uint32_t>(), s->sorted_idx.as<int32_t>());
+  NB_LAUNCH_CHECK(ctx);
+  int bits = 1;
+  while (bits < 32 && (1ll << bits) < (long long)s->total_cells) bits++;
+  if (int rc = sort_pairs(ctx, s->keys.as<uint32_t>(), s->sorted_idx.as<int32_t>(), n, bits, st)) return rc;
+  sh_ranges_kernel<<<(unsigned)((n + 1 + 255) / 256), 256, 0, st>>>(s->keys.as<uint32_t>(), n, s->total_cells,
+                                                                    s->cell_start.as<int32_t>(),
+                                                                    s->cell_end.as<int32_t>());
+  NB_LAUNCH_CHECK(ctx);
+  sh_gather_kernel<<<gn, 256, 0, st>>>(*d, n, s->sorted_idx.as<int32_t>(), s->spos.as<float4>());
+  NB_LAUNCH_CHECK(ctx);
+  s->built = true;
+  return NB_OK;
+}
+
+int sh_forces(nb_context* ctx, const nb_particles* d, float cutoff, float G, float eps, cudaStream_t st) {
+  SH* s = sh_get(ctx);
+  const size_t n = d->count;
+  if (n == 0) return NB_OK;
+  if (!s->built || s->n != n) {
+    set_error("spatial hash: forces requested without a grid built for these particles");
+    return NB_ERR_INVALID;
+  }
+  SHMisc* misc = s->misc.as<SHMisc>();
+  ProfScope prof(ctx, st);
+  sh_force_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(
+      n, s->spos.as<float4>(), s->sorted_idx.as<int32_t>(), s->cell_start.as<int32_t>(), s->cell_end.as<int32_t>(),
+      misc, s->cell_size, cutoff * cutoff, G, eps * eps, d->acc_x, d->acc_y, d->acc_z, &misc->pairs);
+  NB_LAUNCH_CHECK(ctx);
+  return NB_OK;
+}
+
+}  // namespace nb
+
+using namespace nb;
+
+extern "C" {
+
+int nb_sh_build(nb_context* ctx, const nb_particles* d, float cell_size, nb_stream s) {
+  if (!ctx || !d || (d->count && (!d->pos_x || !d->pos_y || !d->pos_z || !d->mass))) {
+    set_error("spatial hash build: null argument");
+    return NB_ERR_INVALID;
+  }
+  NB_CUDA(cudaSetDevice(ctx->device));
+  return sh_build(ctx, d, cell_size, (cudaStream_t)s);
+}
+
+int nb_sh_forces(nb_context* ctx, const nb_particles* d, float cutoff, float G, float eps, nb_stream s) {
+  if (!ctx || !d || (d->count && (!d->acc_x || !d->acc_y || !d->acc_z))) {
+    set_error("spatial hash forces: null argument");
+    return NB_ERR_INVALID;
+  }
+  NB_CUDA(cudaSetDevice(ctx->device));
+  return sh_forces(ctx, d, cutoff, G, eps, (cudaStream_t)s);
+}
+
+int nb_sh_total_cells(nb_context* ctx, int* total_cells) {
+  if (!ctx || !ctx->sh || !ctx->sh->built || !total_cells) {
+    set_error("spatial hash: no grid built");
+    return NB_ERR_INVALID;
+  }
+  *total_cells = ctx->sh->total_cells;
+  return NB_OK;
+}
+
+int nb_sh_export(nb_context* ctx, int32_t dims[3], float bbox_padded[6], int32_t* particle_cell, int32_t* cell_start,
+                 int32_t* cell_end, int32_t* sorted_indices) {
+  if (!ctx || !ctx->sh || !ctx->sh->built) {
+    set_error("spatial hash export: no grid built");
+    return NB_ERR_INVALID;
+  }
+  NB_CUDA(cudaSetDevice(ctx->device));
+  NB_CUDA(cudaDeviceSynchronize());
+  SH* s = ctx->sh;
+  if (dims) memcpy(dims, s->dims, sizeof s->dims);
+  if (bbox_padded) memcpy(bbox_padded, s->bbox, sizeof s->bbox);
+  if (particle_cell) NB_CUDA(cudaMemcpy(particle_cell, s->particle_cell.p, s->n * 4, cudaMemcpyDeviceToHost));
+  if (cell_start) NB_CUDA(cudaMemcpy(cell_start, s->cell_start.p, (size_t)s->total_cells * 4, cudaMemcpyDeviceToHost));
+  if (cell_end) NB_CUDA(cudaMemcpy(cell_end, s->cell_end.p, (size_t)s->total_cells * 4, cudaMemcpyDeviceToHost));
+  if (sorted_indices) NB_CUDA(cudaMemcpy(sorted_indices, s->sorted_idx.p, s->n * 4, cudaMemcpyDeviceToHost));
+  return NB_OK;
+}
+
+}  // extern "C"
