@@ -9,9 +9,11 @@
 // tree over those keys (Karras 2012), and the traversal keeps the reference's acceptance test
 // (is-leaf or size^2/(d^2+eps^2) < theta^2, :167) and monopole formula (:175-181), with "size" the
 // side of the Morton cell the node lives in (== the reference's octree cell 2*half_size at every
-// third level for a cubic box).  32 Morton-consecutive bodies walk the tree together: a node is
-// used only if every lane accepts it (__all_sync), so each body's force is at least as accurate as
+// third level for a cubic box).  Bodies walk the tree in groups (maximal subtrees of <= 64 leaves,
+// one warp each): a node is used only if it passes the test at the group's bounding box, which
+// implies it passes for every body of the group, so each body's force is at least as accurate as
 // with its own per-body test.
+#include <cstdlib>
 #include <cstring>
 
 #include "common.cuh"
@@ -26,7 +28,12 @@ int sort_pairs(nb_context* ctx, uint32_t* d_keys, int32_t* d_vals, size_t n, int
 struct BH {
   size_t n = 0;
   nb::DevBuf keys, perm, node_com, meta, parent, flags, misc;  // misc: size2 table[32] + counter + bbox floats
+  nb::DevBuf range, groups;  // int2 {first,last} per internal node; int2 {first,count} per traversal group
   float h_bbox[6] = {0, 0, 0, 0, 0, 0};
+  int* h_flag = nullptr;  // host-mapped: traversal stack overflow
+  int* d_flag = nullptr;
+  int group = 64;         // max bodies per traversal group / warp (32 or 64; NB_BH_GROUP overrides)
+  int occ = 0;
   bool built = false;
 };
 
@@ -43,7 +50,8 @@ __device__ __forceinline__ unsigned expand_bits(unsigned v) {
   return v;
 }
 
-// misc layout (floats): [0..31] size2 table by prefix length, [32..37] bbox, [40..41] u64 counter
+// misc layout (floats): [0..31] size2 table by prefix length, [32..37] bbox, [40..41] u64 counter,
+// [44] int number of traversal groups, [45] int work-queue cursor of the traversal kernel
 __global__ void bh_prepare_kernel(const int* __restrict__ bb_ord, float* __restrict__ misc) {
   const int t = threadIdx.x;
   __shared__ float bb[6];
@@ -52,6 +60,7 @@ __global__ void bh_prepare_kernel(const int* __restrict__ bb_ord, float* __restr
     misc[32 + t] = bb[t];
   }
   if (t == 6) *reinterpret_cast<unsigned long long*>(misc + 40) = 0ull;
+  if (t == 7) reinterpret_cast<int*>(misc)[44] = 0;  // number of traversal groups
   __syncthreads();
   if (t <= 30) {
     // side of the Morton cell at prefix length L: x is split first, then y, then z
@@ -105,7 +114,8 @@ __device__ __forceinline__ int bh_delta(const uint32_t* __restrict__ k, int n, i
 
 // Karras 2012, sec. 4: one thread per internal node.  meta[i] = {left, right, prefix, 0}.
 __global__ void __launch_bounds__(256) bh_karras_kernel(const uint32_t* __restrict__ keys, int n,
-                                                        int4* __restrict__ meta, int32_t* __restrict__ parent) {
+                                                        int4* __restrict__ meta, int32_t* __restrict__ parent,
+                                                        int2* __restrict__ range) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n - 1) return;
   const int leaf0 = n - 1;
@@ -130,6 +140,7 @@ __global__ void __launch_bounds__(256) bh_karras_kernel(const uint32_t* __restri
   int p = dnode - 2;
   if (p > 30) p = 30;
   meta[i] = make_int4(lc, rc, p, 0);
+  range[i] = make_int2(lo, hi);
   parent[lc] = i;
   parent[rc] = i;
   if (i == 0) parent[0] = -1;
@@ -163,76 +174,183 @@ __global__ void __launch_bounds__(256) bh_com_kernel(int n, const int4* __restri
   }
 }
 
-// ---- traversal ---------------------------------------------------------------------------------------
-constexpr int BH_WARPS = 8;
-constexpr int BH_STACK = 96;
+// Traversal groups = maximal subtrees with at most `gmax` leaves: the bodies of a group share a
+// Morton prefix, so the group's bounding box is as tight as its cell (a fixed run of 32
+// consecutive sorted bodies can straddle distant cells in sparse regions).  One thread per leaf
+// climbs to its group's root; the leaf that is the root's first body publishes {first, count}.
+__global__ void __launch_bounds__(256) bh_groups_kernel(int n, int gmax, const int32_t* __restrict__ parent,
+                                                        const int2* __restrict__ range, int2* __restrict__ groups,
+                                                        int* __restrict__ ngroups) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  int first = k, count = 1;
+  int p = parent[n - 1 + k];
+  while (p >= 0) {
+    const int2 r = range[p];
+    if (r.y - r.x + 1 > gmax) break;
+    first = r.x;
+    count = r.y - r.x + 1;
+    p = parent[p];
+  }
+  if (first == k) groups[atomicAdd(ngroups, 1)] = make_int2(first, count);
+}
 
+// ---- traversal ---------------------------------------------------------------------------------------
+// One warp owns 32*BPL Morton-consecutive bodies and a stack of node indices in shared memory.
+// Each round the warp pops up to 32 nodes, ONE PER LANE: every lane fetches its node and tests it
+// against the group's bounding box (dmin = distance from the node's centre of mass to the box, so
+// dmin <= every body's own distance and a node the group accepts is a node every body would accept
+// with the reference's per-body test, :160-172).  __ballot_sync + popc compact the accepted nodes
+// into an interaction list and the children of the rejected ones back onto the stack.  Whenever
+// the list holds 32 entries they are evaluated: entry e is a warp-broadcast LDS.128 and every lane
+// adds the monopole term (:175-181) for its own bodies.  Order is deterministic (lane order), and
+// oracle/lbvh.c restates it step for step.
+constexpr int BH_WARPS = 4;
+constexpr int BH_STACK = 2048;
+constexpr int BH_LIST = 64;
+constexpr int BH_SMEM_PER_WARP = BH_STACK * 4 + BH_LIST * 16;
+
+template <int BPL, bool EPS0>
 __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const float4* __restrict__ node_com,
                                                                   const int4* __restrict__ meta,
                                                                   const int32_t* __restrict__ perm,
                                                                   const float* __restrict__ misc, float theta2, float G,
                                                                   float eps2, float* __restrict__ ax,
                                                                   float* __restrict__ ay, float* __restrict__ az,
-                                                                  unsigned long long* __restrict__ counter) {
-  __shared__ int stack[BH_WARPS][BH_STACK];
+                                                                  unsigned long long* __restrict__ counter,
+                                                                  int* __restrict__ overflow,
+                                                                  const int2* __restrict__ groups,
+                                                                  const int* __restrict__ ngroups,
+                                                                  int* __restrict__ cursor) {
+  extern __shared__ __align__(16) unsigned char bh_smem[];
   __shared__ float size2_tab[32];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   if (threadIdx.x < 32) size2_tab[threadIdx.x] = misc[threadIdx.x];
   __syncthreads();
+  float4* list = reinterpret_cast<float4*>(bh_smem + (size_t)w * BH_SMEM_PER_WARP);
+  int* stack = reinterpret_cast<int*>(bh_smem + (size_t)w * BH_SMEM_PER_WARP + BH_LIST * 16);
   const int leaf0 = n - 1;
-  const long long group = (long long)blockIdx.x * BH_WARPS + w;
-  const long long k = group * 32 + lane;
-  if (group * 32 >= n) return;
-  const bool live = k < n;
-  const float4 me = live ? node_com[leaf0 + k] : make_float4(0.f, 0.f, 0.f, 0.f);
-  float sx = 0.f, sy = 0.f, sz = 0.f;
+  const unsigned lt = (1u << lane) - 1u;
+  const int total_groups = *ngroups;
+  unsigned long long visits_bodies = 0;
+
+  for (;;) {  // persistent warp: pull traversal groups from a work queue until it is empty
+  int g = 0;
+  if (lane == 0) g = atomicAdd(cursor, 1);
+  g = __shfl_sync(0xffffffffu, g, 0);
+  if (g >= total_groups) break;
+  const int2 grp = groups[g];
+  const int k0 = grp.x, gcnt = grp.y;
+
+  float4 me[BPL];
+  float sx[BPL], sy[BPL], sz[BPL];
+  float lo[3] = {3.0e38f, 3.0e38f, 3.0e38f}, hi[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
+#pragma unroll
+  for (int b = 0; b < BPL; b++) {
+    me[b] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (b * 32 + lane < gcnt) {
+      me[b] = node_com[leaf0 + k0 + b * 32 + lane];
+      lo[0] = fminf(lo[0], me[b].x); hi[0] = fmaxf(hi[0], me[b].x);
+      lo[1] = fminf(lo[1], me[b].y); hi[1] = fmaxf(hi[1], me[b].y);
+      lo[2] = fminf(lo[2], me[b].z); hi[2] = fmaxf(hi[2], me[b].z);
+    }
+    sx[b] = sy[b] = sz[b] = 0.f;
+  }
+#pragma unroll
+  for (int a = 0; a < 3; a++) {
+    lo[a] = warp_min(lo[a]);
+    hi[a] = warp_max(hi[a]);
+  }
+
+  int sp = 1, nl = 0;
   unsigned visits = 0;
-  int* st = stack[w];
-  int sp = 0;
-  int ni = 0;
+  if (lane == 0) stack[0] = 0;
+  __syncwarp();
   for (;;) {
-    const float4 c = node_com[ni];  // same address in every lane: one broadcast load
-    bool descend = false;
-    if (c.w != 0.f) {  // total_mass == 0 -> skip (:157-158)
-      const float dx = c.x - me.x, dy = c.y - me.y, dz = c.z - me.z;
-      const float d2 = fmaf(dz, dz, fmaf(dy, dy, fmaf(dx, dx, eps2)));
-      const bool is_leaf = ni >= leaf0;
-      int4 m = make_int4(0, 0, 31, 0);
-      if (!is_leaf) m = meta[ni];
-      const float size2 = size2_tab[m.z];
-      const bool accept = !live || is_leaf || (size2 < theta2 * d2);  // size2/dist2 < theta2 (:167)
-      if (__all_sync(0xffffffffu, accept)) {
-        if (live && !(is_leaf && ni == leaf0 + (int)k)) {  // own leaf skipped (:174)
-          const float inv = rsq(d2);
-          const float f = (G * c.w) * (inv * inv * inv);
-          sx = fmaf(f, dx, sx);
-          sy = fmaf(f, dy, sy);
-          sz = fmaf(f, dz, sz);
+    const int m = min(sp, 32);
+    const bool have = lane < m;
+    const int ni = have ? stack[sp - m + lane] : 0;
+    sp -= m;
+    __syncwarp();
+    float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (have) c = node_com[ni];
+    const bool valid = have && c.w != 0.f;  // total_mass == 0 -> skipped (:157-158)
+    const bool leaf = ni >= leaf0;
+    int4 mt = make_int4(0, 0, 31, 0);
+    bool acc = leaf;
+    if (valid && !leaf) {
+      mt = meta[ni];
+      const float ddx = fmaxf(fmaxf(lo[0] - c.x, c.x - hi[0]), 0.f);
+      const float ddy = fmaxf(fmaxf(lo[1] - c.y, c.y - hi[1]), 0.f);
+      const float ddz = fmaxf(fmaxf(lo[2] - c.z, c.z - hi[2]), 0.f);
+      const float d2 = fmaf(ddz, ddz, fmaf(ddy, ddy, fmaf(ddx, ddx, eps2)));
+      acc = size2_tab[mt.z] < theta2 * d2;  // size2 / dist2 < theta2 (:167)
+    }
+    const bool is_acc = valid && acc, is_rej = valid && !acc;
+    const unsigned amask = __ballot_sync(0xffffffffu, is_acc), rmask = __ballot_sync(0xffffffffu, is_rej);
+    if (is_acc) list[nl + __popc(amask & lt)] = c;
+    const int npush = 2 * __popc(rmask);
+    if (sp + npush > BH_STACK) {  // never silently drop subtrees (the reference does, :186-194)
+      if (lane == 0) *overflow = 1;
+      break;
+    }
+    if (is_rej) {
+      const int pos = sp + 2 * __popc(rmask & lt);
+      stack[pos] = mt.x;
+      stack[pos + 1] = mt.y;
+    }
+    nl += __popc(amask);
+    sp += npush;
+    __syncwarp();
+    const bool done = (sp == 0);
+    while (nl >= 32 || (done && nl > 0)) {
+      const int ne = min(nl, 32);
+      auto body = [&](int e) {
+        const float4 p = list[e];  // warp-broadcast LDS.128
+        const float gm = G * p.w;
+#pragma unroll
+        for (int b = 0; b < BPL; b++) {
+          const float dx = p.x - me[b].x, dy = p.y - me[b].y, dz = p.z - me[b].z;
+          const float d2 = fmaf(dz, dz, fmaf(dy, dy, fmaf(dx, dx, eps2)));
+          float inv = rsq(d2);
+          if (EPS0) inv = (d2 > 0.f) ? inv : 0.f;  // own leaf / exact coincidence at eps = 0
+          const float f = gm * (inv * inv * inv);
+          sx[b] = fmaf(f, dx, sx[b]);
+          sy[b] = fmaf(f, dy, sy[b]);
+          sz[b] = fmaf(f, dz, sz[b]);
         }
-        visits++;
+      };
+      if (ne == 32) {
+#pragma unroll 8
+        for (int e = 0; e < 32; e++) body(e);
       } else {
-        descend = true;
-        if (lane == 0) st[sp] = m.y;  // right child waits, left child is next
-        sp++;
-        ni = m.x;
-        __syncwarp();
+        for (int e = 0; e < ne; e++) body(e);
       }
+      visits += ne;
+      __syncwarp();
+      const int rest = nl - ne;  // < 32
+      float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (lane < rest) t = list[ne + lane];
+      __syncwarp();
+      if (lane < rest) list[lane] = t;
+      __syncwarp();
+      nl = rest;
     }
-    if (!descend) {
-      if (sp == 0) break;
-      ni = st[--sp];
+    if (done) break;
+  }
+#pragma unroll
+  for (int b = 0; b < BPL; b++) {
+    if (b * 32 + lane < gcnt) {
+      const int i = perm[k0 + b * 32 + lane];
+      ax[i] = sx[b];
+      ay[i] = sy[b];
+      az[i] = sz[b];
     }
   }
-  if (live) {
-    const int i = perm[k];
-    ax[i] = sx;
-    ay[i] = sy;
-    az[i] = sz;
-  }
-  if (lane == 0) {
-    const int cnt = (int)min((long long)32, (long long)n - group * 32);
-    atomicAdd(counter, (unsigned long long)visits * cnt);
-  }
+  visits_bodies += (unsigned long long)visits * (unsigned long long)gcnt;
+  __syncwarp();
+  }  // next group
+  if (lane == 0 && visits_bodies) atomicAdd(counter, visits_bodies);
 }
 
 static BH* bh_get(nb_context* ctx) {
@@ -244,7 +362,8 @@ void bh_destroy(nb_context* ctx) {
   if (!ctx->bh) return;
   BH* b = ctx->bh;
   b->keys.release(); b->perm.release(); b->node_com.release(); b->meta.release();
-  b->parent.release(); b->flags.release(); b->misc.release();
+  b->parent.release(); b->flags.release(); b->misc.release(); b->range.release(); b->groups.release();
+  if (b->h_flag) cudaFreeHost(b->h_flag);
   delete b;
   ctx->bh = nullptr;
 }
@@ -266,6 +385,14 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
   if (int rc = b->parent.ensure(2 * n * 4)) return rc;
   if (int rc = b->flags.ensure(n * 4)) return rc;
   if (int rc = b->misc.ensure(64 * 4)) return rc;
+  if (int rc = b->range.ensure(n * sizeof(int2))) return rc;
+  if (int rc = b->groups.ensure(n * sizeof(int2))) return rc;
+  {
+    const char* e = getenv("NB_BH_GROUP");
+    const int g = (e && atoi(e) == 32) ? 32 : 64;
+    if (g != b->group) b->occ = 0;
+    b->group = g;
+  }
   float* misc = b->misc.as<float>();
   if (int rc = bbox_device(ctx, d, st)) return rc;
   bh_prepare_kernel<<<1, 32, 0, st>>>(ctx->bbox_dev.as<int>(), misc);
@@ -282,12 +409,25 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
   if (n > 1) {
     NB_CUDA(cudaMemsetAsync(b->flags.p, 0, (n - 1) * 4, st));
     const unsigned gi = (unsigned)((n - 1 + 255) / 256);
-    bh_karras_kernel<<<gi, 256, 0, st>>>(b->keys.as<uint32_t>(), (int)n, b->meta.as<int4>(), b->parent.as<int32_t>());
+    bh_karras_kernel<<<gi, 256, 0, st>>>(b->keys.as<uint32_t>(), (int)n, b->meta.as<int4>(), b->parent.as<int32_t>(),
+                                         b->range.as<int2>());
     NB_LAUNCH_CHECK(ctx);
     bh_com_kernel<<<gn, 256, 0, st>>>((int)n, b->meta.as<int4>(), b->parent.as<int32_t>(), b->flags.as<int>(), com);
     NB_LAUNCH_CHECK(ctx);
   }
+  bh_groups_kernel<<<gn, 256, 0, st>>>((int)n, b->group, b->parent.as<int32_t>(), b->range.as<int2>(),
+                                       b->groups.as<int2>(), reinterpret_cast<int*>(misc) + 44);
+  NB_LAUNCH_CHECK(ctx);
   b->built = true;
+  return NB_OK;
+}
+
+static int bh_check_overflow(BH* b) {
+  if (b->h_flag && *b->h_flag) {
+    *b->h_flag = 0;
+    set_error("Barnes-Hut traversal stack overflow (tree deeper than the %d-entry warp stack allows)", BH_STACK);
+    return NB_ERR_INTERNAL;
+  }
   return NB_OK;
 }
 
@@ -299,13 +439,44 @@ int bh_forces(nb_context* ctx, const nb_particles* d, float theta, float G, floa
     set_error("Barnes-Hut: forces requested without a tree built for these particles");
     return NB_ERR_INVALID;
   }
+  if (!b->h_flag) {
+    NB_CUDA(cudaHostAlloc(&b->h_flag, sizeof(int), cudaHostAllocMapped));
+    *b->h_flag = 0;
+    NB_CUDA(cudaHostGetDevicePointer(&b->d_flag, b->h_flag, 0));
+  }
+  if (int rc = bh_check_overflow(b)) return rc;  // reported by an earlier (asynchronous) launch
   float* misc = b->misc.as<float>();
-  const long long groups = ((long long)n + 31) / 32;
-  const unsigned grid = (unsigned)((groups + BH_WARPS - 1) / BH_WARPS);
+  int* cursor = reinterpret_cast<int*>(misc) + 45;
+  NB_CUDA(cudaMemsetAsync(cursor, 0, sizeof(int), st));
+  const size_t smem = (size_t)BH_WARPS * BH_SMEM_PER_WARP;
+  const float eps2 = eps * eps;
+  const bool eps0 = !(eps2 > 0.f);
+  if (!b->occ) {
+    int o = 0;
+    if (b->group == 64)
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, bh_force_kernel<2, false>, BH_WARPS * 32, smem);
+    else
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, bh_force_kernel<1, false>, BH_WARPS * 32, smem);
+    b->occ = o > 0 ? o : 1;
+  }
+  long long max_groups = (long long)n;  // upper bound (the real count lives on the device)
+  long long want = (max_groups + BH_WARPS - 1) / BH_WARPS;
+  long long cap = (long long)b->occ * ctx->sm_count;
+  const unsigned grid = (unsigned)(want < cap ? want : cap);
   ProfScope prof(ctx, st);
-  bh_force_kernel<<<grid, BH_WARPS * 32, 0, st>>>((int)n, b->node_com.as<float4>(), b->meta.as<int4>(),
-                                                  b->perm.as<int32_t>(), misc, theta * theta, G, eps * eps, d->acc_x,
-                                                  d->acc_y, d->acc_z, reinterpret_cast<unsigned long long*>(misc + 40));
+#define NB_BH_LAUNCH(BPL_, E_)                                                                                     \
+  bh_force_kernel<BPL_, E_><<<grid, BH_WARPS * 32, smem, st>>>(                                                    \
+      (int)n, b->node_com.as<float4>(), b->meta.as<int4>(), b->perm.as<int32_t>(), misc, theta * theta, G, eps2,  \
+      d->acc_x, d->acc_y, d->acc_z, reinterpret_cast<unsigned long long*>(misc + 40), b->d_flag,                   \
+      b->groups.as<int2>(), reinterpret_cast<const int*>(misc) + 44, cursor)
+  if (b->group == 64) {
+    if (eps0) NB_BH_LAUNCH(2, true);
+    else NB_BH_LAUNCH(2, false);
+  } else {
+    if (eps0) NB_BH_LAUNCH(1, true);
+    else NB_BH_LAUNCH(1, false);
+  }
+#undef NB_BH_LAUNCH
   NB_LAUNCH_CHECK(ctx);
   return NB_OK;
 }
@@ -377,6 +548,7 @@ int nb_bh_stats(nb_context* ctx, uint64_t* interactions, int* node_count) {
   }
   NB_CUDA(cudaSetDevice(ctx->device));
   NB_CUDA(cudaDeviceSynchronize());
+  if (int rc = bh_check_overflow(ctx->bh)) return rc;
   if (interactions) NB_CUDA(cudaMemcpy(interactions, ctx->bh->misc.as<float>() + 40, 8, cudaMemcpyDeviceToHost));
   if (node_count) *node_count = (int)(2 * ctx->bh->n - 1);
   return NB_OK;

@@ -85,7 +85,7 @@ void orc_lbvh_com(int n, const int32_t* left, const int32_t* right, const float*
     const float* a = node_com + 4 * (size_t)l;
     const float* b = node_com + 4 * (size_t)r;
     float* c = node_com + 4 * (size_t)i;
-    /* same operation order as the GPU kernel (nbody_b200/csrc/lbvh.cu: bh_com_kernel):
+    /* same operation order as the GPU kernel (nbody_b200/csrc/bh.cu: bh_com_kernel):
      * m = ma + mb; c = (ca*ma + cb*mb) / m with separately rounded mul, add, div. */
     float m = a[3] + b[3];
     if (m > 0.0f) {
@@ -116,59 +116,125 @@ float orc_lbvh_cell_size(int L, const float bbox[6]) {
 }
 
 void orc_lbvh_forces(int n, const int32_t* left, const int32_t* right, const int32_t* prefix,
-                     const float* node_com, const float* sx, const float* sy, const float* sz,
-                     const float bbox[6], float theta, float G, float eps, int group, float* ax, float* ay,
-                     float* az, uint64_t* interactions) {
+                     const int32_t* range_first, const int32_t* range_last, const float* node_com,
+                     const float* sx, const float* sy, const float* sz, const float bbox[6], float theta, float G,
+                     float eps, int group, float* ax, float* ay, float* az, uint64_t* interactions) {
+  /* Sequential restatement of nbody_b200/csrc/bh.cu: bh_groups_kernel + bh_force_kernel.  Traversal
+   * groups are the maximal subtrees with at most `group` (32 or 64) leaves (a lone leaf whose
+   * parent is larger is a group of one).  A group (one warp) owns a stack of node indices.  Each round pops the top
+   * min(32, size) entries (one per lane, bottom-to-top = lane 0..m-1).  A node is used for the whole
+   * group iff it is a leaf or size^2 < theta^2 * (dmin^2 + eps^2), dmin = distance from the node's
+   * centre of mass to the group's bounding box (<= every body's own distance, so every body of the
+   * group would also accept it under the reference's per-body test,
+   * src/cuda/force_barnes_hut.cu:160-172); otherwise its children are pushed (left, right) in lane
+   * order.  Accepted nodes are appended in lane order to an interaction list that is evaluated 32
+   * entries at a time, each body accumulating in list order with the reference's monopole formula
+   * (:175-181).  A term with d^2 == 0 (the body's own leaf or an exact coincidence at eps = 0)
+   * contributes nothing; with eps > 0 the own leaf contributes exactly +0. */
   const float theta2 = theta * theta, eps2 = eps * eps;
   const int leaf0 = n - 1;
-  float size2_of[31];
+  float size2_of[32];
   for (int L = 0; L <= 30; L++) {
     float s = orc_lbvh_cell_size(L, bbox);
     size2_of[L] = s * s;
   }
+  size2_of[31] = 0.0f;
   uint64_t total = 0;
-  const int ngroups = (n + group - 1) / group;
-#pragma omp parallel for schedule(dynamic, 16) reduction(+ : total)
-  for (int g = 0; g < ngroups; g++) {
-    const int k0 = g * group, k1 = (k0 + group < n) ? k0 + group : n, cnt = k1 - k0;
-    float accx[64], accy[64], accz[64], dxs[64], dys[64], dzs[64], d2s[64];
-    for (int t = 0; t < cnt; t++) accx[t] = accy[t] = accz[t] = 0.0f;
-    int32_t stack[192];
+  /* groups: top-down, a node whose leaf range fits becomes a group */
+  int32_t* gfirst = (int32_t*)malloc(sizeof(int32_t) * (size_t)n);
+  int32_t* gcount = (int32_t*)malloc(sizeof(int32_t) * (size_t)n);
+  int ngroups = 0;
+  {
+    int32_t* st = (int32_t*)malloc(sizeof(int32_t) * (size_t)(2 * n + 2));
     int sp = 0;
-    stack[sp++] = 0;
+    st[sp++] = 0;
     while (sp > 0) {
-      const int ni = stack[--sp];
-      const float* c = node_com + 4 * (size_t)ni;
-      if (c[3] == 0.0f) continue; /* src/cuda/force_barnes_hut.cu:157-158 */
-      const int is_leaf = ni >= leaf0;
-      const float size2 = is_leaf ? 0.0f : size2_of[prefix[ni]];
-      int all_accept = 1;
-      for (int t = 0; t < cnt; t++) {
-        const int k = k0 + t;
-        float dx = c[0] - sx[k], dy = c[1] - sy[k], dz = c[2] - sz[k];
-        float d2 = fmaf(dz, dz, fmaf(dy, dy, fmaf(dx, dx, eps2)));
-        dxs[t] = dx; dys[t] = dy; dzs[t] = dz; d2s[t] = d2;
-        /* reference test: size2 / dist2 < theta2 (:167); evaluated as size2 < theta2*dist2 */
-        if (!(is_leaf || size2 < theta2 * d2)) all_accept = 0;
-      }
-      if (all_accept) {
-        for (int t = 0; t < cnt; t++) {
-          if (is_leaf && ni == leaf0 + k0 + t) continue; /* own leaf, :174 */
-          float inv = 1.0f / sqrtf(d2s[t]);
-          float f = (G * c[3]) * (inv * inv * inv);
-          accx[t] = fmaf(f, dxs[t], accx[t]);
-          accy[t] = fmaf(f, dys[t], accy[t]);
-          accz[t] = fmaf(f, dzs[t], accz[t]);
-        }
-        total += (uint64_t)cnt;
+      const int ni = st[--sp];
+      if (ni >= leaf0) {
+        gfirst[ngroups] = ni - leaf0;
+        gcount[ngroups++] = 1;
+      } else if (range_last[ni] - range_first[ni] + 1 <= group) {
+        gfirst[ngroups] = range_first[ni];
+        gcount[ngroups++] = range_last[ni] - range_first[ni] + 1;
       } else {
-        stack[sp++] = right[ni];
-        stack[sp++] = left[ni];
+        st[sp++] = right[ni];
+        st[sp++] = left[ni];
       }
     }
+    free(st);
+  }
+#pragma omp parallel for schedule(dynamic, 16) reduction(+ : total)
+  for (int g = 0; g < ngroups; g++) {
+    const int k0 = gfirst[g], cnt = gcount[g];
+    float accx[64], accy[64], accz[64];
+    float lo[3] = {3.0e38f, 3.0e38f, 3.0e38f}, hi[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
+    for (int t = 0; t < cnt; t++) {
+      accx[t] = accy[t] = accz[t] = 0.0f;
+      lo[0] = fminf(lo[0], sx[k0 + t]); hi[0] = fmaxf(hi[0], sx[k0 + t]);
+      lo[1] = fminf(lo[1], sy[k0 + t]); hi[1] = fmaxf(hi[1], sy[k0 + t]);
+      lo[2] = fminf(lo[2], sz[k0 + t]); hi[2] = fmaxf(hi[2], sz[k0 + t]);
+    }
+    int32_t* stack = (int32_t*)malloc(sizeof(int32_t) * 8192);
+    int32_t list[96];
+    int sp = 0, nl = 0;
+    stack[sp++] = 0;
+    for (;;) {
+      const int m = sp < 32 ? sp : 32;
+      int32_t popped[32];
+      for (int l = 0; l < m; l++) popped[l] = stack[sp - m + l];
+      sp -= m;
+      int32_t push[64];
+      int np = 0;
+      for (int l = 0; l < m; l++) {
+        const int ni = popped[l];
+        const float* c = node_com + 4 * (size_t)ni;
+        if (c[3] == 0.0f) continue; /* src/cuda/force_barnes_hut.cu:157-158 */
+        int accept = 1;
+        if (ni < leaf0) {
+          float ddx = fmaxf(fmaxf(lo[0] - c[0], c[0] - hi[0]), 0.0f);
+          float ddy = fmaxf(fmaxf(lo[1] - c[1], c[1] - hi[1]), 0.0f);
+          float ddz = fmaxf(fmaxf(lo[2] - c[2], c[2] - hi[2]), 0.0f);
+          float d2 = fmaf(ddz, ddz, fmaf(ddy, ddy, fmaf(ddx, ddx, eps2)));
+          accept = size2_of[prefix[ni]] < theta2 * d2;
+        }
+        if (accept) {
+          list[nl++] = ni;
+        } else {
+          push[np++] = left[ni];
+          push[np++] = right[ni];
+        }
+      }
+      for (int q = 0; q < np; q++) stack[sp++] = push[q];
+      const int done = (sp == 0);
+      while (nl >= 32 || (done && nl > 0)) {
+        const int ne = nl < 32 ? nl : 32;
+        for (int e = 0; e < ne; e++) {
+          const float* c = node_com + 4 * (size_t)list[e];
+          const float gm = G * c[3];
+          for (int t = 0; t < cnt; t++) {
+            const int k = k0 + t;
+            float dx = c[0] - sx[k], dy = c[1] - sy[k], dz = c[2] - sz[k];
+            float d2 = fmaf(dz, dz, fmaf(dy, dy, fmaf(dx, dx, eps2)));
+            if (!(d2 > 0.0f)) continue;
+            float inv = 1.0f / sqrtf(d2);
+            float f = gm * (inv * inv * inv);
+            accx[t] = fmaf(f, dx, accx[t]);
+            accy[t] = fmaf(f, dy, accy[t]);
+            accz[t] = fmaf(f, dz, accz[t]);
+          }
+        }
+        total += (uint64_t)ne * (uint64_t)cnt;
+        for (int e = ne; e < nl; e++) list[e - ne] = list[e];
+        nl -= ne;
+      }
+      if (done) break;
+    }
+    free(stack);
     for (int t = 0; t < cnt; t++) {
       ax[k0 + t] = accx[t]; ay[k0 + t] = accy[t]; az[k0 + t] = accz[t];
     }
   }
+  free(gfirst);
+  free(gcount);
   if (interactions) *interactions = total;
 }

@@ -109,13 +109,14 @@ void orc_lbvh_com(int n, const int32_t* left, const int32_t* right, const float*
                   const float* sz, const float* sm, float* node_com);
 /* cell side used by the opening test for a node with common-prefix length L */
 float orc_lbvh_cell_size(int prefix_len, const float bbox[6]);
-/* warp-cooperative traversal restated sequentially: groups of `group` consecutive sorted bodies
- * descend together; a node is used iff every body of the group accepts it
- * (is-leaf or size^2/(d^2+eps^2) < theta^2, src/cuda/force_barnes_hut.cu:167-172), else both
- * children are visited (left first).  Outputs in SORTED order. *interactions = node-body
+/* warp-cooperative traversal restated sequentially (see lbvh.c): a traversal group = a maximal
+ * subtree with at most `group` (32 or 64) leaves; it shares a node stack popped 32 at a time; a node is used iff it is a
+ * leaf or size^2 < theta^2 (dmin^2 + eps^2), dmin = distance from its COM to the group's bounding
+ * box; accepted nodes are evaluated 32 at a time in list order (monopole,
+ * src/cuda/force_barnes_hut.cu:175-181).  Outputs in SORTED order. *interactions = node-body
  * force evaluations. */
 void orc_lbvh_forces(int n, const int32_t* left, const int32_t* right, const int32_t* prefix,
-                     const float* node_com, const float* sx, const float* sy, const float* sz,
+                     const int32_t* range_first, const int32_t* range_last, const float* node_com, const float* sx, const float* sy, const float* sz,
                      const float bbox[6], float theta, float G, float eps, int group, float* ax, float* ay,
                      float* az, uint64_t* interactions);
 

@@ -101,19 +101,22 @@ def test_morton_sort_lbvh_bit_exact(orc, n, kind):
         assert abs(t["node_com"][0, 3] - st["mass"].sum(dtype=np.float64)) <= 1e-3 * st["mass"].sum()
 
 
+@pytest.mark.parametrize("group", [64, 32])
 @pytest.mark.parametrize("n,theta", [(1, 0.5), (2, 0.5), (30, 0.1), (1000, 0.5), (20000, 0.5), (20000, 0.8),
                                      (100000, 0.5)])
-def test_bh_forces_vs_lbvh_oracle(orc, n, theta):
-    """Same tree, same group traversal, same operation order: only rsqrt differs (<= 1e-5)."""
+def test_bh_forces_vs_lbvh_oracle(orc, n, theta, group, monkeypatch):
+    """Same tree, same traversal groups, same operation order: only rsqrt differs (<= 1e-5)."""
     from nbody_b200 import ics
+    monkeypatch.setenv("NB_BH_GROUP", str(group))
     st = ics.plummer(n, seed=8) if n > 3 else ics.uniform_box(n, -1, 1, seed=8)
     d, calc = _build(st, theta)
     out = d.numpy()
     t = calc.getTree().export()
     sp = t["perm"]
     sx, sy, sz = (st[k][sp] for k in ("pos_x", "pos_y", "pos_z"))
-    tree = dict(left=t["left"], right=t["right"], prefix=t["prefix"])
-    ax, ay, az, inter = orc.lbvh_forces(tree, t["node_com"], sx, sy, sz, t["bbox"], theta, 1.0, 0.01, 32)
+    tree = orc.lbvh_build(t["keys"]) if n > 1 else dict(left=t["left"], right=t["right"], prefix=t["prefix"],
+                                                        first=np.zeros(1, np.int32), last=np.zeros(1, np.int32))
+    ax, ay, az, inter = orc.lbvh_forces(tree, t["node_com"], sx, sy, sz, t["bbox"], theta, 1.0, 0.01, group)
     got = (out["acc_x"][sp], out["acc_y"][sp], out["acc_z"][sp])
     if n == 1:
         assert got[0][0] == 0

@@ -1,0 +1,67 @@
+#!/usr/bin/env python
+"""Per-stage timings of the Barnes-Hut and spatial-hash paths (CUDA events), configs 4 and 5 of
+BASELINE.json.  usage: tools/bench_paths.py bh 1048576 [plummer|sphere]  |  sh 10000000"""
+import ctypes as C
+import json
+import os
+import sys
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch  # noqa: E402
+
+import nbody_b200 as nb  # noqa: E402
+from nbody_b200 import _lib, ics  # noqa: E402
+
+
+def timed(fn, reps=5, warm=2):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps
+
+
+def main():
+    kind, n = sys.argv[1], int(sys.argv[2])
+    L, ctx = _lib.lib(), nb.get_context()
+    if kind == "bh":
+        ic = sys.argv[3] if len(sys.argv) > 3 else "plummer"
+        st = ics.plummer(n, seed=42) if ic == "plummer" else ics.uniform_sphere(n, 1.0, 1.0 / n, seed=42)
+        h = nb.ParticleDataManager.fromState(st)
+        d = nb.ParticleData()
+        nb.ParticleDataManager.allocateDevice(d, n)
+        nb.ParticleDataManager.copyToDevice(d, h)
+        s = None
+        build = timed(lambda: _lib.check(L.nb_bh_build(ctx.handle, C.byref(d.c), s)))
+        force = timed(lambda: _lib.check(L.nb_bh_forces(ctx.handle, C.byref(d.c), 0.5, 1.0, 0.01, s)))
+        _lib.check(L.nb_bh_build(ctx.handle, C.byref(d.c), s))
+        _lib.check(L.nb_bh_forces(ctx.handle, C.byref(d.c), 0.5, 1.0, 0.01, s))
+        inter, cnt = C.c_uint64(0), C.c_int(0)
+        _lib.check(L.nb_bh_stats(ctx.handle, C.byref(inter), C.byref(cnt)))
+        print(json.dumps(dict(path="barnes_hut", n=n, ic=ic, theta=0.5, build_ms=build, force_ms=force,
+                              step_ms=build + force, interactions=inter.value, per_body=inter.value / n,
+                              g_interactions_per_s=inter.value / force / 1e6)))
+    else:
+        side = (n / 8.0) ** (1.0 / 3.0)     # ~8 bodies per unit cell
+        st = ics.uniform_box(n, 0.0, side, seed=42)
+        h = nb.ParticleDataManager.fromState(st)
+        d = nb.ParticleData()
+        nb.ParticleDataManager.allocateDevice(d, n)
+        nb.ParticleDataManager.copyToDevice(d, h)
+        build = timed(lambda: _lib.check(L.nb_sh_build(ctx.handle, C.byref(d.c), 1.0, None)))
+        force = timed(lambda: _lib.check(L.nb_sh_forces(ctx.handle, C.byref(d.c), 2.0, 1.0, 0.01, None)))
+        t = C.c_int(0)
+        L.nb_sh_total_cells(ctx.handle, C.byref(t))
+        print(json.dumps(dict(path="spatial_hash", n=n, side=side, cells=t.value, build_ms=build, force_ms=force,
+                              step_ms=build + force, build_gbs=136.0 * n / build / 1e6)))
+
+
+if __name__ == "__main__":
+    main()
