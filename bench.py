@@ -25,6 +25,11 @@ import sys
 import threading
 import time
 
+if "reference" in sys.argv:
+    # torchrun exports OMP_NUM_THREADS=1; the CPU arm uses every host thread, and libgomp reads the
+    # variable when it is first loaded, so fix it before anything can pull OpenMP in.
+    os.environ["OMP_NUM_THREADS"] = str(len(os.sched_getaffinity(0)))
+
 import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
@@ -120,6 +125,7 @@ def cpu_sample_rate(state, n_targets: int, reps: int = 1):
     """Oracle port of the reference CPU loop on a bounded sample: the first n_targets targets of the
     workload against ALL sources.  Returns (G-interactions/s, threads, seconds)."""
     from oracle import bindings as orc
+    orc.set_num_threads(len(os.sched_getaffinity(0)))  # all host threads, whatever OMP_NUM_THREADS says
     n = state["pos_x"].size
     n_targets = min(n_targets, n)
     t0 = time.perf_counter()
@@ -285,7 +291,7 @@ def main():
     }
 
     cpu = None
-    if not args.no_cpu_baseline:
+    if not args.no_cpu_baseline and world == 1:   # rank 0 at N = 1 only
         sample = 16384 if n >= (1 << 20) else min(n, 4096)
         rate, threads, sec = cpu_sample_rate(state, sample)
         cpu = {"value": rate, "unit": "G-interactions/s", "cores": threads, "kind": "port",

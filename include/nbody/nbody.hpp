@@ -1,0 +1,614 @@
+// nbody.hpp -- C++20 host layer of the B200-native engine: the reference's class names
+// (namespace nbody: ParticleData, SimulationConfig, ForceCalculator family, Integrator,
+// ParticleDataManager, ParticleInitializer, ParticleSystem, exceptions) as thin inline wrappers over
+// the C ABI in include/nbody_b200.h.  Header-only; link with -lnbody_b200.  No CUDA headers are
+// needed by host code: device memory goes through nb_particles_alloc_device.
+//
+// Source compatibility: code written against the reference's include/nbody/{types,
+// force_calculator,integrator,particle_data,particle_system,error_handling}.hpp compiles against
+// the forwarding headers next to this file.  Reference file:line for each piece is cited inline.
+#pragma once
+
+#include <algorithm>
+#include <cmath>
+#include <cstddef>
+#include <cstdint>
+#include <memory>
+#include <random>
+#include <sstream>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../nbody_b200.h"
+
+namespace nbody {
+
+// ---- enums / PODs (include/nbody/types.hpp:66-86, 123-198, 234-313, 343-382) -----------------------
+enum class ForceMethod { DIRECT_N2, BARNES_HUT, SPATIAL_HASH };
+enum class InitDistribution { UNIFORM, SPHERICAL, DISK };
+
+struct Vec3 {
+  float x = 0, y = 0, z = 0;
+  constexpr Vec3() = default;
+  constexpr Vec3(float x_, float y_, float z_) : x(x_), y(y_), z(z_) {}
+  constexpr Vec3 operator+(const Vec3& v) const { return {x + v.x, y + v.y, z + v.z}; }
+  constexpr Vec3 operator-(const Vec3& v) const { return {x - v.x, y - v.y, z - v.z}; }
+  constexpr Vec3 operator*(float s) const { return {x * s, y * s, z * s}; }
+  constexpr Vec3 operator/(float s) const { return {x / s, y / s, z / s}; }
+  Vec3& operator+=(const Vec3& v) { x += v.x; y += v.y; z += v.z; return *this; }
+  Vec3& operator-=(const Vec3& v) { x -= v.x; y -= v.y; z -= v.z; return *this; }
+  constexpr float dot(const Vec3& v) const { return x * v.x + y * v.y + z * v.z; }
+  constexpr float length2() const { return dot(*this); }
+  float length() const { return std::sqrt(length2()); }
+  Vec3 normalized() const { const float l = length(); return l > 0 ? *this / l : Vec3(); }
+};
+inline constexpr Vec3 operator*(float s, const Vec3& v) { return v * s; }
+
+// Layout-identical to nb_particles (13 float* + count, 112 bytes): passed to the C ABI by cast.
+struct ParticleData {
+  float *pos_x = nullptr, *pos_y = nullptr, *pos_z = nullptr;
+  float *vel_x = nullptr, *vel_y = nullptr, *vel_z = nullptr;
+  float *acc_x = nullptr, *acc_y = nullptr, *acc_z = nullptr;
+  float *acc_old_x = nullptr, *acc_old_y = nullptr, *acc_old_z = nullptr;
+  float* mass = nullptr;
+  std::size_t count = 0;
+};
+static_assert(sizeof(ParticleData) == sizeof(nb_particles) && sizeof(ParticleData) == 112);
+inline nb_particles* as_nb(ParticleData* p) { return reinterpret_cast<nb_particles*>(p); }
+inline const nb_particles* as_nb(const ParticleData* p) { return reinterpret_cast<const nb_particles*>(p); }
+
+struct SimulationConfig {
+  std::size_t particle_count = 10000;
+  InitDistribution init_distribution = InitDistribution::SPHERICAL;
+  ForceMethod force_method = ForceMethod::DIRECT_N2;
+  float dt = 0.001f;
+  float G = 1.0f;
+  float softening = 0.1f;
+  float barnes_hut_theta = 0.5f;
+  float spatial_hash_cell_size = 1.0f;
+  float spatial_hash_cutoff = 2.0f;
+  int cuda_block_size = 256;  // accepted and validated; a hint only for the sm_100a kernels
+};
+static_assert(sizeof(SimulationConfig) == 48);
+
+struct UniformDistParams { Vec3 min_bounds, max_bounds; float min_mass = 1.0f, max_mass = 1.0f; };
+struct SphericalDistParams { Vec3 center; float radius = 10.0f, min_mass = 1.0f, max_mass = 1.0f; };
+struct DiskDistParams {
+  Vec3 center;
+  float radius = 10.0f, thickness = 1.0f, min_mass = 1.0f, max_mass = 1.0f, rotation_speed = 1.0f;
+};
+
+// ---- exceptions (include/nbody/error_handling.hpp:29-102) --------------------------------------------
+class CudaException : public std::runtime_error {
+ public:
+  CudaException(const char* msg, const char* file, int line)
+      : std::runtime_error(format(msg, file, line)), msg_(msg ? msg : ""), file_(file ? file : ""), line_(line) {}
+  const char* getErrorMsg() const { return msg_.c_str(); }
+  const char* getFile() const { return file_.c_str(); }
+  int getLine() const { return line_; }
+
+ private:
+  static std::string format(const char* m, const char* f, int l) {
+    std::ostringstream o;
+    o << "CUDA Error: " << (m ? m : "") << " at " << (f ? f : "?") << ":" << l;
+    return o.str();
+  }
+  std::string msg_, file_;
+  int line_;
+};
+
+class ResourceException : public std::runtime_error {
+ public:
+  ResourceException(const char* msg, std::size_t required, std::size_t available)
+      : std::runtime_error(std::string(msg) + " - Required: " + std::to_string(required) +
+                           " bytes, Available: " + std::to_string(available) + " bytes"),
+        required_(required), available_(available) {}
+  std::size_t getRequired() const { return required_; }
+  std::size_t getAvailable() const { return available_; }
+
+ private:
+  std::size_t required_, available_;
+};
+
+class ValidationException : public std::runtime_error {
+ public:
+  explicit ValidationException(const std::string& m) : std::runtime_error("Validation Error: " + m) {}
+};
+
+// C-ABI return code -> the exception type the reference would have thrown
+inline void nb_throw(int rc, const char* file, int line) {
+  if (rc == NB_OK) return;
+  const char* m = nb_last_error();
+  switch (rc) {
+    case NB_ERR_INVALID: throw ValidationException(m);
+    case NB_ERR_RESOURCE: throw ResourceException(m, 0, 0);
+    case NB_ERR_GRID_TOO_LARGE: throw std::runtime_error(m);  // force_spatial_hash.cu:252-254
+    default:
+      if (rc > 0) throw CudaException(m, file, line);
+      throw std::runtime_error(m);
+  }
+}
+#define NB_CALL(expr) ::nbody::nb_throw((expr), __FILE__, __LINE__)
+
+// ---- validation (src/utils/error_handling.cpp:46-123) -------------------------------------------------
+inline bool nb_finite(float v) { return !(std::isnan(v) || std::isinf(v)); }
+inline void validateParticleCountRange(std::size_t n) {
+  if (n == 0) throw ValidationException("Particle count must be greater than 0");
+  if (n > 100000000) throw ValidationException("Particle count exceeds maximum supported (100M)");
+}
+inline void validateTimeStep(float dt) {
+  if (dt <= 0) throw ValidationException("Time step must be positive");
+  if (!nb_finite(dt)) throw ValidationException("Time step must be a finite number");
+  if (dt > 1.0f) throw ValidationException("Time step is too large (max 1.0)");
+}
+inline void validateSoftening(float e) {
+  if (e < 0) throw ValidationException("Softening parameter must be non-negative");
+  if (!nb_finite(e)) throw ValidationException("Softening parameter must be a finite number");
+}
+inline void validateTheta(float t) {
+  if (t < 0 || t > 2.0f) throw ValidationException("Barnes-Hut theta must be between 0 and 2");
+  if (!nb_finite(t)) throw ValidationException("Barnes-Hut theta must be a finite number");
+}
+inline void validateSimulationConfig(const SimulationConfig& c) {
+  validateParticleCountRange(c.particle_count);
+  validateTimeStep(c.dt);
+  validateSoftening(c.softening);
+  if (c.force_method == ForceMethod::BARNES_HUT) validateTheta(c.barnes_hut_theta);
+  if (c.G <= 0 || !nb_finite(c.G)) throw ValidationException("Gravitational constant must be positive and finite");
+  if (c.force_method == ForceMethod::SPATIAL_HASH) {
+    if (c.spatial_hash_cell_size <= 0 || !nb_finite(c.spatial_hash_cell_size))
+      throw ValidationException("Spatial hash cell size must be positive and finite");
+    if (c.spatial_hash_cutoff <= 0 || !nb_finite(c.spatial_hash_cutoff))
+      throw ValidationException("Spatial hash cutoff must be positive and finite");
+  }
+  if (c.cuda_block_size <= 0 || c.cuda_block_size > 1024)
+    throw ValidationException("CUDA block size must be between 1 and 1024");
+}
+inline void validateResourceRequirements(std::size_t n) {  // error_handling.cpp:25-44
+  std::size_t total = 0;
+  NB_CALL(nb_device_info(0, nullptr, nullptr, nullptr, &total, nullptr));
+  const std::size_t need = n * sizeof(float) * 13 * 2;
+  if (need > total * 0.8) throw ResourceException("Insufficient GPU memory", need, static_cast<std::size_t>(total * 0.8));
+}
+inline void validateParticleCount(std::size_t n) {
+  validateParticleCountRange(n);
+  validateResourceRequirements(n);
+}
+
+// ---- one engine context per process/device (the reference is single-device, device 0) -----------------
+class Engine {
+ public:
+  static nb_context* get() {
+    static Engine e;
+    return e.ctx_;
+  }
+
+ private:
+  Engine() { NB_CALL(nb_context_create(0, 0, &ctx_)); }
+  ~Engine() { nb_context_destroy(ctx_); }
+  nb_context* ctx_ = nullptr;
+};
+
+// ---- ParticleDataManager / ParticleInitializer (src/cuda/particle_init.cu:143-357) ----------------------
+class ParticleDataManager {
+ public:
+  static void allocateDevice(ParticleData& d, std::size_t n) { NB_CALL(nb_particles_alloc_device(as_nb(&d), n)); }
+  static void freeDevice(ParticleData& d) { nb_particles_free_device(as_nb(&d)); d = ParticleData(); }
+  static void allocateHost(ParticleData& h, std::size_t n) {
+    h = ParticleData();
+    float** f[13] = {&h.pos_x, &h.pos_y, &h.pos_z, &h.vel_x, &h.vel_y, &h.vel_z, &h.acc_x,
+                     &h.acc_y, &h.acc_z, &h.acc_old_x, &h.acc_old_y, &h.acc_old_z, &h.mass};
+    try {
+      for (auto p : f) *p = new float[n ? n : 1]();
+    } catch (const std::bad_alloc&) {
+      for (auto p : f) delete[] *p;
+      h = ParticleData();
+      throw ResourceException("Failed to allocate host memory for particles", n * 13 * sizeof(float), 0);
+    }
+    h.count = n;
+  }
+  static void freeHost(ParticleData& h) {
+    for (float* p : {h.pos_x, h.pos_y, h.pos_z, h.vel_x, h.vel_y, h.vel_z, h.acc_x, h.acc_y, h.acc_z, h.acc_old_x,
+                     h.acc_old_y, h.acc_old_z, h.mass})
+      delete[] p;
+    h = ParticleData();
+  }
+  static void copyToDevice(ParticleData& d, const ParticleData& h) {
+    NB_CALL(nb_particles_upload(Engine::get(), as_nb(&d), as_nb(&h), nullptr));
+    NB_CALL(nb_synchronize(Engine::get(), nullptr));
+  }
+  static void copyToHost(ParticleData& h, const ParticleData& d) {
+    NB_CALL(nb_particles_download(Engine::get(), as_nb(&h), as_nb(&d), nullptr));
+  }
+};
+
+class ParticleInitializer {
+ public:
+  static void initUniform(ParticleData& h, const UniformDistParams& p, unsigned seed = 42) {
+    std::mt19937 rng(seed);
+    std::uniform_real_distribution<float> dx(p.min_bounds.x, p.max_bounds.x), dy(p.min_bounds.y, p.max_bounds.y),
+        dz(p.min_bounds.z, p.max_bounds.z), dm(p.min_mass, p.max_mass);
+    for (std::size_t i = 0; i < h.count; i++) {
+      h.pos_x[i] = dx(rng); h.pos_y[i] = dy(rng); h.pos_z[i] = dz(rng);
+      h.vel_x[i] = h.vel_y[i] = h.vel_z[i] = 0.0f;
+      h.mass[i] = dm(rng);
+    }
+    zeroAccelerations(h);
+  }
+  static void initSpherical(ParticleData& h, const SphericalDistParams& p, unsigned seed = 42) {
+    std::mt19937 rng(seed);
+    std::uniform_real_distribution<float> u(0.0f, 1.0f), dm(p.min_mass, p.max_mass);
+    for (std::size_t i = 0; i < h.count; i++) {
+      const float r = std::cbrt(u(rng)) * p.radius, th = u(rng) * 2.0f * 3.14159265f, ph = std::acos(2.0f * u(rng) - 1.0f);
+      h.pos_x[i] = p.center.x + r * std::sin(ph) * std::cos(th);
+      h.pos_y[i] = p.center.y + r * std::sin(ph) * std::sin(th);
+      h.pos_z[i] = p.center.z + r * std::cos(ph);
+      h.vel_x[i] = h.vel_y[i] = h.vel_z[i] = 0.0f;
+      h.mass[i] = dm(rng);
+    }
+    zeroAccelerations(h);
+  }
+  static void initDisk(ParticleData& h, const DiskDistParams& p, unsigned seed = 42) {
+    std::mt19937 rng(seed);
+    std::uniform_real_distribution<float> u(0.0f, 1.0f), dm(p.min_mass, p.max_mass);
+    for (std::size_t i = 0; i < h.count; i++) {
+      const float r = std::sqrt(u(rng)) * p.radius, th = u(rng) * 2.0f * 3.14159265f, z = (u(rng) - 0.5f) * p.thickness;
+      h.pos_x[i] = p.center.x + r * std::cos(th);
+      h.pos_y[i] = p.center.y + r * std::sin(th);
+      h.pos_z[i] = p.center.z + z;
+      const float v = p.rotation_speed * std::sqrt(r);
+      h.vel_x[i] = -v * std::sin(th); h.vel_y[i] = v * std::cos(th); h.vel_z[i] = 0.0f;
+      h.mass[i] = dm(rng);
+    }
+    zeroAccelerations(h);
+  }
+  static void zeroVelocities(ParticleData& h) {
+    std::fill_n(h.vel_x, h.count, 0.0f); std::fill_n(h.vel_y, h.count, 0.0f); std::fill_n(h.vel_z, h.count, 0.0f);
+  }
+  static void zeroAccelerations(ParticleData& h) {
+    for (float* a : {h.acc_x, h.acc_y, h.acc_z, h.acc_old_x, h.acc_old_y, h.acc_old_z}) std::fill_n(a, h.count, 0.0f);
+  }
+};
+
+// ---- force calculators (include/nbody/force_calculator.hpp) ----------------------------------------------
+class ForceCalculator {
+ public:
+  virtual ~ForceCalculator() = default;
+  virtual void computeForces(ParticleData* d_particles) = 0;
+  virtual ForceMethod getMethod() const = 0;
+  void setSofteningParameter(float eps) { softening_eps_ = eps; softening_eps2_ = eps * eps; }
+  void setGravitationalConstant(float G) { G_ = G; }
+  float getSofteningParameter() const noexcept { return softening_eps_; }
+  float getSofteningSquared() const noexcept { return softening_eps2_; }
+  float getGravitationalConstant() const noexcept { return G_; }
+
+ protected:
+  float softening_eps_ = 0.01f, softening_eps2_ = 0.0001f, G_ = 1.0f;
+};
+
+class DirectForceCalculator : public ForceCalculator {
+ public:
+  explicit DirectForceCalculator(int block_size = 256) : block_size_(block_size) {}
+  void computeForces(ParticleData* d) override {  // src/cuda/force_direct.cu:103-106
+    NB_CALL(nb_direct_forces(Engine::get(), as_nb(d), G_, softening_eps2_, nullptr));
+  }
+  ForceMethod getMethod() const noexcept override { return ForceMethod::DIRECT_N2; }
+  void setBlockSize(int s) { block_size_ = s; }
+  int getBlockSize() const noexcept { return block_size_; }
+
+ private:
+  int block_size_;
+};
+
+// What getTree() hands out: the device tree read back on demand (the reference exposes its host octree).
+class BarnesHutTree {
+ public:
+  int getNodeCount() const { int c = 0; NB_CALL(nb_bh_stats(Engine::get(), nullptr, &c)); return c; }
+  std::uint64_t getInteractionCount() const { std::uint64_t v = 0; NB_CALL(nb_bh_stats(Engine::get(), &v, nullptr)); return v; }
+  // sorted Morton keys + permutation, LBVH topology, node centres of mass (x,y,z,m)
+  void exportTree(std::size_t n, std::vector<std::uint32_t>& keys, std::vector<std::int32_t>& perm,
+                  std::vector<std::int32_t>& left, std::vector<std::int32_t>& right, std::vector<float>& node_com) const {
+    keys.resize(n); perm.resize(n); left.resize(n > 1 ? n - 1 : 1); right.resize(left.size()); node_com.resize(4 * (2 * n - 1));
+    NB_CALL(nb_bh_export(Engine::get(), keys.data(), perm.data(), left.data(), right.data(), nullptr, nullptr,
+                         node_com.data(), nullptr));
+  }
+  float getRootMass(std::size_t n) const {
+    std::vector<float> com(4 * (2 * n - 1));
+    NB_CALL(nb_bh_export(Engine::get(), nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, com.data(), nullptr));
+    return com[3];
+  }
+};
+
+class BarnesHutCalculator : public ForceCalculator {
+ public:
+  explicit BarnesHutCalculator(float theta = 0.5f) : theta_(theta) {}
+  void computeForces(ParticleData* d) override {  // src/cuda/force_barnes_hut.cu:526-532
+    if (!tree_) tree_ = std::make_unique<BarnesHutTree>();
+    NB_CALL(nb_bh_build(Engine::get(), as_nb(d), nullptr));
+    NB_CALL(nb_bh_forces(Engine::get(), as_nb(d), theta_, G_, softening_eps_, nullptr));
+  }
+  ForceMethod getMethod() const noexcept override { return ForceMethod::BARNES_HUT; }
+  void setTheta(float t) { theta_ = t; }
+  float getTheta() const noexcept { return theta_; }
+  BarnesHutTree* getTree() noexcept { return tree_.get(); }
+
+ private:
+  std::unique_ptr<BarnesHutTree> tree_;
+  float theta_;
+};
+
+class SpatialHashGrid {
+ public:
+  int getTotalCells() const { int t = 0; NB_CALL(nb_sh_total_cells(Engine::get(), &t)); return t; }
+  void copyCellDataToHost(std::size_t n, std::vector<int>& cell_start, std::vector<int>& cell_end,
+                          std::vector<int>& particle_cells, std::vector<int>& sorted_indices) const {
+    const int t = getTotalCells();
+    cell_start.resize(t); cell_end.resize(t); particle_cells.resize(n); sorted_indices.resize(n);
+    NB_CALL(nb_sh_export(Engine::get(), nullptr, nullptr, particle_cells.data(), cell_start.data(), cell_end.data(),
+                         sorted_indices.data()));
+  }
+};
+
+class SpatialHashCalculator : public ForceCalculator {
+ public:
+  explicit SpatialHashCalculator(float cell_size = 1.0f, float cutoff_radius = 2.0f)
+      : cell_size_(cell_size), cutoff_radius_(cutoff_radius) {}
+  void computeForces(ParticleData* d) override {  // src/cuda/force_spatial_hash.cu:370-377
+    if (!grid_) grid_ = std::make_unique<SpatialHashGrid>();
+    NB_CALL(nb_sh_build(Engine::get(), as_nb(d), cell_size_, nullptr));
+    NB_CALL(nb_sh_forces(Engine::get(), as_nb(d), cutoff_radius_, G_, softening_eps_, nullptr));
+  }
+  ForceMethod getMethod() const noexcept override { return ForceMethod::SPATIAL_HASH; }
+  void setCellSize(float s) { cell_size_ = s; }
+  void setCutoffRadius(float r) { cutoff_radius_ = r; }
+  float getCellSize() const noexcept { return cell_size_; }
+  float getCutoffRadius() const noexcept { return cutoff_radius_; }
+  SpatialHashGrid* getGrid() noexcept { return grid_.get(); }
+
+ private:
+  std::unique_ptr<SpatialHashGrid> grid_;
+  float cell_size_, cutoff_radius_;
+};
+
+// src/cuda/force_spatial_hash.cu:380-401: the bare factory leaves Direct at G = 1, eps = 0.01.
+inline std::unique_ptr<ForceCalculator> createForceCalculator(ForceMethod method, const SimulationConfig& cfg) {
+  switch (method) {
+    case ForceMethod::BARNES_HUT: {
+      auto c = std::make_unique<BarnesHutCalculator>(cfg.barnes_hut_theta);
+      c->setGravitationalConstant(cfg.G);
+      c->setSofteningParameter(cfg.softening);
+      return c;
+    }
+    case ForceMethod::SPATIAL_HASH: {
+      auto c = std::make_unique<SpatialHashCalculator>(cfg.spatial_hash_cell_size, cfg.spatial_hash_cutoff);
+      c->setGravitationalConstant(cfg.G);
+      c->setSofteningParameter(cfg.softening);
+      return c;
+    }
+    default: return std::make_unique<DirectForceCalculator>(cfg.cuda_block_size);
+  }
+}
+
+// ---- integrator (include/nbody/integrator.hpp, src/cuda/integrator.cu:205-293) ------------------------------
+class Integrator {
+ public:
+  explicit Integrator(int block_size = 256) : block_size_(block_size) {}
+  // Velocity Verlet.  With our DirectForceCalculator the step runs fused (store+drift+pack, force,
+  // reduce+kick); with any other ForceCalculator it is the reference's 4-call sequence (:224-238).
+  void integrate(ParticleData* d, ForceCalculator* fc, float dt) {
+    if (auto* direct = dynamic_cast<DirectForceCalculator*>(fc)) {
+      NB_CALL(nb_step_direct(Engine::get(), as_nb(d), dt, direct->getGravitationalConstant(),
+                             direct->getSofteningSquared(), nullptr));
+      return;
+    }
+    storeOldAccelerations(d);
+    updatePositions(d, dt);
+    fc->computeForces(d);
+    updateVelocities(d, dt);
+  }
+  void updatePositions(ParticleData* d, float dt) { NB_CALL(nb_update_positions(Engine::get(), as_nb(d), dt, nullptr)); }
+  void updateVelocities(ParticleData* d, float dt) { NB_CALL(nb_update_velocities(Engine::get(), as_nb(d), dt, nullptr)); }
+  void storeOldAccelerations(ParticleData* d) { NB_CALL(nb_store_accelerations(Engine::get(), as_nb(d), nullptr)); }
+  float computeKineticEnergy(const ParticleData* d) {
+    double ke = 0;
+    NB_CALL(nb_kinetic_energy(Engine::get(), as_nb(d), &ke, nullptr));
+    return static_cast<float>(ke);
+  }
+  float computePotentialEnergy(const ParticleData* d, float G, float eps) {
+    double pe = 0;
+    NB_CALL(nb_potential_energy(Engine::get(), as_nb(d), G, eps, &pe, nullptr));
+    return static_cast<float>(pe);
+  }
+  // fp64 variants (the drift criterion is evaluated in double)
+  double computeTotalEnergyF64(const ParticleData* d, float G, float eps) {
+    double ke = 0, pe = 0;
+    NB_CALL(nb_kinetic_energy(Engine::get(), as_nb(d), &ke, nullptr));
+    NB_CALL(nb_potential_energy(Engine::get(), as_nb(d), G, eps, &pe, nullptr));
+    return ke + pe;
+  }
+  float computeTotalEnergy(const ParticleData* d, float G, float eps) {
+    return computeKineticEnergy(d) + computePotentialEnergy(d, G, eps);
+  }
+  void ensureScratchBuffer(std::size_t) {}  // scratch lives in the engine context
+  void setBlockSize(int s) { block_size_ = s; }
+  int getBlockSize() const noexcept { return block_size_; }
+
+ private:
+  int block_size_;
+};
+
+// ---- ParticleSystem (src/core/particle_system.cpp) ---------------------------------------------------------
+struct SimulationState {  // include/nbody/simulation_state.hpp
+  std::size_t particle_count = 0;
+  float simulation_time = 0, dt = 0.001f, G = 1.0f, softening = 0.01f;
+  ForceMethod force_method = ForceMethod::DIRECT_N2;
+  std::vector<float> pos_x, pos_y, pos_z, vel_x, vel_y, vel_z, mass;
+};
+
+class ParticleSystem {
+ public:
+  ParticleSystem() = default;
+  ~ParticleSystem() { release(); }
+  ParticleSystem(const ParticleSystem&) = delete;
+  ParticleSystem& operator=(const ParticleSystem&) = delete;
+
+  void initialize(const SimulationConfig& cfg) {  // :40-100
+    validateSimulationConfig(cfg);
+    validateResourceRequirements(cfg.particle_count);
+    config_ = cfg;
+    dt_ = cfg.dt; G_ = cfg.G; softening_ = cfg.softening; force_method_ = cfg.force_method; paused_ = false;
+    release();
+    allocate(cfg.particle_count);
+    switch (cfg.init_distribution) {
+      case InitDistribution::UNIFORM: {
+        UniformDistParams p; p.min_bounds = Vec3(-10, -10, -10); p.max_bounds = Vec3(10, 10, 10);
+        ParticleInitializer::initUniform(h_, p);
+        break;
+      }
+      case InitDistribution::SPHERICAL: {
+        SphericalDistParams p; p.radius = 10.0f;
+        ParticleInitializer::initSpherical(h_, p);
+        break;
+      }
+      case InitDistribution::DISK: {
+        DiskDistParams p; p.radius = 10.0f; p.thickness = 1.0f; p.rotation_speed = 0.5f;
+        ParticleInitializer::initDisk(h_, p);
+        break;
+      }
+    }
+    start();
+    time_ = 0.0f;
+  }
+  void update(float dt) {  // :115-127
+    if (!initialized_ || paused_) return;
+    integrator_->integrate(&d_, calc_.get(), dt);
+    time_ += dt;
+  }
+  void reset() { if (initialized_) initialize(config_); }
+  void pause() { paused_ = true; }
+  void resume() { paused_ = false; }
+  bool isPaused() const { return paused_; }
+  bool isInitialized() const { return initialized_; }
+
+  void setForceMethod(ForceMethod m) {  // :137-143
+    if (m != force_method_) { force_method_ = m; config_.force_method = m; makeCalculator(); }
+  }
+  void setGravitationalConstant(float G) {
+    if (G <= 0 || !nb_finite(G)) throw ValidationException("Gravitational constant must be positive and finite");
+    G_ = G; config_.G = G;
+    if (calc_) calc_->setGravitationalConstant(G);
+  }
+  void setSofteningParameter(float e) {
+    validateSoftening(e);
+    softening_ = e; config_.softening = e;
+    if (calc_) calc_->setSofteningParameter(e);
+  }
+  void setTimeStep(float dt) { validateTimeStep(dt); dt_ = dt; config_.dt = dt; }
+  void setBarnesHutTheta(float t) {
+    validateTheta(t);
+    config_.barnes_hut_theta = t;
+    if (auto* bh = dynamic_cast<BarnesHutCalculator*>(calc_.get())) bh->setTheta(t);
+  }
+  void setSpatialHashCellSize(float s) {
+    if (s <= 0 || !nb_finite(s)) throw ValidationException("Spatial hash cell size must be positive and finite");
+    config_.spatial_hash_cell_size = s;
+    if (auto* sh = dynamic_cast<SpatialHashCalculator*>(calc_.get())) sh->setCellSize(s);
+  }
+  void setSpatialHashCutoff(float c) {
+    if (c <= 0 || !nb_finite(c)) throw ValidationException("Spatial hash cutoff must be positive and finite");
+    config_.spatial_hash_cutoff = c;
+    if (auto* sh = dynamic_cast<SpatialHashCalculator*>(calc_.get())) sh->setCutoffRadius(c);
+  }
+
+  std::size_t getParticleCount() const { return count_; }
+  float getSimulationTime() const { return time_; }
+  float getTimeStep() const { return dt_; }
+  float getGravitationalConstant() const { return G_; }
+  float getSofteningParameter() const { return softening_; }
+  ForceMethod getForceMethod() const { return force_method_; }
+  ParticleData* getDeviceData() { return &d_; }
+  const ParticleData* getDeviceData() const { return &d_; }
+  ForceCalculator* getForceCalculator() { return calc_.get(); }
+  void copyToHost(ParticleData& h) const { ParticleDataManager::copyToHost(h, d_); }
+
+  SimulationState getState() const {  // :213-238
+    SimulationState s;
+    s.particle_count = count_; s.simulation_time = time_; s.dt = dt_; s.G = G_; s.softening = softening_;
+    s.force_method = force_method_;
+    ParticleData h;
+    ParticleDataManager::allocateHost(h, count_);
+    ParticleDataManager::copyToHost(h, d_);
+    s.pos_x.assign(h.pos_x, h.pos_x + count_); s.pos_y.assign(h.pos_y, h.pos_y + count_);
+    s.pos_z.assign(h.pos_z, h.pos_z + count_); s.vel_x.assign(h.vel_x, h.vel_x + count_);
+    s.vel_y.assign(h.vel_y, h.vel_y + count_); s.vel_z.assign(h.vel_z, h.vel_z + count_);
+    s.mass.assign(h.mass, h.mass + count_);
+    ParticleDataManager::freeHost(h);
+    return s;
+  }
+  void setState(const SimulationState& s) {  // :240-292
+    SimulationConfig c = config_;
+    c.particle_count = s.particle_count; c.dt = s.dt; c.G = s.G; c.softening = s.softening; c.force_method = s.force_method;
+    validateSimulationConfig(c);
+    validateResourceRequirements(s.particle_count);
+    release();
+    allocate(s.particle_count);
+    std::copy(s.pos_x.begin(), s.pos_x.end(), h_.pos_x); std::copy(s.pos_y.begin(), s.pos_y.end(), h_.pos_y);
+    std::copy(s.pos_z.begin(), s.pos_z.end(), h_.pos_z); std::copy(s.vel_x.begin(), s.vel_x.end(), h_.vel_x);
+    std::copy(s.vel_y.begin(), s.vel_y.end(), h_.vel_y); std::copy(s.vel_z.begin(), s.vel_z.end(), h_.vel_z);
+    std::copy(s.mass.begin(), s.mass.end(), h_.mass);
+    ParticleInitializer::zeroAccelerations(h_);
+    config_ = c;
+    time_ = s.simulation_time; dt_ = s.dt; G_ = s.G; softening_ = s.softening; force_method_ = s.force_method;
+    start();
+    paused_ = false;
+  }
+  float computeKineticEnergy() const { return integrator_ ? integrator_->computeKineticEnergy(&d_) : 0.0f; }
+  float computePotentialEnergy() const { return integrator_ ? integrator_->computePotentialEnergy(&d_, G_, softening_) : 0.0f; }
+  float computeTotalEnergy() const { return computeKineticEnergy() + computePotentialEnergy(); }
+  double computeTotalEnergyF64() const { return integrator_ ? integrator_->computeTotalEnergyF64(&d_, G_, softening_) : 0.0; }
+  void synchronize() const { NB_CALL(nb_synchronize(Engine::get(), nullptr)); }
+
+ private:
+  void allocate(std::size_t n) {
+    count_ = n;
+    ParticleDataManager::allocateDevice(d_, n);
+    ParticleDataManager::allocateHost(h_, n);
+    allocated_ = true;
+  }
+  void release() {
+    if (allocated_) { ParticleDataManager::freeDevice(d_); ParticleDataManager::freeHost(h_); }
+    allocated_ = initialized_ = false;
+  }
+  void makeCalculator() {  // :109-113
+    calc_ = createForceCalculator(force_method_, config_);
+    calc_->setGravitationalConstant(G_);
+    calc_->setSofteningParameter(softening_);
+  }
+  void start() {
+    ParticleDataManager::copyToDevice(d_, h_);
+    makeCalculator();
+    integrator_ = std::make_unique<Integrator>(config_.cuda_block_size);
+    calc_->computeForces(&d_);  // a(0), :91 / :283
+    initialized_ = true;
+  }
+
+  std::size_t count_ = 0;
+  float dt_ = 0.001f, G_ = 1.0f, softening_ = 0.01f, time_ = 0.0f;
+  ForceMethod force_method_ = ForceMethod::DIRECT_N2;
+  bool paused_ = false, initialized_ = false, allocated_ = false;
+  SimulationConfig config_;
+  ParticleData d_, h_;
+  std::unique_ptr<ForceCalculator> calc_;
+  mutable std::unique_ptr<Integrator> integrator_;
+};
+
+// src/cuda/force_direct.cu:109-117 (the reference's only CPU force code; part of its public header)
+inline Vec3 computeGravitationalForceCPU(const Vec3& p1, const Vec3& p2, float /*m1*/, float m2, float G, float eps) {
+  const Vec3 r = p2 - p1;
+  const float d2 = r.length2() + eps * eps;
+  const float inv = 1.0f / std::sqrt(d2);
+  return r * (G * m2 * inv * inv * inv);
+}
+
+}  // namespace nbody

@@ -105,6 +105,7 @@ def lib():
     L.orc_spatial_forces.argtypes = [i, f32p, f32p, f32p, f32p, i32p, i32p, i32p, i32p, f, f32p, f, f, f,
                                      f32p, f32p, f32p, C.POINTER(C.c_uint64)]
     L.orc_num_threads.restype = i
+    L.orc_set_num_threads.argtypes = [i]
     _LIB = L
     return L
 
@@ -306,3 +307,7 @@ def spatial_forces(px, py, pz, m, grid, cutoff, G, eps):
 
 def num_threads():
     return lib().orc_num_threads()
+
+
+def set_num_threads(t: int):
+    lib().orc_set_num_threads(int(t))

@@ -139,6 +139,7 @@ void orc_spatial_forces(int n, const float* px, const float* py, const float* pz
                         float G, float eps, float* ax, float* ay, float* az, uint64_t* pairs);
 
 int orc_num_threads(void);
+void orc_set_num_threads(int t); /* overrides OMP_NUM_THREADS (torchrun sets it to 1) */
 
 #ifdef __cplusplus
 }

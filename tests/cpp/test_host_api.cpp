@@ -1,0 +1,146 @@
+// test_host_api.cpp -- the reference's own test cases re-expressed against the C++ drop-in headers
+// (tests/test_force_calculation.cpp, test_integrator.cpp, test_barnes_hut.cpp, test_spatial_hash.cpp,
+// test_validation.cpp).  Plain asserts (GoogleTest is not in this image).  Needs a B200; run by
+// tests/test_gpu_cpp_host.py.
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+
+#include "nbody/force_calculator.hpp"
+#include "nbody/integrator.hpp"
+#include "nbody/particle_data.hpp"
+#include "nbody/particle_system.hpp"
+
+using namespace nbody;
+
+#define CHECK(cond)                                                        \
+  do {                                                                     \
+    if (!(cond)) {                                                         \
+      fprintf(stderr, "FAILED %s:%d: %s\n", __FILE__, __LINE__, #cond);    \
+      exit(1);                                                             \
+    }                                                                      \
+  } while (0)
+
+template <class F>
+static bool throws_validation(F&& f) {
+  try { f(); } catch (const ValidationException&) { return true; } catch (...) { return false; }
+  return false;
+}
+
+static void two_body_unit_force() {  // tests/test_force_calculation.cpp:13-30 + :62-96 on the device
+  Vec3 f = computeGravitationalForceCPU(Vec3(0, 0, 0), Vec3(1, 0, 0), 1, 1, 1, 0);
+  CHECK(std::fabs(f.length() - 1.0f) < 1e-6f);
+  ParticleData h, d;
+  ParticleDataManager::allocateHost(h, 2);
+  ParticleDataManager::allocateDevice(d, 2);
+  h.pos_x[1] = 1.0f;
+  h.mass[0] = h.mass[1] = 1.0f;
+  ParticleDataManager::copyToDevice(d, h);
+  DirectForceCalculator calc;
+  calc.setSofteningParameter(0.0f);
+  calc.computeForces(&d);
+  ParticleDataManager::copyToHost(h, d);
+  CHECK(std::fabs(h.acc_x[0] - 1.0f) < 1e-6f && std::fabs(h.acc_x[1] + 1.0f) < 1e-6f);
+  ParticleDataManager::freeDevice(d);
+  ParticleDataManager::freeHost(h);
+}
+
+static void integrator_cases() {  // tests/test_integrator.cpp:15-84, 90-162
+  ParticleData h, d;
+  ParticleDataManager::allocateHost(h, 2);
+  ParticleDataManager::allocateDevice(d, 2);
+  h.mass[0] = 1; h.mass[1] = 2;
+  h.vel_x[0] = 1; h.vel_x[1] = 2;
+  ParticleDataManager::copyToDevice(d, h);
+  Integrator integ;
+  CHECK(std::fabs(integ.computeKineticEnergy(&d) - 4.5f) < 1e-5f);
+  integ.updatePositions(&d, 0.1f);
+  ParticleDataManager::copyToHost(h, d);
+  CHECK(std::fabs(h.pos_x[0] - 0.1f) < 1e-6f);
+  // circular two-body orbit: drift < 1 % over 100 steps
+  h.pos_x[0] = -2.5f; h.pos_x[1] = 2.5f; h.mass[1] = 1;
+  const float v = std::sqrt(1.0f / 10.0f);
+  h.vel_x[0] = h.vel_x[1] = 0; h.vel_y[0] = -v; h.vel_y[1] = v;
+  ParticleDataManager::copyToDevice(d, h);
+  DirectForceCalculator calc;
+  calc.setSofteningParameter(0.01f);
+  calc.computeForces(&d);
+  const double e0 = integ.computeTotalEnergyF64(&d, 1.0f, 0.01f);
+  for (int i = 0; i < 100; i++) integ.integrate(&d, &calc, 0.001f);
+  const double e1 = integ.computeTotalEnergyF64(&d, 1.0f, 0.01f);
+  CHECK(std::fabs((e1 - e0) / e0) < 0.01);
+  ParticleDataManager::freeDevice(d);
+  ParticleDataManager::freeHost(h);
+}
+
+static void particle_system_cases() {
+  ParticleSystem sys;
+  SimulationConfig cfg;
+  cfg.particle_count = 3000;
+  sys.initialize(cfg);
+  const double e0 = sys.computeTotalEnergyF64();
+  for (int i = 0; i < 20; i++) sys.update(cfg.dt);
+  CHECK(std::fabs((sys.computeTotalEnergyF64() - e0) / e0) < 1e-3);
+  CHECK(std::fabs(sys.getSimulationTime() - 20 * cfg.dt) < 1e-6f);
+  // pause / resume (tests/test_serialization.cpp:171-217)
+  SimulationState a = sys.getState();
+  sys.pause();
+  sys.update(cfg.dt);
+  SimulationState b = sys.getState();
+  CHECK(a.pos_x == b.pos_x && a.vel_z == b.vel_z && a.simulation_time == b.simulation_time);
+  sys.resume();
+  // state round trip
+  ParticleSystem other;
+  other.setState(a);
+  SimulationState c = other.getState();
+  CHECK(c.pos_x == a.pos_x && c.mass == a.mass && c.particle_count == a.particle_count);
+  // Barnes-Hut and spatial hash through the same facade
+  sys.setForceMethod(ForceMethod::BARNES_HUT);
+  sys.setBarnesHutTheta(0.5f);
+  sys.update(cfg.dt);
+  auto* bh = dynamic_cast<BarnesHutCalculator*>(sys.getForceCalculator());
+  CHECK(bh && bh->getTree() && bh->getTree()->getNodeCount() == 2 * 3000 - 1);
+  CHECK(std::fabs(bh->getTree()->getRootMass(3000) - 3000.0f) < 3.0f);  // tests/test_barnes_hut.cpp:38-62
+  sys.setForceMethod(ForceMethod::SPATIAL_HASH);
+  sys.update(cfg.dt);
+  auto* sh = dynamic_cast<SpatialHashCalculator*>(sys.getForceCalculator());
+  std::vector<int> cs, ce, pc, si;
+  sh->getGrid()->copyCellDataToHost(3000, cs, ce, pc, si);
+  long total = 0;
+  for (size_t k = 0; k < cs.size(); k++) total += ce[k] - cs[k];
+  CHECK(total == 3000);  // tests/test_spatial_hash.cpp:89-130
+  SimulationState s = sys.getState();
+  for (float x : s.pos_x) CHECK(std::isfinite(x));
+}
+
+static void validation_cases() {  // tests/test_validation.cpp
+  SimulationConfig c;
+  c.dt = 0.0f;            CHECK(throws_validation([&] { validateSimulationConfig(c); })); c.dt = 0.001f;
+  c.particle_count = 0;   CHECK(throws_validation([&] { validateSimulationConfig(c); })); c.particle_count = 10;
+  c.softening = -1.0f;    CHECK(throws_validation([&] { validateSimulationConfig(c); })); c.softening = 0.0f;
+  c.cuda_block_size = 2048; CHECK(throws_validation([&] { validateSimulationConfig(c); })); c.cuda_block_size = 1024;
+  validateSimulationConfig(c);
+  ParticleSystem sys;
+  CHECK(throws_validation([&] { sys.setGravitationalConstant(-1.0f); }));
+  CHECK(throws_validation([&] { sys.setBarnesHutTheta(3.0f); }));
+  CHECK(throws_validation([&] { sys.setTimeStep(2.0f); }));
+  bool threw = false;
+  try {
+    SimulationConfig big;
+    big.particle_count = 200;
+    big.force_method = ForceMethod::SPATIAL_HASH;
+    big.spatial_hash_cell_size = 0.001f;  // > 1e8 cells -> std::runtime_error (force_spatial_hash.cu:252-254)
+    sys.initialize(big);
+  } catch (const std::runtime_error&) { threw = true; }
+  CHECK(threw);
+}
+
+int main() {
+  two_body_unit_force();
+  integrator_cases();
+  particle_system_cases();
+  validation_cases();
+  puts("cpp host api: all checks passed");
+  return 0;
+}
