@@ -7,8 +7,9 @@
 A "step" is one Velocity-Verlet step (store-acc + drift, N^2 force evaluation, kick) =
 Integrator::integrate of the reference (src/cuda/integrator.cu:224-238) = N^2 pair interactions.
   N = 1 : configs[1] of BASELINE.json -- 1 Mi bodies, Plummer, fp32, one B200.
-  N > 1 : configs[2] -- 4 Mi bodies target-sharded over N GPUs, NCCL all-gather of packed positions
-          each step overlapped with the local-source pass (strong scaling: total work fixed).
+  N > 1 : configs[2] -- 4 Mi bodies target-sharded over N GPUs; the all-gather of packed positions is
+          fused into our own kernels over NVLink peer memory (NB_MGPU_EXCHANGE=nccl selects the NCCL
+          all-gather overlapped with the local-source pass instead).  Strong scaling: total work fixed.
 `value` times K steps with state resident in HBM; `e2e` times the host-buffer C-ABI call
 (nb_host_step_direct / ShardedDirectSystem.host_update): pinned host state in, one step, host state
 out, copies inside the timed region.  The CPU legs (cpu_baseline, --impl reference) run the oracle
@@ -261,6 +262,8 @@ def main():
     h2d = 10 * 4 * count
     d2h = 12 * 4 * count
 
+    exchange = system.exchange
+    system.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -272,10 +275,9 @@ def main():
     sm_max = float(peaks.get("sm_max_mhz", 1965.0))
     clock_peak_tf = 148 * 128 * 2 * sm_max * 1e6 / 1e12
     kernel_ms = kms.value / max(kl.value, 1)                  # per force-kernel launch (CUDA events)
-    pairs_per_launch = float(count) * float(n) / (1 if world == 1 else 2)  # N>1: local + remote pass
-    if world > 1:
-        kernel_ms = kms.value / args.steps                    # both passes of one step
-        pairs_per_launch = float(count) * float(n)
+    pairs_per_launch = float(count) * float(n)
+    if world > 1 and exchange == "nccl":
+        kernel_ms = kms.value / args.steps                    # local + remote pass of one step
     achieved_tf = pairs_per_launch * FLOP_PER_INTERACTION / (kernel_ms * 1e-3) / 1e12 if kernel_ms > 0 else None
     roofline = {
         "bound": "fp32", "kernel": "nb::direct_force_kernel<256,2,1024>",
@@ -319,6 +321,9 @@ def main():
         "scaling": "strong" if args.gpus > 1 else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": wl, "bodies": n, "ic": "plummer_henon_seed42", "softening": SOFTENING, "dt": DT,
                    "G": G_CONST, "parallelism": f"target_sharded_x{world}" if world > 1 else "single_gpu",
+                   "exchange": ("peer-memory push fused into the pack kernel + flag-gated force kernel (no NCCL in the step)"
+                                if exchange == "peer" else "NCCL all_gather_into_tensor overlapped with the local pass")
+                   if world > 1 else "none",
                    "cache": "positions (16 MiB+ packed) are rewritten every step; compute bound, L2 state irrelevant"},
         "tflops_20flop": value * 1e9 * FLOP_PER_INTERACTION / 1e12,
         "pct_fp32_peak_datasheet": 100.0 * value * 1e9 * FLOP_PER_INTERACTION / 1e12 / (FP32_PEAK_DATASHEET_TF * args.gpus),

@@ -5,19 +5,28 @@
 // needed by host code: device memory goes through nb_particles_alloc_device.
 //
 // Source compatibility: code written against the reference's include/nbody/{types,
-// force_calculator,integrator,particle_data,particle_system,error_handling}.hpp compiles against
+// force_calculator,integrator,particle_data,particle_system,error_handling,simulation_state,
+// serialization,performance_observability}.hpp compiles against
 // the forwarding headers next to this file.  Reference file:line for each piece is cited inline.
 #pragma once
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstddef>
 #include <cstdint>
+#include <fstream>
+#include <initializer_list>
+#include <istream>
+#include <map>
 #include <memory>
+#include <mutex>
+#include <ostream>
 #include <random>
 #include <sstream>
 #include <stdexcept>
 #include <string>
+#include <string_view>
 #include <vector>
 
 #include "../nbody_b200.h"
@@ -444,7 +453,234 @@ struct SimulationState {  // include/nbody/simulation_state.hpp
   float simulation_time = 0, dt = 0.001f, G = 1.0f, softening = 0.01f;
   ForceMethod force_method = ForceMethod::DIRECT_N2;
   std::vector<float> pos_x, pos_y, pos_z, vel_x, vel_y, vel_z, mass;
+
+  void serialize(std::ostream& out) const;             // src/utils/simulation_state.cpp:42-44
+  static SimulationState deserialize(std::istream& in);  // :46-48
+  // equality within 1e-6 absolute on every scalar and component (:7-40)
+  bool operator==(const SimulationState& o) const {
+    auto near = [](float a, float b) { return !(std::abs(a - b) > 1e-6f); };
+    if (particle_count != o.particle_count || force_method != o.force_method) return false;
+    if (!near(simulation_time, o.simulation_time) || !near(dt, o.dt) || !near(G, o.G) || !near(softening, o.softening))
+      return false;
+    const std::vector<float>* mine[7] = {&pos_x, &pos_y, &pos_z, &vel_x, &vel_y, &vel_z, &mass};
+    const std::vector<float>* theirs[7] = {&o.pos_x, &o.pos_y, &o.pos_z, &o.vel_x, &o.vel_y, &o.vel_z, &o.mass};
+    for (int a = 0; a < 7; a++)
+      for (std::size_t i = 0; i < particle_count; i++)
+        if (!near((*mine[a])[i], (*theirs[a])[i])) return false;
+    return true;
+  }
 };
+
+// ---- .nbody checkpoint format (include/nbody/serialization.hpp, src/utils/serialization.cpp) ----------------
+// 56-byte header {magic "NBOD", version 1, u64 count, time, dt, G, softening, u32 method, 4 reserved
+// words} followed by seven fp32 arrays of `count` values: pos x/y/z, vel x/y/z, mass.  Files written
+// by either implementation load in the other (tests/golden/ref_checkpoint.nbody).
+constexpr std::uint32_t NBODY_MAGIC = 0x4E424F44;
+constexpr std::uint32_t NBODY_VERSION = 1;
+constexpr std::uint64_t MAX_PARTICLE_COUNT = 100'000'000;
+
+struct FileHeader {
+  std::uint32_t magic, version;
+  std::uint64_t particle_count;
+  float simulation_time, dt, G, softening;
+  std::uint32_t force_method;
+  std::uint32_t reserved[4];
+};
+static_assert(sizeof(FileHeader) == 56, "FileHeader must match the reference's 56-byte header");
+
+class Serializer {
+ public:
+  static void save(const std::string& filename, const SimulationState& state) {
+    std::ofstream f(filename, std::ios::binary);
+    if (!f) throw std::runtime_error("Failed to open file for writing: " + filename);
+    save(f, state);
+  }
+  static SimulationState load(const std::string& filename) {
+    std::ifstream f(filename, std::ios::binary);
+    if (!f) throw std::runtime_error("Failed to open file for reading: " + filename);
+    return load(f);
+  }
+  static void save(std::ostream& out, const SimulationState& st) {
+    FileHeader h{};
+    h.magic = NBODY_MAGIC; h.version = NBODY_VERSION; h.particle_count = st.particle_count;
+    h.simulation_time = st.simulation_time; h.dt = st.dt; h.G = st.G; h.softening = st.softening;
+    h.force_method = static_cast<std::uint32_t>(st.force_method);
+    out.write(reinterpret_cast<const char*>(&h), sizeof h);
+    for (const std::vector<float>* a : {&st.pos_x, &st.pos_y, &st.pos_z, &st.vel_x, &st.vel_y, &st.vel_z, &st.mass})
+      out.write(reinterpret_cast<const char*>(a->data()), static_cast<std::streamsize>(a->size() * sizeof(float)));
+  }
+  static SimulationState load(std::istream& in) {
+    const FileHeader h = readHeader(in);
+    if (h.particle_count > MAX_PARTICLE_COUNT)
+      throw ValidationException("Particle count (" + std::to_string(h.particle_count) + ") exceeds maximum allowed (" +
+                                std::to_string(MAX_PARTICLE_COUNT) + ")");
+    SimulationState st;
+    st.particle_count = h.particle_count; st.simulation_time = h.simulation_time; st.dt = h.dt; st.G = h.G;
+    st.softening = h.softening; st.force_method = static_cast<ForceMethod>(h.force_method);
+    for (std::vector<float>* a : {&st.pos_x, &st.pos_y, &st.pos_z, &st.vel_x, &st.vel_y, &st.vel_z, &st.mass}) {
+      a->resize(st.particle_count);
+      const auto bytes = static_cast<std::streamsize>(st.particle_count * sizeof(float));
+      in.read(reinterpret_cast<char*>(a->data()), bytes);
+      if (!in || in.gcount() != bytes)
+        throw std::runtime_error("Failed to read particle data: file may be truncated or corrupted");
+    }
+    return st;
+  }
+  static bool validateFile(const std::string& filename) {
+    std::ifstream f(filename, std::ios::binary);
+    return f ? validateStream(f) : false;
+  }
+  static bool validateStream(std::istream& in) {
+    try {
+      const FileHeader h = readHeader(in);
+      return h.magic == NBODY_MAGIC && h.version == NBODY_VERSION;
+    } catch (...) {
+      return false;
+    }
+  }
+
+ private:
+  static FileHeader readHeader(std::istream& in) {
+    FileHeader h;
+    in.read(reinterpret_cast<char*>(&h), sizeof h);
+    if (!in || in.gcount() != static_cast<std::streamsize>(sizeof h))
+      throw std::runtime_error("Failed to read file header: file may be truncated or corrupted");
+    if (h.magic != NBODY_MAGIC) throw std::runtime_error("Invalid file format: wrong magic number");
+    if (h.version != NBODY_VERSION) throw std::runtime_error("Unsupported file version");
+    return h;
+  }
+};
+inline void SimulationState::serialize(std::ostream& out) const { Serializer::save(out, *this); }
+inline SimulationState SimulationState::deserialize(std::istream& in) { return Serializer::load(in); }
+
+// ---- benchmark records (include/nbody/performance_observability.hpp, src/utils/performance_observability.cpp) ----
+using Milliseconds = std::chrono::duration<double, std::milli>;
+struct PhaseTiming {
+  std::string name;
+  Milliseconds total_duration{0.0};
+  std::size_t samples = 0;
+};
+class PhaseProfiler {  // accumulates per-name totals in first-seen order (:52-77)
+ public:
+  void record(std::string_view name, Milliseconds d) {
+    std::lock_guard<std::mutex> lock(mutex_);
+    for (auto& p : phases_)
+      if (p.name == name) {
+        p.total_duration += d;
+        p.samples++;
+        return;
+      }
+    phases_.push_back(PhaseTiming{std::string(name), d, 1});
+  }
+  std::vector<PhaseTiming> snapshot() const {
+    std::lock_guard<std::mutex> lock(mutex_);
+    return phases_;
+  }
+  void reset() {
+    std::lock_guard<std::mutex> lock(mutex_);
+    phases_.clear();
+  }
+
+ private:
+  mutable std::mutex mutex_;
+  std::vector<PhaseTiming> phases_;
+};
+class ScopedPhaseProfile {
+ public:
+  ScopedPhaseProfile(PhaseProfiler& p, std::string name)
+      : profiler_(p), name_(std::move(name)), t0_(std::chrono::steady_clock::now()) {}
+  ~ScopedPhaseProfile() {
+    profiler_.record(name_, std::chrono::duration_cast<Milliseconds>(std::chrono::steady_clock::now() - t0_));
+  }
+  ScopedPhaseProfile(const ScopedPhaseProfile&) = delete;
+  ScopedPhaseProfile& operator=(const ScopedPhaseProfile&) = delete;
+
+ private:
+  PhaseProfiler& profiler_;
+  std::string name_;
+  std::chrono::steady_clock::time_point t0_;
+};
+inline PhaseProfiler& globalPhaseProfiler() {
+  static PhaseProfiler p;
+  return p;
+}
+inline std::vector<PhaseTiming> consumeGlobalPhaseSnapshot() {
+  auto v = globalPhaseProfiler().snapshot();
+  globalPhaseProfiler().reset();
+  return v;
+}
+struct BenchmarkRunRecord {
+  std::string benchmark_name;
+  ForceMethod force_method = ForceMethod::DIRECT_N2;
+  std::size_t particle_count = 0, iterations = 0;
+  std::map<std::string, double> metrics, parameters;
+  std::vector<PhaseTiming> phase_timings;
+};
+inline std::string forceMethodToString(ForceMethod m) {
+  switch (m) {
+    case ForceMethod::DIRECT_N2: return "direct_n2";
+    case ForceMethod::BARNES_HUT: return "barnes_hut";
+    case ForceMethod::SPATIAL_HASH: return "spatial_hash";
+  }
+  return "unknown";
+}
+namespace detail {
+inline void jsonString(std::ostream& o, std::string_view v) {  // the five escapes of :10-35
+  o << '"';
+  for (char ch : v) {
+    if (ch == '\\') o << "\\\\";
+    else if (ch == '"') o << "\\\"";
+    else if (ch == '\n') o << "\\n";
+    else if (ch == '\r') o << "\\r";
+    else if (ch == '\t') o << "\\t";
+    else o << ch;
+  }
+  o << '"';
+}
+inline void jsonNumberMap(std::ostream& o, const std::map<std::string, double>& m) {
+  o << '{';
+  const char* sep = "";
+  for (const auto& [k, v] : m) {
+    o << sep;
+    jsonString(o, k);
+    o << ':' << v;  // default ostream formatting (6 significant digits), as the reference
+    sep = ",";
+  }
+  o << '}';
+}
+}  // namespace detail
+// byte-identical to serializeBenchmarkRunRecord (:102-133) for the same record
+inline std::string serializeBenchmarkRunRecord(const BenchmarkRunRecord& r) {
+  std::ostringstream o;
+  o << "{\"benchmark_name\":";
+  detail::jsonString(o, r.benchmark_name);
+  o << ",\"force_method\":\"" << forceMethodToString(r.force_method) << "\",\"particle_count\":" << r.particle_count
+    << ",\"iterations\":" << r.iterations << ",\"metrics\":";
+  detail::jsonNumberMap(o, r.metrics);
+  o << ",\"parameters\":";
+  detail::jsonNumberMap(o, r.parameters);
+  o << ",\"phase_timings\":[";
+  const char* sep = "";
+  for (const auto& ph : r.phase_timings) {
+    o << sep << "{\"name\":";
+    detail::jsonString(o, ph.name);
+    o << ",\"total_duration_ms\":" << ph.total_duration.count() << ",\"samples\":" << ph.samples << '}';
+    sep = ",";
+  }
+  o << "]}";
+  return o.str();
+}
+inline std::string serializeBenchmarkRunRecords(const std::vector<BenchmarkRunRecord>& rs) {
+  std::string out = "{\"benchmarks\":[";
+  for (std::size_t i = 0; i < rs.size(); i++) out += (i ? "," : "") + serializeBenchmarkRunRecord(rs[i]);
+  return out + "]}";
+}
+inline void writeBenchmarkRunRecords(const std::string& path, const std::vector<BenchmarkRunRecord>& rs) {
+  std::ofstream f(path);
+  if (!f) throw std::runtime_error("Failed to open benchmark output file: " + path);
+  f << serializeBenchmarkRunRecords(rs) << "\n";
+}
+#define NBODY_PROFILE_SCOPE(name) ::nbody::ScopedPhaseProfile nbody_scoped_phase_profile_##__LINE__(::nbody::globalPhaseProfiler(), (name))
 
 class ParticleSystem {
  public:
@@ -563,6 +799,9 @@ class ParticleSystem {
     start();
     paused_ = false;
   }
+  // src/core/particle_system.cpp:294-302: .nbody checkpoint through the Serializer
+  void saveState(const std::string& filename) const { Serializer::save(filename, getState()); }
+  void loadState(const std::string& filename) { setState(Serializer::load(filename)); }
   float computeKineticEnergy() const { return integrator_ ? integrator_->computeKineticEnergy(&d_) : 0.0f; }
   float computePotentialEnergy() const { return integrator_ ? integrator_->computePotentialEnergy(&d_, G_, softening_) : 0.0f; }
   float computeTotalEnergy() const { return computeKineticEnergy() + computePotentialEnergy(); }

@@ -104,6 +104,8 @@ int nb_bh_forces(nb_context* ctx, const nb_particles* d, float theta, float G, f
 int nb_bh_export(nb_context* ctx, uint32_t* keys, int32_t* perm, int32_t* left, int32_t* right,
                  int32_t* parent, int32_t* prefix, float* node_com, float* bbox);
 int nb_bh_stats(nb_context* ctx, uint64_t* interactions, int* node_count);
+/* deepest per-warp traversal stack reached by the last nb_bh_forces, and its capacity (overflow is an error, never a drop) */
+int nb_bh_max_stack(nb_context* ctx, int* deepest, int* capacity);
 
 /* ---- spatial hash: SpatialHashGrid::build / computeForces (src/cuda/force_spatial_hash.cu:235-316),
  *      SpatialHashCalculator::computeForces (:370-377). ------------------------------------------ */
@@ -133,6 +135,28 @@ int nb_mgpu_pack_local(nb_context* ctx, const nb_particles* d_local, float* gath
 int nb_mgpu_forces_local(nb_context* ctx, const float* gathered_src, float eps2, nb_stream s);
 int nb_mgpu_forces_remote(nb_context* ctx, const float* gathered_src, float eps2, nb_stream s);
 int nb_mgpu_finish(nb_context* ctx, const nb_particles* d_local, float dt, int do_kick, nb_stream s);
+
+/* Peer exchange (default transport of nbody_b200/dist.py): the all-gather is fused into the pack
+ * kernel, which stores every packed body into all R replicated source buffers over NVLink peer
+ * mappings and then raises a per-peer step flag; ONE force launch sweeps all N sources in ring
+ * order starting with the local slice and waits for a peer's flag when it reaches that peer's
+ * tiles.  No collective-library call in the step.  Setup (collective, once, after nb_mgpu_layout):
+ * every rank calls nb_mgpu_peer_alloc, the 64-byte CUDA-IPC handles are exchanged by the caller
+ * (any transport), every rank calls nb_mgpu_peer_open for each other rank, then a barrier.
+ * nb_mgpu_peer_step must be called the same number of times on every rank (it is the collective);
+ * do_step = 0: forces only (pack without drift, reduce without kick). */
+int nb_mgpu_peer_alloc(nb_context* ctx, unsigned char ipc_handle_out[64]);
+int nb_mgpu_peer_open(nb_context* ctx, int peer_rank, const unsigned char ipc_handle[64]);
+int nb_mgpu_peer_step(nb_context* ctx, const nb_particles* d_local, float dt, float G, float eps2, int do_step,
+                      nb_stream s);
+/* the two halves of nb_mgpu_peer_step (pack + push + flag | gated forces + reduce [+ kick]) */
+int nb_mgpu_peer_push(nb_context* ctx, const nb_particles* d_local, float dt, float G, int do_drift, nb_stream s);
+int nb_mgpu_peer_forces(nb_context* ctx, const nb_particles* d_local, float dt, float eps2, int do_kick, nb_stream s);
+/* same-process peers (several contexts in one process, e.g. one host thread driving all GPUs with
+ * cudaDeviceEnablePeerAccess): map by raw device pointer instead of by IPC handle */
+int nb_mgpu_peer_block(nb_context* ctx, void** block, size_t* bytes);
+int nb_mgpu_peer_map(nb_context* ctx, int peer_rank, void* peer_block);
+int nb_mgpu_peer_close(nb_context* ctx);
 
 #ifdef __cplusplus
 }

@@ -5,6 +5,7 @@ Layout:  csrc/        hand-written CUDA for sm_100a + the C ABI (include/nbody_b
          _lib.py      ctypes loader (fails loudly when libnbody_b200.so is missing)
          api.py       Python mirror of the reference's classes over the C ABI
          ics.py       synthetic initial conditions (Plummer, uniform sphere/box, disk)
+         serialization.py  the reference's .nbody checkpoint format
          dist.py      one-process-per-GPU target sharding for direct N^2 (torch.distributed)
 """
 from .api import (  # noqa: F401
@@ -13,5 +14,6 @@ from .api import (  # noqa: F401
     SimulationConfig, SimulationState, SpatialHashCalculator, ValidationException, createForceCalculator,
     get_context, validateSimulationConfig,
 )
+from .serialization import Serializer  # noqa: F401
 
 __version__ = "0.1.0"

@@ -76,6 +76,7 @@ SYMBOLS = {
     "nb_bh_forces": (_i, [_vp, _pp, _f, _f, _f, _vp]),
     "nb_bh_export": (_i, [_vp] + [_vp] * 8),
     "nb_bh_stats": (_i, [_vp, C.POINTER(C.c_uint64), C.POINTER(_i)]),
+    "nb_bh_max_stack": (_i, [_vp, C.POINTER(_i), C.POINTER(_i)]),
     "nb_sh_build": (_i, [_vp, _pp, _f, _vp]),
     "nb_sh_forces": (_i, [_vp, _pp, _f, _f, _f, _vp]),
     "nb_sh_export": (_i, [_vp] + [_vp] * 6),
@@ -87,6 +88,14 @@ SYMBOLS = {
     "nb_mgpu_forces_local": (_i, [_vp, _vp, _f, _vp]),
     "nb_mgpu_forces_remote": (_i, [_vp, _vp, _f, _vp]),
     "nb_mgpu_finish": (_i, [_vp, _pp, _f, _i, _vp]),
+    "nb_mgpu_peer_alloc": (_i, [_vp, _vp]),
+    "nb_mgpu_peer_open": (_i, [_vp, _i, _vp]),
+    "nb_mgpu_peer_step": (_i, [_vp, _pp, _f, _f, _f, _i, _vp]),
+    "nb_mgpu_peer_push": (_i, [_vp, _pp, _f, _f, _i, _vp]),
+    "nb_mgpu_peer_forces": (_i, [_vp, _pp, _f, _f, _i, _vp]),
+    "nb_mgpu_peer_block": (_i, [_vp, C.POINTER(_vp), C.POINTER(_sz)]),
+    "nb_mgpu_peer_map": (_i, [_vp, _i, _vp]),
+    "nb_mgpu_peer_close": (_i, [_vp]),
 }
 
 

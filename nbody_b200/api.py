@@ -653,6 +653,14 @@ class ParticleSystem:
         self._install(st)  # accelerations zeroed then recomputed (particle_system.cpp:261, 283)
         self.is_paused_ = False
 
+    def saveState(self, filename):  # particle_system.cpp:294-297
+        from .serialization import Serializer
+        Serializer.save(filename, self.getState())
+
+    def loadState(self, filename):  # particle_system.cpp:299-302
+        from .serialization import Serializer
+        self.setState(Serializer.load(filename))
+
     def computeKineticEnergy(self):
         return self.integrator_.computeKineticEnergy(self.d_particles_) if self.integrator_ else 0.0
 

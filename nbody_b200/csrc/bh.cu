@@ -27,13 +27,15 @@ int sort_pairs(nb_context* ctx, uint32_t* d_keys, int32_t* d_vals, size_t n, int
 
 struct BH {
   size_t n = 0;
-  nb::DevBuf keys, perm, node_com, meta, parent, flags, misc;  // misc: size2 table[32] + counter + bbox floats
+  nb::DevBuf keys, perm, packed, node_com, meta, parent, flags, misc;  // misc: size2 table[32] + counter + bbox floats
   nb::DevBuf range, groups;  // int2 {first,last} per internal node; int2 {first,count} per traversal group
   float h_bbox[6] = {0, 0, 0, 0, 0, 0};
   int* h_flag = nullptr;  // host-mapped: traversal stack overflow
   int* d_flag = nullptr;
   int group = 64;         // max bodies per traversal group / warp (32 or 64; NB_BH_GROUP overrides)
+  int super = 512;        // max leaves of the subtree a group is cut from (NB_BH_SUPER overrides; >= group)
   int occ = 0;
+  int stack_cap = 2048;   // entries per warp traversal stack (NB_BH_STACK overrides)
   bool built = false;
 };
 
@@ -51,7 +53,8 @@ __device__ __forceinline__ unsigned expand_bits(unsigned v) {
 }
 
 // misc layout (floats): [0..31] size2 table by prefix length, [32..37] bbox, [40..41] u64 counter,
-// [44] int number of traversal groups, [45] int work-queue cursor of the traversal kernel
+// [44] int number of traversal groups, [45] int work-queue cursor of the traversal kernel,
+// [46] int deepest traversal stack of the last force evaluation
 __global__ void bh_prepare_kernel(const int* __restrict__ bb_ord, float* __restrict__ misc) {
   const int t = threadIdx.x;
   __shared__ float bb[6];
@@ -61,6 +64,7 @@ __global__ void bh_prepare_kernel(const int* __restrict__ bb_ord, float* __restr
   }
   if (t == 6) *reinterpret_cast<unsigned long long*>(misc + 40) = 0ull;
   if (t == 7) reinterpret_cast<int*>(misc)[44] = 0;  // number of traversal groups
+  if (t == 8) reinterpret_cast<int*>(misc)[46] = 0;  // deepest traversal stack seen
   __syncthreads();
   if (t <= 30) {
     // side of the Morton cell at prefix length L: x is split first, then y, then z
@@ -76,18 +80,23 @@ __global__ void bh_prepare_kernel(const int* __restrict__ bb_ord, float* __restr
 
 // :260-274 (host part: size = max-min+0.001f, inv = 1.0f/size) and :113-127 (device part)
 __global__ void __launch_bounds__(256) bh_morton_kernel(const float* __restrict__ px, const float* __restrict__ py,
-                                                        const float* __restrict__ pz, size_t n,
+                                                        const float* __restrict__ pz,
+                                                        const float* __restrict__ mass, size_t n,
                                                         const float* __restrict__ misc, uint32_t* __restrict__ keys,
-                                                        int32_t* __restrict__ perm) {
+                                                        int32_t* __restrict__ perm, float4* __restrict__ packed) {
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
+  const float x = px[i], y = py[i], z = pz[i];
+  // {x,y,z,m} in body order: the leaf gather after the sort is then ONE random 16-B read per body
+  // instead of four random 4-B reads (each of which costs a whole DRAM sector)
+  packed[i] = make_float4(x, y, z, mass[i]);
   const float mnx = misc[32], mny = misc[33], mnz = misc[34];
   const float ix = __fdiv_rn(1.0f, __fadd_rn(__fsub_rn(misc[35], mnx), 0.001f));
   const float iy = __fdiv_rn(1.0f, __fadd_rn(__fsub_rn(misc[36], mny), 0.001f));
   const float iz = __fdiv_rn(1.0f, __fadd_rn(__fsub_rn(misc[37], mnz), 0.001f));
-  const float nx = __fmul_rn(__fsub_rn(px[i], mnx), ix);
-  const float ny = __fmul_rn(__fsub_rn(py[i], mny), iy);
-  const float nz = __fmul_rn(__fsub_rn(pz[i], mnz), iz);
+  const float nx = __fmul_rn(__fsub_rn(x, mnx), ix);
+  const float ny = __fmul_rn(__fsub_rn(y, mny), iy);
+  const float nz = __fmul_rn(__fsub_rn(z, mnz), iz);
   // static_cast<unsigned>(x * 1024.0f) clamped to [0, 1023] (:31-35); cvt.rzi.u32.f32 saturates
   const unsigned ux = min(__float2uint_rz(__fmul_rn(nx, 1024.0f)), 1023u);
   const unsigned uy = min(__float2uint_rz(__fmul_rn(ny, 1024.0f)), 1023u);
@@ -97,12 +106,12 @@ __global__ void __launch_bounds__(256) bh_morton_kernel(const float* __restrict_
 }
 
 // leaves of the tree = bodies in sorted order, packed {x,y,z,m}
-__global__ void __launch_bounds__(256) bh_gather_kernel(nb_particles d, size_t n, const int32_t* __restrict__ perm,
+__global__ void __launch_bounds__(256) bh_gather_kernel(const float4* __restrict__ packed, size_t n,
+                                                        const int32_t* __restrict__ perm,
                                                         float4* __restrict__ leaves) {
   const size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= n) return;
-  const int i = perm[k];
-  leaves[k] = make_float4(d.pos_x[i], d.pos_y[i], d.pos_z[i], d.mass[i]);
+  leaves[k] = __ldg(packed + perm[k]);
 }
 
 __device__ __forceinline__ int bh_delta(const uint32_t* __restrict__ k, int n, int i, int j) {
@@ -174,11 +183,14 @@ __global__ void __launch_bounds__(256) bh_com_kernel(int n, const int4* __restri
   }
 }
 
-// Traversal groups = maximal subtrees with at most `gmax` leaves: the bodies of a group share a
-// Morton prefix, so the group's bounding box is as tight as its cell (a fixed run of 32
-// consecutive sorted bodies can straddle distant cells in sparse regions).  One thread per leaf
-// climbs to its group's root; the leaf that is the root's first body publishes {first, count}.
-__global__ void __launch_bounds__(256) bh_groups_kernel(int n, int gmax, const int32_t* __restrict__ parent,
+// Traversal groups.  A "supergroup" is a maximal subtree with at most `smax` leaves: its bodies share
+// a Morton prefix, so it is as compact as its cell (a fixed run of consecutive sorted bodies can
+// straddle distant cells in sparse regions).  Each supergroup of c bodies is cut into
+// ceil(c / gmax) runs of consecutive bodies of (almost) equal length <= gmax, run i starting at
+// floor(i * c / runs): with smax == gmax the groups are the subtrees themselves (mean fill 69 % of
+// gmax), with smax = 8 * gmax the runs are 89-100 % full and still confined to one cell.
+// One thread per leaf climbs to its supergroup's root; the leaf that starts a run publishes it.
+__global__ void __launch_bounds__(256) bh_groups_kernel(int n, int smax, int gmax, const int32_t* __restrict__ parent,
                                                         const int2* __restrict__ range, int2* __restrict__ groups,
                                                         int* __restrict__ ngroups) {
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
@@ -187,12 +199,18 @@ __global__ void __launch_bounds__(256) bh_groups_kernel(int n, int gmax, const i
   int p = parent[n - 1 + k];
   while (p >= 0) {
     const int2 r = range[p];
-    if (r.y - r.x + 1 > gmax) break;
+    if (r.y - r.x + 1 > smax) break;
     first = r.x;
     count = r.y - r.x + 1;
     p = parent[p];
   }
-  if (first == k) groups[atomicAdd(ngroups, 1)] = make_int2(first, count);
+  const int runs = (count + gmax - 1) / gmax;
+  const int r = k - first;
+  const int i = (int)(((long long)r * runs + count - 1) / count);  // first run starting at or after r
+  if (i < runs && (int)(((long long)i * count) / runs) == r) {
+    const int next = (int)(((long long)(i + 1) * count) / runs);
+    groups[atomicAdd(ngroups, 1)] = make_int2(k, next - r);
+  }
 }
 
 // ---- traversal ---------------------------------------------------------------------------------------
@@ -206,9 +224,7 @@ __global__ void __launch_bounds__(256) bh_groups_kernel(int n, int gmax, const i
 // adds the monopole term (:175-181) for its own bodies.  Order is deterministic (lane order), and
 // oracle/lbvh.c restates it step for step.
 constexpr int BH_WARPS = 4;
-constexpr int BH_STACK = 2048;
 constexpr int BH_LIST = 64;
-constexpr int BH_SMEM_PER_WARP = BH_STACK * 4 + BH_LIST * 16;
 
 template <int BPL, bool EPS0>
 __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const float4* __restrict__ node_com,
@@ -221,14 +237,17 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
                                                                   int* __restrict__ overflow,
                                                                   const int2* __restrict__ groups,
                                                                   const int* __restrict__ ngroups,
-                                                                  int* __restrict__ cursor) {
+                                                                  int* __restrict__ cursor, int stack_cap,
+                                                                  int* __restrict__ max_stack) {
   extern __shared__ __align__(16) unsigned char bh_smem[];
   __shared__ float size2_tab[32];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   if (threadIdx.x < 32) size2_tab[threadIdx.x] = misc[threadIdx.x];
   __syncthreads();
-  float4* list = reinterpret_cast<float4*>(bh_smem + (size_t)w * BH_SMEM_PER_WARP);
-  int* stack = reinterpret_cast<int*>(bh_smem + (size_t)w * BH_SMEM_PER_WARP + BH_LIST * 16);
+  const size_t smem_per_warp = (size_t)stack_cap * 4 + BH_LIST * 16;
+  float4* list = reinterpret_cast<float4*>(bh_smem + (size_t)w * smem_per_warp);
+  int* stack = reinterpret_cast<int*>(bh_smem + (size_t)w * smem_per_warp + BH_LIST * 16);
+  int deepest = 0;
   const int leaf0 = n - 1;
   const unsigned lt = (1u << lane) - 1u;
   const int total_groups = *ngroups;
@@ -242,14 +261,17 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
   const int2 grp = groups[g];
   const int k0 = grp.x, gcnt = grp.y;
 
-  float4 me[BPL];
+  // scalar loads on purpose: a float4 load pins x,y,z to one aligned register quad, and ptxas then
+  // re-packs the (body 0, body 1) pairs with MOVs for every list entry (4.5 MOVs per entry measured)
+  struct { float x, y, z; } me[BPL];
   float sx[BPL], sy[BPL], sz[BPL];
   float lo[3] = {3.0e38f, 3.0e38f, 3.0e38f}, hi[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
 #pragma unroll
   for (int b = 0; b < BPL; b++) {
-    me[b] = make_float4(0.f, 0.f, 0.f, 0.f);
+    me[b].x = me[b].y = me[b].z = 0.f;
     if (b * 32 + lane < gcnt) {
-      me[b] = node_com[leaf0 + k0 + b * 32 + lane];
+      const float* q = reinterpret_cast<const float*>(node_com + leaf0 + k0 + b * 32 + lane);
+      me[b].x = __ldg(q); me[b].y = __ldg(q + 1); me[b].z = __ldg(q + 2);
       lo[0] = fminf(lo[0], me[b].x); hi[0] = fmaxf(hi[0], me[b].x);
       lo[1] = fminf(lo[1], me[b].y); hi[1] = fmaxf(hi[1], me[b].y);
       lo[2] = fminf(lo[2], me[b].z); hi[2] = fmaxf(hi[2], me[b].z);
@@ -261,6 +283,9 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
     lo[a] = warp_min(lo[a]);
     hi[a] = warp_max(hi[a]);
   }
+  const f2 e2 = pk(eps2, eps2);
+  const f2 xi2 = pk(me[0].x, me[BPL - 1].x), yi2 = pk(me[0].y, me[BPL - 1].y), zi2 = pk(me[0].z, me[BPL - 1].z);
+  f2 sx2 = pk(0.f, 0.f), sy2 = sx2, sz2 = sx2;
 
   int sp = 1, nl = 0;
   unsigned visits = 0;
@@ -273,13 +298,15 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
     sp -= m;
     __syncwarp();
     float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (have) c = node_com[ni];
-    const bool valid = have && c.w != 0.f;  // total_mass == 0 -> skipped (:157-158)
-    const bool leaf = ni >= leaf0;
     int4 mt = make_int4(0, 0, 31, 0);
+    const bool leaf = ni >= leaf0;
+    if (have) {  // both fetches issue together (no dependence of the second on the first's data)
+      c = node_com[ni];
+      if (!leaf) mt = meta[ni];
+    }
+    const bool valid = have && c.w != 0.f;  // total_mass == 0 -> skipped (:157-158)
     bool acc = leaf;
     if (valid && !leaf) {
-      mt = meta[ni];
       const float ddx = fmaxf(fmaxf(lo[0] - c.x, c.x - hi[0]), 0.f);
       const float ddy = fmaxf(fmaxf(lo[1] - c.y, c.y - hi[1]), 0.f);
       const float ddz = fmaxf(fmaxf(lo[2] - c.z, c.z - hi[2]), 0.f);
@@ -288,9 +315,10 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
     }
     const bool is_acc = valid && acc, is_rej = valid && !acc;
     const unsigned amask = __ballot_sync(0xffffffffu, is_acc), rmask = __ballot_sync(0xffffffffu, is_rej);
-    if (is_acc) list[nl + __popc(amask & lt)] = c;
+    if (is_acc) list[nl + __popc(amask & lt)] = make_float4(c.x, c.y, c.z, G * c.w);  // G*M once per node
     const int npush = 2 * __popc(rmask);
-    if (sp + npush > BH_STACK) {  // never silently drop subtrees (the reference does, :186-194)
+    deepest = max(deepest, sp + npush);
+    if (sp + npush > stack_cap) {  // never silently drop subtrees (the reference does, :186-194)
       if (lane == 0) *overflow = 1;
       break;
     }
@@ -306,18 +334,36 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
     while (nl >= 32 || (done && nl > 0)) {
       const int ne = min(nl, 32);
       auto body = [&](int e) {
-        const float4 p = list[e];  // warp-broadcast LDS.128
-        const float gm = G * p.w;
+        const float4 p = list[e];  // warp-broadcast LDS.128; p.w = G * M
+        const float gm = p.w;
+        if constexpr (BPL == 2) {
+          // the lane's two bodies as one packed fp32x2 pair (FADD2/FFMA2/FMUL2, as in direct.cu)
+          const f2 dx = sub2(pk(p.x, p.x), xi2), dy = sub2(pk(p.y, p.y), yi2), dz = sub2(pk(p.z, p.z), zi2);
+          const f2 d2 = fma2(dz, dz, fma2(dy, dy, fma2(dx, dx, e2)));
+          float r0, r1;
+          upk(d2, r0, r1);
+          float i0 = rsq(r0), i1 = rsq(r1);
+          if (EPS0) {  // own leaf / exact coincidence at eps = 0
+            i0 = (r0 > 0.f) ? i0 : 0.f;
+            i1 = (r1 > 0.f) ? i1 : 0.f;
+          }
+          const f2 ri = pk(i0, i1);
+          const f2 f = mul2(pk(gm, gm), mul2(mul2(ri, ri), ri));
+          sx2 = fma2(f, dx, sx2);
+          sy2 = fma2(f, dy, sy2);
+          sz2 = fma2(f, dz, sz2);
+        } else {
 #pragma unroll
-        for (int b = 0; b < BPL; b++) {
-          const float dx = p.x - me[b].x, dy = p.y - me[b].y, dz = p.z - me[b].z;
-          const float d2 = fmaf(dz, dz, fmaf(dy, dy, fmaf(dx, dx, eps2)));
-          float inv = rsq(d2);
-          if (EPS0) inv = (d2 > 0.f) ? inv : 0.f;  // own leaf / exact coincidence at eps = 0
-          const float f = gm * (inv * inv * inv);
-          sx[b] = fmaf(f, dx, sx[b]);
-          sy[b] = fmaf(f, dy, sy[b]);
-          sz[b] = fmaf(f, dz, sz[b]);
+          for (int b = 0; b < BPL; b++) {
+            const float dx = p.x - me[b].x, dy = p.y - me[b].y, dz = p.z - me[b].z;
+            const float d2 = fmaf(dz, dz, fmaf(dy, dy, fmaf(dx, dx, eps2)));
+            float inv = rsq(d2);
+            if (EPS0) inv = (d2 > 0.f) ? inv : 0.f;  // own leaf / exact coincidence at eps = 0
+            const float f = gm * (inv * inv * inv);
+            sx[b] = fmaf(f, dx, sx[b]);
+            sy[b] = fmaf(f, dy, sy[b]);
+            sz[b] = fmaf(f, dz, sz[b]);
+          }
         }
       };
       if (ne == 32) {
@@ -338,6 +384,11 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
     }
     if (done) break;
   }
+  if constexpr (BPL == 2) {
+    upk(sx2, sx[0], sx[1]);
+    upk(sy2, sy[0], sy[1]);
+    upk(sz2, sz[0], sz[1]);
+  }
 #pragma unroll
   for (int b = 0; b < BPL; b++) {
     if (b * 32 + lane < gcnt) {
@@ -350,7 +401,10 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
   visits_bodies += (unsigned long long)visits * (unsigned long long)gcnt;
   __syncwarp();
   }  // next group
-  if (lane == 0 && visits_bodies) atomicAdd(counter, visits_bodies);
+  if (lane == 0 && visits_bodies) {
+    atomicAdd(counter, visits_bodies);
+    atomicMax(max_stack, deepest);
+  }
 }
 
 static BH* bh_get(nb_context* ctx) {
@@ -361,7 +415,7 @@ static BH* bh_get(nb_context* ctx) {
 void bh_destroy(nb_context* ctx) {
   if (!ctx->bh) return;
   BH* b = ctx->bh;
-  b->keys.release(); b->perm.release(); b->node_com.release(); b->meta.release();
+  b->keys.release(); b->perm.release(); b->packed.release(); b->node_com.release(); b->meta.release();
   b->parent.release(); b->flags.release(); b->misc.release(); b->range.release(); b->groups.release();
   if (b->h_flag) cudaFreeHost(b->h_flag);
   delete b;
@@ -380,6 +434,7 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
   b->n = n;
   if (int rc = b->keys.ensure(n * 4)) return rc;
   if (int rc = b->perm.ensure(n * 4)) return rc;
+  if (int rc = b->packed.ensure(n * sizeof(float4))) return rc;
   if (int rc = b->node_com.ensure((2 * n) * sizeof(float4))) return rc;
   if (int rc = b->meta.ensure(n * sizeof(int4))) return rc;
   if (int rc = b->parent.ensure(2 * n * 4)) return rc;
@@ -392,18 +447,28 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
     const int g = (e && atoi(e) == 32) ? 32 : 64;
     if (g != b->group) b->occ = 0;
     b->group = g;
+    if (const char* ce = getenv("NB_BH_STACK")) {
+      int c = atoi(ce);
+      c = c < 512 ? 512 : (c > 2816 ? 2816 : c);  // 4 warps x (cap x 4 + 1 KiB) <= 48 KiB
+      if (c != b->stack_cap) b->occ = 0;
+      b->stack_cap = c;
+    }
+    const char* se = getenv("NB_BH_SUPER");
+    int sg = se ? atoi(se) : 8 * g;
+    if (sg < g) sg = g;
+    b->super = sg;
   }
   float* misc = b->misc.as<float>();
   if (int rc = bbox_device(ctx, d, st)) return rc;
   bh_prepare_kernel<<<1, 32, 0, st>>>(ctx->bbox_dev.as<int>(), misc);
   NB_LAUNCH_CHECK(ctx);
   const unsigned gn = (unsigned)((n + 255) / 256);
-  bh_morton_kernel<<<gn, 256, 0, st>>>(d->pos_x, d->pos_y, d->pos_z, n, misc, b->keys.as<uint32_t>(),
-                                       b->perm.as<int32_t>());
+  bh_morton_kernel<<<gn, 256, 0, st>>>(d->pos_x, d->pos_y, d->pos_z, d->mass, n, misc, b->keys.as<uint32_t>(),
+                                       b->perm.as<int32_t>(), b->packed.as<float4>());
   NB_LAUNCH_CHECK(ctx);
   if (int rc = sort_pairs(ctx, b->keys.as<uint32_t>(), b->perm.as<int32_t>(), n, 30, st)) return rc;
   float4* com = b->node_com.as<float4>();
-  bh_gather_kernel<<<gn, 256, 0, st>>>(*d, n, b->perm.as<int32_t>(), com + (n - 1));
+  bh_gather_kernel<<<gn, 256, 0, st>>>(b->packed.as<float4>(), n, b->perm.as<int32_t>(), com + (n - 1));
   NB_LAUNCH_CHECK(ctx);
   NB_CUDA(cudaMemsetAsync(b->parent.p, 0xff, sizeof(int32_t), st));  // parent[0] = -1 (also when n == 1)
   if (n > 1) {
@@ -415,7 +480,7 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
     bh_com_kernel<<<gn, 256, 0, st>>>((int)n, b->meta.as<int4>(), b->parent.as<int32_t>(), b->flags.as<int>(), com);
     NB_LAUNCH_CHECK(ctx);
   }
-  bh_groups_kernel<<<gn, 256, 0, st>>>((int)n, b->group, b->parent.as<int32_t>(), b->range.as<int2>(),
+  bh_groups_kernel<<<gn, 256, 0, st>>>((int)n, b->super, b->group, b->parent.as<int32_t>(), b->range.as<int2>(),
                                        b->groups.as<int2>(), reinterpret_cast<int*>(misc) + 44);
   NB_LAUNCH_CHECK(ctx);
   b->built = true;
@@ -425,7 +490,7 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
 static int bh_check_overflow(BH* b) {
   if (b->h_flag && *b->h_flag) {
     *b->h_flag = 0;
-    set_error("Barnes-Hut traversal stack overflow (tree deeper than the %d-entry warp stack allows)", BH_STACK);
+    set_error("Barnes-Hut traversal stack overflow (tree deeper than the %d-entry warp stack allows)", b->stack_cap);
     return NB_ERR_INTERNAL;
   }
   return NB_OK;
@@ -448,7 +513,7 @@ int bh_forces(nb_context* ctx, const nb_particles* d, float theta, float G, floa
   float* misc = b->misc.as<float>();
   int* cursor = reinterpret_cast<int*>(misc) + 45;
   NB_CUDA(cudaMemsetAsync(cursor, 0, sizeof(int), st));
-  const size_t smem = (size_t)BH_WARPS * BH_SMEM_PER_WARP;
+  const size_t smem = (size_t)BH_WARPS * ((size_t)b->stack_cap * 4 + BH_LIST * 16);
   const float eps2 = eps * eps;
   const bool eps0 = !(eps2 > 0.f);
   if (!b->occ) {
@@ -468,7 +533,8 @@ int bh_forces(nb_context* ctx, const nb_particles* d, float theta, float G, floa
   bh_force_kernel<BPL_, E_><<<grid, BH_WARPS * 32, smem, st>>>(                                                    \
       (int)n, b->node_com.as<float4>(), b->meta.as<int4>(), b->perm.as<int32_t>(), misc, theta * theta, G, eps2,  \
       d->acc_x, d->acc_y, d->acc_z, reinterpret_cast<unsigned long long*>(misc + 40), b->d_flag,                   \
-      b->groups.as<int2>(), reinterpret_cast<const int*>(misc) + 44, cursor)
+      b->groups.as<int2>(), reinterpret_cast<const int*>(misc) + 44, cursor, b->stack_cap,                        \
+      reinterpret_cast<int*>(misc) + 46)
   if (b->group == 64) {
     if (eps0) NB_BH_LAUNCH(2, true);
     else NB_BH_LAUNCH(2, false);
@@ -551,6 +617,18 @@ int nb_bh_stats(nb_context* ctx, uint64_t* interactions, int* node_count) {
   if (int rc = bh_check_overflow(ctx->bh)) return rc;
   if (interactions) NB_CUDA(cudaMemcpy(interactions, ctx->bh->misc.as<float>() + 40, 8, cudaMemcpyDeviceToHost));
   if (node_count) *node_count = (int)(2 * ctx->bh->n - 1);
+  return NB_OK;
+}
+
+int nb_bh_max_stack(nb_context* ctx, int* deepest, int* capacity) {
+  if (!ctx || !ctx->bh || !ctx->bh->built) {
+    set_error("Barnes-Hut stats: no tree built");
+    return NB_ERR_INVALID;
+  }
+  NB_CUDA(cudaSetDevice(ctx->device));
+  NB_CUDA(cudaDeviceSynchronize());
+  if (deepest) NB_CUDA(cudaMemcpy(deepest, ctx->bh->misc.as<int>() + 46, 4, cudaMemcpyDeviceToHost));
+  if (capacity) *capacity = ctx->bh->stack_cap;
   return NB_OK;
 }
 

@@ -176,6 +176,7 @@ int nb_context_destroy(nb_context* ctx) {
   if (!ctx) return NB_OK;
   cudaSetDevice(ctx->device);
   cudaDeviceSynchronize();
+  nb_mgpu_peer_close(ctx);
   bh_destroy(ctx);
   sh_destroy(ctx);
   ctx->src.release();

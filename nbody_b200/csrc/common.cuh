@@ -186,4 +186,5 @@ struct nb_context {
   // multi-GPU
   size_t mg_n_total = 0, mg_begin = 0, mg_count = 0, mg_padded = 0;
   int mg_rank = 0, mg_nranks = 1;
+  struct PeerState* peer = nullptr;  // CUDA-IPC exchange blocks (mgpu.cu)
 };

@@ -50,15 +50,100 @@ __global__ void __launch_bounds__(256) pack_kernel(nb_particles d, float4* __res
   src[i] = o;
 }
 
+// pack fused with the all-gather (multi-GPU peer exchange): the packed float4 of every local body is
+// stored straight into slot `slot_off` of EVERY rank's replicated source buffer -- the local one and,
+// through NVLink/NVSwitch peer mappings, the R-1 remote ones -- so no separate collective runs.  The
+// last CTA to finish raises this rank's step flag on every peer (release at system scope); the
+// consumers are the gated force kernels there.
+template <bool DRIFT>
+__global__ void __launch_bounds__(256) pack_push_kernel(nb_particles d, PeerBufs pb, size_t slot_off, size_t n,
+                                                        size_t n_pad, float G, float dt, unsigned step,
+                                                        int flag_index, unsigned* __restrict__ done_counter) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n_pad) {
+    float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (i < n) {
+      float x = d.pos_x[i], y = d.pos_y[i], z = d.pos_z[i];
+      if (DRIFT) {  // same rounding sequence as pack_kernel<true> (integrator.cu:39-48, :11-21)
+        const float dt2_half = __fmul_rn(__fmul_rn(0.5f, dt), dt);
+        const float ax = d.acc_x[i], ay = d.acc_y[i], az = d.acc_z[i];
+        d.acc_old_x[i] = ax;
+        d.acc_old_y[i] = ay;
+        d.acc_old_z[i] = az;
+        x = __fadd_rn(x, __fadd_rn(__fmul_rn(d.vel_x[i], dt), __fmul_rn(ax, dt2_half)));
+        y = __fadd_rn(y, __fadd_rn(__fmul_rn(d.vel_y[i], dt), __fmul_rn(ay, dt2_half)));
+        z = __fadd_rn(z, __fadd_rn(__fmul_rn(d.vel_z[i], dt), __fmul_rn(az, dt2_half)));
+        d.pos_x[i] = x;
+        d.pos_y[i] = y;
+        d.pos_z[i] = z;
+      }
+      o = make_float4(x, y, z, __fmul_rn(G, d.mass[i]));
+    }
+#pragma unroll
+    for (int r = 0; r < NB_MAX_PEERS; r++)
+      if (r < pb.nranks) pb.buf[r][slot_off + i] = o;
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned prev = atomicAdd(done_counter, 1u);
+    if (prev == gridDim.x - 1) {  // every CTA's stores are fenced: publish
+      *done_counter = 0;
+      __threadfence_system();
+      for (int r = 0; r < pb.nranks; r++)
+        if (r != pb.self)
+          asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(pb.flags[r] + flag_index), "r"(step) : "memory");
+    }
+  }
+}
+
+int launch_pack_push(nb_context* ctx, const nb_particles* d, const PeerBufs& pb, size_t slot_off, size_t n,
+                     size_t n_pad, float G, float dt, bool drift, unsigned step, int flag_index, unsigned* done_counter,
+                     cudaStream_t st) {
+  const unsigned grid = (unsigned)((n_pad + 255) / 256);
+  if (grid == 0) return NB_OK;
+  if (drift) pack_push_kernel<true><<<grid, 256, 0, st>>>(*d, pb, slot_off, n, n_pad, G, dt, step, flag_index, done_counter);
+  else pack_push_kernel<false><<<grid, 256, 0, st>>>(*d, pb, slot_off, n, n_pad, G, dt, step, flag_index, done_counter);
+  NB_LAUNCH_CHECK(ctx);
+  return NB_OK;
+}
+
+// spin (bounded) until peer `peer` has published `gate.step`; then order the async-proxy (TMA) reads
+// that follow after the acquire
+__device__ __forceinline__ void peer_wait(const PeerGate& gate, int peer) {
+  const unsigned* f = gate.flags + gate.flag_base + peer;
+  unsigned long long t0 = 0;
+  for (unsigned spins = 0;; spins++) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+    if ((int)(v - gate.step) >= 0) break;
+    if ((spins & 1023u) == 1023u) {  // a dead peer must not hang the GPU: give up after ~20 s and say so
+      unsigned long long now;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > 20000000000ull) {
+        *gate.timeout_flag = 1;
+        break;
+      }
+    }
+  }
+  asm volatile("fence.proxy.async;" ::: "memory");
+}
+
 // ---------------------------------------------------------------------------------------------
 // force kernel
 // ---------------------------------------------------------------------------------------------
-template <int T, int I, int JT, bool EPS0>
+// Source tile j of a pass is tile (j0 + j) mod jwrap of `src`.  GATED (multi-GPU peer exchange,
+// mgpu.cu): tiles [p*gate.ptiles, (p+1)*gate.ptiles) were pushed into `src` by peer p's
+// pack_push_kernel over NVLink; the thread that issues the TMA copies waits for peer p's step flag
+// (ld.acquire.sys) the first time it touches one of p's tiles, so the math starts on the local
+// slice and runs into each peer's slice as it lands.
+template <int T, int I, int JT, bool EPS0, bool GATED>
 __global__ void __launch_bounds__(T) direct_force_kernel(const float4* __restrict__ src,
                                                           const float4* __restrict__ tgt,
                                                           float* __restrict__ partial, long long U, int UJ,
-                                                          int ja0, int na, int jb0, float eps2,
-                                                          unsigned long long slot_base) {
+                                                          int j0, int jwrap, float eps2,
+                                                          unsigned long long slot_base, PeerGate gate) {
   constexpr int P = I / 2;
   constexpr int IT = T * I;
   constexpr uint32_t TILE_BYTES = JT * sizeof(float4);
@@ -79,8 +164,17 @@ __global__ void __launch_bounds__(T) direct_force_kernel(const float4* __restric
 
   int itile = (int)(u0 / UJ);
   int jt = (int)(u0 - (long long)itile * UJ);
+  unsigned ready_peers = 1u << gate.self;  // peers whose slice is known to have landed (thread 0 only)
   auto jtile_ptr = [&](int j) -> const float4* {
-    const int g = (j < na) ? (ja0 + j) : (jb0 + (j - na));
+    int g = j0 + j;
+    if (g >= jwrap) g -= jwrap;
+    if (GATED) {
+      const int peer = g / gate.ptiles;
+      if (!((ready_peers >> peer) & 1u)) {
+        peer_wait(gate, peer);
+        ready_peers |= 1u << peer;
+      }
+    }
     return src + (size_t)g * JT;
   };
   if (tid == 0) {
@@ -235,17 +329,18 @@ template <int T, int I, int JT>
 static int occupancy(bool eps0) {
   int occ = 0;
   if (eps0)
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, direct_force_kernel<T, I, JT, true>, T, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, direct_force_kernel<T, I, JT, true, false>, T, 0);
   else
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, direct_force_kernel<T, I, JT, false>, T, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, direct_force_kernel<T, I, JT, false, false>, T, 0);
   return occ > 0 ? occ : 1;
 }
 
-// Launch one stream-K pass.  Source tiles [ja0, ja0+na) then [jb0, jb0+nb) of `src` (tile = JT
-// bodies) against n_itiles target tiles of `tgt`.
+// Launch one stream-K pass: `njt` source tiles (tile = JT bodies) starting at tile j0 of `src`, wrapping
+// at jwrap, against n_itiles target tiles of `tgt`.  gate != nullptr: peer-gated sources (see the kernel).
 int launch_direct_pass(nb_context* ctx, const DirectCfg& cfg, const float4* src, const float4* tgt, int n_itiles,
-                       int ja0, int na, int jb0, int nbt, float eps2, int pass_index, cudaStream_t st) {
-  const int UJ = na + nbt;
+                       int j0, int njt, int jwrap, float eps2, int pass_index, cudaStream_t st,
+                       const PeerGate* gate) {
+  const int UJ = njt;
   nb_pass& ps = ctx->pass[pass_index];
   ps.UJ = UJ;
   ps.n_itiles = n_itiles;
@@ -272,17 +367,25 @@ int launch_direct_pass(nb_context* ctx, const DirectCfg& cfg, const float4* src,
                                          : ps.slot_base + (size_t)ps.G + n_itiles;
   if (int rc = ctx->partial.ensure(slots * 3 * cfg.IT() * sizeof(float))) return rc;
   float* part = ctx->partial.as<float>();
-#define NB_LAUNCH_DIRECT(T_, I_, JT_, E_)                                                             \
-  direct_force_kernel<T_, I_, JT_, E_><<<ps.G, T_, 0, st>>>(src, tgt, part, ps.U, UJ, ja0, na, jb0, eps2, \
-                                                            (unsigned long long)ps.slot_base)
+  PeerGate none{};
+  const PeerGate gt = gate ? *gate : none;
+#define NB_LAUNCH_DIRECT(T_, I_, JT_, E_, G_)                                                                  \
+  direct_force_kernel<T_, I_, JT_, E_, G_><<<ps.G, T_, 0, st>>>(src, tgt, part, ps.U, UJ, j0, jwrap, eps2,     \
+                                                                (unsigned long long)ps.slot_base, gt)
+#define NB_LAUNCH_DIRECT_E(T_, I_, JT_, E_)            \
+  do {                                                 \
+    if (gate) NB_LAUNCH_DIRECT(T_, I_, JT_, E_, true); \
+    else NB_LAUNCH_DIRECT(T_, I_, JT_, E_, false);     \
+  } while (0)
   ProfScope prof(ctx, st);
   if (big) {
-    if (eps0) NB_LAUNCH_DIRECT(256, 2, 1024, true);
-    else NB_LAUNCH_DIRECT(256, 2, 1024, false);
+    if (eps0) NB_LAUNCH_DIRECT_E(256, 2, 1024, true);
+    else NB_LAUNCH_DIRECT_E(256, 2, 1024, false);
   } else {
-    if (eps0) NB_LAUNCH_DIRECT(128, 2, 256, true);
-    else NB_LAUNCH_DIRECT(128, 2, 256, false);
+    if (eps0) NB_LAUNCH_DIRECT_E(128, 2, 256, true);
+    else NB_LAUNCH_DIRECT_E(128, 2, 256, false);
   }
+#undef NB_LAUNCH_DIRECT_E
 #undef NB_LAUNCH_DIRECT
   NB_LAUNCH_CHECK(ctx);
   return NB_OK;
@@ -340,7 +443,7 @@ int direct_run(nb_context* ctx, const nb_particles* d, float dt, float G, float 
   const int n_itiles = (int)((n + cfg.IT() - 1) / cfg.IT());
   const int n_jt = (int)((n + cfg.JT - 1) / cfg.JT);
   ctx->n_pass = 1;
-  if (int rc = launch_direct_pass(ctx, cfg, src, src, n_itiles, 0, n_jt, 0, 0, eps2, 0, st)) return rc;
+  if (int rc = launch_direct_pass(ctx, cfg, src, src, n_itiles, 0, n_jt, n_jt, eps2, 0, st, nullptr)) return rc;
   return launch_reduce(ctx, cfg, d, n, dt, step, st);
 }
 

@@ -9,11 +9,34 @@ struct DirectCfg {
   int IT() const { return T * I; }
 };
 
+constexpr int NB_MAX_PEERS = 8;
+
+// multi-GPU peer exchange (mgpu.cu): every rank's replicated source buffer and flag block, as mapped
+// into this process (own allocation + cudaIpc mappings of the peers')
+struct PeerBufs {
+  float4* buf[NB_MAX_PEERS];
+  unsigned* flags[NB_MAX_PEERS];
+  int nranks, self;
+};
+// what the gated force kernel needs to wait for a peer's slice
+struct PeerGate {
+  const unsigned* flags;   // this rank's flag block
+  int flag_base;           // parity * NB_MAX_PEERS
+  unsigned step;           // value a peer stores when its slice of this step has landed
+  int ptiles;              // source tiles per peer slice
+  int self;
+  int* timeout_flag;       // host-mapped: set when a wait gave up
+};
+
 const DirectCfg& direct_cfg(size_t n_total_sources);
+int launch_pack_push(nb_context* ctx, const nb_particles* d, const PeerBufs& pb, size_t slot_off, size_t n,
+                     size_t n_pad, float G, float dt, bool drift, unsigned step, int flag_index, unsigned* done_counter,
+                     cudaStream_t st);
 int launch_pack(nb_context* ctx, const nb_particles* d, float4* src, size_t n, size_t n_pad, float G, float dt,
                 bool drift, cudaStream_t st);
 int launch_direct_pass(nb_context* ctx, const DirectCfg& cfg, const float4* src, const float4* tgt, int n_itiles,
-                       int ja0, int na, int jb0, int nbt, float eps2, int pass_index, cudaStream_t st);
+                       int j0, int njt, int jwrap, float eps2, int pass_index, cudaStream_t st,
+                       const PeerGate* gate);
 int launch_reduce(nb_context* ctx, const DirectCfg& cfg, const nb_particles* d, size_t n, float dt, bool kick,
                   cudaStream_t st);
 

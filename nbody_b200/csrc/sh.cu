@@ -32,7 +32,7 @@ struct SH {
   int total_cells = 0;
   int dims[3] = {0, 0, 0};
   float bbox[6] = {0, 0, 0, 0, 0, 0};
-  nb::DevBuf particle_cell, keys, sorted_idx, spos, cell_start, cell_end, misc;
+  nb::DevBuf particle_cell, keys, sorted_idx, packed, spos, cell_start, cell_end, misc;
   SHMisc* h_misc = nullptr;
   bool built = false;
 };
@@ -64,13 +64,17 @@ __global__ void sh_prepare_kernel(const int* __restrict__ bb_ord, float cell, SH
 
 // :28-49
 __global__ void __launch_bounds__(256) sh_assign_kernel(const float* __restrict__ px, const float* __restrict__ py,
-                                                        const float* __restrict__ pz, size_t n, float cell,
+                                                        const float* __restrict__ pz,
+                                                        const float* __restrict__ mass, size_t n, float cell,
                                                         const SHMisc* __restrict__ m, int32_t* __restrict__ pcell,
-                                                        uint32_t* __restrict__ keys, int32_t* __restrict__ vals) {
+                                                        uint32_t* __restrict__ keys, int32_t* __restrict__ vals,
+                                                        float4* __restrict__ packed) {
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const int nx = m->dims[0], ny = m->dims[1], nz = m->dims[2];
-  const float x = __fsub_rn(px[i], m->bbox[0]), y = __fsub_rn(py[i], m->bbox[1]), z = __fsub_rn(pz[i], m->bbox[2]);
+  const float rx = px[i], ry = py[i], rz = pz[i];
+  packed[i] = make_float4(rx, ry, rz, mass[i]);  // body order; gathered into cell order after the sort
+  const float x = __fsub_rn(rx, m->bbox[0]), y = __fsub_rn(ry, m->bbox[1]), z = __fsub_rn(rz, m->bbox[2]);
   int cx = (int)floorf(__fdiv_rn(x, cell)), cy = (int)floorf(__fdiv_rn(y, cell)), cz = (int)floorf(__fdiv_rn(z, cell));
   cx = max(0, min(cx, nx - 1));
   cy = max(0, min(cy, ny - 1));
@@ -81,25 +85,25 @@ __global__ void __launch_bounds__(256) sh_assign_kernel(const float* __restrict_
   vals[i] = (int32_t)i;
 }
 
-// cell_start[c] = #bodies with cell < c ; cell_end[c] = #bodies with cell <= c  (:285-288, :61-68)
-__global__ void __launch_bounds__(256) sh_ranges_kernel(const uint32_t* __restrict__ keys, size_t n, int total_cells,
-                                                        int32_t* __restrict__ cell_start,
-                                                        int32_t* __restrict__ cell_end) {
+// After the sort, one sweep over the sorted (cell, body) pairs does both remaining jobs:
+//   cell_start[c] = #bodies with cell < c ; cell_end[c] = #bodies with cell <= c  (:285-288, :61-68),
+//   read off the places where the sorted key changes (empty cells in between included);
+//   spos[k] = packed[sorted body k]: bodies physically in cell order.
+__global__ void __launch_bounds__(256) sh_ranges_gather_kernel(const uint32_t* __restrict__ keys, size_t n,
+                                                               int total_cells, int32_t* __restrict__ cell_start,
+                                                               int32_t* __restrict__ cell_end,
+                                                               const int32_t* __restrict__ sidx,
+                                                               const float4* __restrict__ packed,
+                                                               float4* __restrict__ spos) {
   const size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (k > n) return;
-  const long long prev = (k == 0) ? -1 : (long long)keys[k - 1];
-  const long long cur = (k == n) ? (long long)total_cells : (long long)keys[k];
+  if (k < n) spos[k] = __ldg(packed + sidx[k]);
+  const int prev = (k == 0) ? -1 : (int)keys[k - 1];
+  const int cur = (k == n) ? total_cells : (int)keys[k];
+  if (prev == cur) return;
   // cells prev+1 .. cur start at k; cells prev .. cur-1 end at k
-  for (long long c = prev + 1; c <= cur && c < total_cells; c++) cell_start[c] = (int32_t)k;
-  for (long long c = (prev < 0 ? 0 : prev); c < cur; c++) cell_end[c] = (int32_t)k;
-}
-
-__global__ void __launch_bounds__(256) sh_gather_kernel(nb_particles d, size_t n, const int32_t* __restrict__ sidx,
-                                                        float4* __restrict__ spos) {
-  const size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (k >= n) return;
-  const int i = sidx[k];
-  spos[k] = make_float4(d.pos_x[i], d.pos_y[i], d.pos_z[i], d.mass[i]);
+  for (int c = prev + 1; c <= cur && c < total_cells; c++) cell_start[c] = (int32_t)k;
+  for (int c = (prev < 0 ? 0 : prev); c < cur; c++) cell_end[c] = (int32_t)k;
 }
 
 // :83-152.  One thread per body in cell order; neighbours read as contiguous float4 runs.
@@ -168,7 +172,7 @@ static SH* sh_get(nb_context* ctx) {
 void sh_destroy(nb_context* ctx) {
   if (!ctx->sh) return;
   SH* s = ctx->sh;
-  s->particle_cell.release(); s->keys.release(); s->sorted_idx.release(); s->spos.release();
+  s->particle_cell.release(); s->keys.release(); s->sorted_idx.release(); s->packed.release(); s->spos.release();
   s->cell_start.release(); s->cell_end.release(); s->misc.release();
   if (s->h_misc) cudaFreeHost(s->h_misc);
   delete s;
@@ -194,6 +198,7 @@ int sh_build(nb_context* ctx, const nb_particles* d, float cell, cudaStream_t st
   if (int rc = s->keys.ensure(n * 4)) return rc;
   if (int rc = s->sorted_idx.ensure(n * 4)) return rc;
   if (int rc = s->spos.ensure(n * sizeof(float4))) return rc;
+  if (int rc = s->packed.ensure(n * sizeof(float4))) return rc;
   if (int rc = s->misc.ensure(sizeof(SHMisc))) return rc;
   if (!s->h_misc) NB_CUDA(cudaMallocHost(&s->h_misc, sizeof(SHMisc)));
   SHMisc* misc = s->misc.as<SHMisc>();
@@ -213,17 +218,16 @@ int sh_build(nb_context* ctx, const nb_particles* d, float cell, cudaStream_t st
   if (int rc = s->cell_start.ensure((size_t)s->total_cells * 4)) return rc;
   if (int rc = s->cell_end.ensure((size_t)s->total_cells * 4)) return rc;
   const unsigned gn = (unsigned)((n + 255) / 256);
-  sh_assign_kernel<<<gn, 256, 0, st>>>(d->pos_x, d->pos_y, d->pos_z, n, cell, misc, s->particle_cell.as<int32_t>(),
-                                       s->keys.as<uint32_t>(), s->sorted_idx.as<int32_t>());
+  sh_assign_kernel<<<gn, 256, 0, st>>>(d->pos_x, d->pos_y, d->pos_z, d->mass, n, cell, misc,
+                                       s->particle_cell.as<int32_t>(), s->keys.as<uint32_t>(),
+                                       s->sorted_idx.as<int32_t>(), s->packed.as<float4>());
   NB_LAUNCH_CHECK(ctx);
   int bits = 1;
   while (bits < 32 && (1ll << bits) < (long long)s->total_cells) bits++;
   if (int rc = sort_pairs(ctx, s->keys.as<uint32_t>(), s->sorted_idx.as<int32_t>(), n, bits, st)) return rc;
-  sh_ranges_kernel<<<(unsigned)((n + 1 + 255) / 256), 256, 0, st>>>(s->keys.as<uint32_t>(), n, s->total_cells,
-                                                                    s->cell_start.as<int32_t>(),
-                                                                    s->cell_end.as<int32_t>());
-  NB_LAUNCH_CHECK(ctx);
-  sh_gather_kernel<<<gn, 256, 0, st>>>(*d, n, s->sorted_idx.as<int32_t>(), s->spos.as<float4>());
+  sh_ranges_gather_kernel<<<(unsigned)((n + 1 + 255) / 256), 256, 0, st>>>(
+      s->keys.as<uint32_t>(), n, s->total_cells, s->cell_start.as<int32_t>(), s->cell_end.as<int32_t>(),
+      s->sorted_idx.as<int32_t>(), s->packed.as<float4>(), s->spos.as<float4>());
   NB_LAUNCH_CHECK(ctx);
   s->built = true;
   return NB_OK;

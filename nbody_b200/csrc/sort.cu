@@ -1,8 +1,9 @@
 // sort.cu -- bounding box reduction and a CUB-free stable LSD radix sort of (u32 key, i32 value)
 // pairs.  Replaces computeBoundingBoxKernel + its 6 malloc / 12 memcpy wrapper
 // (reference src/cuda/force_barnes_hut.cu:66-110, 218-258) and thrust::sort_by_key (:276-280).
-// Both are HBM-bound: bbox reads 12 B/body; the sort moves 20 B/body per 8-bit pass
-// (histogram pass reads the keys, scatter pass reads and writes key + value).
+// Both are HBM-bound: bbox reads 12 B/body; the sort reads the keys once for all digit histograms
+// and then moves 16 B/pair per 8-bit pass.
+#include <cstdlib>
 #include <cstring>
 
 #include "common.cuh"
@@ -92,138 +93,194 @@ int bbox_to_host(nb_context* ctx, float out[6], cudaStream_t st) {
   return NB_OK;
 }
 
-// ---- radix sort -------------------------------------------------------------------------------------
-constexpr int RS_THREADS = 256;
+// ---- radix sort ("onesweep": one histogram read + one read/write sweep per 8-bit digit) ---------------
+// Stable LSD.  rs_hist_all reads the keys once and builds the digit histograms of every pass.  Each
+// pass is ONE kernel: a block takes the next 4096/8192-key tile (ticket order), ranks its keys per
+// digit (each warp owns 512 consecutive keys and ranks them 32 at a time with __match_any_sync, so
+// equal digits keep input order), publishes its per-digit counts and resolves the counts of all
+// earlier tiles by decoupled look-back over a per-tile status word (2 flag bits + 30-bit count, one
+// thread per digit), then moves keys and values through shared memory in digit order so that every
+// global store is a run of consecutive addresses.  Algorithmic traffic: 4 + 16 x passes B/pair
+// (68 B for 30-bit Morton keys) against 80 B for the histogram/scan/scatter-per-pass design it replaces.
 constexpr int RS_ITEMS = 16;
-constexpr int RS_TILE = RS_THREADS * RS_ITEMS;  // 4096 keys per block
-constexpr int RS_WARPS = RS_THREADS / 32;
-constexpr int RS_WARP_KEYS = RS_TILE / RS_WARPS;  // 512 consecutive keys per warp
+constexpr int RS_WARP_KEYS = RS_ITEMS * 32;  // 512 consecutive keys per warp
+constexpr uint32_t RS_FLAG_AGG = 1u << 30, RS_FLAG_INC = 2u << 30, RS_VAL_MASK = (1u << 30) - 1u;
+constexpr int RS_MAX_PASSES = 4;
 
-// hist[digit * nblocks + block] = number of keys of `digit` in the block's tile
-__global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const uint32_t* __restrict__ keys, size_t n, int shift,
-                                                             uint32_t mask, uint32_t* __restrict__ hist, int nblocks) {
-  __shared__ uint32_t sh[256];
-  sh[threadIdx.x] = 0;
+// hist[p][d] += number of keys whose pass-p digit is d
+__global__ void __launch_bounds__(512) rs_hist_all_kernel(const uint32_t* __restrict__ keys, size_t n, int passes,
+                                                          int end_bit, uint32_t* __restrict__ hist) {
+  __shared__ uint32_t sh[RS_MAX_PASSES][256];
+  for (int k = threadIdx.x; k < RS_MAX_PASSES * 256; k += blockDim.x) (&sh[0][0])[k] = 0;
   __syncthreads();
-  const size_t base = (size_t)blockIdx.x * RS_TILE;
+  const uint32_t last_mask = (1u << (end_bit - 8 * (passes - 1))) - 1u;
+  const size_t n4 = n / 4;
+  const uint4* k4 = reinterpret_cast<const uint4*>(keys);
+  auto add = [&](uint32_t k) {
 #pragma unroll
-  for (int k = 0; k < RS_ITEMS; k++) {
-    const size_t i = base + (size_t)k * RS_THREADS + threadIdx.x;
-    if (i < n) atomicAdd(&sh[(keys[i] >> shift) & mask], 1u);
-  }
-  __syncthreads();
-  hist[(size_t)threadIdx.x * nblocks + blockIdx.x] = sh[threadIdx.x];
-}
-
-// one block per digit: exclusive scan of its row in place, row total to totals[digit]
-__global__ void __launch_bounds__(1024) rs_rowscan_kernel(uint32_t* __restrict__ hist, int nblocks,
-                                                          uint32_t* __restrict__ totals) {
-  __shared__ uint32_t wsum[32];
-  __shared__ uint32_t carry_s;
-  uint32_t* row = hist + (size_t)blockIdx.x * nblocks;
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  if (threadIdx.x == 0) carry_s = 0;
-  __syncthreads();
-  for (int b0 = 0; b0 < nblocks; b0 += 1024) {
-    const int i = b0 + threadIdx.x;
-    const uint32_t v = i < nblocks ? row[i] : 0u;
-    uint32_t x = v;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
-      if (lane >= o) x += y;
-    }
-    if (lane == 31) wsum[w] = x;
-    __syncthreads();
-    if (w == 0) {
-      uint32_t s = wsum[lane];
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t y = __shfl_up_sync(0xffffffffu, s, o);
-        if (lane >= o) s += y;
+    for (int p = 0; p < RS_MAX_PASSES; p++) {
+      if (p < passes) {
+        uint32_t d = (k >> (8 * p)) & 0xffu;
+        if (p == passes - 1) d &= last_mask;
+        atomicAdd(&sh[p][d], 1u);
       }
-      wsum[lane] = s;  // inclusive over warps
     }
-    __syncthreads();
-    const uint32_t carry = carry_s;
-    const uint32_t excl = carry + (w ? wsum[w - 1] : 0u) + x - v;
-    if (i < nblocks) row[i] = excl;
-    __syncthreads();
-    if (threadIdx.x == 1023) carry_s = carry + wsum[31];
-    __syncthreads();
+  };
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+    const uint4 v = k4[i];
+    add(v.x); add(v.y); add(v.z); add(v.w);
   }
-  if (threadIdx.x == 0) totals[blockIdx.x] = carry_s;
+  if (blockIdx.x == 0 && threadIdx.x < (int)(n - n4 * 4)) add(keys[n4 * 4 + threadIdx.x]);
+  __syncthreads();
+  for (int k = threadIdx.x; k < passes * 256; k += blockDim.x) {
+    const uint32_t c = (&sh[0][0])[k];
+    if (c) atomicAdd(&hist[k], c);
+  }
 }
 
-// stable scatter: warp w of a block owns 512 consecutive keys and ranks them 32 at a time with
-// __match_any_sync; ranks are made block-wide by a scan over the per-warp digit counts.
-__global__ void __launch_bounds__(RS_THREADS) rs_scatter_kernel(const uint32_t* __restrict__ keys_in,
-                                                                const int32_t* __restrict__ vals_in,
-                                                                uint32_t* __restrict__ keys_out,
-                                                                int32_t* __restrict__ vals_out, size_t n, int shift,
-                                                                uint32_t mask, const uint32_t* __restrict__ hist,
-                                                                const uint32_t* __restrict__ totals, int nblocks) {
-  __shared__ uint32_t cnt[RS_WARPS][256];
-  __shared__ uint32_t base[256];
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  for (int k = threadIdx.x; k < RS_WARPS * 256; k += RS_THREADS) (&cnt[0][0])[k] = 0;
-  // digit base = exclusive scan of the 256 totals (+ this block's offset inside the digit)
-  {
-    const uint32_t v = totals[threadIdx.x];
-    uint32_t x = v;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
-      if (lane >= o) x += y;
-    }
-    __shared__ uint32_t ws[8];
-    if (lane == 31) ws[w] = x;
-    __syncthreads();
-    uint32_t pre = 0;
-    for (int k = 0; k < w; k++) pre += ws[k];
-    base[threadIdx.x] = pre + x - v + hist[(size_t)threadIdx.x * nblocks + blockIdx.x];
-  }
-  __syncthreads();
+__device__ __forceinline__ uint32_t ld_status(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_status(uint32_t* p, uint32_t v) {
+  asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 
-  const size_t wbase = (size_t)blockIdx.x * RS_TILE + (size_t)w * RS_WARP_KEYS;
+// one pass.  status: tiles x 256 words, zeroed; ticket: zeroed; hist: this pass's 256 global digit counts
+template <int WARPS, bool MATCH>
+__global__ void __launch_bounds__(WARPS * 32, 1024 / (WARPS * 32)) rs_onesweep_kernel(const uint32_t* __restrict__ keys_in,
+                                                                 const int32_t* __restrict__ vals_in,
+                                                                 uint32_t* __restrict__ keys_out,
+                                                                 int32_t* __restrict__ vals_out, size_t n, int shift,
+                                                                 uint32_t mask, const uint32_t* __restrict__ hist,
+                                                                 uint32_t* __restrict__ status,
+                                                                 uint32_t* __restrict__ ticket) {
+  constexpr int THREADS = WARPS * 32;
+  constexpr int TILE = WARPS * RS_WARP_KEYS;
+  __shared__ uint32_t cnt[WARPS][256];  // per-warp digit counts, then exclusive offsets across warps
+  __shared__ uint32_t lstart[256];      // first slot of the digit inside the tile's digit-ordered buffer
+  __shared__ uint32_t gbase[256];       // global position of the tile's first key of the digit
+  extern __shared__ __align__(16) uint32_t rs_buf[];  // keys then values of the tile in digit order
+  uint32_t* buf_k = rs_buf;
+  uint32_t* buf_v = rs_buf + TILE;
+  __shared__ uint32_t wsum[8];
+  __shared__ uint32_t tile_s;
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  if (tid == 0) tile_s = atomicAdd(ticket, 1u);
+  for (int k = tid; k < WARPS * 256; k += THREADS) (&cnt[0][0])[k] = 0;
+  __syncthreads();
+  const uint32_t tile = tile_s;
+  const size_t tbase = (size_t)tile * TILE;
+  const uint32_t tcount = (uint32_t)((n - tbase) < (size_t)TILE ? (n - tbase) : (size_t)TILE);
+
+  // ---- load + rank inside the warp's 512 consecutive keys -----------------------------------------
+  // peers = lanes holding the same digit, from 8 independent ballots (pipelined over the 16 keys; the
+  // MATCH instruction serialises over the distinct values in the warp).  The lowest peer adds the
+  // group's size to the warp's digit counter with one shared-memory atomic -- a warp's atomics retire in
+  // issue order, so key k sees the counts of keys < k without any warp synchronisation -- and hands the
+  // old value to its peers by shuffle.
+  const size_t wbase = tbase + (size_t)w * RS_WARP_KEYS;
   uint32_t key[RS_ITEMS];
-  int32_t val[RS_ITEMS];
-  uint32_t rank[RS_ITEMS];
+  uint32_t pos[RS_ITEMS];  // rank among the warp's keys of the same digit
   const uint32_t lt = (1u << lane) - 1u;
 #pragma unroll
   for (int k = 0; k < RS_ITEMS; k++) {
     const size_t i = wbase + (size_t)k * 32 + lane;
-    const bool ok = i < n;
-    key[k] = ok ? keys_in[i] : 0xffffffffu;
-    val[k] = ok ? vals_in[i] : 0;
+    key[k] = (i < n) ? keys_in[i] : 0xffffffffu;
+  }
+  const uint32_t full_valid = (wbase + RS_WARP_KEYS <= n) ? 1u : 0u;
+#pragma unroll
+  for (int k = 0; k < RS_ITEMS; k++) {
+    const size_t i = wbase + (size_t)k * 32 + lane;
+    const bool ok = full_valid || (i < n);
     const uint32_t dgt = (key[k] >> shift) & mask;
-    const uint32_t peers = __match_any_sync(0xffffffffu, dgt);
-    const uint32_t before = cnt[w][dgt];
-    rank[k] = before + __popc(peers & lt);
-    __syncwarp();
-    if ((peers & lt) == 0) cnt[w][dgt] = before + __popc(peers);  // lowest peer lane updates the count
-    __syncwarp();
+    uint32_t peers;
+    if (MATCH) {
+      peers = __match_any_sync(0xffffffffu, ok ? dgt : 0x100u);  // padding forms its own group
+    } else {
+      peers = __ballot_sync(0xffffffffu, ok);  // padding lanes are nobody's peer
+#pragma unroll
+      for (int b = 0; b < 8; b++) {
+        if ((mask >> b) & 1u) {  // warp-uniform: a 6-bit last pass needs 6 ballots
+          const uint32_t v = __ballot_sync(0xffffffffu, (dgt >> b) & 1u);
+          peers &= ((dgt >> b) & 1u) ? v : ~v;
+        }
+      }
+    }
+    const int leader = __ffs(peers) - 1;
+    uint32_t before = 0;
+    if (ok && lane == leader) before = atomicAdd(&cnt[w][dgt], (uint32_t)__popc(peers));
+    before = __shfl_sync(0xffffffffu, before, leader < 0 ? 0 : leader);
+    pos[k] = before + __popc(peers & lt);
   }
   __syncthreads();
-  // per digit: turn per-warp counts into exclusive offsets across warps
-  {
-    uint32_t run = 0;
+
+  // ---- per digit: offsets across warps, tile count; publish, look back -----------------------------
+  uint32_t my_total = 0;
+  if (tid < 256) {
 #pragma unroll
-    for (int k = 0; k < RS_WARPS; k++) {
-      const uint32_t c = cnt[k][threadIdx.x];
-      cnt[k][threadIdx.x] = run;
-      run += c;
+    for (int k = 0; k < WARPS; k++) {
+      const uint32_t c = cnt[k][tid];
+      cnt[k][tid] = my_total;
+      my_total += c;
+    }
+    uint32_t* mine = status + (size_t)tile * 256 + tid;
+    if (tile == 0) st_status(mine, RS_FLAG_INC | my_total);
+    else st_status(mine, RS_FLAG_AGG | my_total);
+  }
+  // exclusive scan of the 256 tile counts (slot of each digit in buf) and of the global histogram
+  {
+    uint32_t x = (tid < 256) ? my_total : 0u, g = (tid < 256) ? hist[tid] : 0u;
+    const uint32_t x0 = x, g0 = g;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t y = __shfl_up_sync(0xffffffffu, x, o), h = __shfl_up_sync(0xffffffffu, g, o);
+      if (lane >= o) { x += y; g += h; }
+    }
+    __shared__ uint32_t gsum[8];
+    if (tid < 256 && lane == 31) { wsum[w] = x; gsum[w] = g; }
+    __syncthreads();
+    if (tid < 256) {
+      uint32_t px = 0, pg = 0;
+      for (int k = 0; k < w; k++) { px += wsum[k]; pg += gsum[k]; }
+      lstart[tid] = px + x - x0;
+      uint32_t excl = 0;  // keys of this digit in earlier tiles
+      if (tile > 0) {
+        const uint32_t* look = status + (size_t)(tile - 1) * 256 + tid;
+        for (;;) {
+          const uint32_t s = ld_status(look);
+          if (s & RS_FLAG_INC) { excl += s & RS_VAL_MASK; break; }
+          if (s & RS_FLAG_AGG) { excl += s & RS_VAL_MASK; look -= 256; }
+        }
+        st_status(status + (size_t)tile * 256 + tid, RS_FLAG_INC | (excl + my_total));
+      }
+      gbase[tid] = pg + g - g0 + excl;
+    }
+  }
+  __syncthreads();
+
+  // ---- registers -> buf (digit order) -> global (runs of consecutive addresses) ---------------------------
+#pragma unroll
+  for (int k = 0; k < RS_ITEMS; k++) {
+    const size_t i = wbase + (size_t)k * 32 + lane;
+    const uint32_t dgt = (key[k] >> shift) & mask;
+    if (i < n) {
+      const uint32_t slot = lstart[dgt] + cnt[w][dgt] + pos[k];
+      buf_k[slot] = key[k];
+      buf_v[slot] = (uint32_t)vals_in[i];
     }
   }
   __syncthreads();
 #pragma unroll
   for (int k = 0; k < RS_ITEMS; k++) {
-    const size_t i = wbase + (size_t)k * 32 + lane;
-    if (i < n) {
-      const uint32_t dgt = (key[k] >> shift) & mask;
-      const size_t pos = (size_t)base[dgt] + cnt[w][dgt] + rank[k];
-      keys_out[pos] = key[k];
-      vals_out[pos] = val[k];
+    const uint32_t p = (uint32_t)k * THREADS + tid;
+    if (p < tcount) {
+      const uint32_t kk = buf_k[p];
+      const uint32_t dgt = (kk >> shift) & mask;
+      const uint32_t g = gbase[dgt] + (p - lstart[dgt]);
+      keys_out[g] = kk;
+      vals_out[g] = (int32_t)buf_v[p];
     }
   }
 }
@@ -233,28 +290,63 @@ int sort_pairs(nb_context* ctx, uint32_t* d_keys, int32_t* d_vals, size_t n, int
   if (n < 2) return NB_OK;
   if (end_bit < 1) end_bit = 1;
   if (end_bit > 32) end_bit = 32;
-  if (n > 0xfffffff0ull) {
+  if (n > (size_t)RS_VAL_MASK) {
     set_error("sort: too many elements");
     return NB_ERR_INVALID;
   }
+  static bool attr_set = false;
+  if (!attr_set) {
+    NB_CUDA(cudaFuncSetAttribute(rs_onesweep_kernel<8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * RS_WARP_KEYS * 8));
+    NB_CUDA(cudaFuncSetAttribute(rs_onesweep_kernel<16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16 * RS_WARP_KEYS * 8));
+    NB_CUDA(cudaFuncSetAttribute(rs_onesweep_kernel<8, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * RS_WARP_KEYS * 8));
+    NB_CUDA(cudaFuncSetAttribute(rs_onesweep_kernel<16, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16 * RS_WARP_KEYS * 8));
+    attr_set = true;
+  }
+  const char* e = getenv("NB_SORT_WARPS");  // tuning knob: 8 (4096-key tiles) or 16 (8192-key tiles)
+  const int warps_cfg = (e && atoi(e) == 8) ? 8 : 16;
+  const char* me = getenv("NB_SORT_MATCH");  // tuning knob: 1 = MATCH.ANY instruction, 0 = eight ballots
+  const bool use_match = me && atoi(me) == 1;
+  const int warps = warps_cfg;
+  const int tile = warps * RS_WARP_KEYS;
+  const size_t smem = (size_t)tile * 8;
   const int passes = (end_bit + 7) / 8;
-  const int nblocks = (int)((n + RS_TILE - 1) / RS_TILE);
+  const size_t ntiles = (n + tile - 1) / tile;
   if (int rc = ctx->sort_keys2.ensure(n * sizeof(uint32_t))) return rc;
   if (int rc = ctx->sort_vals2.ensure(n * sizeof(int32_t))) return rc;
-  if (int rc = ctx->sort_hist.ensure(((size_t)nblocks * 256 + 256) * sizeof(uint32_t))) return rc;
+  // scratch: [passes][256] histograms, [passes] tickets (padded to 64 words), [passes][ntiles][256] status
+  const size_t head = (size_t)RS_MAX_PASSES * 256 + 64;
+  const size_t words = head + (size_t)passes * ntiles * 256;
+  if (int rc = ctx->sort_hist.ensure(words * sizeof(uint32_t))) return rc;
   uint32_t* hist = ctx->sort_hist.as<uint32_t>();
-  uint32_t* totals = hist + (size_t)nblocks * 256;
+  uint32_t* ticket = hist + RS_MAX_PASSES * 256;
+  uint32_t* status = hist + head;
+  NB_CUDA(cudaMemsetAsync(hist, 0, words * sizeof(uint32_t), st));
+  {
+    size_t g = (n / 4 + 511) / 512;
+    const size_t cap = (size_t)ctx->sm_count * 4;
+    if (g > cap) g = cap;
+    if (g < 1) g = 1;
+    rs_hist_all_kernel<<<(unsigned)g, 512, 0, st>>>(d_keys, n, passes, end_bit, hist);
+    NB_LAUNCH_CHECK(ctx);
+  }
   uint32_t *ka = d_keys, *kb = ctx->sort_keys2.as<uint32_t>();
   int32_t *va = d_vals, *vb = ctx->sort_vals2.as<int32_t>();
   for (int p = 0; p < passes; p++) {
     const int shift = p * 8;
     const int bits = (end_bit - shift) < 8 ? (end_bit - shift) : 8;
     const uint32_t mask = (1u << bits) - 1u;
-    rs_hist_kernel<<<nblocks, RS_THREADS, 0, st>>>(ka, n, shift, mask, hist, nblocks);
-    NB_LAUNCH_CHECK(ctx);
-    rs_rowscan_kernel<<<256, 1024, 0, st>>>(hist, nblocks, totals);
-    NB_LAUNCH_CHECK(ctx);
-    rs_scatter_kernel<<<nblocks, RS_THREADS, 0, st>>>(ka, va, kb, vb, n, shift, mask, hist, totals, nblocks);
+    uint32_t* stp = status + (size_t)p * ntiles * 256;
+#define NB_RS_LAUNCH(W_, M_)                                                                                   \
+  rs_onesweep_kernel<W_, M_><<<(unsigned)ntiles, W_ * 32, smem, st>>>(ka, va, kb, vb, n, shift, mask, hist + p * 256, \
+                                                                      stp, ticket + p)
+    if (warps == 8) {
+      if (use_match) NB_RS_LAUNCH(8, true);
+      else NB_RS_LAUNCH(8, false);
+    } else {
+      if (use_match) NB_RS_LAUNCH(16, true);
+      else NB_RS_LAUNCH(16, false);
+    }
+#undef NB_RS_LAUNCH
     NB_LAUNCH_CHECK(ctx);
     uint32_t* tk = ka; ka = kb; kb = tk;
     int32_t* tv = va; va = vb; vb = tv;

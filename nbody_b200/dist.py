@@ -1,19 +1,30 @@
 """Target-sharded direct N^2 across the GPUs of one node: one process per GPU, torch.distributed
-for the plumbing (NCCL all-gather of packed positions over NVLink/NVSwitch), our kernels for the
-work.  The reference is single-GPU; this is new capability named by
-BASELINE.json's north_star.
+for the plumbing, our kernels for the work.  The reference is single-GPU; this
+is new capability named by BASELINE.json's north_star.
 
-Per step on rank r (targets [r*N/R, (r+1)*N/R), all N sources):
-  1. pack: store-acc + drift of the local slice, written as float4 {x,y,z,G*m} into this rank's
-     slot of the replicated source buffer                               (nb_mgpu_pack_local)
-  2. all-gather of the slots, asynchronous on NCCL's stream             (torch.distributed)
-  3. force pass over the LOCAL source slot -- overlaps the gather       (nb_mgpu_forces_local)
-  4. wait for the gather; force pass over the other R-1 slots           (nb_mgpu_forces_remote)
-  5. fixed-order reduction of the stream-K partials + kick              (nb_mgpu_finish)
+Rank r owns targets [r*N/R, (r+1)*N/R) and needs all N sources every step.  Two exchanges:
+
+exchange="peer" (default): the all-gather is fused into our own kernels over NVLink peer memory.
+  Setup: every rank allocates an exchange block, the CUDA-IPC handles travel once through
+  torch.distributed (all_gather_object), every rank maps the others' blocks.  Per step, 3 launches:
+  1. pack_push: store-acc + drift of the local slice, each packed float4 {x,y,z,G*m} stored into
+     ALL R replicated source buffers (local + R-1 peers), then this rank's step flag raised on
+     every peer                                                          (nb_mgpu_peer_step)
+  2. one force launch over all N sources, local slice first, ring order after; the TMA producer
+     thread waits for a peer's flag when it reaches that peer's tiles
+  3. fixed-order reduction of the stream-K partials + kick
+
+exchange="nccl": the baseline the peer path is measured against.
+  1. pack into this rank's slot                                          (nb_mgpu_pack_local)
+  2. all_gather_into_tensor of the slots, asynchronous on NCCL's stream  (torch.distributed)
+  3. force pass over the LOCAL slot -- overlaps the gather               (nb_mgpu_forces_local)
+  4. wait for the gather; force pass over the other R-1 slots            (nb_mgpu_forces_remote)
+  5. reduction + kick                                                    (nb_mgpu_finish)
 """
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -54,7 +65,7 @@ class ShardedDirectSystem:
     """ParticleSystem-like driver for one rank of a target-sharded direct-N^2 run."""
 
     def __init__(self, state_local: dict, n_total: int, rank: int, world: int, G: float = 1.0,
-                 softening: float = 0.01, group=None):
+                 softening: float = 0.01, group=None, exchange: str | None = None):
         import torch
         from . import _lib
         from .api import ParticleData, ParticleDataManager, get_context
@@ -76,15 +87,49 @@ class ShardedDirectSystem:
         self.d = ParticleData()
         ParticleDataManager.allocateDevice(self.d, self.count)
         ParticleDataManager.copyToDevice(self.d, self.h)
-        self.gathered = torch.zeros(world * self.padded * 4, dtype=torch.float32, device="cuda")
+        self.exchange = exchange or os.environ.get("NB_MGPU_EXCHANGE", "peer")
+        if self.exchange not in ("peer", "nccl"):
+            raise ValueError("exchange must be 'peer' or 'nccl'")
+        self.gathered = None
+        if self.exchange == "peer":
+            self._setup_peer()
+        else:
+            self.gathered = torch.zeros(world * self.padded * 4, dtype=torch.float32, device="cuda")
         self.simulation_time = 0.0
+
+    def _setup_peer(self):
+        """Collective: allocate the exchange block, swap CUDA-IPC handles, map the peers' blocks."""
+        handle = (C.c_ubyte * 64)()
+        self.check(self.L.nb_mgpu_peer_alloc(self.ctx.handle, handle))
+        if self.world == 1:
+            return
+        import torch.distributed as dist
+        handles = [None] * self.world
+        dist.all_gather_object(handles, bytes(handle), group=self.group)
+        for r, h in enumerate(handles):
+            if r != self.rank:
+                buf = (C.c_ubyte * 64).from_buffer_copy(h)
+                self.check(self.L.nb_mgpu_peer_open(self.ctx.handle, r, buf))
+        dist.barrier(group=self.group)  # nobody pushes before everybody has mapped and zeroed
+
+    def close(self):
+        if self.exchange == "peer":
+            self.torch.cuda.synchronize()
+            if self.world > 1:
+                import torch.distributed as dist
+                dist.barrier(group=self.group)  # peers may still be reading our block
+            self.check(self.L.nb_mgpu_peer_close(self.ctx.handle))
 
     def _stream(self):
         return C.c_void_p(self.torch.cuda.current_stream().cuda_stream)
 
     def _evaluate(self, dt: float, step: bool):
-        L, ctx, gp = self.L, self.ctx.handle, C.c_void_p(self.gathered.data_ptr())
+        L, ctx = self.L, self.ctx.handle
         s = self._stream()
+        if self.exchange == "peer":
+            self.check(L.nb_mgpu_peer_step(ctx, C.byref(self.d.c), dt, self.G, self.eps2, 1 if step else 0, s))
+            return
+        gp = C.c_void_p(self.gathered.data_ptr())
         self.check(L.nb_mgpu_pack_local(ctx, C.byref(self.d.c), gp, dt, self.G, 1 if step else 0, s))
         work = None
         if self.world > 1:

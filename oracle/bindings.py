@@ -96,7 +96,7 @@ def lib():
     L.orc_lbvh_com.argtypes = [i, i32p, i32p, f32p, f32p, f32p, f32p, f32p]
     L.orc_lbvh_cell_size.argtypes = [i, f32p]
     L.orc_lbvh_cell_size.restype = f
-    L.orc_lbvh_forces.argtypes = [i, i32p, i32p, i32p, i32p, i32p, f32p, f32p, f32p, f32p, f32p, f, f, f, i,
+    L.orc_lbvh_forces.argtypes = [i, i32p, i32p, i32p, i32p, i32p, f32p, f32p, f32p, f32p, f32p, f, f, f, i, i,
                                   f32p, f32p, f32p, C.POINTER(C.c_uint64)]
     L.orc_cell_index.argtypes = [f, f, f, f, i32p]
     L.orc_grid_dims.argtypes = [f32p, f, i32p]
@@ -260,13 +260,14 @@ def lbvh_cell_size(L, bb):
     return lib().orc_lbvh_cell_size(int(L), _f32(bb))
 
 
-def lbvh_forces(tree, com, sx, sy, sz, bb, theta, G, eps, group=32):
+def lbvh_forces(tree, com, sx, sy, sz, bb, theta, G, eps, group=32, super_=None):
     n = sx.size
     ax, ay, az = (np.zeros(n, np.float32) for _ in range(3))
     cnt = C.c_uint64(0)
     lib().orc_lbvh_forces(n, tree["left"], tree["right"], tree["prefix"], tree["first"], tree["last"],
                           np.ascontiguousarray(com).reshape(-1),
-                          _f32(sx), _f32(sy), _f32(sz), _f32(bb), theta, G, eps, group, ax, ay, az, C.byref(cnt))
+                          _f32(sx), _f32(sy), _f32(sz), _f32(bb), theta, G, eps, group,
+                          8 * group if super_ is None else super_, ax, ay, az, C.byref(cnt))
     return ax, ay, az, cnt.value
 
 

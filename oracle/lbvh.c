@@ -118,10 +118,13 @@ float orc_lbvh_cell_size(int L, const float bbox[6]) {
 void orc_lbvh_forces(int n, const int32_t* left, const int32_t* right, const int32_t* prefix,
                      const int32_t* range_first, const int32_t* range_last, const float* node_com,
                      const float* sx, const float* sy, const float* sz, const float bbox[6], float theta, float G,
-                     float eps, int group, float* ax, float* ay, float* az, uint64_t* interactions) {
-  /* Sequential restatement of nbody_b200/csrc/bh.cu: bh_groups_kernel + bh_force_kernel.  Traversal
-   * groups are the maximal subtrees with at most `group` (32 or 64) leaves (a lone leaf whose
-   * parent is larger is a group of one).  A group (one warp) owns a stack of node indices.  Each round pops the top
+                     float eps, int group, int super, float* ax, float* ay, float* az, uint64_t* interactions) {
+  /* Sequential restatement of nbody_b200/csrc/bh.cu: bh_groups_kernel + bh_force_kernel.  A
+   * supergroup is a maximal subtree with at most `super` (>= group) leaves (a lone leaf whose parent
+   * is larger is a supergroup of one); its c bodies are cut into ceil(c / group) runs of consecutive
+   * bodies, run i starting at floor(i * c / runs): those runs are the traversal groups (with
+   * super == group they are the subtrees themselves).
+   * A group (one warp) owns a stack of node indices.  Each round pops the top
    * min(32, size) entries (one per lane, bottom-to-top = lane 0..m-1).  A node is used for the whole
    * group iff it is a leaf or size^2 < theta^2 * (dmin^2 + eps^2), dmin = distance from the node's
    * centre of mass to the group's bounding box (<= every body's own distance, so every body of the
@@ -133,6 +136,7 @@ void orc_lbvh_forces(int n, const int32_t* left, const int32_t* right, const int
    * contributes nothing; with eps > 0 the own leaf contributes exactly +0. */
   const float theta2 = theta * theta, eps2 = eps * eps;
   const int leaf0 = n - 1;
+  if (super < group) super = group;
   float size2_of[32];
   for (int L = 0; L <= 30; L++) {
     float s = orc_lbvh_cell_size(L, bbox);
@@ -153,9 +157,14 @@ void orc_lbvh_forces(int n, const int32_t* left, const int32_t* right, const int
       if (ni >= leaf0) {
         gfirst[ngroups] = ni - leaf0;
         gcount[ngroups++] = 1;
-      } else if (range_last[ni] - range_first[ni] + 1 <= group) {
-        gfirst[ngroups] = range_first[ni];
-        gcount[ngroups++] = range_last[ni] - range_first[ni] + 1;
+      } else if (range_last[ni] - range_first[ni] + 1 <= super) {
+        const int first = range_first[ni], c = range_last[ni] - range_first[ni] + 1;
+        const int runs = (c + group - 1) / group;
+        for (int i = 0; i < runs; i++) {
+          const int b0 = (int)(((long long)i * c) / runs), b1 = (int)(((long long)(i + 1) * c) / runs);
+          gfirst[ngroups] = first + b0;
+          gcount[ngroups++] = b1 - b0;
+        }
       } else {
         st[sp++] = right[ni];
         st[sp++] = left[ni];

@@ -117,8 +117,8 @@ float orc_lbvh_cell_size(int prefix_len, const float bbox[6]);
  * force evaluations. */
 void orc_lbvh_forces(int n, const int32_t* left, const int32_t* right, const int32_t* prefix,
                      const int32_t* range_first, const int32_t* range_last, const float* node_com, const float* sx, const float* sy, const float* sz,
-                     const float bbox[6], float theta, float G, float eps, int group, float* ax, float* ay,
-                     float* az, uint64_t* interactions);
+                     const float bbox[6], float theta, float G, float eps, int group, int super, float* ax,
+                     float* ay, float* az, uint64_t* interactions);
 
 /* ---- spatial hash -------------------------------------------------------------------- */
 /* src/cuda/force_spatial_hash.cu:14-17 */

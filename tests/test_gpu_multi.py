@@ -1,0 +1,22 @@
+"""Multi-GPU (>= 2 B200s on the box; skipped on a 1-GPU box): the peer-memory exchange under real
+concurrency, launched with torchrun like bench.py."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_peer_exchange_two_ranks():
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29617",
+                        os.path.join(ROOT, "tests", "mgpu", "peer_check.py"), "100003"],
+                       capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    assert "peer_check ok" in r.stdout

@@ -19,10 +19,12 @@ def _device_data(state):
     return d
 
 
-@pytest.mark.parametrize("n,bits", [(1, 32), (2, 32), (33, 8), (4096, 32), (4097, 30), (100003, 30), (1 << 20, 21),
-                                    (3000017, 32)])
-def test_radix_sort_stable_bit_exact(orc, n, bits):
+@pytest.mark.parametrize("warps", [16, 8])
+@pytest.mark.parametrize("n,bits", [(1, 32), (2, 32), (33, 8), (4096, 32), (4097, 30), (8191, 32), (8192, 30), (8193, 13),
+                                    (16385, 1), (100003, 30), (1 << 20, 21), (3000017, 32)])
+def test_radix_sort_stable_bit_exact(orc, n, bits, warps, monkeypatch):
     import torch
+    monkeypatch.setenv("NB_SORT_WARPS", str(warps))  # both tile shapes of the onesweep kernel
     import nbody_b200 as nb
     from nbody_b200 import _lib
     rng = np.random.default_rng(n)
@@ -31,6 +33,8 @@ def test_radix_sort_stable_bit_exact(orc, n, bits):
     keys = rng.integers(0, min(hi, max(n // 3, 1)) + 1, n, dtype=np.uint64).astype(np.uint32)
     if bits == 32 and n > 100:
         keys[::7] = rng.integers(0, 1 << 32, keys[::7].size, dtype=np.uint64).astype(np.uint32)
+    if n == 8192:
+        keys[:] = 0x2AAAAAAA  # one digit bin per pass holds the whole tile
     vals = np.arange(n, dtype=np.int32)
     dk = torch.from_numpy(keys.view(np.int32)).cuda()
     dv = torch.from_numpy(vals).cuda()
@@ -101,13 +105,18 @@ def test_morton_sort_lbvh_bit_exact(orc, n, kind):
         assert abs(t["node_com"][0, 3] - st["mass"].sum(dtype=np.float64)) <= 1e-3 * st["mass"].sum()
 
 
-@pytest.mark.parametrize("group", [64, 32])
+@pytest.mark.parametrize("group,sup", [(64, None), (32, None), (64, 64), (32, 100)])
 @pytest.mark.parametrize("n,theta", [(1, 0.5), (2, 0.5), (30, 0.1), (1000, 0.5), (20000, 0.5), (20000, 0.8),
                                      (100000, 0.5)])
-def test_bh_forces_vs_lbvh_oracle(orc, n, theta, group, monkeypatch):
-    """Same tree, same traversal groups, same operation order: only rsqrt differs (<= 1e-5)."""
+def test_bh_forces_vs_lbvh_oracle(orc, n, theta, group, sup, monkeypatch):
+    """Same tree, same traversal groups, same operation order: only rsqrt differs (<= 1e-5).
+    sup = leaves of the subtrees the groups are cut from (default 8 x group; == group: the subtrees)."""
     from nbody_b200 import ics
     monkeypatch.setenv("NB_BH_GROUP", str(group))
+    if sup is None:
+        monkeypatch.delenv("NB_BH_SUPER", raising=False)
+    else:
+        monkeypatch.setenv("NB_BH_SUPER", str(sup))
     st = ics.plummer(n, seed=8) if n > 3 else ics.uniform_box(n, -1, 1, seed=8)
     d, calc = _build(st, theta)
     out = d.numpy()
@@ -116,7 +125,7 @@ def test_bh_forces_vs_lbvh_oracle(orc, n, theta, group, monkeypatch):
     sx, sy, sz = (st[k][sp] for k in ("pos_x", "pos_y", "pos_z"))
     tree = orc.lbvh_build(t["keys"]) if n > 1 else dict(left=t["left"], right=t["right"], prefix=t["prefix"],
                                                         first=np.zeros(1, np.int32), last=np.zeros(1, np.int32))
-    ax, ay, az, inter = orc.lbvh_forces(tree, t["node_com"], sx, sy, sz, t["bbox"], theta, 1.0, 0.01, group)
+    ax, ay, az, inter = orc.lbvh_forces(tree, t["node_com"], sx, sy, sz, t["bbox"], theta, 1.0, 0.01, group, sup)
     got = (out["acc_x"][sp], out["acc_y"][sp], out["acc_z"][sp])
     if n == 1:
         assert got[0][0] == 0

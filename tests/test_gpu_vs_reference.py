@@ -187,3 +187,66 @@ def test_sharded_path_emulated_on_one_gpu(orc, n, world):
         e = rel_err((o["acc_x"], o["acc_y"], o["acc_z"]),
                     (so["acc_x"][b:b + c], so["acc_y"][b:b + c], so["acc_z"][b:b + c]))
         assert e.max() < 2e-6, e.max()   # same kernel, different partial-sum split
+
+
+@pytest.mark.parametrize("n,world", [(5000, 2), (40000, 4), (100000, 8), (33000, 3)])
+def test_peer_exchange_emulated_on_one_gpu(orc, n, world):
+    """The peer-memory exchange (pack_push + flag-gated force kernel) with every rank as its own
+    context on ONE GPU, mapped to each other by raw pointer: all ranks push, then all ranks run
+    their gated force pass.  Two Verlet steps (both buffer parities) = the single-GPU fused step."""
+    import torch
+    import nbody_b200 as nb
+    from nbody_b200 import _lib, ics
+    from nbody_b200.api import Context
+    from nbody_b200.dist import shard_layout, slice_state
+    L = _lib.lib()
+    st = ics.plummer(n, seed=32)
+    dt, G, eps2 = float(np.float32(1e-3)), 1.0, float(np.float32(0.01) ** 2)
+    single = _device_data(st)
+    ctx0 = nb.get_context()
+    _lib.check(L.nb_direct_forces(ctx0.handle, C.byref(single.c), G, eps2, None))
+    ctxs, parts, blocks = [], [], []
+    for r in range(world):
+        b, c, p = shard_layout(n, r, world)
+        cx = Context(0)
+        _lib.check(L.nb_mgpu_layout(cx.handle, n, r, world, None, None, None, None))
+        h = (C.c_ubyte * 64)()
+        _lib.check(L.nb_mgpu_peer_alloc(cx.handle, h))
+        blk, nbytes = C.c_void_p(), C.c_size_t()
+        _lib.check(L.nb_mgpu_peer_block(cx.handle, C.byref(blk), C.byref(nbytes)))
+        assert nbytes.value == 4096 + 2 * world * p * 16
+        ctxs.append(cx); blocks.append(blk); parts.append((b, c, _device_data(slice_state(st, b, c))))
+    for r, cx in enumerate(ctxs):
+        for q in range(world):
+            if q != r:
+                _lib.check(L.nb_mgpu_peer_map(cx.handle, q, blocks[q]))
+
+    def evaluate(step):
+        for cx, (b, c, d) in zip(ctxs, parts):
+            _lib.check(L.nb_mgpu_peer_push(cx.handle, C.byref(d.c), dt, G, step, None))
+        for cx, (b, c, d) in zip(ctxs, parts):
+            _lib.check(L.nb_mgpu_peer_forces(cx.handle, C.byref(d.c), dt, eps2, step, None))
+
+    evaluate(0)  # a(0)
+    torch.cuda.synchronize()
+    so = single.numpy()
+    for b, c, d in parts:
+        o = d.numpy()
+        e = rel_err((o["acc_x"], o["acc_y"], o["acc_z"]),
+                    (so["acc_x"][b:b + c], so["acc_y"][b:b + c], so["acc_z"][b:b + c]))
+        assert e.max() < 5e-6, e.max()   # same kernel, different source order and partial-sum split
+    for _ in range(2):
+        _lib.check(L.nb_step_direct(ctx0.handle, C.byref(single.c), dt, G, eps2, None))
+        evaluate(1)
+    torch.cuda.synchronize()
+    so = single.numpy()
+    for b, c, d in parts:
+        o = d.numpy()
+        for k in ("pos_x", "pos_y", "pos_z", "acc_old_x"):
+            assert np.allclose(o[k], so[k][b:b + c], rtol=0, atol=1e-6 * max(1.0, float(np.abs(so[k]).max())))
+        e = rel_err((o["vel_x"], o["vel_y"], o["vel_z"]),
+                    (so["vel_x"][b:b + c], so["vel_y"][b:b + c], so["vel_z"][b:b + c]))
+        assert e.max() < 1e-5
+    for cx in ctxs:
+        _lib.check(L.nb_mgpu_peer_close(cx.handle))
+        cx.close()

@@ -45,9 +45,36 @@ def main():
         _lib.check(L.nb_bh_forces(ctx.handle, C.byref(d.c), 0.5, 1.0, 0.01, s))
         inter, cnt = C.c_uint64(0), C.c_int(0)
         _lib.check(L.nb_bh_stats(ctx.handle, C.byref(inter), C.byref(cnt)))
-        print(json.dumps(dict(path="barnes_hut", n=n, ic=ic, theta=0.5, build_ms=build, force_ms=force,
+        deep, cap = C.c_int(0), C.c_int(0)
+        _lib.check(L.nb_bh_max_stack(ctx.handle, C.byref(deep), C.byref(cap)))
+        print(json.dumps(dict(path="barnes_hut", n=n, ic=ic, theta=0.5, group=os.environ.get("NB_BH_GROUP", "64"),
+                              stack_deepest=deep.value, stack_cap=cap.value,
+                              super=os.environ.get("NB_BH_SUPER", "default"), build_ms=build, force_ms=force,
                               step_ms=build + force, interactions=inter.value, per_body=inter.value / n,
                               g_interactions_per_s=inter.value / force / 1e6)))
+    elif kind == "sort":
+        # 30-bit keys in random order (what the Morton sort sees), restored before every repetition
+        bits = int(sys.argv[3]) if len(sys.argv) > 3 else 30
+        g = torch.Generator(device="cuda").manual_seed(42)
+        k0 = torch.randint(0, 1 << bits, (n,), device="cuda", dtype=torch.int64, generator=g).to(torch.int32)
+        v0 = torch.arange(n, device="cuda", dtype=torch.int32)
+        k, v = k0.clone(), v0.clone()
+        ms = []
+        for rep in range(7):
+            k.copy_(k0); v.copy_(v0)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            _lib.check(L.nb_sort_pairs(ctx.handle, k.data_ptr(), v.data_ptr(), n, bits, None))
+            e1.record()
+            torch.cuda.synchronize()
+            ms.append(e0.elapsed_time(e1))
+        best = min(ms[2:])
+        passes = (bits + 7) // 8
+        algo = (4 + 16 * passes) * n
+        assert bool((k[1:] >= k[:-1]).all())
+        print(json.dumps(dict(path="radix_sort_pairs", n=n, bits=bits, passes=passes, ms=best, ms_all=ms,
+                              warps=os.environ.get("NB_SORT_WARPS", "16"), algorithmic_bytes=algo,
+                              gbs=algo / best / 1e6, gkeys_per_s=n / best / 1e6)))
     else:
         side = (n / 8.0) ** (1.0 / 3.0)     # ~8 bodies per unit cell
         st = ics.uniform_box(n, 0.0, side, seed=42)
