@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libnbody_b200.so")
+LIB_PATH = os.environ.get("NB_LIB_PATH") or os.path.join(_HERE, "libnbody_b200.so")  # NB_LIB_PATH: A/B runs of an older build
 
 
 class CudaException(RuntimeError):
@@ -81,6 +81,7 @@ SYMBOLS = {
     "nb_sh_forces": (_i, [_vp, _pp, _f, _f, _f, _vp]),
     "nb_sh_export": (_i, [_vp] + [_vp] * 6),
     "nb_sh_total_cells": (_i, [_vp, C.POINTER(_i)]),
+    "nb_sh_stats": (_i, [_vp, C.POINTER(C.c_uint64)]),
     "nb_sort_pairs": (_i, [_vp, _vp, _vp, _sz, _i, _vp]),
     "nb_bounding_box": (_i, [_vp, _pp, _vp, _vp]),
     "nb_mgpu_layout": (_i, [_vp, _sz, _i, _i, C.POINTER(_sz), C.POINTER(_sz), C.POINTER(_sz), C.POINTER(_sz)]),

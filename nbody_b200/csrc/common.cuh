@@ -166,7 +166,7 @@ struct nb_context {
   nb::DevBuf partial;   // stream-K partial accelerations
   nb_pass pass[2];
   int n_pass = 0;
-  int direct_occ[4] = {0, 0, 0, 0};  // resident CTAs/SM per kernel config (lazy)
+  int direct_occ[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // resident CTAs/SM per kernel variant (lazy)
   // energy
   nb::DevBuf red;       // per-CTA fp64 partials
   double* h_red = nullptr;  // pinned

@@ -110,7 +110,7 @@ int launch_pack_push(nb_context* ctx, const nb_particles* d, const PeerBufs& pb,
 
 // spin (bounded) until peer `peer` has published `gate.step`; then order the async-proxy (TMA) reads
 // that follow after the acquire
-__device__ __forceinline__ void peer_wait(const PeerGate& gate, int peer) {
+__device__ __noinline__ void peer_wait(const PeerGate& gate, int peer) {  // cold: keep it out of the hot kernel's registers
   const unsigned* f = gate.flags + gate.flag_base + peer;
   unsigned long long t0 = 0;
   for (unsigned spins = 0;; spins++) {
@@ -139,7 +139,7 @@ __device__ __forceinline__ void peer_wait(const PeerGate& gate, int peer) {
 // (ld.acquire.sys) the first time it touches one of p's tiles, so the math starts on the local
 // slice and runs into each peer's slice as it lands.
 template <int T, int I, int JT, bool EPS0, bool GATED>
-__global__ void __launch_bounds__(T) direct_force_kernel(const float4* __restrict__ src,
+__global__ void __launch_bounds__(T, T == 256 ? 5 : 1) direct_force_kernel(const float4* __restrict__ src,
                                                           const float4* __restrict__ tgt,
                                                           float* __restrict__ partial, long long U, int UJ,
                                                           int j0, int jwrap, float eps2,
@@ -326,12 +326,17 @@ static const size_t kSmallN = 32768;
 const DirectCfg& direct_cfg(size_t n_total_sources) { return n_total_sources < kSmallN ? kCfgSmall : kCfgBig; }
 
 template <int T, int I, int JT>
-static int occupancy(bool eps0) {
+static int occupancy(bool eps0, bool gated) {
   int occ = 0;
-  if (eps0)
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, direct_force_kernel<T, I, JT, true, false>, T, 0);
-  else
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, direct_force_kernel<T, I, JT, false, false>, T, 0);
+#define NB_OCC(E_, G_) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, direct_force_kernel<T, I, JT, E_, G_>, T, 0)
+  if (eps0) {
+    if (gated) NB_OCC(true, true);
+    else NB_OCC(true, false);
+  } else {
+    if (gated) NB_OCC(false, true);
+    else NB_OCC(false, false);
+  }
+#undef NB_OCC
   return occ > 0 ? occ : 1;
 }
 
@@ -352,8 +357,9 @@ int launch_direct_pass(nb_context* ctx, const DirectCfg& cfg, const float4* src,
   }
   const bool big = (cfg.T == kCfgBig.T);
   const bool eps0 = !(eps2 > 0.f);
-  int& occ = ctx->direct_occ[(big ? 0 : 2) + (eps0 ? 1 : 0)];
-  if (occ == 0) occ = big ? occupancy<256, 2, 1024>(eps0) : occupancy<128, 2, 256>(eps0);
+  // stream-K cuts the work into exactly as many runs as CTAs are co-resident: ask about THIS kernel variant
+  int& occ = ctx->direct_occ[(gate ? 4 : 0) + (big ? 0 : 2) + (eps0 ? 1 : 0)];
+  if (occ == 0) occ = big ? occupancy<256, 2, 1024>(eps0, gate != nullptr) : occupancy<128, 2, 256>(eps0, gate != nullptr);
   int use_occ = occ;
   if (const char* e = getenv("NB_DIRECT_OCC")) {  // tuning knob: resident CTAs per SM
     const int v = atoi(e);

@@ -97,7 +97,13 @@ __global__ void __launch_bounds__(256) sh_ranges_gather_kernel(const uint32_t* _
                                                                float4* __restrict__ spos) {
   const size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (k > n) return;
-  if (k < n) spos[k] = __ldg(packed + sidx[k]);
+  if (k < n) {
+    // cell-ordered bodies, two per 32 bytes: {x0,x1, y0,y1, z0,z1, m0,m1}, so that the force kernel's
+    // LDG.128s land directly in aligned (body 2q, body 2q+1) register pairs for the fp32x2 pipe
+    const float4 b = __ldg(packed + sidx[k]);
+    float* o = reinterpret_cast<float*>(spos) + (k >> 1) * 8 + (k & 1);
+    o[0] = b.x; o[2] = b.y; o[4] = b.z; o[6] = b.w;
+  }
   const int prev = (k == 0) ? -1 : (int)keys[k - 1];
   const int cur = (k == n) ? total_cells : (int)keys[k];
   if (prev == cur) return;
@@ -106,7 +112,14 @@ __global__ void __launch_bounds__(256) sh_ranges_gather_kernel(const uint32_t* _
   for (int c = (prev < 0 ? 0 : prev); c < cur; c++) cell_end[c] = (int32_t)k;
 }
 
-// :83-152.  One thread per body in cell order; neighbours read as contiguous float4 runs.
+// :83-152.  One thread per body in cell order.  The 27 neighbour cells are 9 contiguous x-runs of
+// the cell-ordered array; a run is swept two candidates at a time, branch-free, on the packed
+// fp32x2 pipe: un-softened r^2 with the reference's unfused mul/add sequence (:128-130), cutoff test
+// per half, softened monopole, weight forced to 0 for candidates outside the cutoff or outside the
+// run.  The body itself is inside its own cell's run: its term is G m * rsqrt(eps^2)^3 * 0 = 0
+// exactly for eps > 0 and is zeroed by a select for eps = 0 (as are exact coincidences).
+// Accumulation: even and odd candidates in separate halves, added at the end.
+template <bool EPS0>
 __global__ void __launch_bounds__(128) sh_force_kernel(size_t n, const float4* __restrict__ spos,
                                                        const int32_t* __restrict__ sidx,
                                                        const int32_t* __restrict__ cell_start,
@@ -118,12 +131,15 @@ __global__ void __launch_bounds__(128) sh_force_kernel(size_t n, const float4* _
   unsigned cnt = 0;
   if (k < n) {
     const int nx = m->dims[0], ny = m->dims[1], nz = m->dims[2];
-    const float4 me = spos[k];
+    const float* mine = reinterpret_cast<const float*>(spos) + (k >> 1) * 8 + (k & 1);
+    const float mex = __ldg(mine), mey = __ldg(mine + 2), mez = __ldg(mine + 4);
     // own cell recomputed WITHOUT clamp (:100-102)
-    const int cx = (int)floorf(__fdiv_rn(__fsub_rn(me.x, m->bbox[0]), cell));
-    const int cy = (int)floorf(__fdiv_rn(__fsub_rn(me.y, m->bbox[1]), cell));
-    const int cz = (int)floorf(__fdiv_rn(__fsub_rn(me.z, m->bbox[2]), cell));
-    float sx = 0.f, sy = 0.f, sz = 0.f;
+    const int cx = (int)floorf(__fdiv_rn(__fsub_rn(mex, m->bbox[0]), cell));
+    const int cy = (int)floorf(__fdiv_rn(__fsub_rn(mey, m->bbox[1]), cell));
+    const int cz = (int)floorf(__fdiv_rn(__fsub_rn(mez, m->bbox[2]), cell));
+    const f2 xi = pk(mex, mex), yi = pk(mey, mey), zi = pk(mez, mez);
+    const f2 e2 = pk(eps2, eps2), g2 = pk(G, G);
+    f2 sx = pk(0.f, 0.f), sy = sx, sz = sx;
     for (int dz = -1; dz <= 1; dz++) {
       const int z = cz + dz;
       if (z < 0 || z >= nz) continue;
@@ -135,27 +151,39 @@ __global__ void __launch_bounds__(128) sh_force_kernel(size_t n, const float4* _
         if (x0 > x1) continue;
         const int row = y * nx + z * nx * ny;
         const int j0 = cell_start[row + x0], j1 = cell_end[row + x1];
-        for (int j = j0; j < j1; j++) {
-          if (j == (int)k) continue;  // j == i (:125-126)
-          const float4 p = spos[j];
-          const float ddx = p.x - me.x, ddy = p.y - me.y, ddz = p.z - me.z;
-          float dist2 = __fadd_rn(__fadd_rn(__fmul_rn(ddx, ddx), __fmul_rn(ddy, ddy)), __fmul_rn(ddz, ddz));
-          if (dist2 < cutoff2) {  // un-softened test (:131-135)
-            dist2 = __fadd_rn(dist2, eps2);
-            const float inv = rsq(dist2);
-            const float f = (G * p.w) * (inv * inv * inv);
-            sx = fmaf(f, ddx, sx);
-            sy = fmaf(f, ddy, sy);
-            sz = fmaf(f, ddz, sz);
-            cnt++;
+#pragma unroll 2
+        for (int jj = j0 & ~1; jj < j1; jj += 2) {  // two iterations in flight: the loop is load-latency bound
+          const float4* q = spos + jj;  // pair jj/2 = two float4
+          const float4 a = __ldg(q), b = __ldg(q + 1);  // {x0,x1,y0,y1} {z0,z1,m0,m1}
+          const f2 ddx = sub2(pk(a.x, a.y), xi), ddy = sub2(pk(a.z, a.w), yi), ddz = sub2(pk(b.x, b.y), zi);
+          f2 d2 = add2(add2(mul2(ddx, ddx), mul2(ddy, ddy)), mul2(ddz, ddz));
+          float r0, r1;
+          upk(d2, r0, r1);
+          const bool in0 = (r0 < cutoff2) && (jj >= j0);  // un-softened test (:131-135)
+          const bool in1 = (r1 < cutoff2) && (jj + 1 < j1);
+          cnt += (in0 ? 1u : 0u) + (in1 ? 1u : 0u);
+          upk(add2(d2, e2), r0, r1);
+          float i0 = rsq(r0), i1 = rsq(r1);
+          if (EPS0) {
+            i0 = (r0 > 0.f) ? i0 : 0.f;
+            i1 = (r1 > 0.f) ? i1 : 0.f;
           }
+          i0 = in0 ? i0 : 0.f;
+          i1 = in1 ? i1 : 0.f;
+          const f2 inv = pk(i0, i1);
+          const f2 f = mul2(mul2(g2, pk(b.z, b.w)), mul2(mul2(inv, inv), inv));
+          sx = fma2(f, ddx, sx);
+          sy = fma2(f, ddy, sy);
+          sz = fma2(f, ddz, sz);
         }
       }
     }
+    float e, o;
     const int i = sidx[k];
-    ax[i] = sx;
-    ay[i] = sy;
-    az[i] = sz;
+    upk(sx, e, o); ax[i] = e + o;
+    upk(sy, e, o); ay[i] = e + o;
+    upk(sz, e, o); az[i] = e + o;
+    cnt -= 1;  // the body itself (always inside its own run and inside the cutoff)
   }
   // one atomic per warp
   unsigned long long c = cnt;
@@ -197,7 +225,7 @@ int sh_build(nb_context* ctx, const nb_particles* d, float cell, cudaStream_t st
   if (int rc = s->particle_cell.ensure(n * 4)) return rc;
   if (int rc = s->keys.ensure(n * 4)) return rc;
   if (int rc = s->sorted_idx.ensure(n * 4)) return rc;
-  if (int rc = s->spos.ensure(n * sizeof(float4))) return rc;
+  if (int rc = s->spos.ensure((n + 1) / 2 * 2 * sizeof(float4))) return rc;
   if (int rc = s->packed.ensure(n * sizeof(float4))) return rc;
   if (int rc = s->misc.ensure(sizeof(SHMisc))) return rc;
   if (!s->h_misc) NB_CUDA(cudaMallocHost(&s->h_misc, sizeof(SHMisc)));
@@ -242,10 +270,16 @@ int sh_forces(nb_context* ctx, const nb_particles* d, float cutoff, float G, flo
     return NB_ERR_INVALID;
   }
   SHMisc* misc = s->misc.as<SHMisc>();
+  NB_CUDA(cudaMemsetAsync(&misc->pairs, 0, sizeof(unsigned long long), st));
+  const float eps2 = eps * eps;
   ProfScope prof(ctx, st);
-  sh_force_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(
-      n, s->spos.as<float4>(), s->sorted_idx.as<int32_t>(), s->cell_start.as<int32_t>(), s->cell_end.as<int32_t>(),
-      misc, s->cell_size, cutoff * cutoff, G, eps * eps, d->acc_x, d->acc_y, d->acc_z, &misc->pairs);
+#define NB_SH_LAUNCH(E_)                                                                                          \
+  sh_force_kernel<E_><<<(unsigned)((n + 127) / 128), 128, 0, st>>>(                                               \
+      n, s->spos.as<float4>(), s->sorted_idx.as<int32_t>(), s->cell_start.as<int32_t>(), s->cell_end.as<int32_t>(), \
+      misc, s->cell_size, cutoff * cutoff, G, eps2, d->acc_x, d->acc_y, d->acc_z, &misc->pairs)
+  if (eps2 > 0.f) NB_SH_LAUNCH(false);
+  else NB_SH_LAUNCH(true);
+#undef NB_SH_LAUNCH
   NB_LAUNCH_CHECK(ctx);
   return NB_OK;
 }
@@ -272,6 +306,17 @@ int nb_sh_forces(nb_context* ctx, const nb_particles* d, float cutoff, float G, 
   }
   NB_CUDA(cudaSetDevice(ctx->device));
   return sh_forces(ctx, d, cutoff, G, eps, (cudaStream_t)s);
+}
+
+int nb_sh_stats(nb_context* ctx, uint64_t* pairs) {
+  if (!ctx || !ctx->sh || !ctx->sh->built || !pairs) {
+    set_error("spatial hash: no grid built");
+    return NB_ERR_INVALID;
+  }
+  NB_CUDA(cudaSetDevice(ctx->device));
+  NB_CUDA(cudaDeviceSynchronize());
+  NB_CUDA(cudaMemcpy(pairs, &ctx->sh->misc.as<SHMisc>()->pairs, 8, cudaMemcpyDeviceToHost));
+  return NB_OK;
 }
 
 int nb_sh_total_cells(nb_context* ctx, int* total_cells) {

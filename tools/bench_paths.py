@@ -84,10 +84,12 @@ def main():
         nb.ParticleDataManager.copyToDevice(d, h)
         build = timed(lambda: _lib.check(L.nb_sh_build(ctx.handle, C.byref(d.c), 1.0, None)))
         force = timed(lambda: _lib.check(L.nb_sh_forces(ctx.handle, C.byref(d.c), 2.0, 1.0, 0.01, None)))
-        t = C.c_int(0)
+        t, pairs = C.c_int(0), C.c_uint64(0)
         L.nb_sh_total_cells(ctx.handle, C.byref(t))
+        _lib.check(L.nb_sh_stats(ctx.handle, C.byref(pairs)))
         print(json.dumps(dict(path="spatial_hash", n=n, side=side, cells=t.value, build_ms=build, force_ms=force,
-                              step_ms=build + force, build_gbs=136.0 * n / build / 1e6)))
+                              step_ms=build + force, build_gbs=136.0 * n / build / 1e6, pairs_in_cutoff=pairs.value,
+                              pairs_per_body=pairs.value / n, g_pairs_per_s=pairs.value / force / 1e6)))
 
 
 if __name__ == "__main__":
