@@ -125,6 +125,25 @@ int nb_sort_pairs(nb_context* ctx, uint32_t* d_keys, int32_t* d_vals, size_t n, 
 /* bbox kernel (src/cuda/force_barnes_hut.cu:218-258); out = 6 host floats; synchronises. */
 int nb_bounding_box(nb_context* ctx, const nb_particles* d, float out[6], nb_stream s);
 
+/* ---- headless point-splat renderer: the reference's GL point-sprite
+ *      pipeline -- vertex + fragment shaders src/render/renderer.cpp:16-77, blend state :110-113,
+ *      draw call :184-224 -- as CUDA kernels writing a device RGBA8 framebuffer (row 0 = bottom row,
+ *      as glReadPixels returns it).  Matrices are column-major like glm's.  No GL anywhere. ------- */
+typedef struct nb_render_params {
+  float view[16], proj[16];     /* Camera::getViewMatrix / getProjectionMatrix (src/render/camera.cpp:36-44) */
+  float point_size;             /* uniform pointSize (default 2), divided by max(-viewPos.z, 0.1)            */
+  float max_depth, max_velocity;/* uniforms maxDepth (100), maxVelocity (10)                                  */
+  int color_mode;               /* 0 depth, 1 velocity, 2 density (include/nbody/types.hpp ColorMode)        */
+  int width, height;
+  float point_size_min, point_size_max; /* GL's implementation point-size range; 1 and 63 by default        */
+  float clear_color[4];         /* 0.02, 0.02, 0.05, 1 (renderer.cpp:9-11, :188)                             */
+} nb_render_params;
+int nb_render_splats(nb_context* ctx, const nb_particles* d, const nb_render_params* p, uint8_t* d_rgba, nb_stream s);
+int nb_render_stats(nb_context* ctx, uint64_t* fragments);
+/* copyPositionsToVBOKernel / copyVelocitiesToVBOKernel (src/render/cuda_gl_interop.cpp:7-28): SoA ->
+ * interleaved xyz device buffers (either may be NULL) */
+int nb_interop_pack(nb_context* ctx, const nb_particles* d, float* d_positions_xyz, float* d_velocities_xyz, nb_stream s);
+
 /* ---- multi-GPU direct N^2 (no counterpart in the reference; target-sharded) ---
  * The caller (one process per GPU) provides the exchange: `gathered_src` is this rank's replicated
  * packed source buffer.  Flow per step: nb_mgpu_pack_local -> (all-gather of the local slice, any

@@ -6,6 +6,7 @@ Layout:  csrc/        hand-written CUDA for sm_100a + the C ABI (include/nbody_b
          api.py       Python mirror of the reference's classes over the C ABI
          ics.py       synthetic initial conditions (Plummer, uniform sphere/box, disk)
          serialization.py  the reference's .nbody checkpoint format
+         render.py    headless Camera / ColorMapper / Renderer over the CUDA splat kernels
          dist.py      one-process-per-GPU target sharding for direct N^2 (torch.distributed)
 """
 from .api import (  # noqa: F401
@@ -15,5 +16,6 @@ from .api import (  # noqa: F401
     get_context, validateSimulationConfig,
 )
 from .serialization import Serializer  # noqa: F401
+from .render import Camera, ColorMapper, ColorMode, Renderer  # noqa: F401
 
 __version__ = "0.1.0"

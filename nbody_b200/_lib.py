@@ -82,6 +82,9 @@ SYMBOLS = {
     "nb_sh_export": (_i, [_vp] + [_vp] * 6),
     "nb_sh_total_cells": (_i, [_vp, C.POINTER(_i)]),
     "nb_sh_stats": (_i, [_vp, C.POINTER(C.c_uint64)]),
+    "nb_render_splats": (_i, [_vp, _pp, _vp, _vp, _vp]),
+    "nb_render_stats": (_i, [_vp, C.POINTER(C.c_uint64)]),
+    "nb_interop_pack": (_i, [_vp, _pp, _vp, _vp, _vp]),
     "nb_sort_pairs": (_i, [_vp, _vp, _vp, _sz, _i, _vp]),
     "nb_bounding_box": (_i, [_vp, _pp, _vp, _vp]),
     "nb_mgpu_layout": (_i, [_vp, _sz, _i, _i, C.POINTER(_sz), C.POINTER(_sz), C.POINTER(_sz), C.POINTER(_sz)]),
@@ -111,7 +114,12 @@ def lib():
             "(or `make -C nbody_b200/csrc`). There is no CPU or PyTorch fallback.")
     L = C.CDLL(LIB_PATH)
     for name, (res, args) in SYMBOLS.items():
-        fn = getattr(L, name)  # AttributeError if the library does not export it
+        try:
+            fn = getattr(L, name)  # AttributeError if the library does not export it
+        except AttributeError:
+            if os.environ.get("NB_LIB_PATH"):
+                continue  # A/B run of an older build: it may predate newer entry points
+            raise
         fn.restype = res
         fn.argtypes = args
     _lib = L

@@ -81,6 +81,7 @@ int kinetic_energy(nb_context* ctx, const nb_particles* d, double* ke, cudaStrea
 int potential_energy(nb_context* ctx, const nb_particles* d, float G, float eps, double* pe, cudaStream_t st);
 void bh_destroy(nb_context* ctx);
 void sh_destroy(nb_context* ctx);
+void render_destroy(nb_context* ctx);
 
 static int check_ctx(nb_context* ctx) {
   if (!ctx) {
@@ -177,6 +178,7 @@ int nb_context_destroy(nb_context* ctx) {
   cudaSetDevice(ctx->device);
   cudaDeviceSynchronize();
   nb_mgpu_peer_close(ctx);
+  render_destroy(ctx);
   bh_destroy(ctx);
   sh_destroy(ctx);
   ctx->src.release();

@@ -178,6 +178,8 @@ struct nb_context {
   struct BH* bh = nullptr;
   // spatial hash
   struct SH* sh = nullptr;
+  // splat renderer
+  struct RenderState* render = nullptr;
   // radix sort scratch
   nb::DevBuf sort_keys2, sort_vals2, sort_hist;
   // bbox scratch (6 ordered ints) + pinned readback

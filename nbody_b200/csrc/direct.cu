@@ -138,8 +138,12 @@ __device__ __noinline__ void peer_wait(const PeerGate& gate, int peer) {  // col
 // pack_push_kernel over NVLink; the thread that issues the TMA copies waits for peer p's step flag
 // (ld.acquire.sys) the first time it touches one of p's tiles, so the math starts on the local
 // slice and runs into each peer's slice as it lands.
+#ifndef NB_DIRECT_MINB
+// the gated variant needs the cap to stay at 48 registers (5 CTAs/SM like the plain one)
+#define NB_DIRECT_MINB(T, GATED) (((GATED) && (T) == 256) ? 5 : 0)  /* 0 = no constraint */
+#endif
 template <int T, int I, int JT, bool EPS0, bool GATED>
-__global__ void __launch_bounds__(T, T == 256 ? 5 : 1) direct_force_kernel(const float4* __restrict__ src,
+__global__ void __launch_bounds__(T, NB_DIRECT_MINB(T, GATED)) direct_force_kernel(const float4* __restrict__ src,
                                                           const float4* __restrict__ tgt,
                                                           float* __restrict__ partial, long long U, int UJ,
                                                           int j0, int jwrap, float eps2,

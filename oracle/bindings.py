@@ -104,6 +104,9 @@ def lib():
     L.orc_cell_ranges.argtypes = [i, i32p, i, i32p, i32p, i32p]
     L.orc_spatial_forces.argtypes = [i, f32p, f32p, f32p, f32p, i32p, i32p, i32p, i32p, f, f32p, f, f, f,
                                      f32p, f32p, f32p, C.POINTER(C.c_uint64)]
+    L.orc_render_splats.argtypes = [i, f32p, f32p, f32p, f32p, f32p, f32p, f32p, f32p, f, f, f, i, i, i, f, f, f32p,
+                                    np.ctypeslib.ndpointer(np.uint8, flags="C_CONTIGUOUS")]
+    L.orc_render_splats.restype = C.c_uint64
     L.orc_num_threads.restype = i
     L.orc_set_num_threads.argtypes = [i]
     _LIB = L
@@ -304,6 +307,18 @@ def spatial_forces(px, py, pz, m, grid, cutoff, G, eps):
                              grid["dims"], grid["cell_size"], grid["bbox"], cutoff, G, eps, ax, ay, az,
                              C.byref(cnt))
     return ax, ay, az, cnt.value
+
+
+def render_splats(state, view, proj, point_size, max_depth, max_velocity, color_mode, width, height,
+                  size_min=1.0, size_max=63.0, clear=(0.02, 0.02, 0.05, 1.0)):
+    """height x width x 4 uint8 (row 0 = bottom row) and the fragment count."""
+    n = state["pos_x"].size
+    img = np.zeros(width * height * 4, np.uint8)
+    frags = lib().orc_render_splats(n, _f32(state["pos_x"]), _f32(state["pos_y"]), _f32(state["pos_z"]),
+                                    _f32(state["vel_x"]), _f32(state["vel_y"]), _f32(state["vel_z"]), _f32(view),
+                                    _f32(proj), point_size, max_depth, max_velocity, int(color_mode), width, height,
+                                    size_min, size_max, _f32(np.asarray(clear, np.float32)), img)
+    return img.reshape(height, width, 4), int(frags)
 
 
 def num_threads():

@@ -138,6 +138,13 @@ void orc_spatial_forces(int n, const float* px, const float* py, const float* pz
                         const int32_t dims[3], float cell_size, const float bbox_padded[6], float cutoff,
                         float G, float eps, float* ax, float* ay, float* az, uint64_t* pairs);
 
+/* ---- headless point-splat renderer (render.c) ------------------------------------------ */
+/* src/render/renderer.cpp:16-77, :110-113, :184-224; returns the number of fragments generated */
+uint64_t orc_render_splats(int n, const float* px, const float* py, const float* pz, const float* vx, const float* vy,
+                           const float* vz, const float view[16], const float proj[16], float point_size,
+                           float max_depth, float max_velocity, int color_mode, int width, int height,
+                           float size_min, float size_max, const float clear[4], uint8_t* rgba);
+
 int orc_num_threads(void);
 void orc_set_num_threads(int t); /* overrides OMP_NUM_THREADS (torchrun sets it to 1) */
 

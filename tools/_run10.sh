@@ -1,0 +1,19 @@
+for rep in 1 2; do
+for lib in build/ab/libnbody_b200_59d6739.so nbody_b200/libnbody_b200.so; do
+NB_LIB_PATH=$PWD/$lib python - <<'PY'
+import os, ctypes as C, numpy as np, torch
+import nbody_b200 as nb
+from nbody_b200 import _lib, ics
+L=_lib.lib(); ctx=nb.get_context()
+n=1<<20; st=ics.plummer(n,seed=42)
+h=nb.ParticleDataManager.fromState(st); d=nb.ParticleData(); nb.ParticleDataManager.allocateDevice(d,n); nb.ParticleDataManager.copyToDevice(d,h)
+for _ in range(2): _lib.check(L.nb_step_direct(ctx.handle,C.byref(d.c),1e-3,1.0,1e-4,None))
+torch.cuda.synchronize()
+e0,e1=torch.cuda.Event(enable_timing=True),torch.cuda.Event(enable_timing=True)
+e0.record()
+for _ in range(4): _lib.check(L.nb_step_direct(ctx.handle,C.byref(d.c),1e-3,1.0,1e-4,None))
+e1.record(); torch.cuda.synchronize()
+print(os.environ["NB_LIB_PATH"].split("/")[-1], "ms/step", e0.elapsed_time(e1)/4)
+PY
+done; done
+nvidia-smi --query-gpu=clocks.sm,clocks.mem,power.draw,temperature.gpu --format=csv

@@ -52,6 +52,25 @@ def main():
                               super=os.environ.get("NB_BH_SUPER", "default"), build_ms=build, force_ms=force,
                               step_ms=build + force, interactions=inter.value, per_body=inter.value / n,
                               g_interactions_per_s=inter.value / force / 1e6)))
+    elif kind == "render":
+        # default camera and uniforms of the reference's Renderer; Plummer sphere scaled into view
+        w, h = (int(sys.argv[3]), int(sys.argv[4])) if len(sys.argv) > 4 else (1280, 720)
+        st = ics.plummer(n, seed=42)
+        for k in ("pos_x", "pos_y", "pos_z"):
+            st[k] = (st[k] * np.float32(8.0)).astype(np.float32)
+        hd = nb.ParticleDataManager.fromState(st)
+        d = nb.ParticleData()
+        nb.ParticleDataManager.allocateDevice(d, n)
+        nb.ParticleDataManager.copyToDevice(d, hd)
+        r = nb.Renderer()
+        r.initialize(w, h)
+        ms = timed(lambda: r.render(d))
+        frags = r.fragments()
+        img = r.readPixels()
+        r.savePPM(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out",
+                               f"render_{n}.ppm")) if os.path.isdir("gpurun_out") and n <= (1 << 20) else None
+        print(json.dumps(dict(path="splat_render", n=n, width=w, height=h, ms=ms, fragments=frags,
+                              lit_pixels=int((img != img[0, 0]).any(axis=2).sum()), gbodies_per_s=n / ms / 1e6)))
     elif kind == "sort":
         # 30-bit keys in random order (what the Morton sort sees), restored before every repetition
         bits = int(sys.argv[3]) if len(sys.argv) > 3 else 30
