@@ -60,6 +60,22 @@ int nb_synchronize(nb_context* ctx, nb_stream stream);
 /* number of this library's kernels launched through ctx since creation (bench.py gpu_launches) */
 uint64_t nb_launch_count(const nb_context* ctx);
 
+/* ---- streams and CUDA graphs for host code without CUDA headers.  A step at small N is launch-bound;
+ * run one step eagerly, capture the next on a stream from nb_stream_create, replay with
+ * nb_graph_launch (named as future work by the reference,
+ * openspec/changes/evolve-nbody-platform/tasks.md:24-31).  Capturable: nb_direct_forces,
+ * nb_step_direct, nb_bh_build, nb_bh_forces, nb_store_accelerations, nb_update_positions,
+ * nb_update_velocities.  Everything that synchronises (nb_sh_build, energies, exports, stats,
+ * nb_render_splats) is not. */
+typedef struct nb_graph nb_graph;
+int nb_stream_create(nb_context* ctx, nb_stream* out);
+int nb_stream_destroy(nb_context* ctx, nb_stream s);
+int nb_graph_begin_capture(nb_context* ctx, nb_stream s);
+int nb_graph_end_capture(nb_context* ctx, nb_stream s, nb_graph** out);
+int nb_graph_launch(nb_graph* g, nb_stream s);
+int nb_graph_node_count(const nb_graph* g, size_t* nodes);
+int nb_graph_destroy(nb_graph* g);
+
 /* optional device-side timing of the dominant kernels (CUDA events on the launching stream around
  * every direct-force / BH-traversal / SH-force launch).  nb_profile_read synchronises, returns the
  * summed kernel milliseconds and launch count since the last read, and resets them. */

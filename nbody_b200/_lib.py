@@ -57,6 +57,13 @@ SYMBOLS = {
     "nb_context_sm_count": (_i, [_vp]),
     "nb_synchronize": (_i, [_vp, _vp]),
     "nb_launch_count": (C.c_uint64, [_vp]),
+    "nb_stream_create": (_i, [_vp, C.POINTER(_vp)]),
+    "nb_stream_destroy": (_i, [_vp, _vp]),
+    "nb_graph_begin_capture": (_i, [_vp, _vp]),
+    "nb_graph_end_capture": (_i, [_vp, _vp, C.POINTER(_vp)]),
+    "nb_graph_launch": (_i, [_vp, _vp]),
+    "nb_graph_node_count": (_i, [_vp, C.POINTER(_sz)]),
+    "nb_graph_destroy": (_i, [_vp]),
     "nb_profile_enable": (_i, [_vp, _i]),
     "nb_profile_read": (_i, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]),
     "nb_particles_alloc_device": (_i, [_pp, _sz]),

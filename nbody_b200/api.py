@@ -512,6 +512,8 @@ class ParticleSystem:
         self.force_method_ = ForceMethod.DIRECT_N2
         self.is_paused_ = False
         self.is_initialized_ = False
+        self.use_graph_ = False
+        self.graph_, self.graph_key_, self.graph_warm_key_, self.graph_stream_ = None, None, None, None
         self.config_ = SimulationConfig()
         self.d_particles_ = ParticleData()
         self.h_particles_ = ParticleData()
@@ -557,8 +559,61 @@ class ParticleSystem:
     def update(self, dt: float):  # particle_system.cpp:115-127
         if not self.is_initialized_ or self.is_paused_:
             return
-        self.integrator_.integrate(self.d_particles_, self.force_calculator_, dt)
+        if self.use_graph_ and self.force_method_ in (ForceMethod.DIRECT_N2, ForceMethod.BARNES_HUT):
+            self._update_graphed(dt)
+        else:
+            self.integrator_.integrate(self.d_particles_, self.force_calculator_, dt)
         self.simulation_time_ += dt
+
+    # ---- CUDA-graph replay of the steady-state step --------------------
+    def setUseCudaGraph(self, on: bool):
+        """Replay update() as one captured graph launch: the first step with a given set of
+        parameters runs eagerly (sizes all scratch), the second is captured, later ones replay."""
+        self.use_graph_ = bool(on)
+        if not on:
+            self._drop_graph()
+
+    def _drop_graph(self):
+        if getattr(self, "graph_", None):
+            check(_lib.lib().nb_graph_destroy(self.graph_))
+        self.graph_, self.graph_key_, self.graph_warm_key_ = None, None, None
+
+    def _graph_key(self, dt):
+        fc, d = self.force_calculator_, self.d_particles_.c
+        extra = fc.getTheta() if self.force_method_ == ForceMethod.BARNES_HUT else 0.0
+        return (float(np.float32(dt)), int(self.force_method_), fc.getGravitationalConstant(),
+                fc.getSofteningParameter(), extra, int(d.count), int(d.pos_x or 0), int(d.acc_x or 0), id(fc))
+
+    def _update_graphed(self, dt):
+        import torch
+        L, ctx = _lib.lib(), get_context()
+        key = self._graph_key(dt)
+        if self.graph_ and self.graph_key_ == key:
+            check(L.nb_graph_launch(self.graph_, _stream()))
+            return
+        if self.graph_warm_key_ != key:      # first step with these parameters: eager
+            self._drop_graph()
+            self.integrator_.integrate(self.d_particles_, self.force_calculator_, dt)
+            self.graph_warm_key_ = key
+            return
+        if self.graph_stream_ is None:
+            self.graph_stream_ = torch.cuda.Stream()
+        with torch.cuda.stream(self.graph_stream_):
+            check(L.nb_graph_begin_capture(ctx.handle, _stream()))
+            try:
+                self.integrator_.integrate(self.d_particles_, self.force_calculator_, dt)
+            finally:
+                g = C.c_void_p()
+                rc = L.nb_graph_end_capture(ctx.handle, _stream(), C.byref(g))
+            check(rc)
+        self.graph_, self.graph_key_ = g, key
+        check(L.nb_graph_launch(self.graph_, _stream()))
+
+    def graphNodeCount(self) -> int:
+        n = C.c_size_t(0)
+        if self.graph_:
+            check(_lib.lib().nb_graph_node_count(self.graph_, C.byref(n)))
+        return n.value
 
     def reset(self):
         if self.is_initialized_:

@@ -233,6 +233,101 @@ int nb_synchronize(nb_context* ctx, nb_stream stream) {
   return NB_OK;
 }
 
+// ---- CUDA graphs: the steady-state step as one replayable launch -----------------------------------
+// A step at small N is launch-bound (direct: 3 kernels, Barnes-Hut: ~20 kernels and memsets for a few
+// hundred microseconds of work).  The host layer runs one step eagerly (all scratch sized), captures
+// the next on a side stream and replays the instantiated graph from then on; any parameter baked into
+// the launches (dt, G, eps, theta, body count, arrays) invalidates it.  Thin wrappers so that host code
+// needs no CUDA headers.  Capturable: direct / Barnes-Hut forces and steps, the integrator kernels.
+// Not capturable (they synchronise): spatial-hash build, energies, the renderer, *_export, *_stats.
+struct nb_graph {
+  cudaGraph_t graph = nullptr;
+  cudaGraphExec_t exec = nullptr;
+  int device = 0;
+};
+
+int nb_stream_create(nb_context* ctx, nb_stream* out) {
+  NB_ENTER(ctx);
+  if (!out) {
+    set_error("stream create: null argument");
+    return NB_ERR_INVALID;
+  }
+  cudaStream_t st = nullptr;
+  NB_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+  *out = (nb_stream)st;
+  return NB_OK;
+}
+
+int nb_stream_destroy(nb_context* ctx, nb_stream s) {
+  NB_ENTER(ctx);
+  if (s) NB_CUDA(cudaStreamDestroy((cudaStream_t)s));
+  return NB_OK;
+}
+
+int nb_graph_begin_capture(nb_context* ctx, nb_stream s) {
+  NB_ENTER(ctx);
+  if (!s) {
+    set_error("graph capture needs a non-default stream (nb_stream_create)");
+    return NB_ERR_INVALID;
+  }
+  if (ctx->prof) {
+    set_error("graph capture with nb_profile_enable on is not supported");
+    return NB_ERR_INVALID;
+  }
+  NB_CUDA(cudaStreamBeginCapture((cudaStream_t)s, cudaStreamCaptureModeThreadLocal));
+  return NB_OK;
+}
+
+int nb_graph_end_capture(nb_context* ctx, nb_stream s, nb_graph** out) {
+  NB_ENTER(ctx);
+  if (!s || !out) {
+    set_error("graph end capture: null argument");
+    return NB_ERR_INVALID;
+  }
+  cudaGraph_t g = nullptr;
+  NB_CUDA(cudaStreamEndCapture((cudaStream_t)s, &g));
+  cudaGraphExec_t e = nullptr;
+  cudaError_t err = cudaGraphInstantiate(&e, g, 0);
+  if (err != cudaSuccess) {
+    cudaGraphDestroy(g);
+    return cuda_fail(err, "cudaGraphInstantiate", __FILE__, __LINE__);
+  }
+  nb_graph* h = new nb_graph();
+  h->graph = g;
+  h->exec = e;
+  h->device = ctx->device;
+  *out = h;
+  return NB_OK;
+}
+
+int nb_graph_launch(nb_graph* g, nb_stream s) {
+  if (!g || !g->exec) {
+    set_error("graph launch: null graph");
+    return NB_ERR_INVALID;
+  }
+  NB_CUDA(cudaSetDevice(g->device));
+  NB_CUDA(cudaGraphLaunch(g->exec, (cudaStream_t)s));
+  return NB_OK;
+}
+
+int nb_graph_node_count(const nb_graph* g, size_t* nodes) {
+  if (!g || !g->graph || !nodes) {
+    set_error("graph node count: null argument");
+    return NB_ERR_INVALID;
+  }
+  NB_CUDA(cudaGraphGetNodes(g->graph, nullptr, nodes));
+  return NB_OK;
+}
+
+int nb_graph_destroy(nb_graph* g) {
+  if (!g) return NB_OK;
+  cudaSetDevice(g->device);
+  if (g->exec) cudaGraphExecDestroy(g->exec);
+  if (g->graph) cudaGraphDestroy(g->graph);
+  delete g;
+  return NB_OK;
+}
+
 // ---- ParticleDataManager ---------------------------------------------------------------------
 static float** field_ptrs(nb_particles* d, float** out[13]) {
   float** f[13] = {&d->pos_x, &d->pos_y, &d->pos_z, &d->vel_x, &d->vel_y, &d->vel_z, &d->acc_x,

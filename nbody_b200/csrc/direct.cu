@@ -133,7 +133,7 @@ __device__ __noinline__ void peer_wait(const PeerGate& gate, int peer) {  // col
 // ---------------------------------------------------------------------------------------------
 // force kernel
 // ---------------------------------------------------------------------------------------------
-// Source tile j of a pass is tile (j0 + j) mod jwrap of `src`.  GATED (multi-GPU peer exchange,
+// Source tile j of a pass is tile ja0 + j for j < na, then jb0 + (j - na).  GATED (multi-GPU peer exchange,
 // mgpu.cu): tiles [p*gate.ptiles, (p+1)*gate.ptiles) were pushed into `src` by peer p's
 // pack_push_kernel over NVLink; the thread that issues the TMA copies waits for peer p's step flag
 // (ld.acquire.sys) the first time it touches one of p's tiles, so the math starts on the local
@@ -146,7 +146,7 @@ template <int T, int I, int JT, bool EPS0, bool GATED>
 __global__ void __launch_bounds__(T, NB_DIRECT_MINB(T, GATED)) direct_force_kernel(const float4* __restrict__ src,
                                                           const float4* __restrict__ tgt,
                                                           float* __restrict__ partial, long long U, int UJ,
-                                                          int j0, int jwrap, float eps2,
+                                                          int ja0, int na, int jb0, float eps2,
                                                           unsigned long long slot_base, PeerGate gate) {
   constexpr int P = I / 2;
   constexpr int IT = T * I;
@@ -170,8 +170,7 @@ __global__ void __launch_bounds__(T, NB_DIRECT_MINB(T, GATED)) direct_force_kern
   int jt = (int)(u0 - (long long)itile * UJ);
   unsigned ready_peers = 1u << gate.self;  // peers whose slice is known to have landed (thread 0 only)
   auto jtile_ptr = [&](int j) -> const float4* {
-    int g = j0 + j;
-    if (g >= jwrap) g -= jwrap;
+    const int g = (j < na) ? (ja0 + j) : (jb0 + (j - na));
     if (GATED) {
       const int peer = g / gate.ptiles;
       if (!((ready_peers >> peer) & 1u)) {
@@ -344,12 +343,12 @@ static int occupancy(bool eps0, bool gated) {
   return occ > 0 ? occ : 1;
 }
 
-// Launch one stream-K pass: `njt` source tiles (tile = JT bodies) starting at tile j0 of `src`, wrapping
-// at jwrap, against n_itiles target tiles of `tgt`.  gate != nullptr: peer-gated sources (see the kernel).
+// Launch one stream-K pass.  Source tiles [ja0, ja0+na) then [jb0, jb0+nbt) of `src` (tile = JT
+// bodies) against n_itiles target tiles of `tgt`.  gate != nullptr: peer-gated sources (see the kernel).
 int launch_direct_pass(nb_context* ctx, const DirectCfg& cfg, const float4* src, const float4* tgt, int n_itiles,
-                       int j0, int njt, int jwrap, float eps2, int pass_index, cudaStream_t st,
+                       int ja0, int na, int jb0, int nbt, float eps2, int pass_index, cudaStream_t st,
                        const PeerGate* gate) {
-  const int UJ = njt;
+  const int UJ = na + nbt;
   nb_pass& ps = ctx->pass[pass_index];
   ps.UJ = UJ;
   ps.n_itiles = n_itiles;
@@ -380,7 +379,7 @@ int launch_direct_pass(nb_context* ctx, const DirectCfg& cfg, const float4* src,
   PeerGate none{};
   const PeerGate gt = gate ? *gate : none;
 #define NB_LAUNCH_DIRECT(T_, I_, JT_, E_, G_)                                                                  \
-  direct_force_kernel<T_, I_, JT_, E_, G_><<<ps.G, T_, 0, st>>>(src, tgt, part, ps.U, UJ, j0, jwrap, eps2,     \
+  direct_force_kernel<T_, I_, JT_, E_, G_><<<ps.G, T_, 0, st>>>(src, tgt, part, ps.U, UJ, ja0, na, jb0, eps2,   \
                                                                 (unsigned long long)ps.slot_base, gt)
 #define NB_LAUNCH_DIRECT_E(T_, I_, JT_, E_)            \
   do {                                                 \
@@ -453,7 +452,7 @@ int direct_run(nb_context* ctx, const nb_particles* d, float dt, float G, float 
   const int n_itiles = (int)((n + cfg.IT() - 1) / cfg.IT());
   const int n_jt = (int)((n + cfg.JT - 1) / cfg.JT);
   ctx->n_pass = 1;
-  if (int rc = launch_direct_pass(ctx, cfg, src, src, n_itiles, 0, n_jt, n_jt, eps2, 0, st, nullptr)) return rc;
+  if (int rc = launch_direct_pass(ctx, cfg, src, src, n_itiles, 0, n_jt, 0, 0, eps2, 0, st, nullptr)) return rc;
   return launch_reduce(ctx, cfg, d, n, dt, step, st);
 }
 

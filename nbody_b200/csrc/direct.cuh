@@ -35,7 +35,7 @@ int launch_pack_push(nb_context* ctx, const nb_particles* d, const PeerBufs& pb,
 int launch_pack(nb_context* ctx, const nb_particles* d, float4* src, size_t n, size_t n_pad, float G, float dt,
                 bool drift, cudaStream_t st);
 int launch_direct_pass(nb_context* ctx, const DirectCfg& cfg, const float4* src, const float4* tgt, int n_itiles,
-                       int j0, int njt, int jwrap, float eps2, int pass_index, cudaStream_t st,
+                       int ja0, int na, int jb0, int nbt, float eps2, int pass_index, cudaStream_t st,
                        const PeerGate* gate);
 int launch_reduce(nb_context* ctx, const DirectCfg& cfg, const nb_particles* d, size_t n, float dt, bool kick,
                   cudaStream_t st);

@@ -68,8 +68,8 @@ int nb_mgpu_forces_local(nb_context* ctx, const float* gathered_src, float eps2,
   const int n_itiles = (int)((ctx->mg_count + cfg.IT() - 1) / cfg.IT());
   ctx->n_pass = 1;
   ctx->pass[1].U = 0;
-  return launch_direct_pass(ctx, cfg, src, tgt, n_itiles, ctx->mg_rank * ptiles, ptiles, ctx->mg_nranks * ptiles, eps2,
-                            0, (cudaStream_t)s, nullptr);
+  return launch_direct_pass(ctx, cfg, src, tgt, n_itiles, ctx->mg_rank * ptiles, ptiles, 0, 0, eps2, 0,
+                            (cudaStream_t)s, nullptr);
 }
 
 int nb_mgpu_forces_remote(nb_context* ctx, const float* gathered_src, float eps2, nb_stream s) {
@@ -85,8 +85,9 @@ int nb_mgpu_forces_remote(nb_context* ctx, const float* gathered_src, float eps2
   const int n_itiles = (int)((ctx->mg_count + cfg.IT() - 1) / cfg.IT());
   ctx->n_pass = 2;
   // the other R-1 slices in ring order: rank+1, ..., R-1, 0, ..., rank-1
-  return launch_direct_pass(ctx, cfg, src, tgt, n_itiles, ((ctx->mg_rank + 1) % ctx->mg_nranks) * ptiles,
-                            (ctx->mg_nranks - 1) * ptiles, ctx->mg_nranks * ptiles, eps2, 1, (cudaStream_t)s, nullptr);
+  return launch_direct_pass(ctx, cfg, src, tgt, n_itiles, (ctx->mg_rank + 1) * ptiles,
+                            (ctx->mg_nranks - 1 - ctx->mg_rank) * ptiles, 0, ctx->mg_rank * ptiles, eps2, 1,
+                            (cudaStream_t)s, nullptr);
 }
 
 int nb_mgpu_finish(nb_context* ctx, const nb_particles* d_local, float dt, int do_kick, nb_stream s) {
@@ -281,8 +282,10 @@ int nb_mgpu_peer_forces(nb_context* ctx, const nb_particles* d_local, float dt, 
   gate.timeout_flag = ps->d_timeout;
   ctx->n_pass = 1;
   ctx->pass[1].U = 0;
-  if (int rc = launch_direct_pass(ctx, cfg, src, tgt, n_itiles, ctx->mg_rank * ptiles, ctx->mg_nranks * ptiles,
-                                  ctx->mg_nranks * ptiles, eps2, 0, st, ctx->mg_nranks > 1 ? &gate : nullptr))
+  // ring order from the local slice: [rank, R) then [0, rank)
+  if (int rc = launch_direct_pass(ctx, cfg, src, tgt, n_itiles, ctx->mg_rank * ptiles,
+                                  (ctx->mg_nranks - ctx->mg_rank) * ptiles, 0, ctx->mg_rank * ptiles, eps2, 0, st,
+                                  ctx->mg_nranks > 1 ? &gate : nullptr))
     return rc;
   return launch_reduce(ctx, cfg, d_local, ctx->mg_count, dt, do_kick != 0, st);
 }

@@ -52,6 +52,24 @@ def main():
                               super=os.environ.get("NB_BH_SUPER", "default"), build_ms=build, force_ms=force,
                               step_ms=build + force, interactions=inter.value, per_body=inter.value / n,
                               g_interactions_per_s=inter.value / force / 1e6)))
+    elif kind == "graph":
+        # steps/s of ParticleSystem.update, eager launches against CUDA-graph replay (launch-bound sizes)
+        method = nb.ForceMethod.BARNES_HUT if (len(sys.argv) > 3 and sys.argv[3] == "bh") else nb.ForceMethod.DIRECT_N2
+        st = ics.plummer(n, seed=42)
+        out = {}
+        for mode in ("eager", "graph"):
+            s = nb.ParticleSystem()
+            s.config_ = nb.SimulationConfig(particle_count=n, softening=0.01, dt=1e-3, force_method=method)
+            s.setState(nb.SimulationState(n, 0.0, 1e-3, 1.0, 0.01, method,
+                                          {k: st[k] for k in ("pos_x", "pos_y", "pos_z", "vel_x", "vel_y", "vel_z", "mass")}))
+            s.setUseCudaGraph(mode == "graph")
+            for _ in range(3):
+                s.update(1e-3)
+            out[mode] = timed(lambda: s.update(1e-3), reps=100, warm=5)
+            out[mode + "_nodes"] = s.graphNodeCount()
+        print(json.dumps(dict(path="step_graph", method=method.name, n=n, eager_ms=out["eager"], graph_ms=out["graph"],
+                              graph_nodes=out["graph_nodes"], eager_steps_per_s=1e3 / out["eager"],
+                              graph_steps_per_s=1e3 / out["graph"], speedup=out["eager"] / out["graph"])))
     elif kind == "render":
         # default camera and uniforms of the reference's Renderer; Plummer sphere scaled into view
         w, h = (int(sys.argv[3]), int(sys.argv[4])) if len(sys.argv) > 4 else (1280, 720)
