@@ -118,7 +118,8 @@ class ClockSampler:
                     reasons.add(nm)
         if not sm:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
-        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "power_w_max": float(max(pw)),
+        return {"sm_mhz": float(np.median(sm)), "sm_mhz_min": float(min(sm)), "sm_mhz_mean": float(np.mean(sm)),
+                "sm_max_mhz": float(max(mx)), "power_w_max": float(max(pw)), "power_w_mean": float(np.mean(pw)),
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
@@ -276,7 +277,7 @@ def main():
     clock_peak_tf = 148 * 128 * 2 * sm_max * 1e6 / 1e12
     kernel_ms = kms.value / max(kl.value, 1)                  # per force-kernel launch (CUDA events)
     pairs_per_launch = float(count) * float(n)
-    if world > 1 and exchange == "nccl":
+    if world > 1:
         kernel_ms = kms.value / args.steps                    # local + remote pass of one step
     achieved_tf = pairs_per_launch * FLOP_PER_INTERACTION / (kernel_ms * 1e-3) / 1e12 if kernel_ms > 0 else None
     roofline = {
@@ -321,7 +322,7 @@ def main():
         "scaling": "strong" if args.gpus > 1 else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": wl, "bodies": n, "ic": "plummer_henon_seed42", "softening": SOFTENING, "dt": DT,
                    "G": G_CONST, "parallelism": f"target_sharded_x{world}" if world > 1 else "single_gpu",
-                   "exchange": ("peer-memory push fused into the pack kernel + flag-gated force kernel (no NCCL in the step)"
+                   "exchange": ("peer-memory push fused into the pack kernel, flag wait between the local and remote pass (no NCCL in the step)"
                                 if exchange == "peer" else "NCCL all_gather_into_tensor overlapped with the local pass")
                    if world > 1 else "none",
                    "cache": "positions (16 MiB+ packed) are rewritten every step; compute bound, L2 state irrelevant"},

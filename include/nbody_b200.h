@@ -175,9 +175,9 @@ int nb_mgpu_finish(nb_context* ctx, const nb_particles* d_local, float dt, int d
 
 /* Peer exchange (default transport of nbody_b200/dist.py): the all-gather is fused into the pack
  * kernel, which stores every packed body into all R replicated source buffers over NVLink peer
- * mappings and then raises a per-peer step flag; ONE force launch sweeps all N sources in ring
- * order starting with the local slice and waits for a peer's flag when it reaches that peer's
- * tiles.  No collective-library call in the step.  Setup (collective, once, after nb_mgpu_layout):
+ * mappings and then raises a per-peer step flag; the local-source force pass overlaps the peers'
+ * pushes, a one-warp kernel waits for the flags, the remote-source pass follows in ring order.
+ * No collective-library call in the step.  Setup (collective, once, after nb_mgpu_layout):
  * every rank calls nb_mgpu_peer_alloc, the 64-byte CUDA-IPC handles are exchanged by the caller
  * (any transport), every rank calls nb_mgpu_peer_open for each other rank, then a barrier.
  * nb_mgpu_peer_step must be called the same number of times on every rank (it is the collective);
@@ -186,7 +186,7 @@ int nb_mgpu_peer_alloc(nb_context* ctx, unsigned char ipc_handle_out[64]);
 int nb_mgpu_peer_open(nb_context* ctx, int peer_rank, const unsigned char ipc_handle[64]);
 int nb_mgpu_peer_step(nb_context* ctx, const nb_particles* d_local, float dt, float G, float eps2, int do_step,
                       nb_stream s);
-/* the two halves of nb_mgpu_peer_step (pack + push + flag | gated forces + reduce [+ kick]) */
+/* the two halves of nb_mgpu_peer_step (pack + push + flag | local pass, flag wait, remote pass, reduce [+ kick]) */
 int nb_mgpu_peer_push(nb_context* ctx, const nb_particles* d_local, float dt, float G, int do_drift, nb_stream s);
 int nb_mgpu_peer_forces(nb_context* ctx, const nb_particles* d_local, float dt, float eps2, int do_kick, nb_stream s);
 /* same-process peers (several contexts in one process, e.g. one host thread driving all GPUs with
@@ -194,6 +194,25 @@ int nb_mgpu_peer_forces(nb_context* ctx, const nb_particles* d_local, float dt, 
 int nb_mgpu_peer_block(nb_context* ctx, void** block, size_t* bytes);
 int nb_mgpu_peer_map(nb_context* ctx, int peer_rank, void* peer_block);
 int nb_mgpu_peer_close(nb_context* ctx);
+
+/* ---- target-sharded Barnes-Hut over replicated state (named as future
+ * work by the reference, openspec/changes/evolve-nbody-platform/tasks.md:24-31).  Every rank holds
+ * ALL bodies and rebuilds the identical tree; a rank traverses only the groups dealt to it and its
+ * traversal kernel stores the accelerations (sorted order, float4/body) into every rank's exchange
+ * buffer over NVLink peer mappings, then raises its step flag; nb_mgpu_bh_finish waits for all flags,
+ * scatters to body order and kicks every body, so the replicas stay bit-identical and positions are
+ * never exchanged.  Setup as for the direct peer exchange: alloc on every rank, swap the 64-byte
+ * handles, open (or map by pointer inside one process), barrier.  nb_mgpu_bh_step is collective. */
+int nb_mgpu_bh_alloc(nb_context* ctx, size_t n_total, int rank, int nranks, unsigned char ipc_handle_out[64]);
+int nb_mgpu_bh_open(nb_context* ctx, int peer_rank, const unsigned char ipc_handle[64]);
+int nb_mgpu_bh_block(nb_context* ctx, void** block, size_t* bytes);
+int nb_mgpu_bh_map(nb_context* ctx, int peer_rank, void* peer_block);
+int nb_mgpu_bh_step(nb_context* ctx, const nb_particles* d_all, float dt, float theta, float G, float eps,
+                    int do_step, nb_stream s);
+int nb_mgpu_bh_traverse(nb_context* ctx, const nb_particles* d_all, float dt, float theta, float G, float eps,
+                        int do_drift, nb_stream s);
+int nb_mgpu_bh_finish(nb_context* ctx, const nb_particles* d_all, float dt, int do_kick, nb_stream s);
+int nb_mgpu_bh_close(nb_context* ctx);
 
 #ifdef __cplusplus
 }

@@ -107,6 +107,14 @@ SYMBOLS = {
     "nb_mgpu_peer_block": (_i, [_vp, C.POINTER(_vp), C.POINTER(_sz)]),
     "nb_mgpu_peer_map": (_i, [_vp, _i, _vp]),
     "nb_mgpu_peer_close": (_i, [_vp]),
+    "nb_mgpu_bh_alloc": (_i, [_vp, _sz, _i, _i, _vp]),
+    "nb_mgpu_bh_open": (_i, [_vp, _i, _vp]),
+    "nb_mgpu_bh_block": (_i, [_vp, C.POINTER(_vp), C.POINTER(_sz)]),
+    "nb_mgpu_bh_map": (_i, [_vp, _i, _vp]),
+    "nb_mgpu_bh_step": (_i, [_vp, _pp, _f, _f, _f, _f, _i, _vp]),
+    "nb_mgpu_bh_traverse": (_i, [_vp, _pp, _f, _f, _f, _f, _i, _vp]),
+    "nb_mgpu_bh_finish": (_i, [_vp, _pp, _f, _i, _vp]),
+    "nb_mgpu_bh_close": (_i, [_vp]),
 }
 
 

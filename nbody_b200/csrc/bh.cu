@@ -16,7 +16,8 @@
 #include <cstdlib>
 #include <cstring>
 
-#include "common.cuh"
+#include "bh.cuh"
+#include "direct.cuh"
 
 namespace nb {
 
@@ -226,7 +227,13 @@ __global__ void __launch_bounds__(256) bh_groups_kernel(int n, int smax, int gma
 constexpr int BH_WARPS = 4;
 constexpr int BH_LIST = 64;
 
-template <int BPL, bool EPS0>
+// SHARDED (multi-GPU, mgpu.cu): every rank holds the same tree; this rank traverses only the groups it
+// is dealt (by the group's first sorted body, so the deal is identical on every rank although the
+// order of the group array is not) and stores each body's acceleration, in SORTED order, into the
+// exchange buffer of EVERY rank over NVLink peer mappings -- contiguous runs of up to 64 float4 per
+// group and peer -- so the all-gather of accelerations is the traversal kernel's own epilogue.  The
+// last CTA to finish raises this rank's step flag on every peer.
+template <int BPL, bool EPS0, bool SHARDED>
 __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const float4* __restrict__ node_com,
                                                                   const int4* __restrict__ meta,
                                                                   const int32_t* __restrict__ perm,
@@ -238,7 +245,7 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
                                                                   const int2* __restrict__ groups,
                                                                   const int* __restrict__ ngroups,
                                                                   int* __restrict__ cursor, int stack_cap,
-                                                                  int* __restrict__ max_stack) {
+                                                                  int* __restrict__ max_stack, BhShard sh) {
   extern __shared__ __align__(16) unsigned char bh_smem[];
   __shared__ float size2_tab[32];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -260,6 +267,7 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
   if (g >= total_groups) break;
   const int2 grp = groups[g];
   const int k0 = grp.x, gcnt = grp.y;
+  if (SHARDED && (((unsigned)k0 * 2654435761u) >> 20) % (unsigned)sh.nranks != (unsigned)sh.rank) continue;  // dealt to another rank
 
   // scalar loads on purpose: a float4 load pins x,y,z to one aligned register quad, and ptxas then
   // re-packs the (body 0, body 1) pairs with MOVs for every list entry (4.5 MOVs per entry measured)
@@ -392,10 +400,17 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
 #pragma unroll
   for (int b = 0; b < BPL; b++) {
     if (b * 32 + lane < gcnt) {
-      const int i = perm[k0 + b * 32 + lane];
-      ax[i] = sx[b];
-      ay[i] = sy[b];
-      az[i] = sz[b];
+      if (SHARDED) {
+        const float4 v = make_float4(sx[b], sy[b], sz[b], 0.f);
+#pragma unroll
+        for (int r = 0; r < 8; r++)
+          if (r < sh.nranks) sh.out[r][k0 + b * 32 + lane] = v;
+      } else {
+        const int i = perm[k0 + b * 32 + lane];
+        ax[i] = sx[b];
+        ay[i] = sy[b];
+        az[i] = sz[b];
+      }
     }
   }
   visits_bodies += (unsigned long long)visits * (unsigned long long)gcnt;
@@ -404,6 +419,42 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
   if (lane == 0 && visits_bodies) {
     atomicAdd(counter, visits_bodies);
     atomicMax(max_stack, deepest);
+  }
+  if (SHARDED) {
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const unsigned prev = atomicAdd(sh.done_counter, 1u);
+      if (prev == gridDim.x - 1) {  // every CTA's peer stores are fenced: publish
+        *sh.done_counter = 0;
+        __threadfence_system();
+        for (int r = 0; r < sh.nranks; r++)
+          if (r != sh.rank)
+            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(sh.flags[r] + sh.flag_index), "r"(sh.step)
+                         : "memory");
+      }
+    }
+  }
+}
+
+// accelerations arrive in sorted order; hand them back to body order, optionally with the kick
+// (src/cuda/integrator.cu:24-36, same rounding sequence as integrate.cu)
+template <bool KICK>
+__global__ void __launch_bounds__(256) bh_shard_finish_kernel(const float4* __restrict__ acc_sorted,
+                                                              const int32_t* __restrict__ perm, nb_particles d,
+                                                              size_t n, float dt) {
+  const size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int i = perm[k];
+  const float4 a = acc_sorted[k];
+  d.acc_x[i] = a.x;
+  d.acc_y[i] = a.y;
+  d.acc_z[i] = a.z;
+  if (KICK) {
+    const float dt_half = __fmul_rn(0.5f, dt);
+    d.vel_x[i] = __fadd_rn(d.vel_x[i], __fmul_rn(__fadd_rn(d.acc_old_x[i], a.x), dt_half));
+    d.vel_y[i] = __fadd_rn(d.vel_y[i], __fmul_rn(__fadd_rn(d.acc_old_y[i], a.y), dt_half));
+    d.vel_z[i] = __fadd_rn(d.vel_z[i], __fmul_rn(__fadd_rn(d.acc_old_z[i], a.z), dt_half));
   }
 }
 
@@ -496,7 +547,8 @@ static int bh_check_overflow(BH* b) {
   return NB_OK;
 }
 
-int bh_forces(nb_context* ctx, const nb_particles* d, float theta, float G, float eps, cudaStream_t st) {
+int bh_forces(nb_context* ctx, const nb_particles* d, float theta, float G, float eps, cudaStream_t st,
+              const BhShard* shard) {
   BH* b = bh_get(ctx);
   const size_t n = d->count;
   if (n == 0) return NB_OK;
@@ -519,9 +571,9 @@ int bh_forces(nb_context* ctx, const nb_particles* d, float theta, float G, floa
   if (!b->occ) {
     int o = 0;
     if (b->group == 64)
-      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, bh_force_kernel<2, false>, BH_WARPS * 32, smem);
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, bh_force_kernel<2, false, false>, BH_WARPS * 32, smem);
     else
-      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, bh_force_kernel<1, false>, BH_WARPS * 32, smem);
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, bh_force_kernel<1, false, false>, BH_WARPS * 32, smem);
     b->occ = o > 0 ? o : 1;
   }
   long long max_groups = (long long)n;  // upper bound (the real count lives on the device)
@@ -529,12 +581,19 @@ int bh_forces(nb_context* ctx, const nb_particles* d, float theta, float G, floa
   long long cap = (long long)b->occ * ctx->sm_count;
   const unsigned grid = (unsigned)(want < cap ? want : cap);
   ProfScope prof(ctx, st);
-#define NB_BH_LAUNCH(BPL_, E_)                                                                                     \
-  bh_force_kernel<BPL_, E_><<<grid, BH_WARPS * 32, smem, st>>>(                                                    \
+  BhShard none{};
+  const BhShard shv = shard ? *shard : none;
+#define NB_BH_LAUNCH_S(BPL_, E_, S_)                                                                               \
+  bh_force_kernel<BPL_, E_, S_><<<grid, BH_WARPS * 32, smem, st>>>(                                                \
       (int)n, b->node_com.as<float4>(), b->meta.as<int4>(), b->perm.as<int32_t>(), misc, theta * theta, G, eps2,  \
       d->acc_x, d->acc_y, d->acc_z, reinterpret_cast<unsigned long long*>(misc + 40), b->d_flag,                   \
       b->groups.as<int2>(), reinterpret_cast<const int*>(misc) + 44, cursor, b->stack_cap,                        \
-      reinterpret_cast<int*>(misc) + 46)
+      reinterpret_cast<int*>(misc) + 46, shv)
+#define NB_BH_LAUNCH(BPL_, E_)               \
+  do {                                       \
+    if (shard) NB_BH_LAUNCH_S(BPL_, E_, true); \
+    else NB_BH_LAUNCH_S(BPL_, E_, false);    \
+  } while (0)
   if (b->group == 64) {
     if (eps0) NB_BH_LAUNCH(2, true);
     else NB_BH_LAUNCH(2, false);
@@ -542,7 +601,29 @@ int bh_forces(nb_context* ctx, const nb_particles* d, float theta, float G, floa
     if (eps0) NB_BH_LAUNCH(1, true);
     else NB_BH_LAUNCH(1, false);
   }
+#undef NB_BH_LAUNCH_S
 #undef NB_BH_LAUNCH
+  NB_LAUNCH_CHECK(ctx);
+  return NB_OK;
+}
+
+int bh_shard_wait(nb_context* ctx, const unsigned* flags, int flag_base, unsigned step, int nranks, int self,
+                  int* timeout_flag, cudaStream_t st) {
+  return launch_peer_wait(ctx, flags, flag_base, step, nranks, self, timeout_flag, st);
+}
+
+int bh_shard_finish(nb_context* ctx, const float4* acc_sorted, const nb_particles* d, float dt, bool kick,
+                    cudaStream_t st) {
+  BH* b = bh_get(ctx);
+  const size_t n = d->count;
+  if (n == 0) return NB_OK;
+  if (!b->built || b->n != n) {
+    set_error("Barnes-Hut: sharded finish without a tree built for these particles");
+    return NB_ERR_INVALID;
+  }
+  const unsigned gn = (unsigned)((n + 255) / 256);
+  if (kick) bh_shard_finish_kernel<true><<<gn, 256, 0, st>>>(acc_sorted, b->perm.as<int32_t>(), *d, n, dt);
+  else bh_shard_finish_kernel<false><<<gn, 256, 0, st>>>(acc_sorted, b->perm.as<int32_t>(), *d, n, dt);
   NB_LAUNCH_CHECK(ctx);
   return NB_OK;
 }
@@ -568,7 +649,7 @@ int nb_bh_forces(nb_context* ctx, const nb_particles* d, float theta, float G, f
     return NB_ERR_INVALID;
   }
   NB_CUDA(cudaSetDevice(ctx->device));
-  return bh_forces(ctx, d, theta, G, eps, (cudaStream_t)s);
+  return bh_forces(ctx, d, theta, G, eps, (cudaStream_t)s, nullptr);
 }
 
 int nb_bh_export(nb_context* ctx, uint32_t* keys, int32_t* perm, int32_t* left, int32_t* right, int32_t* parent,

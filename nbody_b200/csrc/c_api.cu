@@ -178,6 +178,7 @@ int nb_context_destroy(nb_context* ctx) {
   cudaSetDevice(ctx->device);
   cudaDeviceSynchronize();
   nb_mgpu_peer_close(ctx);
+  nb_mgpu_bh_close(ctx);
   render_destroy(ctx);
   bh_destroy(ctx);
   sh_destroy(ctx);

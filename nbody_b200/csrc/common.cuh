@@ -166,7 +166,7 @@ struct nb_context {
   nb::DevBuf partial;   // stream-K partial accelerations
   nb_pass pass[2];
   int n_pass = 0;
-  int direct_occ[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // resident CTAs/SM per kernel variant (lazy)
+  int direct_occ[4] = {0, 0, 0, 0};  // resident CTAs/SM per kernel config (lazy)
   // energy
   nb::DevBuf red;       // per-CTA fp64 partials
   double* h_red = nullptr;  // pinned
@@ -188,5 +188,8 @@ struct nb_context {
   // multi-GPU
   size_t mg_n_total = 0, mg_begin = 0, mg_count = 0, mg_padded = 0;
   int mg_rank = 0, mg_nranks = 1;
-  struct PeerState* peer = nullptr;  // CUDA-IPC exchange blocks (mgpu.cu)
+  struct PeerState* peer = nullptr;     // CUDA-IPC exchange blocks (mgpu.cu): direct N^2 sources
+  struct PeerState* peer_bh = nullptr;  // ... and sharded Barnes-Hut accelerations
+  size_t bhs_n = 0;
+  int bhs_rank = 0, bhs_nranks = 1;
 };

@@ -54,7 +54,7 @@ __global__ void __launch_bounds__(256) pack_kernel(nb_particles d, float4* __res
 // stored straight into slot `slot_off` of EVERY rank's replicated source buffer -- the local one and,
 // through NVLink/NVSwitch peer mappings, the R-1 remote ones -- so no separate collective runs.  The
 // last CTA to finish raises this rank's step flag on every peer (release at system scope); the
-// consumers are the gated force kernels there.
+// consumer there is peer_flags_wait_kernel, enqueued between the local and the remote force pass.
 template <bool DRIFT>
 __global__ void __launch_bounds__(256) pack_push_kernel(nb_particles d, PeerBufs pb, size_t slot_off, size_t n,
                                                         size_t n_pad, float G, float dt, unsigned step,
@@ -108,46 +108,47 @@ int launch_pack_push(nb_context* ctx, const nb_particles* d, const PeerBufs& pb,
   return NB_OK;
 }
 
-// spin (bounded) until peer `peer` has published `gate.step`; then order the async-proxy (TMA) reads
-// that follow after the acquire
-__device__ __noinline__ void peer_wait(const PeerGate& gate, int peer) {  // cold: keep it out of the hot kernel's registers
-  const unsigned* f = gate.flags + gate.flag_base + peer;
+// One thread per peer spins (bounded) until that peer has raised `step` in this rank's flag block.
+// Runs between the local-source pass and the remote-source pass, so the hot force kernel itself
+// carries no waiting code (an in-kernel gate cost 5 % of the step through register pressure).
+__global__ void peer_flags_wait_kernel(const unsigned* __restrict__ flags, int flag_base, unsigned step, int nranks,
+                                       int self, int* __restrict__ timeout_flag) {
+  const int r = threadIdx.x;
+  if (r >= nranks || r == self) return;
+  const unsigned* f = flags + flag_base + r;
   unsigned long long t0 = 0;
   for (unsigned spins = 0;; spins++) {
     unsigned v;
     asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
-    if ((int)(v - gate.step) >= 0) break;
+    if ((int)(v - step) >= 0) break;
     if ((spins & 1023u) == 1023u) {  // a dead peer must not hang the GPU: give up after ~20 s and say so
       unsigned long long now;
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
       if (t0 == 0) t0 = now;
       else if (now - t0 > 20000000000ull) {
-        *gate.timeout_flag = 1;
+        *timeout_flag = 1;
         break;
       }
     }
   }
-  asm volatile("fence.proxy.async;" ::: "memory");
+}
+
+int launch_peer_wait(nb_context* ctx, const unsigned* flags, int flag_base, unsigned step, int nranks, int self,
+                     int* timeout_flag, cudaStream_t st) {
+  peer_flags_wait_kernel<<<1, 32, 0, st>>>(flags, flag_base, step, nranks, self, timeout_flag);
+  NB_LAUNCH_CHECK(ctx);
+  return NB_OK;
 }
 
 // ---------------------------------------------------------------------------------------------
 // force kernel
 // ---------------------------------------------------------------------------------------------
-// Source tile j of a pass is tile ja0 + j for j < na, then jb0 + (j - na).  GATED (multi-GPU peer exchange,
-// mgpu.cu): tiles [p*gate.ptiles, (p+1)*gate.ptiles) were pushed into `src` by peer p's
-// pack_push_kernel over NVLink; the thread that issues the TMA copies waits for peer p's step flag
-// (ld.acquire.sys) the first time it touches one of p's tiles, so the math starts on the local
-// slice and runs into each peer's slice as it lands.
-#ifndef NB_DIRECT_MINB
-// the gated variant needs the cap to stay at 48 registers (5 CTAs/SM like the plain one)
-#define NB_DIRECT_MINB(T, GATED) (((GATED) && (T) == 256) ? 5 : 0)  /* 0 = no constraint */
-#endif
-template <int T, int I, int JT, bool EPS0, bool GATED>
-__global__ void __launch_bounds__(T, NB_DIRECT_MINB(T, GATED)) direct_force_kernel(const float4* __restrict__ src,
+template <int T, int I, int JT, bool EPS0>
+__global__ void __launch_bounds__(T) direct_force_kernel(const float4* __restrict__ src,
                                                           const float4* __restrict__ tgt,
                                                           float* __restrict__ partial, long long U, int UJ,
                                                           int ja0, int na, int jb0, float eps2,
-                                                          unsigned long long slot_base, PeerGate gate) {
+                                                          unsigned long long slot_base) {
   constexpr int P = I / 2;
   constexpr int IT = T * I;
   constexpr uint32_t TILE_BYTES = JT * sizeof(float4);
@@ -168,16 +169,8 @@ __global__ void __launch_bounds__(T, NB_DIRECT_MINB(T, GATED)) direct_force_kern
 
   int itile = (int)(u0 / UJ);
   int jt = (int)(u0 - (long long)itile * UJ);
-  unsigned ready_peers = 1u << gate.self;  // peers whose slice is known to have landed (thread 0 only)
   auto jtile_ptr = [&](int j) -> const float4* {
     const int g = (j < na) ? (ja0 + j) : (jb0 + (j - na));
-    if (GATED) {
-      const int peer = g / gate.ptiles;
-      if (!((ready_peers >> peer) & 1u)) {
-        peer_wait(gate, peer);
-        ready_peers |= 1u << peer;
-      }
-    }
     return src + (size_t)g * JT;
   };
   if (tid == 0) {
@@ -329,25 +322,19 @@ static const size_t kSmallN = 32768;
 const DirectCfg& direct_cfg(size_t n_total_sources) { return n_total_sources < kSmallN ? kCfgSmall : kCfgBig; }
 
 template <int T, int I, int JT>
-static int occupancy(bool eps0, bool gated) {
+static int occupancy(bool eps0) {
   int occ = 0;
-#define NB_OCC(E_, G_) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, direct_force_kernel<T, I, JT, E_, G_>, T, 0)
-  if (eps0) {
-    if (gated) NB_OCC(true, true);
-    else NB_OCC(true, false);
-  } else {
-    if (gated) NB_OCC(false, true);
-    else NB_OCC(false, false);
-  }
-#undef NB_OCC
+  if (eps0)
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, direct_force_kernel<T, I, JT, true>, T, 0);
+  else
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, direct_force_kernel<T, I, JT, false>, T, 0);
   return occ > 0 ? occ : 1;
 }
 
 // Launch one stream-K pass.  Source tiles [ja0, ja0+na) then [jb0, jb0+nbt) of `src` (tile = JT
-// bodies) against n_itiles target tiles of `tgt`.  gate != nullptr: peer-gated sources (see the kernel).
+// bodies) against n_itiles target tiles of `tgt`.
 int launch_direct_pass(nb_context* ctx, const DirectCfg& cfg, const float4* src, const float4* tgt, int n_itiles,
-                       int ja0, int na, int jb0, int nbt, float eps2, int pass_index, cudaStream_t st,
-                       const PeerGate* gate) {
+                       int ja0, int na, int jb0, int nbt, float eps2, int pass_index, cudaStream_t st) {
   const int UJ = na + nbt;
   nb_pass& ps = ctx->pass[pass_index];
   ps.UJ = UJ;
@@ -360,9 +347,8 @@ int launch_direct_pass(nb_context* ctx, const DirectCfg& cfg, const float4* src,
   }
   const bool big = (cfg.T == kCfgBig.T);
   const bool eps0 = !(eps2 > 0.f);
-  // stream-K cuts the work into exactly as many runs as CTAs are co-resident: ask about THIS kernel variant
-  int& occ = ctx->direct_occ[(gate ? 4 : 0) + (big ? 0 : 2) + (eps0 ? 1 : 0)];
-  if (occ == 0) occ = big ? occupancy<256, 2, 1024>(eps0, gate != nullptr) : occupancy<128, 2, 256>(eps0, gate != nullptr);
+  int& occ = ctx->direct_occ[(big ? 0 : 2) + (eps0 ? 1 : 0)];
+  if (occ == 0) occ = big ? occupancy<256, 2, 1024>(eps0) : occupancy<128, 2, 256>(eps0);
   int use_occ = occ;
   if (const char* e = getenv("NB_DIRECT_OCC")) {  // tuning knob: resident CTAs per SM
     const int v = atoi(e);
@@ -376,25 +362,17 @@ int launch_direct_pass(nb_context* ctx, const DirectCfg& cfg, const float4* src,
                                          : ps.slot_base + (size_t)ps.G + n_itiles;
   if (int rc = ctx->partial.ensure(slots * 3 * cfg.IT() * sizeof(float))) return rc;
   float* part = ctx->partial.as<float>();
-  PeerGate none{};
-  const PeerGate gt = gate ? *gate : none;
-#define NB_LAUNCH_DIRECT(T_, I_, JT_, E_, G_)                                                                  \
-  direct_force_kernel<T_, I_, JT_, E_, G_><<<ps.G, T_, 0, st>>>(src, tgt, part, ps.U, UJ, ja0, na, jb0, eps2,   \
-                                                                (unsigned long long)ps.slot_base, gt)
-#define NB_LAUNCH_DIRECT_E(T_, I_, JT_, E_)            \
-  do {                                                 \
-    if (gate) NB_LAUNCH_DIRECT(T_, I_, JT_, E_, true); \
-    else NB_LAUNCH_DIRECT(T_, I_, JT_, E_, false);     \
-  } while (0)
+#define NB_LAUNCH_DIRECT(T_, I_, JT_, E_)                                                             \
+  direct_force_kernel<T_, I_, JT_, E_><<<ps.G, T_, 0, st>>>(src, tgt, part, ps.U, UJ, ja0, na, jb0, eps2, \
+                                                            (unsigned long long)ps.slot_base)
   ProfScope prof(ctx, st);
   if (big) {
-    if (eps0) NB_LAUNCH_DIRECT_E(256, 2, 1024, true);
-    else NB_LAUNCH_DIRECT_E(256, 2, 1024, false);
+    if (eps0) NB_LAUNCH_DIRECT(256, 2, 1024, true);
+    else NB_LAUNCH_DIRECT(256, 2, 1024, false);
   } else {
-    if (eps0) NB_LAUNCH_DIRECT_E(128, 2, 256, true);
-    else NB_LAUNCH_DIRECT_E(128, 2, 256, false);
+    if (eps0) NB_LAUNCH_DIRECT(128, 2, 256, true);
+    else NB_LAUNCH_DIRECT(128, 2, 256, false);
   }
-#undef NB_LAUNCH_DIRECT_E
 #undef NB_LAUNCH_DIRECT
   NB_LAUNCH_CHECK(ctx);
   return NB_OK;
@@ -452,7 +430,7 @@ int direct_run(nb_context* ctx, const nb_particles* d, float dt, float G, float 
   const int n_itiles = (int)((n + cfg.IT() - 1) / cfg.IT());
   const int n_jt = (int)((n + cfg.JT - 1) / cfg.JT);
   ctx->n_pass = 1;
-  if (int rc = launch_direct_pass(ctx, cfg, src, src, n_itiles, 0, n_jt, 0, 0, eps2, 0, st, nullptr)) return rc;
+  if (int rc = launch_direct_pass(ctx, cfg, src, src, n_itiles, 0, n_jt, 0, 0, eps2, 0, st)) return rc;
   return launch_reduce(ctx, cfg, d, n, dt, step, st);
 }
 

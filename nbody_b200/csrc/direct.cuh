@@ -18,16 +18,6 @@ struct PeerBufs {
   unsigned* flags[NB_MAX_PEERS];
   int nranks, self;
 };
-// what the gated force kernel needs to wait for a peer's slice
-struct PeerGate {
-  const unsigned* flags;   // this rank's flag block
-  int flag_base;           // parity * NB_MAX_PEERS
-  unsigned step;           // value a peer stores when its slice of this step has landed
-  int ptiles;              // source tiles per peer slice
-  int self;
-  int* timeout_flag;       // host-mapped: set when a wait gave up
-};
-
 const DirectCfg& direct_cfg(size_t n_total_sources);
 int launch_pack_push(nb_context* ctx, const nb_particles* d, const PeerBufs& pb, size_t slot_off, size_t n,
                      size_t n_pad, float G, float dt, bool drift, unsigned step, int flag_index, unsigned* done_counter,
@@ -35,8 +25,9 @@ int launch_pack_push(nb_context* ctx, const nb_particles* d, const PeerBufs& pb,
 int launch_pack(nb_context* ctx, const nb_particles* d, float4* src, size_t n, size_t n_pad, float G, float dt,
                 bool drift, cudaStream_t st);
 int launch_direct_pass(nb_context* ctx, const DirectCfg& cfg, const float4* src, const float4* tgt, int n_itiles,
-                       int ja0, int na, int jb0, int nbt, float eps2, int pass_index, cudaStream_t st,
-                       const PeerGate* gate);
+                       int ja0, int na, int jb0, int nbt, float eps2, int pass_index, cudaStream_t st);
+int launch_peer_wait(nb_context* ctx, const unsigned* flags, int flag_base, unsigned step, int nranks, int self,
+                     int* timeout_flag, cudaStream_t st);
 int launch_reduce(nb_context* ctx, const DirectCfg& cfg, const nb_particles* d, size_t n, float dt, bool kick,
                   cudaStream_t st);
 

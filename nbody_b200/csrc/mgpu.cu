@@ -7,6 +7,7 @@
 // overlaps the gather.
 #include <cstring>
 
+#include "bh.cuh"
 #include "direct.cuh"
 
 using namespace nb;
@@ -69,7 +70,7 @@ int nb_mgpu_forces_local(nb_context* ctx, const float* gathered_src, float eps2,
   ctx->n_pass = 1;
   ctx->pass[1].U = 0;
   return launch_direct_pass(ctx, cfg, src, tgt, n_itiles, ctx->mg_rank * ptiles, ptiles, 0, 0, eps2, 0,
-                            (cudaStream_t)s, nullptr);
+                            (cudaStream_t)s);
 }
 
 int nb_mgpu_forces_remote(nb_context* ctx, const float* gathered_src, float eps2, nb_stream s) {
@@ -87,7 +88,7 @@ int nb_mgpu_forces_remote(nb_context* ctx, const float* gathered_src, float eps2
   // the other R-1 slices in ring order: rank+1, ..., R-1, 0, ..., rank-1
   return launch_direct_pass(ctx, cfg, src, tgt, n_itiles, (ctx->mg_rank + 1) * ptiles,
                             (ctx->mg_nranks - 1 - ctx->mg_rank) * ptiles, 0, ctx->mg_rank * ptiles, eps2, 1,
-                            (cudaStream_t)s, nullptr);
+                            (cudaStream_t)s);
 }
 
 int nb_mgpu_finish(nb_context* ctx, const nb_particles* d_local, float dt, int do_kick, nb_stream s) {
@@ -98,11 +99,11 @@ int nb_mgpu_finish(nb_context* ctx, const nb_particles* d_local, float dt, int d
 
 // ---- peer exchange: no collective library in the step ----------------------------------------------------
 // Each rank owns ONE cudaMalloc'ed exchange block {flags[2][8] | replicated sources, parity 0 | parity 1}
-// and maps every peer's block with CUDA IPC.  A step is three launches, as on one GPU:
+// and maps every peer's block with CUDA IPC.  Per step:
 //   pack_push_kernel   store-acc + drift + pack, stored into all R replicated buffers over NVLink, then
 //                      this rank's step flag raised on every peer;
-//   direct_force_kernel<GATED>  all N sources in ring order starting with the local slice; the TMA
-//                      producer thread waits for a peer's flag when it first reaches that peer's tiles;
+//   direct_force_kernel  local-source pass (overlaps the peers' pushes), peer_flags_wait_kernel (one
+//                      thread per peer, acquire at system scope), remote-source pass in ring order;
 //   reduce_kernel      fixed-order sum of the stream-K partials + kick.
 // Buffers alternate by step parity: a rank can only run one step ahead of its slowest peer (it needs
 // that peer's slice of the current step), so the slice it overwrites was consumed two steps ago.
@@ -118,26 +119,32 @@ struct PeerState {
 };
 static const size_t kFlagBytes = 4096;
 
-static PeerState* peer_get(nb_context* ctx) {
-  if (!ctx->peer) ctx->peer = new PeerState();
-  return ctx->peer;
+static int peer_block_close(nb_context* ctx, PeerState*& slot) {
+  if (!slot) return NB_OK;
+  PeerState* ps = slot;
+  cudaSetDevice(ctx->device);
+  cudaDeviceSynchronize();
+  for (int r = 0; r < NB_MAX_PEERS; r++) {
+    if (ps->opened[r] && ps->peer_block[r]) cudaIpcCloseMemHandle(ps->peer_block[r]);
+    ps->peer_block[r] = nullptr;
+    ps->opened[r] = false;
+  }
+  if (ps->block) cudaFree(ps->block);
+  if (ps->done_counter) cudaFree(ps->done_counter);
+  if (ps->h_timeout) cudaFreeHost(ps->h_timeout);
+  delete ps;
+  slot = nullptr;
+  return NB_OK;
 }
 
-static size_t peer_buf_floats4(const nb_context* ctx) { return (size_t)ctx->mg_nranks * ctx->mg_padded; }
-
-int nb_mgpu_peer_alloc(nb_context* ctx, unsigned char handle_out[64]) {
-  if (!ctx || ctx->mg_n_total == 0 || !handle_out) {
-    set_error("mgpu peer: nb_mgpu_layout not called or null handle");
-    return NB_ERR_INVALID;
-  }
-  if (ctx->mg_nranks > NB_MAX_PEERS) {
-    set_error("mgpu peer: at most %d ranks", NB_MAX_PEERS);
-    return NB_ERR_INVALID;
-  }
+// one zeroed cudaMalloc'ed block {flags | payload}, its IPC handle, a done counter and a host-mapped
+// timeout flag
+static int peer_block_alloc(nb_context* ctx, PeerState*& slot, size_t payload_bytes, int self,
+                            unsigned char handle_out[64]) {
   NB_CUDA(cudaSetDevice(ctx->device));
-  nb_mgpu_peer_close(ctx);
-  PeerState* ps = peer_get(ctx);
-  ps->block_bytes = kFlagBytes + 2 * peer_buf_floats4(ctx) * sizeof(float4);
+  peer_block_close(ctx, slot);
+  PeerState* ps = slot = new PeerState();
+  ps->block_bytes = kFlagBytes + payload_bytes;
   NB_CUDA(cudaMalloc(&ps->block, ps->block_bytes));
   NB_CUDA(cudaMemset(ps->block, 0, ps->block_bytes));
   NB_CUDA(cudaMalloc(&ps->done_counter, sizeof(unsigned)));
@@ -151,18 +158,13 @@ int nb_mgpu_peer_alloc(nb_context* ctx, unsigned char handle_out[64]) {
   cudaIpcMemHandle_t h;
   NB_CUDA(cudaIpcGetMemHandle(&h, ps->block));
   memcpy(handle_out, &h, 64);
-  ps->peer_block[ctx->mg_rank] = ps->block;
+  ps->peer_block[self] = ps->block;
   return NB_OK;
 }
 
-int nb_mgpu_peer_open(nb_context* ctx, int peer_rank, const unsigned char handle[64]) {
-  if (!ctx || !ctx->peer || !ctx->peer->block || !handle || peer_rank < 0 || peer_rank >= ctx->mg_nranks) {
-    set_error("mgpu peer open: bad arguments or nb_mgpu_peer_alloc not called");
-    return NB_ERR_INVALID;
-  }
-  if (peer_rank == ctx->mg_rank) return NB_OK;
+static int peer_block_open(nb_context* ctx, PeerState* ps, int self, int peer_rank, const unsigned char handle[64]) {
+  if (peer_rank == self) return NB_OK;
   NB_CUDA(cudaSetDevice(ctx->device));
-  PeerState* ps = ctx->peer;
   cudaIpcMemHandle_t h;
   memcpy(&h, handle, 64);
   void* p = nullptr;
@@ -172,22 +174,31 @@ int nb_mgpu_peer_open(nb_context* ctx, int peer_rank, const unsigned char handle
   return NB_OK;
 }
 
-int nb_mgpu_peer_close(nb_context* ctx) {
-  if (!ctx || !ctx->peer) return NB_OK;
-  PeerState* ps = ctx->peer;
-  cudaSetDevice(ctx->device);
-  cudaDeviceSynchronize();
-  for (int r = 0; r < NB_MAX_PEERS; r++) {
-    if (ps->opened[r] && ps->peer_block[r]) cudaIpcCloseMemHandle(ps->peer_block[r]);
-    ps->peer_block[r] = nullptr;
-    ps->opened[r] = false;
+static size_t peer_buf_floats4(const nb_context* ctx) { return (size_t)ctx->mg_nranks * ctx->mg_padded; }
+
+int nb_mgpu_peer_alloc(nb_context* ctx, unsigned char handle_out[64]) {
+  if (!ctx || ctx->mg_n_total == 0 || !handle_out) {
+    set_error("mgpu peer: nb_mgpu_layout not called or null handle");
+    return NB_ERR_INVALID;
   }
-  if (ps->block) cudaFree(ps->block);
-  if (ps->done_counter) cudaFree(ps->done_counter);
-  if (ps->h_timeout) cudaFreeHost(ps->h_timeout);
-  delete ps;
-  ctx->peer = nullptr;
-  return NB_OK;
+  if (ctx->mg_nranks > NB_MAX_PEERS) {
+    set_error("mgpu peer: at most %d ranks", NB_MAX_PEERS);
+    return NB_ERR_INVALID;
+  }
+  return peer_block_alloc(ctx, ctx->peer, 2 * peer_buf_floats4(ctx) * sizeof(float4), ctx->mg_rank, handle_out);
+}
+
+int nb_mgpu_peer_open(nb_context* ctx, int peer_rank, const unsigned char handle[64]) {
+  if (!ctx || !ctx->peer || !ctx->peer->block || !handle || peer_rank < 0 || peer_rank >= ctx->mg_nranks) {
+    set_error("mgpu peer open: bad arguments or nb_mgpu_peer_alloc not called");
+    return NB_ERR_INVALID;
+  }
+  return peer_block_open(ctx, ctx->peer, ctx->mg_rank, peer_rank, handle);
+}
+
+int nb_mgpu_peer_close(nb_context* ctx) {
+  if (!ctx) return NB_OK;
+  return peer_block_close(ctx, ctx->peer);
 }
 
 int nb_mgpu_peer_block(nb_context* ctx, void** block, size_t* bytes) {
@@ -273,20 +284,21 @@ int nb_mgpu_peer_forces(nb_context* ctx, const nb_particles* d_local, float dt, 
   const float4* tgt = src + (size_t)ctx->mg_rank * ctx->mg_padded;
   const int ptiles = (int)(ctx->mg_padded / cfg.JT);
   const int n_itiles = (int)((ctx->mg_count + cfg.IT() - 1) / cfg.IT());
-  PeerGate gate{};
-  gate.flags = pb.flags[ctx->mg_rank];
-  gate.flag_base = parity * NB_MAX_PEERS;
-  gate.step = step;
-  gate.ptiles = ptiles;
-  gate.self = ctx->mg_rank;
-  gate.timeout_flag = ps->d_timeout;
+  // local-source pass: needs nothing from the peers and overlaps their pushes
   ctx->n_pass = 1;
   ctx->pass[1].U = 0;
-  // ring order from the local slice: [rank, R) then [0, rank)
-  if (int rc = launch_direct_pass(ctx, cfg, src, tgt, n_itiles, ctx->mg_rank * ptiles,
-                                  (ctx->mg_nranks - ctx->mg_rank) * ptiles, 0, ctx->mg_rank * ptiles, eps2, 0, st,
-                                  ctx->mg_nranks > 1 ? &gate : nullptr))
+  if (int rc = launch_direct_pass(ctx, cfg, src, tgt, n_itiles, ctx->mg_rank * ptiles, ptiles, 0, 0, eps2, 0, st))
     return rc;
+  if (ctx->mg_nranks > 1) {
+    if (int rc = launch_peer_wait(ctx, pb.flags[ctx->mg_rank], parity * NB_MAX_PEERS, step, ctx->mg_nranks,
+                                  ctx->mg_rank, ps->d_timeout, st))
+      return rc;
+    // the other R-1 slices in ring order: rank+1, ..., R-1, 0, ..., rank-1
+    ctx->n_pass = 2;
+    if (int rc = launch_direct_pass(ctx, cfg, src, tgt, n_itiles, (ctx->mg_rank + 1) * ptiles,
+                                    (ctx->mg_nranks - 1 - ctx->mg_rank) * ptiles, 0, ctx->mg_rank * ptiles, eps2, 1, st))
+      return rc;
+  }
   return launch_reduce(ctx, cfg, d_local, ctx->mg_count, dt, do_kick != 0, st);
 }
 
@@ -294,6 +306,132 @@ int nb_mgpu_peer_step(nb_context* ctx, const nb_particles* d_local, float dt, fl
                       nb_stream s) {
   if (int rc = nb_mgpu_peer_push(ctx, d_local, dt, G, do_step, s)) return rc;
   return nb_mgpu_peer_forces(ctx, d_local, dt, eps2, do_step, s);
+}
+
+// ---- target-sharded Barnes-Hut over replicated state --------------------------
+// Every rank holds ALL bodies.  Per step every rank drifts all bodies and rebuilds the identical tree
+// (deterministic kernels on identical inputs), traverses only the groups dealt to it, and stores the
+// accelerations -- sorted order, float4 per body -- into every rank's exchange buffer from the
+// traversal kernel's epilogue (NVLink peer stores, no collective).  After the per-peer flags are up,
+// every rank scatters the complete acceleration array back to body order and kicks all bodies, so
+// the replicas stay bit-identical without ever exchanging positions.  Buffers alternate by parity
+// as in the direct path.
+static int bhs_check(nb_context* ctx, const nb_particles* d, const char* what) {
+  if (!ctx || !ctx->peer_bh || !ctx->peer_bh->block || !d) {
+    set_error("mgpu bh %s: nb_mgpu_bh_alloc not called or null particles", what);
+    return NB_ERR_INVALID;
+  }
+  if (d->count != ctx->bhs_n) {
+    set_error("mgpu bh %s: %zu bodies, exchange block sized for %zu (every rank holds all bodies)", what, d->count,
+              ctx->bhs_n);
+    return NB_ERR_INVALID;
+  }
+  if (*ctx->peer_bh->h_timeout) {
+    set_error("mgpu bh %s: a peer's accelerations did not arrive within 20 s (peer process gone?)", what);
+    return NB_ERR_INTERNAL;
+  }
+  NB_CUDA(cudaSetDevice(ctx->device));
+  for (int r = 0; r < ctx->bhs_nranks; r++)
+    if (!ctx->peer_bh->peer_block[r]) {
+      set_error("mgpu bh %s: rank %d's exchange block is not mapped (nb_mgpu_bh_open / _map)", what, r);
+      return NB_ERR_INVALID;
+    }
+  return NB_OK;
+}
+
+int nb_mgpu_bh_alloc(nb_context* ctx, size_t n_total, int rank, int nranks, unsigned char handle_out[64]) {
+  if (!ctx || n_total == 0 || nranks < 1 || nranks > NB_MAX_PEERS || rank < 0 || rank >= nranks || !handle_out) {
+    set_error("mgpu bh alloc: bad arguments (at most %d ranks)", NB_MAX_PEERS);
+    return NB_ERR_INVALID;
+  }
+  ctx->bhs_n = n_total;
+  ctx->bhs_rank = rank;
+  ctx->bhs_nranks = nranks;
+  return peer_block_alloc(ctx, ctx->peer_bh, 2 * n_total * sizeof(float4), rank, handle_out);
+}
+
+int nb_mgpu_bh_open(nb_context* ctx, int peer_rank, const unsigned char handle[64]) {
+  if (!ctx || !ctx->peer_bh || !handle || peer_rank < 0 || peer_rank >= ctx->bhs_nranks) {
+    set_error("mgpu bh open: bad arguments or nb_mgpu_bh_alloc not called");
+    return NB_ERR_INVALID;
+  }
+  return peer_block_open(ctx, ctx->peer_bh, ctx->bhs_rank, peer_rank, handle);
+}
+
+int nb_mgpu_bh_block(nb_context* ctx, void** block, size_t* bytes) {
+  if (!ctx || !ctx->peer_bh || !ctx->peer_bh->block) {
+    set_error("mgpu bh: nb_mgpu_bh_alloc not called");
+    return NB_ERR_INVALID;
+  }
+  if (block) *block = ctx->peer_bh->block;
+  if (bytes) *bytes = ctx->peer_bh->block_bytes;
+  return NB_OK;
+}
+
+int nb_mgpu_bh_map(nb_context* ctx, int peer_rank, void* peer_block) {
+  if (!ctx || !ctx->peer_bh || !peer_block || peer_rank < 0 || peer_rank >= ctx->bhs_nranks) {
+    set_error("mgpu bh map: bad arguments or nb_mgpu_bh_alloc not called");
+    return NB_ERR_INVALID;
+  }
+  if (peer_rank != ctx->bhs_rank) ctx->peer_bh->peer_block[peer_rank] = peer_block;
+  return NB_OK;
+}
+
+int nb_mgpu_bh_close(nb_context* ctx) {
+  if (!ctx) return NB_OK;
+  return peer_block_close(ctx, ctx->peer_bh);
+}
+
+// first half: [store-acc + drift,] tree build, this rank's share of the traversal pushed to every rank
+int nb_mgpu_bh_traverse(nb_context* ctx, const nb_particles* d_all, float dt, float theta, float G, float eps,
+                        int do_drift, nb_stream s) {
+  if (int rc = bhs_check(ctx, d_all, "traverse")) return rc;
+  cudaStream_t st = (cudaStream_t)s;
+  PeerState* ps = ctx->peer_bh;
+  if (do_drift) {
+    if (int rc = nb_store_accelerations(ctx, d_all, s)) return rc;
+    if (int rc = nb_update_positions(ctx, d_all, dt, s)) return rc;
+  }
+  if (int rc = bh_build(ctx, d_all, st)) return rc;
+  const unsigned step = ++ps->step;
+  const int parity = (int)(step & 1u);
+  BhShard sh{};
+  sh.rank = ctx->bhs_rank;
+  sh.nranks = ctx->bhs_nranks;
+  for (int r = 0; r < ctx->bhs_nranks; r++) {
+    unsigned char* base = static_cast<unsigned char*>(ps->peer_block[r]);
+    sh.flags[r] = reinterpret_cast<unsigned*>(base);
+    sh.out[r] = reinterpret_cast<float4*>(base + kFlagBytes) + (size_t)parity * ctx->bhs_n;
+  }
+  sh.flag_index = parity * NB_MAX_PEERS + ctx->bhs_rank;
+  sh.step = step;
+  sh.done_counter = ps->done_counter;
+  return bh_forces(ctx, d_all, theta, G, eps, st, &sh);
+}
+
+// second half: wait for every peer's share, scatter to body order [+ kick all bodies]
+int nb_mgpu_bh_finish(nb_context* ctx, const nb_particles* d_all, float dt, int do_kick, nb_stream s) {
+  if (int rc = bhs_check(ctx, d_all, "finish")) return rc;
+  cudaStream_t st = (cudaStream_t)s;
+  PeerState* ps = ctx->peer_bh;
+  if (ps->step == 0) {
+    set_error("mgpu bh finish: nb_mgpu_bh_traverse has not run");
+    return NB_ERR_INVALID;
+  }
+  const int parity = (int)(ps->step & 1u);
+  unsigned char* base = static_cast<unsigned char*>(ps->block);
+  if (ctx->bhs_nranks > 1)
+    if (int rc = bh_shard_wait(ctx, reinterpret_cast<const unsigned*>(base), parity * NB_MAX_PEERS, ps->step,
+                               ctx->bhs_nranks, ctx->bhs_rank, ps->d_timeout, st))
+      return rc;
+  const float4* acc = reinterpret_cast<const float4*>(base + kFlagBytes) + (size_t)parity * ctx->bhs_n;
+  return bh_shard_finish(ctx, acc, d_all, dt, do_kick != 0, st);
+}
+
+int nb_mgpu_bh_step(nb_context* ctx, const nb_particles* d_all, float dt, float theta, float G, float eps, int do_step,
+                    nb_stream s) {
+  if (int rc = nb_mgpu_bh_traverse(ctx, d_all, dt, theta, G, eps, do_step, s)) return rc;
+  return nb_mgpu_bh_finish(ctx, d_all, dt, do_step, s);
 }
 
 }  // extern "C"

@@ -6,13 +6,14 @@ Rank r owns targets [r*N/R, (r+1)*N/R) and needs all N sources every step.  Two 
 
 exchange="peer" (default): the all-gather is fused into our own kernels over NVLink peer memory.
   Setup: every rank allocates an exchange block, the CUDA-IPC handles travel once through
-  torch.distributed (all_gather_object), every rank maps the others' blocks.  Per step, 3 launches:
+  torch.distributed (all_gather_object), every rank maps the others' blocks.  Per step:
   1. pack_push: store-acc + drift of the local slice, each packed float4 {x,y,z,G*m} stored into
      ALL R replicated source buffers (local + R-1 peers), then this rank's step flag raised on
      every peer                                                          (nb_mgpu_peer_step)
-  2. one force launch over all N sources, local slice first, ring order after; the TMA producer
-     thread waits for a peer's flag when it reaches that peer's tiles
-  3. fixed-order reduction of the stream-K partials + kick
+  2. force pass over the LOCAL slice (overlaps the peers' pushes)
+  3. a one-warp kernel waits for the R-1 peer flags (acquire at system scope)
+  4. force pass over the other R-1 slices in ring order
+  5. fixed-order reduction of the stream-K partials + kick
 
 exchange="nccl": the baseline the peer path is measured against.
   1. pack into this rank's slot                                          (nb_mgpu_pack_local)
@@ -162,3 +163,63 @@ class ShardedDirectSystem:
 
     def local_arrays(self) -> dict:
         return self.d.numpy()
+
+
+class ShardedBarnesHutSystem:
+    """One rank of a target-sharded Barnes-Hut run over REPLICATED state.
+
+    Every rank holds all N bodies.  Per step (nb_mgpu_bh_step): drift all bodies and rebuild the tree
+    (identical on every rank), traverse only the groups dealt to this rank with the accelerations
+    stored into every rank's exchange buffer from the traversal kernel's epilogue (NVLink peer stores,
+    sorted order), wait for the peers' flags, scatter to body order and kick all bodies.  Positions are
+    never exchanged: the replicas evolve bit-identically."""
+
+    def __init__(self, state_full: dict, rank: int, world: int, G: float = 1.0, softening: float = 0.01,
+                 theta: float = 0.5, group=None):
+        import torch
+        from . import _lib
+        from .api import ParticleData, ParticleDataManager, get_context
+        self.torch, self.L, self.check = torch, _lib.lib(), _lib.check
+        self.rank, self.world, self.group = rank, world, group
+        self.G = float(np.float32(G))
+        self.eps = float(np.float32(softening))
+        self.theta = float(np.float32(theta))
+        self.ctx = get_context()
+        self.n = int(state_full["pos_x"].size)
+        h = ParticleDataManager.fromState(state_full)
+        self.d = ParticleData()
+        ParticleDataManager.allocateDevice(self.d, self.n)
+        ParticleDataManager.copyToDevice(self.d, h)
+        handle = (C.c_ubyte * 64)()
+        self.check(self.L.nb_mgpu_bh_alloc(self.ctx.handle, self.n, rank, world, handle))
+        if world > 1:
+            import torch.distributed as dist
+            handles = [None] * world
+            dist.all_gather_object(handles, bytes(handle), group=group)
+            for r, hb in enumerate(handles):
+                if r != rank:
+                    self.check(self.L.nb_mgpu_bh_open(self.ctx.handle, r, (C.c_ubyte * 64).from_buffer_copy(hb)))
+            dist.barrier(group=group)
+        self.simulation_time = 0.0
+
+    def _stream(self):
+        return C.c_void_p(self.torch.cuda.current_stream().cuda_stream)
+
+    def compute_forces(self):
+        self.check(self.L.nb_mgpu_bh_step(self.ctx.handle, C.byref(self.d.c), 0.0, self.theta, self.G, self.eps, 0,
+                                          self._stream()))
+
+    def update(self, dt: float):
+        self.check(self.L.nb_mgpu_bh_step(self.ctx.handle, C.byref(self.d.c), float(np.float32(dt)), self.theta,
+                                          self.G, self.eps, 1, self._stream()))
+        self.simulation_time += dt
+
+    def arrays(self) -> dict:
+        return self.d.numpy()
+
+    def close(self):
+        self.torch.cuda.synchronize()
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.barrier(group=self.group)
+        self.check(self.L.nb_mgpu_bh_close(self.ctx.handle))

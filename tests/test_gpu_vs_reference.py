@@ -191,9 +191,9 @@ def test_sharded_path_emulated_on_one_gpu(orc, n, world):
 
 @pytest.mark.parametrize("n,world", [(5000, 2), (40000, 4), (100000, 8), (33000, 3)])
 def test_peer_exchange_emulated_on_one_gpu(orc, n, world):
-    """The peer-memory exchange (pack_push + flag-gated force kernel) with every rank as its own
+    """The peer-memory exchange (pack_push, local pass, flag wait, remote pass) with every rank as its own
     context on ONE GPU, mapped to each other by raw pointer: all ranks push, then all ranks run
-    their gated force pass.  Two Verlet steps (both buffer parities) = the single-GPU fused step."""
+    their force passes.  Two Verlet steps (both buffer parities) = the single-GPU fused step."""
     import torch
     import nbody_b200 as nb
     from nbody_b200 import _lib, ics
@@ -249,4 +249,63 @@ def test_peer_exchange_emulated_on_one_gpu(orc, n, world):
         assert e.max() < 1e-5
     for cx in ctxs:
         _lib.check(L.nb_mgpu_peer_close(cx.handle))
+        cx.close()
+
+
+@pytest.mark.parametrize("n,world", [(3000, 2), (50000, 4), (120000, 8)])
+def test_sharded_barnes_hut_emulated_on_one_gpu(orc, n, world):
+    """Target-sharded Barnes-Hut over replicated state with every rank as its own context on ONE GPU
+    (exchange blocks mapped by raw pointer): all ranks traverse their share and push, then all ranks
+    finish.  Every replica must equal the single-GPU Barnes-Hut step BIT FOR BIT (same tree, same
+    groups, each body evaluated exactly once, same kick)."""
+    import torch
+    import nbody_b200 as nb
+    from nbody_b200 import _lib, ics
+    from nbody_b200.api import Context
+    L = _lib.lib()
+    st = ics.plummer(n, seed=33)
+    dt, G, eps, theta = float(np.float32(1e-3)), 1.0, float(np.float32(0.01)), 0.5
+    single = _device_data(st)
+    calc = nb.BarnesHutCalculator(theta)
+    calc.setSofteningParameter(0.01)
+    integ = nb.Integrator()
+    calc.computeForces(single)
+    ctxs, datas, blocks = [], [], []
+    for r in range(world):
+        cx = Context(0)
+        h = (C.c_ubyte * 64)()
+        _lib.check(L.nb_mgpu_bh_alloc(cx.handle, n, r, world, h))
+        blk, nbytes = C.c_void_p(), C.c_size_t()
+        _lib.check(L.nb_mgpu_bh_block(cx.handle, C.byref(blk), C.byref(nbytes)))
+        assert nbytes.value == 4096 + 2 * n * 16
+        ctxs.append(cx); blocks.append(blk); datas.append(_device_data(st))
+    for r, cx in enumerate(ctxs):
+        for q in range(world):
+            if q != r:
+                _lib.check(L.nb_mgpu_bh_map(cx.handle, q, blocks[q]))
+
+    def evaluate(step):
+        for cx, d in zip(ctxs, datas):
+            _lib.check(L.nb_mgpu_bh_traverse(cx.handle, C.byref(d.c), dt, theta, G, eps, step, None))
+        for cx, d in zip(ctxs, datas):
+            _lib.check(L.nb_mgpu_bh_finish(cx.handle, C.byref(d.c), dt, step, None))
+
+    evaluate(0)
+    for _ in range(3):
+        integ.integrate(single, calc, dt)
+        evaluate(1)
+    torch.cuda.synchronize()
+    so = single.numpy()
+    shares = []
+    for cx, d in zip(ctxs, datas):
+        o = d.numpy()
+        for k in ("pos_x", "pos_y", "pos_z", "vel_x", "vel_y", "vel_z", "acc_x", "acc_y", "acc_z", "acc_old_y"):
+            assert np.array_equal(o[k], so[k]), k
+        inter = C.c_uint64(0)
+        _lib.check(L.nb_bh_stats(cx.handle, C.byref(inter), None))
+        shares.append(inter.value)
+    assert sum(shares) == calc.getTree().interactions()      # every group evaluated by exactly one rank
+    assert max(shares) < 2.0 * sum(shares) / world or n < 10000   # and the deal is roughly even
+    for cx in ctxs:
+        _lib.check(L.nb_mgpu_bh_close(cx.handle))
         cx.close()
