@@ -192,6 +192,12 @@ class Engine {
     static Engine e;
     return e.ctx_;
   }
+  // stream the compute wrappers launch on: the legacy default stream (what the reference uses
+  // everywhere) unless a graph capture has redirected it
+  static nb_stream& stream() {
+    static thread_local nb_stream s = nullptr;
+    return s;
+  }
 
  private:
   Engine() { NB_CALL(nb_context_create(0, 0, &ctx_)); }
@@ -300,7 +306,7 @@ class DirectForceCalculator : public ForceCalculator {
  public:
   explicit DirectForceCalculator(int block_size = 256) : block_size_(block_size) {}
   void computeForces(ParticleData* d) override {  // src/cuda/force_direct.cu:103-106
-    NB_CALL(nb_direct_forces(Engine::get(), as_nb(d), G_, softening_eps2_, nullptr));
+    NB_CALL(nb_direct_forces(Engine::get(), as_nb(d), G_, softening_eps2_, Engine::stream()));
   }
   ForceMethod getMethod() const noexcept override { return ForceMethod::DIRECT_N2; }
   void setBlockSize(int s) { block_size_ = s; }
@@ -334,8 +340,8 @@ class BarnesHutCalculator : public ForceCalculator {
   explicit BarnesHutCalculator(float theta = 0.5f) : theta_(theta) {}
   void computeForces(ParticleData* d) override {  // src/cuda/force_barnes_hut.cu:526-532
     if (!tree_) tree_ = std::make_unique<BarnesHutTree>();
-    NB_CALL(nb_bh_build(Engine::get(), as_nb(d), nullptr));
-    NB_CALL(nb_bh_forces(Engine::get(), as_nb(d), theta_, G_, softening_eps_, nullptr));
+    NB_CALL(nb_bh_build(Engine::get(), as_nb(d), Engine::stream()));
+    NB_CALL(nb_bh_forces(Engine::get(), as_nb(d), theta_, G_, softening_eps_, Engine::stream()));
   }
   ForceMethod getMethod() const noexcept override { return ForceMethod::BARNES_HUT; }
   void setTheta(float t) { theta_ = t; }
@@ -408,7 +414,7 @@ class Integrator {
   void integrate(ParticleData* d, ForceCalculator* fc, float dt) {
     if (auto* direct = dynamic_cast<DirectForceCalculator*>(fc)) {
       NB_CALL(nb_step_direct(Engine::get(), as_nb(d), dt, direct->getGravitationalConstant(),
-                             direct->getSofteningSquared(), nullptr));
+                             direct->getSofteningSquared(), Engine::stream()));
       return;
     }
     storeOldAccelerations(d);
@@ -416,9 +422,9 @@ class Integrator {
     fc->computeForces(d);
     updateVelocities(d, dt);
   }
-  void updatePositions(ParticleData* d, float dt) { NB_CALL(nb_update_positions(Engine::get(), as_nb(d), dt, nullptr)); }
-  void updateVelocities(ParticleData* d, float dt) { NB_CALL(nb_update_velocities(Engine::get(), as_nb(d), dt, nullptr)); }
-  void storeOldAccelerations(ParticleData* d) { NB_CALL(nb_store_accelerations(Engine::get(), as_nb(d), nullptr)); }
+  void updatePositions(ParticleData* d, float dt) { NB_CALL(nb_update_positions(Engine::get(), as_nb(d), dt, Engine::stream())); }
+  void updateVelocities(ParticleData* d, float dt) { NB_CALL(nb_update_velocities(Engine::get(), as_nb(d), dt, Engine::stream())); }
+  void storeOldAccelerations(ParticleData* d) { NB_CALL(nb_store_accelerations(Engine::get(), as_nb(d), Engine::stream())); }
   float computeKineticEnergy(const ParticleData* d) {
     double ke = 0;
     NB_CALL(nb_kinetic_energy(Engine::get(), as_nb(d), &ke, nullptr));
@@ -682,6 +688,156 @@ inline void writeBenchmarkRunRecords(const std::string& path, const std::vector<
 }
 #define NBODY_PROFILE_SCOPE(name) ::nbody::ScopedPhaseProfile nbody_scoped_phase_profile_##__LINE__(::nbody::globalPhaseProfiler(), (name))
 
+// ---- headless render classes (include/nbody/camera.hpp, renderer.hpp; src/render/camera.cpp, renderer.cpp) ----
+// Same names and members as the reference's, with Vec3 / Mat4 in place of glm types and a device
+// RGBA8 framebuffer (PPM file on request) in place of the GL context.  render() runs the CUDA splat
+// kernels (nb_render_splats) on the device ParticleData directly; the reference copies it into GL
+// buffers first (CudaGLInterop, K16 = nb_interop_pack).
+enum class ColorMode { DEPTH, VELOCITY, DENSITY };
+struct Mat4 {
+  float m[16] = {0};  // column-major, m[col * 4 + row], like glm::mat4
+  float& at(int col, int row) { return m[col * 4 + row]; }
+  float at(int col, int row) const { return m[col * 4 + row]; }
+};
+inline Vec3 cross(const Vec3& a, const Vec3& b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+inline Mat4 lookAt(const Vec3& eye, const Vec3& center, const Vec3& up) {  // glm::lookAt, right-handed
+  const Vec3 f = (center - eye).normalized(), s = cross(f, up).normalized(), u = cross(s, f);
+  Mat4 r;
+  r.at(0, 0) = s.x; r.at(1, 0) = s.y; r.at(2, 0) = s.z;
+  r.at(0, 1) = u.x; r.at(1, 1) = u.y; r.at(2, 1) = u.z;
+  r.at(0, 2) = -f.x; r.at(1, 2) = -f.y; r.at(2, 2) = -f.z;
+  r.at(3, 0) = -s.dot(eye); r.at(3, 1) = -u.dot(eye); r.at(3, 2) = f.dot(eye); r.at(3, 3) = 1.0f;
+  return r;
+}
+inline Mat4 perspective(float fovy_rad, float aspect, float z_near, float z_far) {  // glm::perspective, RH, -1..1
+  const float t = std::tan(fovy_rad / 2.0f);
+  Mat4 r;
+  r.at(0, 0) = 1.0f / (aspect * t);
+  r.at(1, 1) = 1.0f / t;
+  r.at(2, 2) = -(z_far + z_near) / (z_far - z_near);
+  r.at(2, 3) = -1.0f;
+  r.at(3, 2) = -(2.0f * z_far * z_near) / (z_far - z_near);
+  return r;
+}
+class Camera {  // camera.hpp:9-88
+ public:
+  Camera(float fov = 45.0f, float aspect = 16.0f / 9.0f, float z_near = 0.1f, float z_far = 1000.0f)
+      : fov_(fov), aspect_(aspect), near_(z_near), far_(z_far) {}
+  Mat4 getViewMatrix() const { return lookAt(position_, target_, up_); }
+  Mat4 getProjectionMatrix() const { return perspective(fov_ * 3.14159265358979323846f / 180.0f, aspect_, near_, far_); }
+  void setPosition(const Vec3& p) { position_ = p; }
+  void setTarget(const Vec3& t) { target_ = t; }
+  void setUp(const Vec3& u) { up_ = u; }
+  Vec3 getPosition() const { return position_; }
+  Vec3 getTarget() const { return target_; }
+  Vec3 getUp() const { return up_; }
+  Vec3 getForward() const { return (target_ - position_).normalized(); }
+  Vec3 getRight() const { return cross(getForward(), up_).normalized(); }
+  void setFOV(float f) { fov_ = f; }
+  void setAspectRatio(float a) { aspect_ = a; }
+  void setNearFar(float n, float f) { near_ = n; far_ = f; }
+  float getFOV() const { return fov_; }
+  float getAspectRatio() const { return aspect_; }
+  float getNear() const { return near_; }
+  float getFar() const { return far_; }
+  void rotate(float yaw, float pitch) {  // camera.cpp:46-65
+    const Vec3 d = position_ - target_;
+    const float dist = d.length();
+    const float theta = std::atan2(d.x, d.z) + yaw;
+    const float phi = std::clamp(std::acos(d.y / dist) + pitch, 0.1f, 3.04f);
+    position_ = target_ + Vec3(dist * std::sin(phi) * std::sin(theta), dist * std::cos(phi), dist * std::sin(phi) * std::cos(theta));
+  }
+  void orbit(float yaw, float pitch) { rotate(yaw, pitch); }
+  void pan(float dx, float dy) {  // :67-75
+    const Vec3 right = getRight(), up = cross(right, getForward()).normalized(), off = right * dx + up * dy;
+    position_ += off;
+    target_ += off;
+  }
+  void zoom(float delta) {  // :77-85
+    const Vec3 d = target_ - position_;
+    position_ = target_ - d.normalized() * std::clamp(d.length() - delta, 1.0f, 1000.0f);
+  }
+  void reset() { position_ = Vec3(0, 0, 50); target_ = Vec3(0, 0, 0); up_ = Vec3(0, 1, 0); }
+  void setOrbitDistance(float dist) { position_ = target_ + (position_ - target_).normalized() * dist; }
+  float getOrbitDistance() const { return (position_ - target_).length(); }
+
+ private:
+  Vec3 position_{0, 0, 50}, target_{0, 0, 0}, up_{0, 1, 0};
+  float fov_, aspect_, near_, far_;
+};
+struct ColorMapper {  // camera.cpp:104-128
+  static Vec3 gradientMap(float t, const Vec3& lo, const Vec3& hi) { return lo * (1.0f - t) + hi * t; }
+  static Vec3 velocityToColor(float v, float vmax) { return gradientMap(std::clamp(v / vmax, 0.0f, 1.0f), {0, 0, 1}, {1, 0, 0}); }
+  static Vec3 depthToColor(float d, float dmax) { return gradientMap(std::clamp(d / dmax, 0.0f, 1.0f), {1, 0.5f, 0}, {0, 0.5f, 1}); }
+  static Vec3 densityToColor(float d, float dmax) { return gradientMap(std::clamp(d / dmax, 0.0f, 1.0f), {0.2f, 0.2f, 0.8f}, {1, 1, 0.2f}); }
+};
+class Renderer {  // renderer.hpp:20-80
+ public:
+  Renderer() = default;
+  ~Renderer() { cleanup(); }
+  Renderer(const Renderer&) = delete;
+  Renderer& operator=(const Renderer&) = delete;
+  void initialize(int width, int height) {  // renderer.cpp:93-121 without GLEW / shader compilation / VAO
+    cleanup();
+    width_ = width; height_ = height;
+    NB_CALL(nb_device_alloc(Engine::get(), static_cast<std::size_t>(width) * height * 4, &framebuffer_));
+    camera_.setPosition(Vec3(0, 0, 50));
+    camera_.setTarget(Vec3(0, 0, 0));
+    camera_.setAspectRatio(static_cast<float>(width) / static_cast<float>(height));
+    is_initialized_ = true;
+  }
+  void cleanup() {
+    if (framebuffer_) nb_device_free(Engine::get(), framebuffer_);
+    framebuffer_ = nullptr;
+    is_initialized_ = false;
+  }
+  void onResize(int width, int height) { initialize(width, height); }
+  // one frame into the device framebuffer; asynchronous apart from one 8-byte readback
+  void render(const ParticleData* d_particles) {
+    if (!is_initialized_) return;  // :185-186
+    nb_render_params p{};
+    const Mat4 v = camera_.getViewMatrix(), pr = camera_.getProjectionMatrix();
+    std::copy(v.m, v.m + 16, p.view);
+    std::copy(pr.m, pr.m + 16, p.proj);
+    p.point_size = point_size_; p.max_depth = max_depth_; p.max_velocity = max_velocity_;
+    p.color_mode = static_cast<int>(color_mode_); p.width = width_; p.height = height_;
+    p.point_size_min = 1.0f; p.point_size_max = 63.0f;
+    p.clear_color[0] = 0.02f; p.clear_color[1] = 0.02f; p.clear_color[2] = 0.05f; p.clear_color[3] = 1.0f;  // :9-11
+    NB_CALL(nb_render_splats(Engine::get(), as_nb(d_particles), &p, static_cast<std::uint8_t*>(framebuffer_), Engine::stream()));
+  }
+  std::vector<std::uint8_t> readPixels() const {  // height x width x RGBA, row 0 = bottom row (glReadPixels order)
+    std::vector<std::uint8_t> px(static_cast<std::size_t>(width_) * height_ * 4);
+    if (framebuffer_) NB_CALL(nb_device_download(Engine::get(), px.data(), framebuffer_, px.size(), Engine::stream()));
+    return px;
+  }
+  void savePPM(const std::string& filename) const {
+    const auto px = readPixels();
+    std::ofstream f(filename, std::ios::binary);
+    if (!f) throw std::runtime_error("Failed to open file for writing: " + filename);
+    f << "P6\n" << width_ << ' ' << height_ << "\n255\n";
+    for (int y = height_ - 1; y >= 0; y--)
+      for (int x = 0; x < width_; x++) f.write(reinterpret_cast<const char*>(&px[(static_cast<std::size_t>(y) * width_ + x) * 4]), 3);
+  }
+  void setColorMode(ColorMode m) { color_mode_ = m; }
+  ColorMode getColorMode() const { return color_mode_; }
+  void setPointSize(float s) { point_size_ = s; }
+  void setMaxDepth(float d) { max_depth_ = d; }
+  void setMaxVelocity(float v) { max_velocity_ = v; }
+  Camera& getCamera() { return camera_; }
+  const Camera& getCamera() const { return camera_; }
+  bool isInitialized() const { return is_initialized_; }
+  int getWidth() const { return width_; }
+  int getHeight() const { return height_; }
+
+ private:
+  ColorMode color_mode_ = ColorMode::DEPTH;  // renderer.cpp:79-88
+  float point_size_ = 2.0f, max_depth_ = 100.0f, max_velocity_ = 10.0f;
+  int width_ = 1280, height_ = 720;
+  bool is_initialized_ = false;
+  void* framebuffer_ = nullptr;
+  Camera camera_;
+};
+
 class ParticleSystem {
  public:
   ParticleSystem() = default;
@@ -718,8 +874,20 @@ class ParticleSystem {
   }
   void update(float dt) {  // :115-127
     if (!initialized_ || paused_) return;
-    integrator_->integrate(&d_, calc_.get(), dt);
+    if (use_graph_ && force_method_ != ForceMethod::SPATIAL_HASH) updateGraphed(dt);
+    else integrator_->integrate(&d_, calc_.get(), dt);
     time_ += dt;
+  }
+  // CUDA-graph replay of the steady-state step: the first step with a given parameter set runs
+  // eagerly (sizes all scratch), the second is captured on a side stream, later ones replay.
+  void setUseCudaGraph(bool on) {
+    use_graph_ = on;
+    if (!on) dropGraph();
+  }
+  std::size_t graphNodeCount() const {
+    std::size_t n = 0;
+    if (graph_) NB_CALL(nb_graph_node_count(graph_, &n));
+    return n;
   }
   void reset() { if (initialized_) initialize(config_); }
   void pause() { paused_ = true; }
@@ -816,8 +984,63 @@ class ParticleSystem {
     allocated_ = true;
   }
   void release() {
+    dropGraph();
     if (allocated_) { ParticleDataManager::freeDevice(d_); ParticleDataManager::freeHost(h_); }
     allocated_ = initialized_ = false;
+  }
+  struct GraphKey {
+    float dt = 0, G = 0, eps = 0, theta = 0;
+    int method = -1;
+    std::size_t count = 0;
+    const void *pos = nullptr, *calc = nullptr;
+    bool operator==(const GraphKey&) const = default;
+  };
+  GraphKey graphKey(float dt) const {
+    GraphKey k;
+    k.dt = dt; k.G = calc_->getGravitationalConstant(); k.eps = calc_->getSofteningParameter();
+    k.theta = config_.barnes_hut_theta; k.method = static_cast<int>(force_method_); k.count = count_;
+    k.pos = d_.pos_x; k.calc = calc_.get();
+    return k;
+  }
+  void dropGraph() {
+    if (graph_) nb_graph_destroy(graph_);
+    graph_ = nullptr;
+    graph_valid_ = warm_valid_ = false;
+  }
+  void updateGraphed(float dt) {
+    const GraphKey key = graphKey(dt);
+    if (graph_ && graph_valid_ && key == graph_key_) {
+      NB_CALL(nb_graph_launch(graph_, Engine::stream()));
+      return;
+    }
+    if (!(warm_valid_ && key == warm_key_)) {
+      dropGraph();
+      integrator_->integrate(&d_, calc_.get(), dt);
+      warm_key_ = key;
+      warm_valid_ = true;
+      return;
+    }
+    if (!graph_stream_) NB_CALL(nb_stream_create(Engine::get(), &graph_stream_));
+    nb_stream outer = Engine::stream();
+    Engine::stream() = graph_stream_;
+    int rc = nb_graph_begin_capture(Engine::get(), graph_stream_);
+    if (rc == 0) {
+      try {
+        integrator_->integrate(&d_, calc_.get(), dt);
+      } catch (...) {
+        nb_graph* dead = nullptr;
+        nb_graph_end_capture(Engine::get(), graph_stream_, &dead);
+        nb_graph_destroy(dead);
+        Engine::stream() = outer;
+        throw;
+      }
+      rc = nb_graph_end_capture(Engine::get(), graph_stream_, &graph_);
+    }
+    Engine::stream() = outer;
+    NB_CALL(rc);
+    graph_key_ = key;
+    graph_valid_ = true;
+    NB_CALL(nb_graph_launch(graph_, Engine::stream()));
   }
   void makeCalculator() {  // :109-113
     calc_ = createForceCalculator(force_method_, config_);
@@ -836,6 +1059,10 @@ class ParticleSystem {
   float dt_ = 0.001f, G_ = 1.0f, softening_ = 0.01f, time_ = 0.0f;
   ForceMethod force_method_ = ForceMethod::DIRECT_N2;
   bool paused_ = false, initialized_ = false, allocated_ = false;
+  bool use_graph_ = false, graph_valid_ = false, warm_valid_ = false;
+  nb_graph* graph_ = nullptr;
+  nb_stream graph_stream_ = nullptr;
+  GraphKey graph_key_, warm_key_;
   SimulationConfig config_;
   ParticleData d_, h_;
   std::unique_ptr<ForceCalculator> calc_;

@@ -67,6 +67,9 @@ uint64_t nb_launch_count(const nb_context* ctx);
  * nb_step_direct, nb_bh_build, nb_bh_forces, nb_store_accelerations, nb_update_positions,
  * nb_update_velocities.  Everything that synchronises (nb_sh_build, energies, exports, stats,
  * nb_render_splats) is not. */
+int nb_device_alloc(nb_context* ctx, size_t bytes, void** out);   /* raw device buffer (e.g. a framebuffer) */
+int nb_device_free(nb_context* ctx, void* p);
+int nb_device_download(nb_context* ctx, void* host_dst, const void* device_src, size_t bytes, nb_stream s); /* synchronises */
 typedef struct nb_graph nb_graph;
 int nb_stream_create(nb_context* ctx, nb_stream* out);
 int nb_stream_destroy(nb_context* ctx, nb_stream s);

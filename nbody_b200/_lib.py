@@ -57,6 +57,9 @@ SYMBOLS = {
     "nb_context_sm_count": (_i, [_vp]),
     "nb_synchronize": (_i, [_vp, _vp]),
     "nb_launch_count": (C.c_uint64, [_vp]),
+    "nb_device_alloc": (_i, [_vp, _sz, C.POINTER(_vp)]),
+    "nb_device_free": (_i, [_vp, _vp]),
+    "nb_device_download": (_i, [_vp, _vp, _vp, _sz, _vp]),
     "nb_stream_create": (_i, [_vp, C.POINTER(_vp)]),
     "nb_stream_destroy": (_i, [_vp, _vp]),
     "nb_graph_begin_capture": (_i, [_vp, _vp]),

@@ -247,6 +247,41 @@ struct nb_graph {
   int device = 0;
 };
 
+// raw device buffers for host code without CUDA headers (the renderer's framebuffer)
+int nb_device_alloc(nb_context* ctx, size_t bytes, void** out) {
+  NB_ENTER(ctx);
+  if (!out) {
+    set_error("device alloc: null argument");
+    return NB_ERR_INVALID;
+  }
+  *out = nullptr;
+  if (bytes == 0) return NB_OK;
+  cudaError_t e = cudaMalloc(out, bytes);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    set_error("device alloc of %zu bytes failed: %s", bytes, cudaGetErrorString(e));
+    return NB_ERR_RESOURCE;
+  }
+  return NB_OK;
+}
+
+int nb_device_free(nb_context* ctx, void* p) {
+  NB_ENTER(ctx);
+  if (p) NB_CUDA(cudaFree(p));
+  return NB_OK;
+}
+
+int nb_device_download(nb_context* ctx, void* host_dst, const void* device_src, size_t bytes, nb_stream s) {
+  NB_ENTER(ctx);
+  if (bytes && (!host_dst || !device_src)) {
+    set_error("device download: null argument");
+    return NB_ERR_INVALID;
+  }
+  NB_CUDA(cudaMemcpyAsync(host_dst, device_src, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)s));
+  NB_CUDA(cudaStreamSynchronize((cudaStream_t)s));
+  return NB_OK;
+}
+
 int nb_stream_create(nb_context* ctx, nb_stream* out) {
   NB_ENTER(ctx);
   if (!out) {

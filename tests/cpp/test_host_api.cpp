@@ -11,6 +11,8 @@
 #include "nbody/integrator.hpp"
 #include "nbody/particle_data.hpp"
 #include "nbody/particle_system.hpp"
+#include "nbody/renderer.hpp"
+#include "nbody/serialization.hpp"
 
 using namespace nbody;
 
@@ -136,11 +138,76 @@ static void validation_cases() {  // tests/test_validation.cpp
   CHECK(threw);
 }
 
+static void graph_replay_matches_eager() {
+  for (ForceMethod m : {ForceMethod::DIRECT_N2, ForceMethod::BARNES_HUT}) {
+    SimulationConfig cfg;
+    cfg.particle_count = 6000;
+    cfg.force_method = m;
+    cfg.init_distribution = InitDistribution::SPHERICAL;
+    ParticleSystem eager, graphed;
+    eager.initialize(cfg);
+    graphed.initialize(cfg);
+    graphed.setUseCudaGraph(true);
+    for (int i = 0; i < 5; i++) {
+      eager.update(cfg.dt);
+      graphed.update(cfg.dt);
+    }
+    CHECK(graphed.graphNodeCount() >= 3);
+    SimulationState a = eager.getState(), b = graphed.getState();
+    for (std::size_t i = 0; i < a.particle_count; i++)
+      CHECK(a.pos_x[i] == b.pos_x[i] && a.vel_y[i] == b.vel_y[i] && a.pos_z[i] == b.pos_z[i]);
+  }
+}
+
+static void checkpoint_round_trip_through_the_system() {  // tests/test_serialization.cpp of the reference
+  SimulationConfig cfg;
+  cfg.particle_count = 777;
+  ParticleSystem a;
+  a.initialize(cfg);
+  a.update(cfg.dt);
+  const char* path = "/tmp/nbody_b200_test_checkpoint.nbody";
+  a.saveState(path);
+  CHECK(Serializer::validateFile(path));
+  ParticleSystem b;
+  b.loadState(path);
+  CHECK(b.getState() == a.getState());
+  CHECK(b.getParticleCount() == 777);
+  std::remove(path);
+}
+
+static void headless_renderer() {
+  const int w = 64, h = 36;
+  Renderer r;
+  r.initialize(w, h);
+  const Mat4 pr = r.getCamera().getProjectionMatrix();
+  CHECK(std::fabs(pr.at(1, 1) - 2.4142135f) < 1e-5f && pr.at(2, 3) == -1.0f);
+  // one body on the centre of pixel (w/2, h/2) at depth 50: t = 0.5 -> grey, alpha 1
+  ParticleData hp, dp;
+  ParticleDataManager::allocateHost(hp, 1);
+  ParticleDataManager::allocateDevice(dp, 1);
+  hp.pos_x[0] = 0.5f * 50.0f / (w / 2 * pr.at(0, 0));
+  hp.pos_y[0] = 0.5f * 50.0f / (h / 2 * pr.at(1, 1));
+  hp.mass[0] = 1.0f;
+  ParticleDataManager::copyToDevice(dp, hp);
+  r.render(&dp);
+  const auto px = r.readPixels();
+  const std::uint8_t* c = &px[((h / 2) * w + w / 2) * 4];
+  CHECK(c[0] == 128 && c[1] == 128 && c[2] == 128 && c[3] == 255);
+  CHECK(px[0] == 5 && px[1] == 5 && px[2] == 13 && px[3] == 255);  // clear colour
+  const Vec3 col = ColorMapper::velocityToColor(5.0f, 10.0f);
+  CHECK(col.x == 0.5f && col.y == 0.0f && col.z == 0.5f);
+  ParticleDataManager::freeDevice(dp);
+  ParticleDataManager::freeHost(hp);
+}
+
 int main() {
   two_body_unit_force();
   integrator_cases();
   particle_system_cases();
   validation_cases();
+  graph_replay_matches_eager();
+  headless_renderer();
+  checkpoint_round_trip_through_the_system();
   puts("cpp host api: all checks passed");
   return 0;
 }
