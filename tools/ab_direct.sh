@@ -1,7 +1,8 @@
-for rep in 1 2; do
-for lib in build/ab/libnbody_b200_59d6739.so nbody_b200/libnbody_b200.so; do
+#!/bin/bash
+# A/B of libnbody_b200 builds on ONE box: ms/step of nb_step_direct at 1 Mi bodies for each .so given
+for lib in "$@"; do
 NB_LIB_PATH=$PWD/$lib python - <<'PY'
-import os, ctypes as C, numpy as np, torch
+import os, ctypes as C, torch
 import nbody_b200 as nb
 from nbody_b200 import _lib, ics
 L=_lib.lib(); ctx=nb.get_context()
@@ -13,7 +14,6 @@ e0,e1=torch.cuda.Event(enable_timing=True),torch.cuda.Event(enable_timing=True)
 e0.record()
 for _ in range(4): _lib.check(L.nb_step_direct(ctx.handle,C.byref(d.c),1e-3,1.0,1e-4,None))
 e1.record(); torch.cuda.synchronize()
-print(os.environ["NB_LIB_PATH"].split("/")[-1], "ms/step", e0.elapsed_time(e1)/4)
+print(os.environ["NB_LIB_PATH"].split("/")[-1], "ms/step %.3f" % (e0.elapsed_time(e1)/4), flush=True)
 PY
-done; done
-nvidia-smi --query-gpu=clocks.sm,clocks.mem,power.draw,temperature.gpu --format=csv
+done
