@@ -184,6 +184,7 @@ int nb_context_destroy(nb_context* ctx) {
   sh_destroy(ctx);
   ctx->src.release();
   ctx->partial.release();
+  ctx->direct_work.release();
   ctx->red.release();
   ctx->sort_keys2.release();
   ctx->sort_vals2.release();

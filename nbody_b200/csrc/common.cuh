@@ -144,13 +144,16 @@ struct ProfScope {
 };
 }  // namespace nb
 
-// One stream-K pass of the direct kernel (see direct.cu).
+// One pass of the direct kernel (see direct.cu): n_itiles target tiles x UJ source tiles, cut into
+// `chunks` = n_itiles * C chunks that G CTAs claim dynamically; chunk c writes partial slot slot_base + c.
 struct nb_pass {
-  long long U;      // work units = n_itiles * UJ
-  int UJ;           // source tiles per target tile
-  int G;            // CTAs the units are split over (== gridDim.x of that launch)
+  long long U;       // work units = n_itiles * UJ
+  long long chunks;  // n_itiles * C
+  int UJ;            // source tiles per target tile
+  int C;             // chunks per target tile
+  int G;             // gridDim.x of that launch
   int n_itiles;
-  size_t slot_base; // first partial slot of this pass
+  size_t slot_base;  // first partial slot of this pass
 };
 
 struct nb_context {
@@ -163,7 +166,8 @@ struct nb_context {
   std::vector<cudaEvent_t> prof_pool;
   // direct N^2
   nb::DevBuf src;       // packed float4 (x,y,z,G*m), tile padded
-  nb::DevBuf partial;   // stream-K partial accelerations
+  nb::DevBuf partial;   // per-chunk partial accelerations
+  nb::DevBuf direct_work;  // chunk counters of the two passes
   nb_pass pass[2];
   int n_pass = 0;
   int direct_occ[4] = {0, 0, 0, 0};  // resident CTAs/SM per kernel config (lazy)

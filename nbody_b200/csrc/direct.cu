@@ -9,10 +9,12 @@
 //     with Blackwell FFMA2/FADD2/FMUL2 (12 packed instructions + 2 MUFU.RSQ per two pairs), the
 //     source being a warp-broadcast LDS.128;
 //   * source tiles are staged by 1-D TMA bulk copies (cp.async.bulk + mbarrier), double buffered;
-//   * work is split "stream-K": the (target tile x source tile) unit space is cut into gridDim.x
-//     equal contiguous runs, so all 148 SMs finish together for any N; every run writes fp32
-//     partials, and a reduce kernel adds them in a fixed order (deterministic) and applies the kick;
-//   * accumulation is two-level: plain fp32 inside a source tile, Kahan-compensated across tiles.
+//   * the (target tile x source tile) unit space is cut into chunks that a persistent grid (5 CTAs per
+//     SM) claims from a global counter, so all 148 SMs and all resident CTAs finish together for any
+//     N; chunk c writes fp32 partials to slot c, and a reduce kernel adds a tile's chunks in chunk
+//     order (deterministic, no float atomics) and applies the kick;
+//   * accumulation is three-level: plain fp32 inside a source tile, Kahan-compensated across the
+//     tiles of a chunk and across the chunks of a target tile.
 #include "direct.cuh"
 
 #include <cstdlib>
@@ -143,132 +145,192 @@ int launch_peer_wait(nb_context* ctx, const unsigned* flags, int flag_base, unsi
 // ---------------------------------------------------------------------------------------------
 // force kernel
 // ---------------------------------------------------------------------------------------------
+// build-time tuning knobs (A/B builds through tools/ab_direct.sh)
+#ifndef NB_DIRECT_THREADS_PER_SM
+#define NB_DIRECT_THREADS_PER_SM 1280  // 5 CTAs of 256 threads: caps the kernel at 48 registers
+#endif
+#ifndef NB_DIRECT_UNROLL
+#define NB_DIRECT_UNROLL 64  // sources per trip of the pair loop (8: 440.5 ms per 1 Mi step, 32: 430.9, 64: 429.4)
+#endif
+#ifndef NB_DIRECT_BIG_T
+#define NB_DIRECT_BIG_T 256  // threads per CTA of the large-N configuration
+#endif
+#ifndef NB_DIRECT_BIG_JT
+#define NB_DIRECT_BIG_JT 1024  // sources per shared-memory tile of the large-N configuration
+#endif
+#define NB_PRAGMA_(x) _Pragma(#x)
+#define NB_PRAGMA_UNROLL(n) NB_PRAGMA_(unroll n)
+
+#ifdef NB_DIRECT_TRACE  // experiment: where and when each CTA of the force kernel runs
+__device__ unsigned long long nb_direct_trace_buf[3 * 4096];
+#endif
+
+// Work distribution: the (target tile x source tile) unit space is cut into n_chunks CHUNKS, chunk c =
+// target tile c / C, source tiles [jc*UJ/C, (jc+1)*UJ/C) with jc = c % C, and CTAs claim chunks from a
+// global counter (work[0]) until none are left.  A static equal split is not balanced on this machine:
+// with 5 CTAs resident per SM the warp schedulers favour some CTAs, equal shares finished between 151
+// and 457 ms of a 457 ms launch (profiles/r01_direct_cta_trace.log) and the SM ran under-occupied for
+// most of it.  Which CTA computes a chunk does not affect its result, and chunk c always lands in
+// partial slot c, so the sums stay reproducible.  The last CTA to leave re-arms the counters (work[1]
+// counts leavers), which keeps the launch replayable from a CUDA graph.
 template <int T, int I, int JT, bool EPS0>
-__global__ void __launch_bounds__(T) direct_force_kernel(const float4* __restrict__ src,
+__global__ void __launch_bounds__(T, NB_DIRECT_THREADS_PER_SM / T) direct_force_kernel(const float4* __restrict__ src,
                                                           const float4* __restrict__ tgt,
-                                                          float* __restrict__ partial, long long U, int UJ,
-                                                          int ja0, int na, int jb0, float eps2,
-                                                          unsigned long long slot_base) {
+                                                          float* __restrict__ partial, unsigned* __restrict__ work,
+                                                          int n_chunks, int C, int UJ, int ja0, int na, int jb0,
+                                                          float eps2, unsigned long long slot_base) {
   constexpr int P = I / 2;
   constexpr int IT = T * I;
   constexpr uint32_t TILE_BYTES = JT * sizeof(float4);
   static_assert(I % 2 == 0, "targets per thread must be even (packed fp32x2)");
   __shared__ __align__(128) float4 tile[2][JT];
   __shared__ __align__(8) uint64_t full[2];
+  __shared__ int claimed[2];
 
   const int tid = threadIdx.x;
-  const long long u0 = (U * (long long)blockIdx.x) / gridDim.x;
-  const long long u1 = (U * (long long)(blockIdx.x + 1)) / gridDim.x;
-  if (tid == 0) {
-    mbar_init(&full[0], 1);
-    mbar_init(&full[1], 1);
-    mbar_fence_init();
-  }
-  __syncthreads();
-#ifdef NB_DIRECT_PAD  // experiment: shift the hot loop's code address by NB_DIRECT_PAD instructions
-#pragma unroll
-  for (int k = 0; k < NB_DIRECT_PAD; k++) asm volatile("nanosleep.u32 0;");
-#endif
-  if (u0 >= u1) return;
-
-  int itile = (int)(u0 / UJ);
-  int jt = (int)(u0 - (long long)itile * UJ);
   auto jtile_ptr = [&](int j) -> const float4* {
     const int g = (j < na) ? (ja0 + j) : (jb0 + (j - na));
     return src + (size_t)g * JT;
   };
+  auto first_jtile = [&](int c) -> int { return (int)(((long long)(c % C) * UJ) / C); };
   if (tid == 0) {
-    mbar_expect_tx(&full[0], TILE_BYTES);
-    tma_load_1d(&tile[0][0], jtile_ptr(jt), TILE_BYTES, &full[0]);
+    mbar_init(&full[0], 1);
+    mbar_init(&full[1], 1);
+    mbar_fence_init();
+    const int c = (int)atomicAdd(&work[0], 1u);
+    claimed[0] = c;
+    if (c < n_chunks) {
+      mbar_expect_tx(&full[0], TILE_BYTES);
+      tma_load_1d(&tile[0][0], jtile_ptr(first_jtile(c)), TILE_BYTES, &full[0]);
+    }
   }
+  __syncthreads();
+#ifdef NB_DIRECT_TRACE
+  if (tid == 0 && blockIdx.x < 4096) {
+    unsigned sm;
+    unsigned long long t;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(sm));
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    nb_direct_trace_buf[3 * blockIdx.x] = sm;
+    nb_direct_trace_buf[3 * blockIdx.x + 1] = t;
+  }
+#endif
 
   f2 xi[P], yi[P], zi[P];
-  f2 sx[P], sy[P], sz[P];  // Kahan sums across tiles
+  f2 sx[P], sy[P], sz[P];  // Kahan sums across the tiles of a chunk
   f2 cx[P], cy[P], cz[P];  // Kahan compensation
   const f2 zero2 = pk(0.f, 0.f);
   const f2 e2 = pk(eps2, eps2);
 
-  auto load_targets = [&](int t) {
-    const float4* base = tgt + (size_t)t * IT + tid;
-#pragma unroll
-    for (int p = 0; p < P; p++) {
-      const float4 a = __ldg(base + (2 * p) * T), b = __ldg(base + (2 * p + 1) * T);
-      xi[p] = pk(a.x, b.x);
-      yi[p] = pk(a.y, b.y);
-      zi[p] = pk(a.z, b.z);
-      sx[p] = sy[p] = sz[p] = zero2;
-      cx[p] = cy[p] = cz[p] = zero2;
-    }
-  };
-  load_targets(itile);
-
-  const int nunits = (int)(u1 - u0);
-  for (int n = 0; n < nunits; n++) {
-    const int st = n & 1;
-    if (n + 1 < nunits && tid == 0) {
-      const int jn = (jt + 1 == UJ) ? 0 : jt + 1;
-      mbar_expect_tx(&full[st ^ 1], TILE_BYTES);
-      tma_load_1d(&tile[st ^ 1][0], jtile_ptr(jn), TILE_BYTES, &full[st ^ 1]);
-    }
-    mbar_wait(&full[st], (uint32_t)((n >> 1) & 1));
-
-    f2 ax[P], ay[P], az[P];
-#pragma unroll
-    for (int p = 0; p < P; p++) ax[p] = ay[p] = az[p] = zero2;
-    const float4* tj = &tile[st][0];
-#pragma unroll 8
-    for (int j = 0; j < JT; j++) {
-      const float4 s = tj[j];  // warp-broadcast LDS.128
-      const f2 px = pk(s.x, s.x), py = pk(s.y, s.y), pz = pk(s.z, s.z), pm = pk(s.w, s.w);
+  int chunk = claimed[0];
+  unsigned n = 0;  // tiles this CTA has consumed: buffer and mbarrier parity
+  for (unsigned k = 0; chunk < n_chunks; k++) {
+    const int itile = chunk / C, jc = chunk - itile * C;
+    int j = (int)(((long long)jc * UJ) / C);
+    const int jend = (int)(((long long)(jc + 1) * UJ) / C);
+    {
+      const float4* base = tgt + (size_t)itile * IT + tid;
 #pragma unroll
       for (int p = 0; p < P; p++) {
-        const f2 dx = sub2(px, xi[p]), dy = sub2(py, yi[p]), dz = sub2(pz, zi[p]);
-        f2 r2 = fma2(dx, dx, e2);
-        r2 = fma2(dy, dy, r2);
-        r2 = fma2(dz, dz, r2);
-        float r0, r1;
-        upk(r2, r0, r1);
-        float i0 = rsq(r0), i1 = rsq(r1);
-        if (EPS0) {  // eps == 0: the self pair (and exact coincidences) must contribute 0, not NaN
-          i0 = (r0 > 0.f) ? i0 : 0.f;
-          i1 = (r1 > 0.f) ? i1 : 0.f;
+        // scalar loads: each lands in its half of the packed pair (a 128-bit load pins a register quad
+        // and the re-pairing moves end up inside the pair loop)
+        const float* a = reinterpret_cast<const float*>(base + (2 * p) * T);
+        const float* b = reinterpret_cast<const float*>(base + (2 * p + 1) * T);
+        xi[p] = pk(__ldg(a), __ldg(b));
+        yi[p] = pk(__ldg(a + 1), __ldg(b + 1));
+        zi[p] = pk(__ldg(a + 2), __ldg(b + 2));
+        sx[p] = sy[p] = sz[p] = zero2;
+        cx[p] = cy[p] = cz[p] = zero2;
+      }
+    }
+    for (; j < jend; j++, n++) {
+      const unsigned st = n & 1u;
+      if (tid == 0) {
+        if (j + 1 < jend) {
+          mbar_expect_tx(&full[st ^ 1], TILE_BYTES);
+          tma_load_1d(&tile[st ^ 1][0], jtile_ptr(j + 1), TILE_BYTES, &full[st ^ 1]);
+        } else {  // last tile of this chunk: claim the next chunk now and prefetch its first tile
+          const int c = (int)atomicAdd(&work[0], 1u);
+          claimed[(k + 1) & 1u] = c;
+          if (c < n_chunks) {
+            mbar_expect_tx(&full[st ^ 1], TILE_BYTES);
+            tma_load_1d(&tile[st ^ 1][0], jtile_ptr(first_jtile(c)), TILE_BYTES, &full[st ^ 1]);
+          }
         }
-        const f2 ri = pk(i0, i1);
-        const f2 w = mul2(mul2(ri, ri), mul2(pm, ri));  // (G m_j) / r^3
-        ax[p] = fma2(w, dx, ax[p]);
-        ay[p] = fma2(w, dy, ay[p]);
-        az[p] = fma2(w, dz, az[p]);
       }
-    }
-    // fold the tile's sums into the compensated running sums
-#pragma unroll
-    for (int p = 0; p < P; p++) {
-      f2 y, t;
-      y = sub2(ax[p], cx[p]); t = add2(sx[p], y); cx[p] = sub2(sub2(t, sx[p]), y); sx[p] = t;
-      y = sub2(ay[p], cy[p]); t = add2(sy[p], y); cy[p] = sub2(sub2(t, sy[p]), y); sy[p] = t;
-      y = sub2(az[p], cz[p]); t = add2(sz[p], y); cz[p] = sub2(sub2(t, sz[p]), y); sz[p] = t;
-    }
-    __syncthreads();  // everyone is done with tile[st] before it is refilled two units later
+      mbar_wait(&full[st], (n >> 1) & 1u);
 
-    ++jt;
-    const bool last = (n + 1 == nunits);
-    if (jt == UJ || last) {
-      float* out = partial + ((size_t)slot_base + blockIdx.x + itile) * (size_t)(3 * IT) + tid;
+      f2 ax[P], ay[P], az[P];
+#pragma unroll
+      for (int p = 0; p < P; p++) ax[p] = ay[p] = az[p] = zero2;
+      const float4* tj = &tile[st][0];
+      NB_PRAGMA_UNROLL(NB_DIRECT_UNROLL)
+      for (int jj = 0; jj < JT; jj++) {
+        const float4 s = tj[jj];  // warp-broadcast LDS.128
+        const f2 px = pk(s.x, s.x), py = pk(s.y, s.y), pz = pk(s.z, s.z), pm = pk(s.w, s.w);
+#pragma unroll
+        for (int p = 0; p < P; p++) {
+          const f2 dx = sub2(px, xi[p]), dy = sub2(py, yi[p]), dz = sub2(pz, zi[p]);
+          f2 r2 = fma2(dx, dx, e2);
+          r2 = fma2(dy, dy, r2);
+          r2 = fma2(dz, dz, r2);
+          float r0, r1;
+          upk(r2, r0, r1);
+          float i0 = rsq(r0), i1 = rsq(r1);
+          if (EPS0) {  // eps == 0: the self pair (and exact coincidences) must contribute 0, not NaN
+            i0 = (r0 > 0.f) ? i0 : 0.f;
+            i1 = (r1 > 0.f) ? i1 : 0.f;
+          }
+          const f2 ri = pk(i0, i1);
+          const f2 w = mul2(mul2(ri, ri), mul2(pm, ri));  // (G m_j) / r^3
+          ax[p] = fma2(w, dx, ax[p]);
+          ay[p] = fma2(w, dy, ay[p]);
+          az[p] = fma2(w, dz, az[p]);
+        }
+      }
+      // fold the tile's sums into the compensated running sums
 #pragma unroll
       for (int p = 0; p < P; p++) {
-        float a, b;
-        upk(sx[p], a, b); out[(2 * p) * T] = a; out[(2 * p + 1) * T] = b;
-        upk(sy[p], a, b); out[IT + (2 * p) * T] = a; out[IT + (2 * p + 1) * T] = b;
-        upk(sz[p], a, b); out[2 * IT + (2 * p) * T] = a; out[2 * IT + (2 * p + 1) * T] = b;
+        f2 y, t;
+        y = sub2(ax[p], cx[p]); t = add2(sx[p], y); cx[p] = sub2(sub2(t, sx[p]), y); sx[p] = t;
+        y = sub2(ay[p], cy[p]); t = add2(sy[p], y); cy[p] = sub2(sub2(t, sy[p]), y); sy[p] = t;
+        y = sub2(az[p], cz[p]); t = add2(sz[p], y); cz[p] = sub2(sub2(t, sz[p]), y); sz[p] = t;
       }
-      if (jt == UJ) {
-        jt = 0;
-        ++itile;
-      }
-      if (!last) load_targets(itile);
+      __syncthreads();  // everyone is done with tile[st] before it is refilled two tiles later
+    }
+    float* out = partial + ((size_t)slot_base + (size_t)chunk) * (size_t)(3 * IT) + tid;
+#pragma unroll
+    for (int p = 0; p < P; p++) {
+      float a, b;
+      upk(sx[p], a, b); out[(2 * p) * T] = a; out[(2 * p + 1) * T] = b;
+      upk(sy[p], a, b); out[IT + (2 * p) * T] = a; out[IT + (2 * p + 1) * T] = b;
+      upk(sz[p], a, b); out[2 * IT + (2 * p) * T] = a; out[2 * IT + (2 * p + 1) * T] = b;
+    }
+    chunk = claimed[(k + 1) & 1u];
+  }
+  if (tid == 0) {
+#ifdef NB_DIRECT_TRACE
+    if (blockIdx.x < 4096) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+      nb_direct_trace_buf[3 * blockIdx.x + 2] = t;
+    }
+#endif
+    // every CTA makes exactly one failing claim before it gets here, so once all have left nobody
+    // touches work[0] again: re-arm both counters for the next launch
+    if (atomicAdd(&work[1], 1u) == gridDim.x - 1) {
+      work[0] = 0u;
+      work[1] = 0u;
     }
   }
 }
+
+#ifdef NB_DIRECT_TRACE
+extern "C" int nb_debug_direct_trace(unsigned long long* out, int n_ctas) {
+  cudaDeviceSynchronize();
+  return (int)cudaMemcpyFromSymbol(out, nb_direct_trace_buf, sizeof(unsigned long long) * 3 * n_ctas);
+}
+#endif
 
 // ---------------------------------------------------------------------------------------------
 // reduce partials in a fixed order (+ optional fused kick, src/cuda/integrator.cu:24-36)
@@ -278,31 +340,22 @@ struct ReduceArgs {
   int npass;
 };
 
-__device__ __forceinline__ void pass_range(const nb_pass& ps, int t, int& c0, int& c1) {
-  const long long A = (long long)t * ps.UJ, B = A + ps.UJ;
-  long long f = ((A + 1) * ps.G + ps.U - 1) / ps.U - 1;
-  long long l = (B * ps.G + ps.U - 1) / ps.U - 1;
-  if (f > ps.G - 1) f = ps.G - 1;
-  if (l > ps.G - 1) l = ps.G - 1;
-  c0 = (int)f;
-  c1 = (int)l;
-}
-
 template <int IT, bool KICK>
 __global__ void __launch_bounds__(256) reduce_kernel(const float* __restrict__ partial, ReduceArgs ra, nb_particles d,
                                                      size_t n, float dt) {
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const int t = (int)(i / IT), r = (int)(i % IT);
-  float ax = 0.f, ay = 0.f, az = 0.f;
+  // chunk sums of this body's target tile in chunk order, compensated (each chunk sum already is)
+  float ax = 0.f, ay = 0.f, az = 0.f, ex = 0.f, ey = 0.f, ez = 0.f;
   for (int ps = 0; ps < ra.npass; ps++) {
-    int c0, c1;
-    pass_range(ra.pass[ps], t, c0, c1);
-    for (int c = c0; c <= c1; c++) {
-      const float* p = partial + (ra.pass[ps].slot_base + (size_t)c + (size_t)t) * (size_t)(3 * IT) + r;
-      ax += p[0];
-      ay += p[IT];
-      az += p[2 * IT];
+    const int C = ra.pass[ps].C;
+    const float* p = partial + (ra.pass[ps].slot_base + (size_t)t * C) * (size_t)(3 * IT) + r;
+    for (int c = 0; c < C; c++, p += 3 * IT) {
+      float y, s;
+      y = __fsub_rn(p[0], ex); s = __fadd_rn(ax, y); ex = __fsub_rn(__fsub_rn(s, ax), y); ax = s;
+      y = __fsub_rn(p[IT], ey); s = __fadd_rn(ay, y); ey = __fsub_rn(__fsub_rn(s, ay), y); ay = s;
+      y = __fsub_rn(p[2 * IT], ez); s = __fadd_rn(az, y); ez = __fsub_rn(__fsub_rn(s, az), y); az = s;
     }
   }
   d.acc_x[i] = ax;
@@ -319,7 +372,7 @@ __global__ void __launch_bounds__(256) reduce_kernel(const float* __restrict__ p
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
-static const DirectCfg kCfgBig = {256, 2, 1024};
+static const DirectCfg kCfgBig = {NB_DIRECT_BIG_T, 2, NB_DIRECT_BIG_JT};
 static const DirectCfg kCfgSmall = {128, 2, 256};
 static const size_t kSmallN = 32768;
 
@@ -335,8 +388,22 @@ static int occupancy(bool eps0) {
   return occ > 0 ? occ : 1;
 }
 
-// Launch one stream-K pass.  Source tiles [ja0, ja0+na) then [jb0, jb0+nbt) of `src` (tile = JT
-// bodies) against n_itiles target tiles of `tgt`.
+// Chunks per target tile: enough chunks that every CTA claims about `per_cta` of them (the tail of a
+// launch is at most one chunk long), never more than one chunk per source tile.
+static int chunks_per_tile(int n_itiles, int UJ, long long ctas) {
+  long long per_cta = 64;
+  if (const char* e = getenv("NB_DIRECT_CHUNKS")) {  // tuning knob: chunks per CTA
+    const long long v = atoll(e);
+    if (v > 0) per_cta = v;
+  }
+  long long c = (per_cta * ctas + n_itiles - 1) / n_itiles;
+  if (c > UJ) c = UJ;
+  if (c < 1) c = 1;
+  return (int)c;
+}
+
+// Launch one pass.  Source tiles [ja0, ja0+na) then [jb0, jb0+nbt) of `src` (tile = JT bodies) against
+// n_itiles target tiles of `tgt`.
 int launch_direct_pass(nb_context* ctx, const DirectCfg& cfg, const float4* src, const float4* tgt, int n_itiles,
                        int ja0, int na, int jb0, int nbt, float eps2, int pass_index, cudaStream_t st) {
   const int UJ = na + nbt;
@@ -344,35 +411,48 @@ int launch_direct_pass(nb_context* ctx, const DirectCfg& cfg, const float4* src,
   ps.UJ = UJ;
   ps.n_itiles = n_itiles;
   ps.U = (long long)n_itiles * UJ;
-  ps.slot_base = (pass_index == 0) ? 0 : ctx->pass[0].slot_base + (size_t)ctx->pass[0].G + ctx->pass[0].n_itiles;
+  ps.slot_base = (pass_index == 0) ? 0 : ctx->pass[0].slot_base + (size_t)ctx->pass[0].chunks;
   if (ps.U == 0) {
     ps.G = 0;
+    ps.C = 0;
+    ps.chunks = 0;
     return NB_OK;
   }
-  const bool big = (cfg.T == kCfgBig.T);
+  const bool big = (&cfg == &kCfgBig);
   const bool eps0 = !(eps2 > 0.f);
   int& occ = ctx->direct_occ[(big ? 0 : 2) + (eps0 ? 1 : 0)];
-  if (occ == 0) occ = big ? occupancy<256, 2, 1024>(eps0) : occupancy<128, 2, 256>(eps0);
+  if (occ == 0) occ = big ? occupancy<NB_DIRECT_BIG_T, 2, NB_DIRECT_BIG_JT>(eps0) : occupancy<128, 2, 256>(eps0);
   int use_occ = occ;
   if (const char* e = getenv("NB_DIRECT_OCC")) {  // tuning knob: resident CTAs per SM
     const int v = atoi(e);
     if (v > 0 && v < occ) use_occ = v;
   }
-  long long g = (long long)use_occ * ctx->sm_count;
-  if (g > ps.U) g = ps.U;
-  ps.G = (int)g;
-  // pass 0 reserves room for a second pass too: the buffer must not move while pass 0 runs
-  const size_t slots = (pass_index == 0) ? 2 * ((size_t)occ * ctx->sm_count + n_itiles)
-                                         : ps.slot_base + (size_t)ps.G + n_itiles;
+  const long long ctas = (long long)use_occ * ctx->sm_count;
+  ps.C = chunks_per_tile(n_itiles, UJ, ctas);
+  ps.chunks = (long long)n_itiles * ps.C;
+  if (ps.chunks > 0x7fffffffll - 65536) {
+    set_error("direct N^2: %lld work chunks exceed the kernel's 32-bit chunk counter", ps.chunks);
+    return NB_ERR_INVALID;
+  }
+  ps.G = (int)(ctas < ps.chunks ? ctas : ps.chunks);
+  // pass 0 reserves room for the remote-source pass of a sharded step too ((R-1) x as many source tiles,
+  // hence at most (R-1) x as many chunks): the buffer must not move while pass 0 runs
+  size_t slots = ps.slot_base + (size_t)ps.chunks;
+  if (pass_index == 0 && ctx->mg_nranks > 1) slots += (size_t)ps.chunks * (size_t)(ctx->mg_nranks - 1);
   if (int rc = ctx->partial.ensure(slots * 3 * cfg.IT() * sizeof(float))) return rc;
+  if (!ctx->direct_work.p) {  // {next chunk, CTAs that left} per pass; the kernels re-arm them
+    if (int rc = ctx->direct_work.ensure(4 * sizeof(unsigned))) return rc;
+    NB_CUDA(cudaMemset(ctx->direct_work.p, 0, 4 * sizeof(unsigned)));
+  }
   float* part = ctx->partial.as<float>();
-#define NB_LAUNCH_DIRECT(T_, I_, JT_, E_)                                                             \
-  direct_force_kernel<T_, I_, JT_, E_><<<ps.G, T_, 0, st>>>(src, tgt, part, ps.U, UJ, ja0, na, jb0, eps2, \
-                                                            (unsigned long long)ps.slot_base)
+  unsigned* work = ctx->direct_work.as<unsigned>() + 2 * pass_index;
+#define NB_LAUNCH_DIRECT(T_, I_, JT_, E_)                                                                     \
+  direct_force_kernel<T_, I_, JT_, E_><<<ps.G, T_, 0, st>>>(src, tgt, part, work, (int)ps.chunks, ps.C, UJ, ja0, na, \
+                                                            jb0, eps2, (unsigned long long)ps.slot_base)
   ProfScope prof(ctx, st);
   if (big) {
-    if (eps0) NB_LAUNCH_DIRECT(256, 2, 1024, true);
-    else NB_LAUNCH_DIRECT(256, 2, 1024, false);
+    if (eps0) NB_LAUNCH_DIRECT(NB_DIRECT_BIG_T, 2, NB_DIRECT_BIG_JT, true);
+    else NB_LAUNCH_DIRECT(NB_DIRECT_BIG_T, 2, NB_DIRECT_BIG_JT, false);
   } else {
     if (eps0) NB_LAUNCH_DIRECT(128, 2, 256, true);
     else NB_LAUNCH_DIRECT(128, 2, 256, false);
@@ -390,10 +470,10 @@ int launch_reduce(nb_context* ctx, const DirectCfg& cfg, const nb_particles* d, 
     if (ctx->pass[p].U > 0) ra.pass[ra.npass++] = ctx->pass[p];
   const unsigned grid = (unsigned)((n + 255) / 256);
   const float* part = ctx->partial.as<float>();
-  const bool big = (cfg.T == kCfgBig.T);
+  const bool big = (&cfg == &kCfgBig);
   if (big) {
-    if (kick) reduce_kernel<512, true><<<grid, 256, 0, st>>>(part, ra, *d, n, dt);
-    else reduce_kernel<512, false><<<grid, 256, 0, st>>>(part, ra, *d, n, dt);
+    if (kick) reduce_kernel<2 * NB_DIRECT_BIG_T, true><<<grid, 256, 0, st>>>(part, ra, *d, n, dt);
+    else reduce_kernel<2 * NB_DIRECT_BIG_T, false><<<grid, 256, 0, st>>>(part, ra, *d, n, dt);
   } else {
     if (kick) reduce_kernel<256, true><<<grid, 256, 0, st>>>(part, ra, *d, n, dt);
     else reduce_kernel<256, false><<<grid, 256, 0, st>>>(part, ra, *d, n, dt);

@@ -144,27 +144,3 @@ def test_shard_layout_properties():
     with pytest.raises(ValueError):
         shard_layout(10, 2, 2)
 
-
-def test_direct_hot_loop_code_address_is_not_64_byte_aligned():
-    """Guard for a measured quirk (profiles/r01_direct_code_alignment_ab.log): the unrolled pair loop of
-    direct_force_kernel<256,2,1024> runs 0.7 % slower when its first instruction sits on a 64-byte
-    boundary (padding the prologue by 1 or 5 instructions: 456.0 ms instead of 452.8 ms per 1 Mi step).
-    If an edit to the prologue moves the loop there, pad it (NB_DIRECT_PAD) rather than lose the 0.7 %."""
-    import re
-    import shutil
-    import subprocess
-    from nbody_b200 import _lib
-    if not shutil.which("cuobjdump"):
-        pytest.skip("cuobjdump not available")
-    sass = subprocess.run(["cuobjdump", "-sass", "-fun",
-                           "_ZN2nb19direct_force_kernelILi256ELi2ELi1024ELb0EEEvPK6float4S3_Pfxiiiify", _lib.LIB_PATH],
-                          capture_output=True, text=True).stdout
-    # the hot loop is the longest backward branch whose body holds the MUFU.RSQ instructions
-    best = None
-    for m in re.finditer(r"/\*([0-9a-f]{4})\*/\s+@P\d\s+BRA\s+0x([0-9a-f]+)", sass):
-        at, to = int(m.group(1), 16), int(m.group(2), 16)
-        if to < at and (best is None or at - to > best[0] - best[1]):
-            best = (at, to)
-    assert best is not None, "hot loop not found (kernel renamed?)"
-    assert best[0] - best[1] > 1500, best
-    assert best[1] % 64 != 0, f"hot loop starts at {best[1]:#x}: on a 64-byte boundary (0.7 % slower)"
