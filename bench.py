@@ -41,6 +41,24 @@ FP32_PEAK_DATASHEET_TF = 80.0    # B200 datasheet, the denominator BASELINE.json
 G_CONST, SOFTENING, DT = 1.0, 0.01, 1e-3
 
 
+_JSON_FD = None
+
+
+def quiet_stdout():
+    """Libraries below us print to fd 1 (NCCL's version banner under NCCL_DEBUG): send fd 1 to stderr while
+    the bench runs and keep the real stdout for the one JSON line."""
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line: dict):
+    sys.stdout.flush()
+    data = (json.dumps(line) + "\n").encode()
+    os.write(_JSON_FD if _JSON_FD is not None else 1, data)
+
+
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -169,11 +187,12 @@ def run_reference_arm(args):
         "e2e": {"value": value, "unit": "G-interactions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 def main():
     args = parse()
+    quiet_stdout()
     if args.impl == "reference":
         run_reference_arm(args)
         return
@@ -290,7 +309,11 @@ def main():
         "frac_of_measured_ffma2": (achieved_tf / 64.3) if achieved_tf else None,
         "flop_per_interaction": FLOP_PER_INTERACTION, "kernel_ms": kernel_ms,
         "kernel_share_of_step": (kms.value / args.steps) / ms_per_step if ms_per_step > 0 else None,
-        "traffic": None,
+        # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the ncu --set full capture of this
+        # command (profiles/r01_direct_force_1mi_ncu_full.txt): 34.8 MB read (the 16 MiB packed sources, once,
+        # + target tiles) + 261.7 MB written (302 MB of per-chunk partials, part still in L2 at kernel end)
+        "traffic": 296489216 if (n == (1 << 20) and world == 1) else None,
+        "traffic_unit": "bytes per launch (compute-bound kernel: 3.7e3 flop per DRAM byte)",
     }
 
     cpu = None
@@ -333,7 +356,7 @@ def main():
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
         "reference_gpu": ref_gpu,
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 if __name__ == "__main__":

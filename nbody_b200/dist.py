@@ -13,7 +13,7 @@ exchange="peer" (default): the all-gather is fused into our own kernels over NVL
   2. force pass over the LOCAL slice (overlaps the peers' pushes)
   3. a one-warp kernel waits for the R-1 peer flags (acquire at system scope)
   4. force pass over the other R-1 slices in ring order
-  5. fixed-order reduction of the stream-K partials + kick
+  5. fixed-order reduction of the per-chunk partials + kick
 
 exchange="nccl": the baseline the peer path is measured against.
   1. pack into this rank's slot                                          (nb_mgpu_pack_local)
