@@ -169,6 +169,15 @@ int nb_context_create(int device, size_t max_bodies_hint, nb_context** out) {
   ctx->cc_major = maj;
   ctx->cc_minor = min;
   (void)max_bodies_hint;
+  // chunk counters of the direct kernel's two passes ({next chunk, CTAs that left} each): zeroed once here,
+  // re-armed by the kernel itself, so the first launch may already sit inside a stream capture
+  if (ctx->direct_work.ensure(4 * sizeof(unsigned)) != NB_OK ||
+      cudaMemset(ctx->direct_work.p, 0, 4 * sizeof(unsigned)) != cudaSuccess) {
+    set_error("cannot allocate the work counters: %s", cudaGetErrorString(cudaGetLastError()));
+    ctx->direct_work.release();
+    delete ctx;
+    return NB_ERR_RESOURCE;
+  }
   *out = ctx;
   return NB_OK;
 }

@@ -152,6 +152,11 @@ int launch_peer_wait(nb_context* ctx, const unsigned* flags, int flag_base, unsi
 #ifndef NB_DIRECT_UNROLL
 #define NB_DIRECT_UNROLL 64  // sources per trip of the pair loop (8: 440.5 ms per 1 Mi step, 32: 430.9, 64: 429.4)
 #endif
+// Tried and dropped (profiles/r01_direct_variants_ab.log): not keeping the warps of a CTA in lockstep --
+// the producer's warp alone waits on a named barrier before refilling a buffer, the others bar.arrive and
+// block only on missing data -- 430.5 ms against 429.8 ms with the plain __syncthreads per tile.
+#if 0
+#endif
 #ifndef NB_DIRECT_BIG_T
 #define NB_DIRECT_BIG_T 256  // threads per CTA of the large-N configuration
 #endif
@@ -440,10 +445,6 @@ int launch_direct_pass(nb_context* ctx, const DirectCfg& cfg, const float4* src,
   size_t slots = ps.slot_base + (size_t)ps.chunks;
   if (pass_index == 0 && ctx->mg_nranks > 1) slots += (size_t)ps.chunks * (size_t)(ctx->mg_nranks - 1);
   if (int rc = ctx->partial.ensure(slots * 3 * cfg.IT() * sizeof(float))) return rc;
-  if (!ctx->direct_work.p) {  // {next chunk, CTAs that left} per pass; the kernels re-arm them
-    if (int rc = ctx->direct_work.ensure(4 * sizeof(unsigned))) return rc;
-    NB_CUDA(cudaMemset(ctx->direct_work.p, 0, 4 * sizeof(unsigned)));
-  }
   float* part = ctx->partial.as<float>();
   unsigned* work = ctx->direct_work.as<unsigned>() + 2 * pass_index;
 #define NB_LAUNCH_DIRECT(T_, I_, JT_, E_)                                                                     \
