@@ -155,8 +155,6 @@ int launch_peer_wait(nb_context* ctx, const unsigned* flags, int flag_base, unsi
 // Tried and dropped (profiles/r01_direct_variants_ab.log): not keeping the warps of a CTA in lockstep --
 // the producer's warp alone waits on a named barrier before refilling a buffer, the others bar.arrive and
 // block only on missing data -- 430.5 ms against 429.8 ms with the plain __syncthreads per tile.
-#if 0
-#endif
 #ifndef NB_DIRECT_BIG_T
 #define NB_DIRECT_BIG_T 256  // threads per CTA of the large-N configuration
 #endif
