@@ -1,0 +1,61 @@
+#!/usr/bin/env python
+"""SURVEY 8(d) config 2, energy-drift check: relative drift of the total energy over 1000 Velocity-Verlet steps
+(dt 1e-3, eps 0.01, Plummer seed 42) at 65 536 and 262 144 bodies, ours and -- same initial conditions -- the
+reference's own kernels (oracle/_ref/libnbody_ref.so), E in fp64 by our diagnostic for both.  A measurement
+script, not a test (the 8192-body version of the same check is tests/test_gpu_vs_reference.py): run on a B200,
+one JSON line per case.  usage: python tests/measure_energy_drift.py [n ...]"""
+import json
+import sys
+import time
+
+import numpy as np
+
+
+def main():
+    import torch
+    import nbody_b200 as nb
+    from nbody_b200 import ics
+    from oracle import ref_bindings as ref
+
+    sizes = [int(a) for a in sys.argv[1:]] or [65536, 262144]
+    steps, dt, eps = 1000, 1e-3, 0.01
+    for n in sizes:
+        st = ics.plummer(n, seed=42)
+
+        def device(state):
+            h = nb.ParticleDataManager.fromState(state)
+            d = nb.ParticleData()
+            nb.ParticleDataManager.allocateDevice(d, h.count)
+            nb.ParticleDataManager.copyToDevice(d, h)
+            return d
+
+        d = device(st)
+        calc = nb.DirectForceCalculator()
+        calc.setSofteningParameter(eps)
+        calc.computeForces(d)
+        integ = nb.Integrator()
+        e0 = integ.computeTotalEnergy(d, 1.0, eps)
+        torch.cuda.synchronize()
+        t0 = time.time()
+        for _ in range(steps):
+            integ.integrate(d, calc, dt)
+        e1 = integ.computeTotalEnergy(d, 1.0, eps)
+        t_ours = time.time() - t0
+        rec = {"bodies": n, "steps": steps, "dt": dt, "softening": eps, "E0": e0, "E_ours": e1,
+               "drift_ours": abs(e1 - e0) / abs(e0), "seconds_ours": t_ours}
+        if ref.available():
+            r = {k: v.copy() for k, v in st.items()}
+            t0 = time.time()
+            ref.run(r, 0, dt, 1.0, eps, steps=steps, initial_forces=True)
+            rec["seconds_reference"] = time.time() - t0
+            er = integ.computeTotalEnergy(device(r), 1.0, eps)
+            rec.update({"E_reference": er, "drift_reference": abs(er - e0) / abs(e0)})
+            # how far apart the two trajectories are after 1000 steps
+            o = d.numpy()
+            dx = np.sqrt((o["pos_x"] - r["pos_x"]) ** 2 + (o["pos_y"] - r["pos_y"]) ** 2 + (o["pos_z"] - r["pos_z"]) ** 2)
+            rec["max_position_difference"] = float(dx.max())
+        print(json.dumps(rec), flush=True)
+
+
+if __name__ == "__main__":
+    main()
