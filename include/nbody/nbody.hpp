@@ -445,6 +445,12 @@ class Integrator {
   float computeTotalEnergy(const ParticleData* d, float G, float eps) {
     return computeKineticEnergy(d) + computePotentialEnergy(d, G, eps);
   }
+  // total mass, centre of mass, momenta, KE and (optionally) PE, total energy, virial ratio -- fp64, one call
+  nb_diagnostics_t computeDiagnostics(const ParticleData* d, float G, float eps, bool with_potential = true) {
+    nb_diagnostics_t out{};
+    NB_CALL(nb_diagnostics(Engine::get(), as_nb(d), G, eps, with_potential ? 1 : 0, &out, nullptr));
+    return out;
+  }
   void ensureScratchBuffer(std::size_t) {}  // scratch lives in the engine context
   void setBlockSize(int s) { block_size_ = s; }
   int getBlockSize() const noexcept { return block_size_; }
@@ -974,6 +980,10 @@ class ParticleSystem {
   float computePotentialEnergy() const { return integrator_ ? integrator_->computePotentialEnergy(&d_, G_, softening_) : 0.0f; }
   float computeTotalEnergy() const { return computeKineticEnergy() + computePotentialEnergy(); }
   double computeTotalEnergyF64() const { return integrator_ ? integrator_->computeTotalEnergyF64(&d_, G_, softening_) : 0.0; }
+  nb_diagnostics_t computeDiagnostics(bool with_potential = true) const {
+    if (!integrator_) throw ValidationException("ParticleSystem is not initialized");
+    return integrator_->computeDiagnostics(&d_, G_, softening_, with_potential);
+  }
   void synchronize() const { NB_CALL(nb_synchronize(Engine::get(), nullptr)); }
 
  private:

@@ -105,6 +105,22 @@ int nb_step_direct(nb_context* ctx, const nb_particles* d, float dt, float G, fl
 /* Integrator::compute{Kinetic,Potential}Energy (:252-289), fp64 accumulation; synchronises. */
 int nb_kinetic_energy(nb_context* ctx, const nb_particles* d, double* ke, nb_stream s);
 int nb_potential_energy(nb_context* ctx, const nb_particles* d, float G, float eps, double* pe, nb_stream s);
+/* Conserved-quantity diagnostics in one call (no reference equivalent -- the reference's
+ * tests compute these on the host, tests/test_integrator.cpp:51-162): fp64 sums over the device arrays.
+ * with_potential != 0 adds the O(N^2) potential energy and the virial ratio 2 KE / |PE|.  Synchronises. */
+typedef struct nb_diagnostics_t {
+  double total_mass;
+  double center_of_mass[3];
+  double momentum[3];          /* sum m v */
+  double angular_momentum[3];  /* sum m x cross v, about the origin */
+  double kinetic;
+  double potential;            /* 0 unless has_potential */
+  double total_energy;         /* kinetic + potential */
+  double virial_ratio;         /* 2 KE / |PE|, 0 unless has_potential */
+  int has_potential;
+} nb_diagnostics_t;
+int nb_diagnostics(nb_context* ctx, const nb_particles* d, float G, float eps, int with_potential,
+                   nb_diagnostics_t* out, nb_stream s);
 
 /* ---- host-buffer entry points (what bench.py's e2e times): host SoA in, host SoA out, H2D and
  *      D2H inside the call.  Equivalent to ParticleSystem::setState -> update x steps -> getState

@@ -80,6 +80,7 @@ SYMBOLS = {
     "nb_step_direct": (_i, [_vp, _pp, _f, _f, _f, _vp]),
     "nb_kinetic_energy": (_i, [_vp, _pp, C.POINTER(C.c_double), _vp]),
     "nb_potential_energy": (_i, [_vp, _pp, _f, _f, C.POINTER(C.c_double), _vp]),
+    "nb_diagnostics": (_i, [_vp, _pp, _f, _f, _i, _vp, _vp]),
     "nb_host_direct_forces": (_i, [_vp, _pp, _f, _f]),
     "nb_host_step_direct": (_i, [_vp, _pp, _f, _f, _f, _i, _i]),
     "nb_bh_build": (_i, [_vp, _pp, _vp]),

@@ -434,6 +434,12 @@ def createForceCalculator(method: ForceMethod, config: SimulationConfig) -> Forc
 
 
 # ---- integrator -----------------------------------------------------------------------------------
+class _Diagnostics(C.Structure):  # nb_diagnostics_t (include/nbody_b200.h)
+    _fields_ = [("total_mass", C.c_double), ("center_of_mass", C.c_double * 3), ("momentum", C.c_double * 3),
+                ("angular_momentum", C.c_double * 3), ("kinetic", C.c_double), ("potential", C.c_double),
+                ("total_energy", C.c_double), ("virial_ratio", C.c_double), ("has_potential", C.c_int)]
+
+
 class Integrator:
     """include/nbody/integrator.hpp:33-150, src/cuda/integrator.cu:205-293."""
 
@@ -477,6 +483,23 @@ class Integrator:
 
     def computeTotalEnergy(self, d_particles, G, eps) -> float:
         return self.computeKineticEnergy(d_particles) + self.computePotentialEnergy(d_particles, G, eps)
+
+    def computeDiagnostics(self, d_particles, G=1.0, eps=0.01, with_potential=True) -> dict:
+        """nb_diagnostics: total mass, centre of mass, linear and angular momentum, KE and -- if asked -- PE, total
+        energy and the virial ratio 2 KE / |PE|, all fp64 sums over the device arrays (no reference equivalent)."""
+        out = _Diagnostics()
+        check(_lib.lib().nb_diagnostics(get_context().handle, C.byref(d_particles.c), float(G), float(eps),
+                                        1 if with_potential else 0, C.byref(out), _stream()))
+        return {
+            "total_mass": out.total_mass,
+            "center_of_mass": np.array(out.center_of_mass[:]),
+            "momentum": np.array(out.momentum[:]),
+            "angular_momentum": np.array(out.angular_momentum[:]),
+            "kinetic": out.kinetic,
+            "potential": out.potential if out.has_potential else None,
+            "total_energy": out.total_energy if out.has_potential else None,
+            "virial_ratio": out.virial_ratio if out.has_potential else None,
+        }
 
     def setBlockSize(self, size):
         self.block_size_ = size
@@ -726,3 +749,9 @@ class ParticleSystem:
 
     def computeTotalEnergy(self):
         return self.computeKineticEnergy() + self.computePotentialEnergy()
+
+    def computeDiagnostics(self, with_potential=True):
+        """Conserved quantities of the current state (see Integrator.computeDiagnostics)."""
+        if not self.integrator_:
+            raise ValidationException("ParticleSystem is not initialized")
+        return self.integrator_.computeDiagnostics(self.d_particles_, self.G_, self.softening_, with_potential)

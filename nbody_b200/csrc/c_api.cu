@@ -79,6 +79,7 @@ int launch_drift(nb_context* ctx, const nb_particles* d, float dt, cudaStream_t 
 int launch_kick(nb_context* ctx, const nb_particles* d, float dt, cudaStream_t st);
 int kinetic_energy(nb_context* ctx, const nb_particles* d, double* ke, cudaStream_t st);
 int potential_energy(nb_context* ctx, const nb_particles* d, float G, float eps, double* pe, cudaStream_t st);
+int moments(nb_context* ctx, const nb_particles* d, double* out11, cudaStream_t st);
 void bh_destroy(nb_context* ctx);
 void sh_destroy(nb_context* ctx);
 void render_destroy(nb_context* ctx);
@@ -500,6 +501,38 @@ int nb_potential_energy(nb_context* ctx, const nb_particles* d, float G, float e
     return NB_ERR_INVALID;
   }
   return potential_energy(ctx, d, G, eps, pe, (cudaStream_t)s);
+}
+
+int nb_diagnostics(nb_context* ctx, const nb_particles* d, float G, float eps, int with_potential,
+                   nb_diagnostics_t* out, nb_stream s) {
+  NB_ENTER(ctx);
+  if (!out) {
+    set_error("diagnostics: null output");
+    return NB_ERR_INVALID;
+  }
+  if (!d || (d->count && (!d->pos_x || !d->pos_y || !d->pos_z || !d->vel_x || !d->vel_y || !d->vel_z || !d->mass))) {
+    set_error("diagnostics: null position/velocity/mass array");
+    return NB_ERR_INVALID;
+  }
+  double m[11];
+  if (int rc = moments(ctx, d, m, (cudaStream_t)s)) return rc;
+  out->total_mass = m[0];
+  for (int a = 0; a < 3; a++) {
+    out->center_of_mass[a] = (m[0] != 0.0) ? m[1 + a] / m[0] : 0.0;
+    out->momentum[a] = m[4 + a];
+    out->angular_momentum[a] = m[7 + a];
+  }
+  out->kinetic = m[10];
+  out->potential = 0.0;
+  out->virial_ratio = 0.0;
+  out->has_potential = 0;
+  if (with_potential) {
+    if (int rc = potential_energy(ctx, d, G, eps, &out->potential, (cudaStream_t)s)) return rc;
+    out->has_potential = 1;
+    if (out->potential != 0.0) out->virial_ratio = 2.0 * out->kinetic / (out->potential < 0 ? -out->potential : out->potential);
+  }
+  out->total_energy = out->kinetic + out->potential;
+  return NB_OK;
 }
 
 // ---- host-buffer entry points ------------------------------------------------------------------

@@ -175,4 +175,53 @@ int potential_energy(nb_context* ctx, const nb_particles* d, float G, float eps,
   return NB_OK;
 }
 
+// ---------------------------------------------------------------------------------------------
+// conserved-quantity diagnostics: one pass over the bodies, fp64 sums of
+//   M, M*x_com (3), P = sum m v (3), L = sum m x cross v (3), KE  -> NB_DIAG_MOMENTS values per CTA,
+// summed on the host in CTA order (deterministic).  The reference has no equivalent; its tests check
+// these quantities on the host (tests/test_integrator.cpp:51-84 for KE).
+// ---------------------------------------------------------------------------------------------
+constexpr int NB_DIAG_MOMENTS = 11;
+__global__ void __launch_bounds__(256) moments_kernel(nb_particles d, size_t n, double* __restrict__ out) {
+  __shared__ double sh[8];
+  double a[NB_DIAG_MOMENTS];
+#pragma unroll
+  for (int q = 0; q < NB_DIAG_MOMENTS; q++) a[q] = 0.0;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const double m = d.mass[i];
+    const double x = d.pos_x[i], y = d.pos_y[i], z = d.pos_z[i];
+    const double vx = d.vel_x[i], vy = d.vel_y[i], vz = d.vel_z[i];
+    a[0] += m;
+    a[1] += m * x; a[2] += m * y; a[3] += m * z;
+    a[4] += m * vx; a[5] += m * vy; a[6] += m * vz;
+    a[7] += m * (y * vz - z * vy); a[8] += m * (z * vx - x * vz); a[9] += m * (x * vy - y * vx);
+    a[10] += 0.5 * m * (vx * vx + vy * vy + vz * vz);
+  }
+#pragma unroll
+  for (int q = 0; q < NB_DIAG_MOMENTS; q++) {
+    const double t = block_sum(a[q], sh);
+    if (threadIdx.x == 0) out[(size_t)blockIdx.x * NB_DIAG_MOMENTS + q] = t;
+    __syncthreads();  // sh is reused by the next moment
+  }
+}
+
+int moments(nb_context* ctx, const nb_particles* d, double* out11, cudaStream_t st) {
+  const size_t n = d->count;
+  for (int q = 0; q < NB_DIAG_MOMENTS; q++) out11[q] = 0.0;
+  if (!n) return NB_OK;
+  size_t grid = (n + 255) / 256;
+  const size_t cap = (size_t)ctx->sm_count * 8;
+  if (grid > cap) grid = cap;
+  if (int rc = ctx->red.ensure(sizeof(double) * grid * NB_DIAG_MOMENTS)) return rc;
+  moments_kernel<<<(unsigned)grid, 256, 0, st>>>(*d, n, ctx->red.as<double>());
+  NB_LAUNCH_CHECK(ctx);
+  if (!ctx->h_red) NB_CUDA(cudaMallocHost(&ctx->h_red, sizeof(double) * 65536));
+  NB_CUDA(cudaMemcpyAsync(ctx->h_red, ctx->red.as<double>(), sizeof(double) * grid * NB_DIAG_MOMENTS,
+                          cudaMemcpyDeviceToHost, st));  // grid <= 8 * SMs: fits the 65536-double staging buffer
+  NB_CUDA(cudaStreamSynchronize(st));
+  for (size_t b = 0; b < grid; b++)
+    for (int q = 0; q < NB_DIAG_MOMENTS; q++) out11[q] += ctx->h_red[b * NB_DIAG_MOMENTS + q];
+  return NB_OK;
+}
+
 }  // namespace nb

@@ -81,6 +81,8 @@ def lib():
     L.orc_kinetic_f64.argtypes = [i, f32p, f32p, f32p, f32p]
     L.orc_kinetic_f64.restype = d
     L.orc_potential_f64.argtypes = [i, f32p, f32p, f32p, f32p, d, d]
+    L.orc_moments_f64.argtypes = [i] + [f32p] * 7 + [C.c_void_p]
+    L.orc_moments_f64.restype = None
     L.orc_potential_f64.restype = d
     L.orc_bbox.argtypes = [i, f32p, f32p, f32p, f32p]
     L.orc_expand_bits.argtypes = [C.c_uint32]
@@ -183,6 +185,14 @@ def store_acc(state):
 
 def kinetic(vx, vy, vz, m):
     return lib().orc_kinetic_f64(vx.size, _f32(vx), _f32(vy), _f32(vz), _f32(m))
+
+
+def moments(state):
+    """{M, sum m x (3), sum m v (3), sum m x cross v (3), KE} in fp64."""
+    out = np.zeros(11, np.float64)
+    lib().orc_moments_f64(state["pos_x"].size, *(_f32(state[k]) for k in ("pos_x", "pos_y", "pos_z", "vel_x", "vel_y",
+                                                                          "vel_z", "mass")), out.ctypes.data)
+    return out
 
 
 def potential(px, py, pz, m, G, eps):

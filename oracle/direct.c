@@ -155,6 +155,21 @@ double orc_kinetic_f64(int n, const float* vx, const float* vy, const float* vz,
   return ke;
 }
 
+/* Conserved-quantity moments in fp64 (checker for nb_diagnostics; the reference's tests compute the same sums on
+ * the host, tests/test_integrator.cpp:51-84): out = {M, sum m x (3), sum m v (3), sum m x cross v (3), KE}. */
+void orc_moments_f64(int n, const float* px, const float* py, const float* pz, const float* vx, const float* vy,
+                     const float* vz, const float* m, double* out11) {
+  for (int q = 0; q < 11; q++) out11[q] = 0.0;
+  for (int i = 0; i < n; i++) {
+    const double mi = m[i], x = px[i], y = py[i], z = pz[i], u = vx[i], v = vy[i], w = vz[i];
+    out11[0] += mi;
+    out11[1] += mi * x; out11[2] += mi * y; out11[3] += mi * z;
+    out11[4] += mi * u; out11[5] += mi * v; out11[6] += mi * w;
+    out11[7] += mi * (y * w - z * v); out11[8] += mi * (z * u - x * w); out11[9] += mi * (x * v - y * u);
+    out11[10] += 0.5 * mi * (u * u + v * v + w * w);
+  }
+}
+
 /* src/cuda/integrator.cu:90-103: pe -= G*m_i*m_j / sqrt(r^2 + eps^2) over j > i; fp64. */
 double orc_potential_f64(int n, const float* px, const float* py, const float* pz, const float* m,
                          double G, double eps) {

@@ -58,6 +58,8 @@ void orc_run_direct(int n, float* const arrays[13], float dt, float G, float eps
 /* ---- energy ------------------------------------------------------------------------ */
 /* src/cuda/integrator.cu:59-63 (KE) and :90-103 (PE), accumulated in fp64 */
 double orc_kinetic_f64(int n, const float* vx, const float* vy, const float* vz, const float* m);
+void orc_moments_f64(int n, const float* px, const float* py, const float* pz, const float* vx, const float* vy,
+                     const float* vz, const float* m, double* out11);
 double orc_potential_f64(int n, const float* px, const float* py, const float* pz, const float* m,
                          double G, double eps);
 

@@ -72,6 +72,13 @@ static void integrator_cases() {  // tests/test_integrator.cpp:15-84, 90-162
   for (int i = 0; i < 100; i++) integ.integrate(&d, &calc, 0.001f);
   const double e1 = integ.computeTotalEnergyF64(&d, 1.0f, 0.01f);
   CHECK(std::fabs((e1 - e0) / e0) < 0.01);
+  // conserved-quantity diagnostics: the equal-mass binary keeps P = 0, L = m (x cross v) summed, M = 2
+  const nb_diagnostics_t dg = integ.computeDiagnostics(&d, 1.0f, 0.01f);
+  CHECK(std::fabs(dg.total_mass - 2.0) < 1e-12);
+  CHECK(std::fabs(dg.momentum[0]) < 1e-6 && std::fabs(dg.momentum[1]) < 1e-6 && std::fabs(dg.momentum[2]) < 1e-12);
+  CHECK(std::fabs(dg.angular_momentum[2] - 5.0 * v) < 1e-4);    // 2 bodies x m r v with r = 2.5
+  CHECK(std::fabs(dg.total_energy - e1) < 1e-9 && dg.has_potential == 1);
+  CHECK(std::fabs(dg.center_of_mass[0]) < 1e-6 && std::fabs(dg.center_of_mass[1]) < 1e-6);
   ParticleDataManager::freeDevice(d);
   ParticleDataManager::freeHost(h);
 }

@@ -245,3 +245,53 @@ def test_direct_is_reproducible_run_to_run():
         if first is None:
             first = got.copy()
         assert np.array_equal(got, first)
+
+
+@pytest.mark.parametrize("n", [1, 777, 100003])
+def test_diagnostics_vs_oracle(orc, n):
+    """nb_diagnostics: fp64 moments, KE, PE and the virial ratio against the oracle's fp64 sums."""
+    import nbody_b200 as nb
+    from nbody_b200 import ics
+    st = ics.plummer(n, seed=21) if n > 1 else ics.uniform_box(1, -1, 1, seed=2)
+    st["pos_x"] += 0.5
+    st["vel_z"] += 0.25
+    d = _device_data(st)
+    got = nb.Integrator().computeDiagnostics(d, 1.0, 0.01)
+    want = orc.moments(st)
+    assert abs(got["total_mass"] - want[0]) <= 1e-12 * abs(want[0])
+    assert np.allclose(got["center_of_mass"], want[1:4] / want[0], rtol=1e-11, atol=1e-13)
+    assert np.allclose(got["momentum"], want[4:7], rtol=1e-11, atol=1e-13)
+    assert np.allclose(got["angular_momentum"], want[7:10], rtol=1e-10, atol=1e-13)
+    assert abs(got["kinetic"] - want[10]) <= 1e-12 * abs(want[10])
+    pe = orc.potential(st["pos_x"], st["pos_y"], st["pos_z"], st["mass"], 1.0, 0.01)
+    if n == 1:
+        assert got["potential"] == 0.0 and got["virial_ratio"] == 0.0
+    else:
+        assert abs(got["potential"] - pe) <= 2e-6 * abs(pe)      # pair terms are fp32 rsqrt, sums fp64
+        assert abs(got["virial_ratio"] - 2 * want[10] / abs(pe)) <= 1e-5
+        assert abs(got["total_energy"] - (want[10] + pe)) <= 2e-6 * abs(pe)
+    light = nb.Integrator().computeDiagnostics(d, 1.0, 0.01, with_potential=False)
+    assert light["potential"] is None and light["kinetic"] == got["kinetic"]
+
+
+def test_verlet_conserves_momentum_and_plummer_is_virialised():
+    """Properties the diagnostics exist for: the pairwise-antisymmetric direct sum keeps total momentum and angular
+    momentum at rounding level over Verlet steps, and the Henon-unit Plummer sphere sits at 2 KE / |PE| ~ 1."""
+    import nbody_b200 as nb
+    from nbody_b200 import ics
+    st = ics.plummer(32768, seed=42)
+    d = _device_data(st)
+    calc = nb.DirectForceCalculator()
+    calc.setSofteningParameter(0.01)
+    calc.computeForces(d)
+    integ = nb.Integrator()
+    a = integ.computeDiagnostics(d, 1.0, 0.01)
+    assert 0.9 < a["virial_ratio"] < 1.1
+    for _ in range(50):
+        integ.integrate(d, calc, 1e-3)
+    b = integ.computeDiagnostics(d, 1.0, 0.01)
+    scale = np.sqrt(2 * a["kinetic"] * a["total_mass"])        # ~ sum m |v|
+    assert np.abs(b["momentum"] - a["momentum"]).max() <= 1e-5 * scale
+    assert np.abs(b["angular_momentum"] - a["angular_momentum"]).max() <= 1e-5 * scale
+    assert np.abs(b["center_of_mass"] - (a["center_of_mass"] + 0.05 * a["momentum"] / a["total_mass"])).max() <= 1e-6
+    assert abs(b["total_energy"] - a["total_energy"]) <= 1e-5 * abs(a["total_energy"])

@@ -121,3 +121,19 @@ def test_grid_ranges_against_numpy(orc):
     # cutoff larger than anything reachable by the 3x3x3 stencil == all pairs within the stencil
     ax, ay, az, pairs = orc.spatial_forces(st["pos_x"], st["pos_y"], st["pos_z"], st["mass"], g, 1e-3, 1.0, 0.1)
     assert pairs == 0 and not ax.any()
+
+
+def test_moments_oracle_matches_numpy(orc):
+    """orc_moments_f64 (checker of nb_diagnostics) against plain numpy fp64 sums."""
+    from nbody_b200 import ics
+    st = ics.plummer(5000, seed=4)
+    st["pos_x"] += 0.25  # off-centre, so that the first moments are not ~0
+    st["vel_y"] += 0.125
+    got = orc.moments(st)
+    m = st["mass"].astype(np.float64)
+    x = np.stack([st[k].astype(np.float64) for k in ("pos_x", "pos_y", "pos_z")])
+    v = np.stack([st[k].astype(np.float64) for k in ("vel_x", "vel_y", "vel_z")])
+    want = np.concatenate([[m.sum()], (m * x).sum(1), (m * v).sum(1), (m * np.cross(x.T, v.T).T).sum(1),
+                           [0.5 * (m * (v * v).sum(0)).sum()]])
+    assert np.allclose(got, want, rtol=1e-12, atol=1e-15)
+    assert abs(got[10] - orc.kinetic(st["vel_x"], st["vel_y"], st["vel_z"], st["mass"])) <= 1e-14
