@@ -87,42 +87,84 @@ __global__ void __launch_bounds__(256) kinetic_kernel(nb_particles d, size_t n, 
   if (threadIdx.x == 0) out[blockIdx.x] = t;
 }
 
-// src/cuda/integrator.cu:81-119 re-tiled: CTA (bi, bj) handles target tile bi against source
-// chunk bj; every ordered pair i != j is visited once and the result halved (= sum over j > i).
-// Pair terms m_j / sqrt(r^2+eps^2) are fp32 (rsqrt), sums are fp64.
+// src/cuda/integrator.cu:81-119 re-tiled.  The reference visits every pair j > i from one thread per i (global
+// loads, triangular imbalance, fp32 sum).  Here the pair set is cut into 512 x 512 tile pairs of the upper
+// triangle (source tile >= target tile): CTA (bi, by) takes target tile bi against up to `chunk` source tiles
+// starting `by * chunk` tiles right of the diagonal.  Each thread holds two targets as one packed fp32x2 pair,
+// the source is a warp-broadcast LDS.128, and the pair term m_j / sqrt(r^2 + eps^2) costs 3 FADD2 + 3 FFMA2 +
+// 2 MUFU.RSQ + 1 FMUL2 + 1 FADD2 per two pairs.  Off-diagonal tiles need no index test (and with eps > 0 no
+// r = 0 test); the diagonal tile keeps j > i.  Pair terms are fp32, a tile's 512 terms are summed in four
+// interleaved fp32 accumulators, everything above that in fp64.
 constexpr int PE_T = 256;
-constexpr int PE_JT = 256;
-__global__ void __launch_bounds__(PE_T) potential_kernel(nb_particles d, size_t n, float eps2, int jchunk_tiles,
+constexpr int PE_TILE = 2 * PE_T;
+template <bool EPS0>
+__global__ void __launch_bounds__(PE_T) potential_kernel(nb_particles d, size_t n, float eps2, int n_tiles, int chunk,
                                                          double* __restrict__ out) {
-  __shared__ float4 tile[PE_JT];
+  __shared__ __align__(16) float4 tile[PE_TILE];
   __shared__ double sh[8];
-  const size_t i = (size_t)blockIdx.x * PE_T + threadIdx.x;
-  const bool live = i < n;
-  const float xi = live ? d.pos_x[i] : 0.f, yi = live ? d.pos_y[i] : 0.f, zi = live ? d.pos_z[i] : 0.f;
-  const size_t j_begin = (size_t)blockIdx.y * jchunk_tiles * PE_JT;
-  size_t j_end = j_begin + (size_t)jchunk_tiles * PE_JT;
-  if (j_end > n) j_end = n;
-  double acc = 0.0;
-  for (size_t jb = j_begin; jb < j_end; jb += PE_JT) {
-    const size_t j = jb + threadIdx.x;
-    tile[threadIdx.x] = (j < n) ? make_float4(d.pos_x[j], d.pos_y[j], d.pos_z[j], d.mass[j]) : make_float4(0, 0, 0, 0);
-    __syncthreads();
-    float s = 0.f;
-#pragma unroll 8
-    for (int k = 0; k < PE_JT; k++) {
-      const float4 p = tile[k];
-      const float dx = p.x - xi, dy = p.y - yi, dz = p.z - zi;
-      const float r2 = fmaf(dz, dz, fmaf(dy, dy, fmaf(dx, dx, eps2)));
-      float t = p.w * rsq(r2);
-      t = (jb + k == i || !(r2 > 0.f)) ? 0.f : t;  // j == i excluded (integrator.cu:97: j starts at i+1)
-      s += t;
+  const int tid = threadIdx.x;
+  const int bi = blockIdx.x;
+  const int jt0 = bi + (int)blockIdx.y * chunk;
+  double* slot = out + (size_t)blockIdx.y * gridDim.x + blockIdx.x;
+  if (jt0 >= n_tiles) {  // nothing right of the diagonal left for this CTA
+    if (tid == 0) *slot = 0.0;
+    return;
+  }
+  const int jt1 = min(jt0 + chunk, n_tiles);
+  const size_t i0 = (size_t)bi * PE_TILE + tid, i1 = i0 + PE_T;
+  const bool live0 = i0 < n, live1 = i1 < n;
+  const f2 xi = pk(live0 ? d.pos_x[i0] : 0.f, live1 ? d.pos_x[i1] : 0.f);
+  const f2 yi = pk(live0 ? d.pos_y[i0] : 0.f, live1 ? d.pos_y[i1] : 0.f);
+  const f2 zi = pk(live0 ? d.pos_z[i0] : 0.f, live1 ? d.pos_z[i1] : 0.f);
+  const f2 e2 = pk(eps2, eps2);
+  const f2 zero2 = pk(0.f, 0.f);
+  double acc0 = 0.0, acc1 = 0.0;
+  for (int jt = jt0; jt < jt1; jt++) {
+    const size_t jb = (size_t)jt * PE_TILE;
+#pragma unroll
+    for (int h = 0; h < 2; h++) {  // padding sources carry zero mass
+      const size_t j = jb + tid + h * PE_T;
+      tile[tid + h * PE_T] = (j < n) ? make_float4(d.pos_x[j], d.pos_y[j], d.pos_z[j], d.mass[j]) : make_float4(0, 0, 0, 0);
     }
-    acc += (double)s;
+    __syncthreads();
+    f2 s[4] = {zero2, zero2, zero2, zero2};
+    if (EPS0 || jt == bi) {
+      // diagonal tile: keep j > i only; eps == 0: a coincident pair (r = 0) contributes nothing instead of inf
+      const bool diag = (jt == bi);
+      const int k_lo0 = diag ? tid + 1 : 0, k_lo1 = diag ? tid + PE_T + 1 : 0;  // first source index kept per target
+#pragma unroll 4
+      for (int k = 0; k < PE_TILE; k++) {
+        const float4 p = tile[k];
+        const f2 dx = sub2(pk(p.x, p.x), xi), dy = sub2(pk(p.y, p.y), yi), dz = sub2(pk(p.z, p.z), zi);
+        const f2 r2 = fma2(dz, dz, fma2(dy, dy, fma2(dx, dx, e2)));
+        float r0, r1;
+        upk(r2, r0, r1);
+        float t0 = p.w * rsq(r0), t1 = p.w * rsq(r1);
+        t0 = (k >= k_lo0 && r0 > 0.f) ? t0 : 0.f;
+        t1 = (k >= k_lo1 && r1 > 0.f) ? t1 : 0.f;
+        s[k & 3] = add2(s[k & 3], pk(t0, t1));
+      }
+    } else {
+#pragma unroll 16
+      for (int k = 0; k < PE_TILE; k++) {
+        const float4 p = tile[k];
+        const f2 dx = sub2(pk(p.x, p.x), xi), dy = sub2(pk(p.y, p.y), yi), dz = sub2(pk(p.z, p.z), zi);
+        const f2 r2 = fma2(dz, dz, fma2(dy, dy, fma2(dx, dx, e2)));
+        float r0, r1;
+        upk(r2, r0, r1);
+        s[k & 3] = add2(s[k & 3], mul2(pk(p.w, p.w), pk(rsq(r0), rsq(r1))));
+      }
+    }
+    float a0, a1, b0, b1;
+    upk(add2(s[0], s[1]), a0, a1);
+    upk(add2(s[2], s[3]), b0, b1);
+    acc0 += (double)a0 + (double)b0;
+    acc1 += (double)a1 + (double)b1;
     __syncthreads();
   }
-  acc = live ? acc * (double)d.mass[i] : 0.0;
-  const double t = block_sum(acc, sh);
-  if (threadIdx.x == 0) out[(size_t)blockIdx.y * gridDim.x + blockIdx.x] = t;
+  const double mine = (live0 ? acc0 * (double)d.mass[i0] : 0.0) + (live1 ? acc1 * (double)d.mass[i1] : 0.0);
+  const double t = block_sum(mine, sh);
+  if (tid == 0) *slot = t;
 }
 
 static int sum_partials(nb_context* ctx, size_t count, double* result, cudaStream_t st) {
@@ -155,23 +197,27 @@ int kinetic_energy(nb_context* ctx, const nb_particles* d, double* ke, cudaStrea
 int potential_energy(nb_context* ctx, const nb_particles* d, float G, float eps, double* pe, cudaStream_t st) {
   const size_t n = d->count;
   *pe = 0.0;
-  if (!n) return NB_OK;
-  const size_t gi = (n + PE_T - 1) / PE_T;
-  const size_t jtiles = (n + PE_JT - 1) / PE_JT;
-  // enough j-splits to fill the machine when there are few target tiles
-  size_t splits = ((size_t)ctx->sm_count * 8 + gi - 1) / gi;
-  if (splits > jtiles) splits = jtiles;
-  if (splits > 65535) splits = 65535;
-  if (splits < 1) splits = 1;
-  const int jchunk_tiles = (int)((jtiles + splits - 1) / splits);
-  const size_t gy = (jtiles + jchunk_tiles - 1) / jchunk_tiles;
-  if (int rc = ctx->red.ensure(sizeof(double) * gi * gy)) return rc;
-  dim3 grid((unsigned)gi, (unsigned)gy);
-  potential_kernel<<<grid, PE_T, 0, st>>>(*d, n, eps * eps, jchunk_tiles, ctx->red.as<double>());
+  if (n < 2) return NB_OK;
+  const long long nt = (long long)((n + PE_TILE - 1) / PE_TILE);
+  // about 128 CTAs' worth of tile pairs per SM, so that the triangle's ragged rows still balance
+  const long long pairs = nt * (nt + 1) / 2;
+  long long chunk = pairs / ((long long)ctx->sm_count * 128);
+  if (chunk < 1) chunk = 1;
+  long long gy = (nt + chunk - 1) / chunk;
+  if (gy > 65535) {
+    gy = 65535;
+    chunk = (nt + gy - 1) / gy;
+    gy = (nt + chunk - 1) / chunk;
+  }
+  if (int rc = ctx->red.ensure(sizeof(double) * (size_t)nt * (size_t)gy)) return rc;
+  dim3 grid((unsigned)nt, (unsigned)gy);
+  const float eps2 = eps * eps;
+  if (eps2 > 0.f) potential_kernel<false><<<grid, PE_T, 0, st>>>(*d, n, eps2, (int)nt, (int)chunk, ctx->red.as<double>());
+  else potential_kernel<true><<<grid, PE_T, 0, st>>>(*d, n, eps2, (int)nt, (int)chunk, ctx->red.as<double>());
   NB_LAUNCH_CHECK(ctx);
   double s = 0.0;
-  if (int rc = sum_partials(ctx, gi * gy, &s, st)) return rc;
-  *pe = -0.5 * (double)G * s;  // pe -= G*m_i*m_j/r over j>i (integrator.cu:97-102)
+  if (int rc = sum_partials(ctx, (size_t)nt * (size_t)gy, &s, st)) return rc;
+  *pe = -(double)G * s;  // pe -= G*m_i*m_j/r over j > i (integrator.cu:97-102)
   return NB_OK;
 }
 

@@ -52,6 +52,28 @@ def main():
                               super=os.environ.get("NB_BH_SUPER", "default"), build_ms=build, force_ms=force,
                               step_ms=build + force, interactions=inter.value, per_body=inter.value / n,
                               g_interactions_per_s=inter.value / force / 1e6)))
+    elif kind == "energy":
+        # potential-energy diagnostic (O(N^2)) and the one-pass moments, wall clock around the synchronising calls
+        import time
+        st = ics.plummer(n, seed=42)
+        h = nb.ParticleDataManager.fromState(st)
+        d = nb.ParticleData()
+        nb.ParticleDataManager.allocateDevice(d, n)
+        nb.ParticleDataManager.copyToDevice(d, h)
+        integ = nb.Integrator()
+        integ.computePotentialEnergy(d, 1.0, 0.01)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        reps = 3
+        for _ in range(reps):
+            pe = integ.computePotentialEnergy(d, 1.0, 0.01)
+        pe_ms = (time.perf_counter() - t0) / reps * 1e3
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            dg = integ.computeDiagnostics(d, 1.0, 0.01, with_potential=False)
+        mo_ms = (time.perf_counter() - t0) / reps * 1e3
+        print(json.dumps(dict(path="energy", n=n, potential=pe, potential_ms=pe_ms,
+                              g_pairs_per_s=0.5 * n * (n - 1) / pe_ms / 1e6, moments_ms=mo_ms, kinetic=dg["kinetic"])))
     elif kind == "graph":
         # steps/s of ParticleSystem.update, eager launches against CUDA-graph replay (launch-bound sizes)
         method = nb.ForceMethod.BARNES_HUT if (len(sys.argv) > 3 and sys.argv[3] == "bh") else nb.ForceMethod.DIRECT_N2
