@@ -205,6 +205,13 @@ int nb_mgpu_peer_alloc(nb_context* ctx, unsigned char ipc_handle_out[64]);
 int nb_mgpu_peer_open(nb_context* ctx, int peer_rank, const unsigned char ipc_handle[64]);
 int nb_mgpu_peer_step(nb_context* ctx, const nb_particles* d_local, float dt, float G, float eps2, int do_step,
                       nb_stream s);
+/* Energy diagnostic of a target-sharded run ("same sharding, all-reduce of two doubles"; the
+ * reference is single-GPU, src/cuda/integrator.cu:252-293).  *partial = sum over this rank's bodies i of
+ * m_i * sum over ALL bodies j != i of G m_j / sqrt(r^2 + eps^2), fp64; the caller all-reduces it together
+ * with nb_kinetic_energy of the local slice and takes PE = -sum / 2.  gathered_src: the replicated packed
+ * source array (NCCL exchange), or NULL for the peer exchange block of the last step.  Synchronises. */
+int nb_mgpu_potential_partial(nb_context* ctx, const nb_particles* d_local, const float* gathered_src, float eps,
+                              double* partial, nb_stream s);
 /* the two halves of nb_mgpu_peer_step (pack + push + flag | local pass, flag wait, remote pass, reduce [+ kick]) */
 int nb_mgpu_peer_push(nb_context* ctx, const nb_particles* d_local, float dt, float G, int do_drift, nb_stream s);
 int nb_mgpu_peer_forces(nb_context* ctx, const nb_particles* d_local, float dt, float eps2, int do_kick, nb_stream s);

@@ -106,6 +106,7 @@ SYMBOLS = {
     "nb_mgpu_peer_alloc": (_i, [_vp, _vp]),
     "nb_mgpu_peer_open": (_i, [_vp, _i, _vp]),
     "nb_mgpu_peer_step": (_i, [_vp, _pp, _f, _f, _f, _i, _vp]),
+    "nb_mgpu_potential_partial": (_i, [_vp, _pp, _vp, _f, C.POINTER(C.c_double), _vp]),
     "nb_mgpu_peer_push": (_i, [_vp, _pp, _f, _f, _i, _vp]),
     "nb_mgpu_peer_forces": (_i, [_vp, _pp, _f, _f, _i, _vp]),
     "nb_mgpu_peer_block": (_i, [_vp, C.POINTER(_vp), C.POINTER(_sz)]),

@@ -28,6 +28,9 @@ int launch_direct_pass(nb_context* ctx, const DirectCfg& cfg, const float4* src,
                        int ja0, int na, int jb0, int nbt, float eps2, int pass_index, cudaStream_t st);
 int launch_peer_wait(nb_context* ctx, const unsigned* flags, int flag_base, unsigned step, int nranks, int self,
                      int* timeout_flag, cudaStream_t st);
+// integrate.cu: this rank's share of the potential-energy pair sum of a target-sharded run
+int potential_partial(nb_context* ctx, const float4* src, size_t n_src, size_t tgt_off, size_t n_tgt,
+                      const float* mass_local, float eps, double* partial, cudaStream_t st);
 int launch_reduce(nb_context* ctx, const DirectCfg& cfg, const nb_particles* d, size_t n, float dt, bool kick,
                   cudaStream_t st);
 

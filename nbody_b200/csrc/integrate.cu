@@ -221,6 +221,103 @@ int potential_energy(nb_context* ctx, const nb_particles* d, float G, float eps,
   return NB_OK;
 }
 
+// Potential energy of a target-sharded run ("energy diagnostic: same sharding, all-reduce of two
+// doubles"): this rank's targets -- n_tgt bodies at tgt_off in the replicated packed source array {x,y,z,G*m} --
+// against ALL sources.  Every ordered pair with i local is visited (no triangle: the other half of a cross-rank
+// pair belongs to the other rank), so the all-reduced sum is halved by the caller.  Same pair arithmetic as
+// potential_kernel; the self pair is excluded by global index in the tiles that overlap the target tile.
+template <bool EPS0>
+__global__ void __launch_bounds__(PE_T) potential_rect_kernel(const float4* __restrict__ src, size_t n_src,
+                                                              size_t tgt_off, size_t n_tgt,
+                                                              const float* __restrict__ mass_local, float eps2,
+                                                              int n_src_tiles, int chunk, double* __restrict__ out) {
+  __shared__ __align__(16) float4 tile[PE_TILE];
+  __shared__ double sh[8];
+  const int tid = threadIdx.x;
+  const int jt0 = (int)blockIdx.y * chunk, jt1 = min(jt0 + chunk, n_src_tiles);
+  const size_t l0 = (size_t)blockIdx.x * PE_TILE + tid, l1 = l0 + PE_T;  // local target indices
+  const bool live0 = l0 < n_tgt, live1 = l1 < n_tgt;
+  const float4 t0 = live0 ? src[tgt_off + l0] : make_float4(0, 0, 0, 0);
+  const float4 t1 = live1 ? src[tgt_off + l1] : make_float4(0, 0, 0, 0);
+  const f2 xi = pk(t0.x, t1.x), yi = pk(t0.y, t1.y), zi = pk(t0.z, t1.z);
+  const f2 e2 = pk(eps2, eps2), zero2 = pk(0.f, 0.f);
+  const size_t g_lo = tgt_off + (size_t)blockIdx.x * PE_TILE, g_hi = g_lo + PE_TILE;  // this CTA's targets, global
+  double acc0 = 0.0, acc1 = 0.0;
+  for (int jt = jt0; jt < jt1; jt++) {
+    const size_t jb = (size_t)jt * PE_TILE;
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      const size_t j = jb + tid + h * PE_T;
+      tile[tid + h * PE_T] = (j < n_src) ? src[j] : make_float4(0, 0, 0, 0);
+    }
+    __syncthreads();
+    f2 s[4] = {zero2, zero2, zero2, zero2};
+    if (EPS0 || (jb < g_hi && jb + PE_TILE > g_lo)) {  // tile holds some of this CTA's own bodies
+      const long long self0 = (long long)(tgt_off + l0) - (long long)jb, self1 = (long long)(tgt_off + l1) - (long long)jb;
+#pragma unroll 4
+      for (int k = 0; k < PE_TILE; k++) {
+        const float4 p = tile[k];
+        const f2 dx = sub2(pk(p.x, p.x), xi), dy = sub2(pk(p.y, p.y), yi), dz = sub2(pk(p.z, p.z), zi);
+        const f2 r2 = fma2(dz, dz, fma2(dy, dy, fma2(dx, dx, e2)));
+        float r0, r1;
+        upk(r2, r0, r1);
+        float u0 = p.w * rsq(r0), u1 = p.w * rsq(r1);
+        u0 = (k != self0 && r0 > 0.f) ? u0 : 0.f;
+        u1 = (k != self1 && r1 > 0.f) ? u1 : 0.f;
+        s[k & 3] = add2(s[k & 3], pk(u0, u1));
+      }
+    } else {
+#pragma unroll 16
+      for (int k = 0; k < PE_TILE; k++) {
+        const float4 p = tile[k];
+        const f2 dx = sub2(pk(p.x, p.x), xi), dy = sub2(pk(p.y, p.y), yi), dz = sub2(pk(p.z, p.z), zi);
+        const f2 r2 = fma2(dz, dz, fma2(dy, dy, fma2(dx, dx, e2)));
+        float r0, r1;
+        upk(r2, r0, r1);
+        s[k & 3] = add2(s[k & 3], mul2(pk(p.w, p.w), pk(rsq(r0), rsq(r1))));
+      }
+    }
+    float a0, a1, b0, b1;
+    upk(add2(s[0], s[1]), a0, a1);
+    upk(add2(s[2], s[3]), b0, b1);
+    acc0 += (double)a0 + (double)b0;
+    acc1 += (double)a1 + (double)b1;
+    __syncthreads();
+  }
+  const double mine = (live0 ? acc0 * (double)mass_local[l0] : 0.0) + (live1 ? acc1 * (double)mass_local[l1] : 0.0);
+  const double t = block_sum(mine, sh);
+  if (tid == 0) out[(size_t)blockIdx.y * gridDim.x + blockIdx.x] = t;
+}
+
+// sum over local targets i of m_i * sum over all sources j != i of (G m_j) / sqrt(r^2 + eps^2)
+int potential_partial(nb_context* ctx, const float4* src, size_t n_src, size_t tgt_off, size_t n_tgt,
+                      const float* mass_local, float eps, double* partial, cudaStream_t st) {
+  *partial = 0.0;
+  if (!n_tgt || !n_src) return NB_OK;
+  const long long gi = (long long)((n_tgt + PE_TILE - 1) / PE_TILE);
+  const long long nt = (long long)((n_src + PE_TILE - 1) / PE_TILE);
+  long long chunk = gi * nt / ((long long)ctx->sm_count * 128);
+  if (chunk < 1) chunk = 1;
+  if (chunk > nt) chunk = nt;
+  long long gy = (nt + chunk - 1) / chunk;
+  if (gy > 65535) {
+    gy = 65535;
+    chunk = (nt + gy - 1) / gy;
+    gy = (nt + chunk - 1) / chunk;
+  }
+  if (int rc = ctx->red.ensure(sizeof(double) * (size_t)gi * (size_t)gy)) return rc;
+  dim3 grid((unsigned)gi, (unsigned)gy);
+  const float eps2 = eps * eps;
+  if (eps2 > 0.f)
+    potential_rect_kernel<false><<<grid, PE_T, 0, st>>>(src, n_src, tgt_off, n_tgt, mass_local, eps2, (int)nt, (int)chunk,
+                                                        ctx->red.as<double>());
+  else
+    potential_rect_kernel<true><<<grid, PE_T, 0, st>>>(src, n_src, tgt_off, n_tgt, mass_local, eps2, (int)nt, (int)chunk,
+                                                       ctx->red.as<double>());
+  NB_LAUNCH_CHECK(ctx);
+  return sum_partials(ctx, (size_t)gi * (size_t)gy, partial, st);
+}
+
 // ---------------------------------------------------------------------------------------------
 // conserved-quantity diagnostics: one pass over the bodies, fp64 sums of
 //   M, M*x_com (3), P = sum m v (3), L = sum m x cross v (3), KE  -> NB_DIAG_MOMENTS values per CTA,

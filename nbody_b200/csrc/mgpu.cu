@@ -308,6 +308,36 @@ int nb_mgpu_peer_step(nb_context* ctx, const nb_particles* d_local, float dt, fl
   return nb_mgpu_peer_forces(ctx, d_local, dt, eps2, do_step, s);
 }
 
+// ---- energy of a target-sharded run ---------------------------------------------------
+// This rank's share of the pair sum; the caller all-reduces {KE_local, partial} and takes PE = -partial_sum / 2.
+// gathered_src: the replicated packed source array of the NCCL path, or null for the peer exchange block of the
+// step that ran last.  Synchronises.
+int nb_mgpu_potential_partial(nb_context* ctx, const nb_particles* d_local, const float* gathered_src, float eps,
+                              double* partial, nb_stream s) {
+  if (!ctx || !d_local || !partial || ctx->mg_n_total == 0) {
+    set_error("mgpu potential: nb_mgpu_layout not called or null argument");
+    return NB_ERR_INVALID;
+  }
+  if (d_local->count != ctx->mg_count || (d_local->count && !d_local->mass)) {
+    set_error("mgpu potential: local particle count %zu does not match the slice (%zu)", d_local->count, ctx->mg_count);
+    return NB_ERR_INVALID;
+  }
+  NB_CUDA(cudaSetDevice(ctx->device));
+  const float4* src = reinterpret_cast<const float4*>(gathered_src);
+  if (!src) {
+    if (int rc = peer_prepare(ctx, d_local, "potential")) return rc;
+    if (ctx->peer->step == 0) {
+      set_error("mgpu potential: no step or force evaluation has filled the exchange block yet");
+      return NB_ERR_INVALID;
+    }
+    PeerBufs pb{};
+    peer_bufs(ctx, (int)(ctx->peer->step & 1u), pb);
+    src = pb.buf[ctx->mg_rank];
+  }
+  return potential_partial(ctx, src, (size_t)ctx->mg_nranks * ctx->mg_padded, (size_t)ctx->mg_rank * ctx->mg_padded,
+                           ctx->mg_count, d_local->mass, eps, partial, (cudaStream_t)s);
+}
+
 // ---- target-sharded Barnes-Hut over replicated state --------------------------
 // Every rank holds ALL bodies.  Per step every rank drifts all bodies and rebuilds the identical tree
 // (deterministic kernels on identical inputs), traverses only the groups dealt to it, and stores the

@@ -97,6 +97,7 @@ class ShardedDirectSystem:
         else:
             self.gathered = torch.zeros(world * self.padded * 4, dtype=torch.float32, device="cuda")
         self.simulation_time = 0.0
+        self._evaluated = False
 
     def _setup_peer(self):
         """Collective: allocate the exchange block, swap CUDA-IPC handles, map the peers' blocks."""
@@ -127,6 +128,7 @@ class ShardedDirectSystem:
     def _evaluate(self, dt: float, step: bool):
         L, ctx = self.L, self.ctx.handle
         s = self._stream()
+        self._evaluated = True
         if self.exchange == "peer":
             self.check(L.nb_mgpu_peer_step(ctx, C.byref(self.d.c), dt, self.G, self.eps2, 1 if step else 0, s))
             return
@@ -163,6 +165,33 @@ class ShardedDirectSystem:
 
     def local_arrays(self) -> dict:
         return self.d.numpy()
+
+    def compute_energy(self) -> dict:
+        """Collective.  Kinetic, potential and total energy of the WHOLE system: every rank
+        sums its own bodies' kinetic energy and its targets' share of the pair sum against the replicated sources
+        (nb_mgpu_potential_partial), then one all-reduce of two doubles."""
+        if not self._evaluated:
+            self.compute_forces()  # fills the replicated source array with the current positions
+        ke, part = C.c_double(0), C.c_double(0)
+        self.check(self.L.nb_kinetic_energy(self.ctx.handle, C.byref(self.d.c), C.byref(ke), self._stream()))
+        gp = C.c_void_p(self.gathered.data_ptr()) if self.gathered is not None else None
+        eps = float(np.sqrt(np.float32(self.eps2)))
+        self.check(self.L.nb_mgpu_potential_partial(self.ctx.handle, C.byref(self.d.c), gp, eps, C.byref(part),
+                                                    self._stream()))
+        return reduce_energy(ke.value, part.value, self.world, self.group, self.torch)
+
+
+def reduce_energy(ke_local: float, pair_sum_local: float, world: int, group, torch, device="cuda") -> dict:
+    """All-reduce of {local kinetic energy, local share of sum_i m_i sum_{j != i} G m_j / r_ij}: every ordered pair
+    appears once in the global sum, so PE = -sum / 2."""
+    ke, part = ke_local, pair_sum_local
+    if world > 1:
+        import torch.distributed as dist
+        t = torch.tensor([ke_local, pair_sum_local], dtype=torch.float64, device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+        ke, part = (float(v) for v in t.cpu())
+    pe = -0.5 * part
+    return {"kinetic": ke, "potential": pe, "total": ke + pe}
 
 
 class ShardedBarnesHutSystem:

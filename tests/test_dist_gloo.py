@@ -50,9 +50,23 @@ def _worker(rank, world, port, n, out_dir):
         if step > 0:
             orc.kick(loc, dt)
         acc_hist.append(np.stack([loc["acc_x"], loc["acc_y"], loc["acc_z"]]))
+    # energy diagnostic of the sharded run: local KE + local share of the pair sum against the
+    # replicated sources, one all-reduce of two doubles (numpy fp64 stands in for nb_mgpu_potential_partial)
+    from nbody_b200.dist import reduce_energy
+    x = src[:, :3].astype(np.float64)
+    gm64 = src[:, 3].astype(np.float64)
+    part = 0.0
+    for li in range(c):
+        r2 = ((x - x[t0 + li]) ** 2).sum(1) + eps2
+        inv = gm64 / np.sqrt(r2)
+        inv[t0 + li] = 0.0
+        part += float(loc["mass"][li]) * inv.sum()
+    ke_local = orc.kinetic(loc["vel_x"], loc["vel_y"], loc["vel_z"], loc["mass"])
+    energy = reduce_energy(ke_local, part, world, None, torch, device="cpu")
     np.savez(os.path.join(out_dir, f"rank{rank}.npz"), begin=b, count=c, acc=np.stack(acc_hist),
              pos=np.stack([loc["pos_x"], loc["pos_y"], loc["pos_z"]]),
-             vel=np.stack([loc["vel_x"], loc["vel_y"], loc["vel_z"]]))
+             vel=np.stack([loc["vel_x"], loc["vel_y"], loc["vel_z"]]),
+             energy=np.array([energy["kinetic"], energy["potential"], energy["total"]]))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -89,3 +103,10 @@ def test_sharded_direct_matches_single_process(tmp_path, n):
         np.testing.assert_allclose(z["vel"], np.stack([full["vel_x"][sl], full["vel_y"][sl], full["vel_z"][sl]]),
                                    rtol=1e-4, atol=1e-6)
     assert covered == n
+    # every rank holds the same whole-system energy, equal to the single-process diagnostic of the final state
+    ke = orc.kinetic(full["vel_x"], full["vel_y"], full["vel_z"], full["mass"])
+    pe = orc.potential(full["pos_x"], full["pos_y"], full["pos_z"], full["mass"], float(G), float(np.sqrt(eps2)))
+    for r in range(world):
+        e = np.load(tmp_path / f"rank{r}.npz")["energy"]
+        assert abs(e[0] - ke) <= 1e-5 * abs(ke) and abs(e[1] - pe) <= 1e-5 * abs(pe)
+        assert abs(e[2] - (ke + pe)) <= 1e-5 * abs(pe)

@@ -187,6 +187,17 @@ def test_sharded_path_emulated_on_one_gpu(orc, n, world):
         e = rel_err((o["acc_x"], o["acc_y"], o["acc_z"]),
                     (so["acc_x"][b:b + c], so["acc_y"][b:b + c], so["acc_z"][b:b + c]))
         assert e.max() < 2e-6, e.max()   # same kernel, different partial-sum split
+    # energy of the sharded run: the ranks' shares of the pair sum add up to -2 PE of the whole system
+    integ = nb.Integrator()
+    pe_single = integ.computePotentialEnergy(single, G, 0.01)
+    total = 0.0
+    for r, (b, c, d) in enumerate(locals_):
+        _lib.check(L.nb_mgpu_layout(ctx.handle, n, r, world, None, None, None, None))
+        part = C.c_double(0)
+        _lib.check(L.nb_mgpu_potential_partial(ctx.handle, C.byref(d.c), gp, 0.01, C.byref(part), None))
+        total += part.value
+    assert abs(-0.5 * total - pe_single) <= 1e-7 * abs(pe_single)
+    assert abs(pe_single - orc.potential(st["pos_x"], st["pos_y"], st["pos_z"], st["mass"], G, 0.01)) <= 2e-6 * abs(pe_single)
 
 
 @pytest.mark.parametrize("n,world", [(5000, 2), (40000, 4), (100000, 8), (33000, 3)])
