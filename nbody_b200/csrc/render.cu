@@ -152,6 +152,14 @@ __global__ void __launch_bounds__(1024) scan_tiles_kernel(unsigned long long* __
   if (threadIdx.x == 0) *total = carry_s;
 }
 
+// shared with sh.cu: in-place exclusive scan of ntiles 64-bit tile sums, grand total to *total (device memory)
+int launch_scan_tiles(nb_context* ctx, unsigned long long* tile_sum, int ntiles, unsigned long long* total,
+                      cudaStream_t st) {
+  scan_tiles_kernel<<<1, 1024, 0, st>>>(tile_sum, ntiles, total);
+  NB_LAUNCH_CHECK(ctx);
+  return NB_OK;
+}
+
 // fragments of body i, emitted in body order: key = pixel (row-major, origin bottom-left), value = body
 __global__ void __launch_bounds__(256) splat_emit_kernel(const float4* __restrict__ splat,
                                                          const uint32_t* __restrict__ count, size_t n,

@@ -7,7 +7,10 @@
 // sort (sort.cu), cell_start/cell_end are read off the sorted keys (identical to the reference's
 // exclusive scan, empty cells included), bodies are physically reordered into cell order as packed
 // float4, and the 27-cell sweep (:83-152) walks 9 contiguous x-runs of that array.  Order inside a
-// cell is ascending body index, so results are reproducible.
+// cell is ascending body index, so results are reproducible.  The force kernel gives every thread TWO
+// targets of the same cell (one packed fp32x2 pair) so that each candidate is loaded once for two
+// interactions: pairs are counted from each cell's first slot (a cell with an odd count ends in a
+// single), and the build lists the pair leaders' slots (flag + scan over the cell-ordered bodies).
 #include <cmath>
 #include <cstring>
 
@@ -16,7 +19,15 @@
 namespace nb {
 int bbox_device(nb_context* ctx, const nb_particles* d, cudaStream_t st);
 int sort_pairs(nb_context* ctx, uint32_t* d_keys, int32_t* d_vals, size_t n, int end_bit, cudaStream_t st);
+int launch_scan_tiles(nb_context* ctx, unsigned long long* tile_sum, int ntiles, unsigned long long* total,
+                      cudaStream_t st);  // render.cu
 }  // namespace nb
+
+#ifndef NB_SH_UNROLL
+#define NB_SH_UNROLL 4  // candidates per trip of the sweep (build-time tuning knob)
+#endif
+#define NB_SH_PRAGMA_(x) _Pragma(#x)
+#define NB_SH_PRAGMA_UNROLL(n) NB_SH_PRAGMA_(unroll n)
 
 struct SHMisc {  // device + pinned host mirror
   float bbox[6];  // padded
@@ -24,6 +35,7 @@ struct SHMisc {  // device + pinned host mirror
   int too_large;
   long long total;
   unsigned long long pairs;
+  unsigned long long n_pairs;  // target pairs = sum over cells of ceil(count / 2)
 };
 
 struct SH {
@@ -32,7 +44,7 @@ struct SH {
   int total_cells = 0;
   int dims[3] = {0, 0, 0};
   float bbox[6] = {0, 0, 0, 0, 0, 0};
-  nb::DevBuf particle_cell, keys, sorted_idx, packed, spos, cell_start, cell_end, misc;
+  nb::DevBuf particle_cell, keys, sorted_idx, packed, spos, pair_slot, tile_sum, cell_start, cell_end, misc;
   SHMisc* h_misc = nullptr;
   bool built = false;
 };
@@ -60,6 +72,7 @@ __global__ void sh_prepare_kernel(const int* __restrict__ bb_ord, float cell, SH
   m->total = total;
   m->too_large = total > 100000000LL ? 1 : 0;
   m->pairs = 0ull;
+  m->n_pairs = 0ull;
 }
 
 // :28-49
@@ -97,13 +110,7 @@ __global__ void __launch_bounds__(256) sh_ranges_gather_kernel(const uint32_t* _
                                                                float4* __restrict__ spos) {
   const size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (k > n) return;
-  if (k < n) {
-    // cell-ordered bodies, two per 32 bytes: {x0,x1, y0,y1, z0,z1, m0,m1}, so that the force kernel's
-    // LDG.128s land directly in aligned (body 2q, body 2q+1) register pairs for the fp32x2 pipe
-    const float4 b = __ldg(packed + sidx[k]);
-    float* o = reinterpret_cast<float*>(spos) + (k >> 1) * 8 + (k & 1);
-    o[0] = b.x; o[2] = b.y; o[4] = b.z; o[6] = b.w;
-  }
+  if (k < n) spos[k] = __ldg(packed + sidx[k]);
   const int prev = (k == 0) ? -1 : (int)keys[k - 1];
   const int cur = (k == n) ? total_cells : (int)keys[k];
   if (prev == cur) return;
@@ -112,33 +119,103 @@ __global__ void __launch_bounds__(256) sh_ranges_gather_kernel(const uint32_t* _
   for (int c = (prev < 0 ? 0 : prev); c < cur; c++) cell_end[c] = (int32_t)k;
 }
 
-// :83-152.  One thread per body in cell order.  The 27 neighbour cells are 9 contiguous x-runs of
-// the cell-ordered array; a run is swept two candidates at a time, branch-free, on the packed
-// fp32x2 pipe: un-softened r^2 with the reference's unfused mul/add sequence (:128-130), cutoff test
-// per half, softened monopole, weight forced to 0 for candidates outside the cutoff or outside the
-// run.  The body itself is inside its own cell's run: its term is G m * rsqrt(eps^2)^3 * 0 = 0
-// exactly for eps > 0 and is zeroed by a select for eps = 0 (as are exact coincidences).
-// Accumulation: even and odd candidates in separate halves, added at the end.
+// Target pairs of the force kernel: slot k leads a pair when it sits an even number of slots after its cell's
+// first slot.  pair_slot[q] = slot of the q-th leader, in slot order: flag, tile sums, scan of the tile sums
+// (launch_scan_tiles), then in-tile scan + scatter.  Tiles of 2048 slots, 8 consecutive slots per thread.
+constexpr int SH_TILE = 2048;
+__device__ __forceinline__ unsigned sh_lead_flags(const uint32_t* __restrict__ keys,
+                                                  const int32_t* __restrict__ cell_start, size_t n, size_t base,
+                                                  unsigned f[8]) {
+  unsigned mine = 0;
+#pragma unroll
+  for (int e = 0; e < 8; e++) {
+    const size_t k = base + e;
+    f[e] = (k < n && (((unsigned)k - (unsigned)cell_start[keys[k]]) & 1u) == 0u) ? 1u : 0u;
+    mine += f[e];
+  }
+  return mine;
+}
+
+__global__ void __launch_bounds__(256) sh_pair_sums_kernel(const uint32_t* __restrict__ keys,
+                                                           const int32_t* __restrict__ cell_start, size_t n,
+                                                           unsigned long long* __restrict__ tile_sum) {
+  __shared__ unsigned ws[8];
+  unsigned f[8];
+  unsigned s = sh_lead_flags(keys, cell_start, n, (size_t)blockIdx.x * SH_TILE + (size_t)threadIdx.x * 8, f);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned t = 0;
+    for (int w = 0; w < 8; w++) t += ws[w];
+    tile_sum[blockIdx.x] = t;
+  }
+}
+
+__global__ void __launch_bounds__(256) sh_pair_fill_kernel(const uint32_t* __restrict__ keys,
+                                                           const int32_t* __restrict__ cell_start, size_t n,
+                                                           const unsigned long long* __restrict__ tile_off,
+                                                           int32_t* __restrict__ pair_slot) {
+  __shared__ unsigned ws[8];
+  const size_t base = (size_t)blockIdx.x * SH_TILE + (size_t)threadIdx.x * 8;
+  unsigned f[8];
+  const unsigned mine = sh_lead_flags(keys, cell_start, n, base, f);
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  unsigned x = mine;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const unsigned y = __shfl_up_sync(0xffffffffu, x, o);
+    if (lane >= o) x += y;
+  }
+  if (lane == 31) ws[w] = x;
+  __syncthreads();
+  unsigned before = x - mine;  // leaders before this thread inside its warp
+  for (int v = 0; v < w; v++) before += ws[v];
+  size_t q = (size_t)tile_off[blockIdx.x] + before;
+#pragma unroll
+  for (int e = 0; e < 8; e++)
+    if (f[e]) pair_slot[q++] = (int32_t)(base + e);
+}
+
+// :83-152.  Thread q takes the q-th target pair: the cell-ordered slots (k0, k0 + 1), k0 = pair_slot[q], as one
+// packed fp32x2 pair when both lie in the same cell, else slot k0 alone (last body of a cell with an odd count).
+// The 27 neighbour cells are 9 contiguous x-runs of the cell-ordered array; every candidate is one LDG.128,
+// broadcast into both halves: un-softened r^2 with the reference's unfused mul/add sequence (:128-130), cutoff
+// test per half, softened monopole, weight forced to 0 outside the cutoff.  A body is inside its own cell's
+// run: its own term is G m * rsqrt(eps^2)^3 * 0 = 0 exactly for eps > 0 and is zeroed by a select for eps = 0
+// (as are exact coincidences).  Candidates are accumulated in run order, i.e. cell order z, y, x then slot
+// (:104-150).
 template <bool EPS0>
 __global__ void __launch_bounds__(128) sh_force_kernel(size_t n, const float4* __restrict__ spos,
+                                                       const uint32_t* __restrict__ keys,
                                                        const int32_t* __restrict__ sidx,
+                                                       const int32_t* __restrict__ pair_slot,
                                                        const int32_t* __restrict__ cell_start,
                                                        const int32_t* __restrict__ cell_end,
                                                        const SHMisc* __restrict__ m, float cell, float cutoff2, float G,
                                                        float eps2, float* __restrict__ ax, float* __restrict__ ay,
                                                        float* __restrict__ az, unsigned long long* __restrict__ pairs) {
-  const size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   unsigned cnt = 0;
-  if (k < n) {
+  size_t k0 = n;
+  bool two = false;
+  if (t < (size_t)m->n_pairs) {
+    k0 = (size_t)pair_slot[t];
+    two = (k0 + 1 < n) && (keys[k0 + 1] == keys[k0]);
+  }
+  if (k0 < n) {
     const int nx = m->dims[0], ny = m->dims[1], nz = m->dims[2];
-    const float* mine = reinterpret_cast<const float*>(spos) + (k >> 1) * 8 + (k & 1);
-    const float mex = __ldg(mine), mey = __ldg(mine + 2), mez = __ldg(mine + 4);
-    // own cell recomputed WITHOUT clamp (:100-102)
+    // scalar loads: each lands in its half of a packed pair (see direct.cu)
+    const float* p0 = reinterpret_cast<const float*>(spos + k0);
+    const float* p1 = reinterpret_cast<const float*>(spos + (two ? k0 + 1 : k0));
+    const float mex = __ldg(p0), mey = __ldg(p0 + 1), mez = __ldg(p0 + 2);
+    const f2 xi = pk(mex, __ldg(p1)), yi = pk(mey, __ldg(p1 + 1)), zi = pk(mez, __ldg(p1 + 2));
+    // own cell recomputed WITHOUT clamp (:100-102); the pair partner has the same cell
     const int cx = (int)floorf(__fdiv_rn(__fsub_rn(mex, m->bbox[0]), cell));
     const int cy = (int)floorf(__fdiv_rn(__fsub_rn(mey, m->bbox[1]), cell));
     const int cz = (int)floorf(__fdiv_rn(__fsub_rn(mez, m->bbox[2]), cell));
-    const f2 xi = pk(mex, mex), yi = pk(mey, mey), zi = pk(mez, mez);
-    const f2 e2 = pk(eps2, eps2), g2 = pk(G, G);
+    const f2 e2 = pk(eps2, eps2);
     f2 sx = pk(0.f, 0.f), sy = sx, sz = sx;
     for (int dz = -1; dz <= 1; dz++) {
       const int z = cz + dz;
@@ -151,17 +228,15 @@ __global__ void __launch_bounds__(128) sh_force_kernel(size_t n, const float4* _
         if (x0 > x1) continue;
         const int row = y * nx + z * nx * ny;
         const int j0 = cell_start[row + x0], j1 = cell_end[row + x1];
-#pragma unroll 2
-        for (int jj = j0 & ~1; jj < j1; jj += 2) {  // two iterations in flight: the loop is load-latency bound
-          const float4* q = spos + jj;  // pair jj/2 = two float4
-          const float4 a = __ldg(q), b = __ldg(q + 1);  // {x0,x1,y0,y1} {z0,z1,m0,m1}
-          const f2 ddx = sub2(pk(a.x, a.y), xi), ddy = sub2(pk(a.z, a.w), yi), ddz = sub2(pk(b.x, b.y), zi);
-          f2 d2 = add2(add2(mul2(ddx, ddx), mul2(ddy, ddy)), mul2(ddz, ddz));
+        NB_SH_PRAGMA_UNROLL(NB_SH_UNROLL)
+        for (int jj = j0; jj < j1; jj++) {
+          const float4 c = __ldg(spos + jj);
+          const f2 ddx = sub2(pk(c.x, c.x), xi), ddy = sub2(pk(c.y, c.y), yi), ddz = sub2(pk(c.z, c.z), zi);
+          const f2 d2 = add2(add2(mul2(ddx, ddx), mul2(ddy, ddy)), mul2(ddz, ddz));
           float r0, r1;
           upk(d2, r0, r1);
-          const bool in0 = (r0 < cutoff2) && (jj >= j0);  // un-softened test (:131-135)
-          const bool in1 = (r1 < cutoff2) && (jj + 1 < j1);
-          cnt += (in0 ? 1u : 0u) + (in1 ? 1u : 0u);
+          const bool in0 = (r0 < cutoff2), in1 = (r1 < cutoff2);  // un-softened test (:131-135)
+          cnt += (in0 ? 1u : 0u) + ((in1 && two) ? 1u : 0u);
           upk(add2(d2, e2), r0, r1);
           float i0 = rsq(r0), i1 = rsq(r1);
           if (EPS0) {
@@ -171,19 +246,21 @@ __global__ void __launch_bounds__(128) sh_force_kernel(size_t n, const float4* _
           i0 = in0 ? i0 : 0.f;
           i1 = in1 ? i1 : 0.f;
           const f2 inv = pk(i0, i1);
-          const f2 f = mul2(mul2(g2, pk(b.z, b.w)), mul2(mul2(inv, inv), inv));
+          const float gm = G * c.w;
+          const f2 f = mul2(pk(gm, gm), mul2(mul2(inv, inv), inv));
           sx = fma2(f, ddx, sx);
           sy = fma2(f, ddy, sy);
           sz = fma2(f, ddz, sz);
         }
       }
     }
-    float e, o;
-    const int i = sidx[k];
-    upk(sx, e, o); ax[i] = e + o;
-    upk(sy, e, o); ay[i] = e + o;
-    upk(sz, e, o); az[i] = e + o;
-    cnt -= 1;  // the body itself (always inside its own run and inside the cutoff)
+    float a, b;
+    const int i = sidx[k0];
+    const int i2 = two ? sidx[k0 + 1] : i;
+    upk(sx, a, b); ax[i] = a; if (two) ax[i2] = b;
+    upk(sy, a, b); ay[i] = a; if (two) ay[i2] = b;
+    upk(sz, a, b); az[i] = a; if (two) az[i2] = b;
+    cnt -= two ? 2u : 1u;  // the bodies themselves (always inside their own run and inside the cutoff)
   }
   // one atomic per warp
   unsigned long long c = cnt;
@@ -200,7 +277,7 @@ static SH* sh_get(nb_context* ctx) {
 void sh_destroy(nb_context* ctx) {
   if (!ctx->sh) return;
   SH* s = ctx->sh;
-  s->particle_cell.release(); s->keys.release(); s->sorted_idx.release(); s->packed.release(); s->spos.release();
+  s->particle_cell.release(); s->keys.release(); s->sorted_idx.release(); s->packed.release(); s->spos.release(); s->pair_slot.release(); s->tile_sum.release();
   s->cell_start.release(); s->cell_end.release(); s->misc.release();
   if (s->h_misc) cudaFreeHost(s->h_misc);
   delete s;
@@ -225,7 +302,9 @@ int sh_build(nb_context* ctx, const nb_particles* d, float cell, cudaStream_t st
   if (int rc = s->particle_cell.ensure(n * 4)) return rc;
   if (int rc = s->keys.ensure(n * 4)) return rc;
   if (int rc = s->sorted_idx.ensure(n * 4)) return rc;
-  if (int rc = s->spos.ensure((n + 1) / 2 * 2 * sizeof(float4))) return rc;
+  if (int rc = s->spos.ensure(n * sizeof(float4))) return rc;
+  if (int rc = s->pair_slot.ensure((n + 1) * 4)) return rc;
+  if (int rc = s->tile_sum.ensure(((n + SH_TILE - 1) / SH_TILE) * sizeof(unsigned long long))) return rc;
   if (int rc = s->packed.ensure(n * sizeof(float4))) return rc;
   if (int rc = s->misc.ensure(sizeof(SHMisc))) return rc;
   if (!s->h_misc) NB_CUDA(cudaMallocHost(&s->h_misc, sizeof(SHMisc)));
@@ -257,6 +336,14 @@ int sh_build(nb_context* ctx, const nb_particles* d, float cell, cudaStream_t st
       s->keys.as<uint32_t>(), n, s->total_cells, s->cell_start.as<int32_t>(), s->cell_end.as<int32_t>(),
       s->sorted_idx.as<int32_t>(), s->packed.as<float4>(), s->spos.as<float4>());
   NB_LAUNCH_CHECK(ctx);
+  const int ntiles = (int)((n + SH_TILE - 1) / SH_TILE);
+  unsigned long long* tile_sum = s->tile_sum.as<unsigned long long>();
+  sh_pair_sums_kernel<<<ntiles, 256, 0, st>>>(s->keys.as<uint32_t>(), s->cell_start.as<int32_t>(), n, tile_sum);
+  NB_LAUNCH_CHECK(ctx);
+  if (int rc = launch_scan_tiles(ctx, tile_sum, ntiles, &misc->n_pairs, st)) return rc;
+  sh_pair_fill_kernel<<<ntiles, 256, 0, st>>>(s->keys.as<uint32_t>(), s->cell_start.as<int32_t>(), n, tile_sum,
+                                              s->pair_slot.as<int32_t>());
+  NB_LAUNCH_CHECK(ctx);
   s->built = true;
   return NB_OK;
 }
@@ -273,10 +360,15 @@ int sh_forces(nb_context* ctx, const nb_particles* d, float cutoff, float G, flo
   NB_CUDA(cudaMemsetAsync(&misc->pairs, 0, sizeof(unsigned long long), st));
   const float eps2 = eps * eps;
   ProfScope prof(ctx, st);
-#define NB_SH_LAUNCH(E_)                                                                                          \
-  sh_force_kernel<E_><<<(unsigned)((n + 127) / 128), 128, 0, st>>>(                                               \
-      n, s->spos.as<float4>(), s->sorted_idx.as<int32_t>(), s->cell_start.as<int32_t>(), s->cell_end.as<int32_t>(), \
-      misc, s->cell_size, cutoff * cutoff, G, eps2, d->acc_x, d->acc_y, d->acc_z, &misc->pairs)
+  // pairs = sum over cells of ceil(count / 2) <= (n + non-empty cells) / 2; threads past the device-side count exit
+  size_t nonempty_bound = n;
+  if ((size_t)s->total_cells < nonempty_bound) nonempty_bound = (size_t)s->total_cells;
+  const size_t threads = (n + nonempty_bound + 1) / 2;
+#define NB_SH_LAUNCH(E_)                                                                                             \
+  sh_force_kernel<E_><<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(                                            \
+      n, s->spos.as<float4>(), s->keys.as<uint32_t>(), s->sorted_idx.as<int32_t>(), s->pair_slot.as<int32_t>(),      \
+      s->cell_start.as<int32_t>(), s->cell_end.as<int32_t>(), misc, s->cell_size, cutoff * cutoff, G, eps2,         \
+      d->acc_x, d->acc_y, d->acc_z, &misc->pairs)
   if (eps2 > 0.f) NB_SH_LAUNCH(false);
   else NB_SH_LAUNCH(true);
 #undef NB_SH_LAUNCH
