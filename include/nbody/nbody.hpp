@@ -15,6 +15,7 @@
 #include <cmath>
 #include <cstddef>
 #include <cstdint>
+#include <cstring>
 #include <fstream>
 #include <initializer_list>
 #include <istream>
@@ -844,6 +845,75 @@ class Renderer {  // renderer.hpp:20-80
   Camera camera_;
 };
 
+// ---- CudaGLInterop (include/nbody/cuda_gl_interop.hpp, src/render/cuda_gl_interop.cpp) -------------------------
+// Headless: the two "VBOs" are plain device buffers of interleaved xyz floats (no GL names: getPositionVBO() is 0,
+// like the reference's own no-graphics build), "mapping" hands out the device pointer, and updatePositions /
+// updateVelocities are the reference's copy kernels (:7-28) as one launch of nb_interop_pack.
+using GLuint = unsigned int;
+class CudaGLInterop {
+ public:
+  CudaGLInterop() = default;
+  ~CudaGLInterop() { cleanup(); }
+  CudaGLInterop(const CudaGLInterop&) = delete;
+  CudaGLInterop& operator=(const CudaGLInterop&) = delete;
+  void initialize(std::size_t particle_count) {  // :64-96
+    cleanup();
+    particle_count_ = particle_count;
+    if (particle_count == 0) return;
+    void *p = nullptr, *v = nullptr;
+    NB_CALL(nb_device_alloc(Engine::get(), particle_count * 3 * sizeof(float), &p));
+    pos_ = static_cast<float*>(p);
+    NB_CALL(nb_device_alloc(Engine::get(), particle_count * 3 * sizeof(float), &v));
+    vel_ = static_cast<float*>(v);
+  }
+  void cleanup() {
+    if (pos_) nb_device_free(Engine::get(), pos_);
+    if (vel_) nb_device_free(Engine::get(), vel_);
+    pos_ = vel_ = nullptr;
+    mapped_ = vel_mapped_ = false;
+    particle_count_ = 0;
+  }
+  float* mapPositionBuffer() { mapped_ = pos_ != nullptr; return pos_; }
+  float* mapVelocityBuffer() { vel_mapped_ = vel_ != nullptr; return vel_; }
+  void unmapPositionBuffer() { mapped_ = false; }
+  void unmapVelocityBuffer() { vel_mapped_ = false; }
+  void unmapAllBuffers() { mapped_ = vel_mapped_ = false; }
+  bool isMapped() const { return mapped_; }
+  bool isVelocityMapped() const { return vel_mapped_; }
+  GLuint getPositionVBO() const { return 0; }
+  GLuint getVelocityVBO() const { return 0; }
+  std::size_t getParticleCount() const { return particle_count_; }
+  void updatePositions(const ParticleData* d) {  // map, copy kernel, unmap
+    checkCount(d);
+    NB_CALL(nb_interop_pack(Engine::get(), as_nb(d), pos_, nullptr, Engine::stream()));
+  }
+  void updateVelocities(const ParticleData* d) {
+    checkCount(d);
+    NB_CALL(nb_interop_pack(Engine::get(), as_nb(d), nullptr, vel_, Engine::stream()));
+  }
+  // compares the position buffer with `count` floats of expected interleaved data (bit-exact copy)
+  bool verifyDataIntegrity(const float* expected, std::size_t count) {
+    if (!pos_ || !expected || count > particle_count_ * 3) return false;
+    std::vector<float> got(count);
+    NB_CALL(nb_device_download(Engine::get(), got.data(), pos_, count * sizeof(float), Engine::stream()));
+    return std::memcmp(got.data(), expected, count * sizeof(float)) == 0;
+  }
+
+ private:
+  void checkCount(const ParticleData* d) const {
+    if (!d || d->count != particle_count_ || !pos_) throw ValidationException("interop buffers are not sized for these particles");
+  }
+  float *pos_ = nullptr, *vel_ = nullptr;
+  bool mapped_ = false, vel_mapped_ = false;
+  std::size_t particle_count_ = 0;
+};
+inline void launchCopyPositionsToVBOKernel(float* d_vbo, const ParticleData* d, int /*block_size*/) {
+  NB_CALL(nb_interop_pack(Engine::get(), as_nb(d), d_vbo, nullptr, Engine::stream()));
+}
+inline void launchCopyVelocitiesToVBOKernel(float* d_vbo, const ParticleData* d, int /*block_size*/) {
+  NB_CALL(nb_interop_pack(Engine::get(), as_nb(d), nullptr, d_vbo, Engine::stream()));
+}
+
 class ParticleSystem {
  public:
   ParticleSystem() = default;
@@ -877,12 +947,34 @@ class ParticleSystem {
     }
     start();
     time_ = 0.0f;
+    resizeInterop();  // :96-99
+  }
+  void initializeWithDistribution(std::size_t particle_count, InitDistribution dist) {  // :102-107
+    SimulationConfig config;
+    config.particle_count = particle_count;
+    config.init_distribution = dist;
+    initialize(config);
   }
   void update(float dt) {  // :115-127
     if (!initialized_ || paused_) return;
     if (use_graph_ && force_method_ != ForceMethod::SPATIAL_HASH) updateGraphed(dt);
     else integrator_->integrate(&d_, calc_.get(), dt);
     time_ += dt;
+    if (interop_) updateInteropBuffer();
+  }
+  // rendering interop (particle_system.cpp:320-345), headless: device buffers instead of GL buffer objects
+  CudaGLInterop* getInterop() noexcept { return interop_.get(); }
+  const CudaGLInterop* getInterop() const noexcept { return interop_.get(); }
+  void initializeInterop() {
+    if (!initialized_) throw ValidationException("ParticleSystem is not initialized");
+    interop_ = std::make_unique<CudaGLInterop>();
+    interop_->initialize(d_.count);
+    updateInteropBuffer();
+  }
+  void updateInteropBuffer() {
+    if (!interop_) return;
+    interop_->updatePositions(&d_);
+    interop_->updateVelocities(&d_);
   }
   // CUDA-graph replay of the steady-state step: the first step with a given parameter set runs
   // eagerly (sizes all scratch), the second is captured on a side stream, later ones replay.
@@ -972,6 +1064,7 @@ class ParticleSystem {
     time_ = s.simulation_time; dt_ = s.dt; G_ = s.G; softening_ = s.softening; force_method_ = s.force_method;
     start();
     paused_ = false;
+    resizeInterop();  // :288-291
   }
   // src/core/particle_system.cpp:294-302: .nbody checkpoint through the Serializer
   void saveState(const std::string& filename) const { Serializer::save(filename, getState()); }
@@ -992,6 +1085,11 @@ class ParticleSystem {
     ParticleDataManager::allocateDevice(d_, n);
     ParticleDataManager::allocateHost(h_, n);
     allocated_ = true;
+  }
+  void resizeInterop() {  // an interop that exists follows the system through re-initialisation
+    if (!interop_) return;
+    interop_->initialize(d_.count);
+    updateInteropBuffer();
   }
   void release() {
     dropGraph();
@@ -1069,6 +1167,7 @@ class ParticleSystem {
   float dt_ = 0.001f, G_ = 1.0f, softening_ = 0.01f, time_ = 0.0f;
   ForceMethod force_method_ = ForceMethod::DIRECT_N2;
   bool paused_ = false, initialized_ = false, allocated_ = false;
+  std::unique_ptr<CudaGLInterop> interop_;
   bool use_graph_ = false, graph_valid_ = false, warm_valid_ = false;
   nb_graph* graph_ = nullptr;
   nb_stream graph_stream_ = nullptr;

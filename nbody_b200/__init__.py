@@ -10,7 +10,7 @@ Layout:  csrc/        hand-written CUDA for sm_100a + the C ABI (include/nbody_b
          dist.py      one-process-per-GPU target sharding for direct N^2 (torch.distributed)
 """
 from .api import (  # noqa: F401
-    BarnesHutCalculator, Context, CudaException, DirectForceCalculator, ForceCalculator, ForceMethod,
+    BarnesHutCalculator, Context, CudaException, CudaGLInterop, DirectForceCalculator, ForceCalculator, ForceMethod,
     InitDistribution, Integrator, ParticleData, ParticleDataManager, ParticleSystem, ResourceException,
     SimulationConfig, SimulationState, SpatialHashCalculator, ValidationException, createForceCalculator,
     get_context, validateSimulationConfig,

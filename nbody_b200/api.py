@@ -511,6 +511,86 @@ class Integrator:
         pass  # scratch is owned by the context
 
 
+# ---- CudaGLInterop, headless (include/nbody/cuda_gl_interop.hpp, src/render/cuda_gl_interop.cpp) ------
+class CudaGLInterop:
+    """The reference's two GL vertex buffers as plain device buffers of interleaved xyz floats: no GL names
+    (getPositionVBO() is 0, like the reference's own no-graphics build), "mapping" hands out the device tensor,
+    updatePositions / updateVelocities are the reference's copy kernels (:7-28) as one nb_interop_pack launch."""
+
+    def __init__(self):
+        self.particle_count_ = 0
+        self.pos_ = self.vel_ = None
+        self.is_mapped_ = self.is_velocity_mapped_ = False
+
+    def initialize(self, particle_count: int):
+        import torch
+        self.cleanup()
+        self.particle_count_ = int(particle_count)
+        if particle_count:
+            self.pos_ = torch.empty(3 * particle_count, dtype=torch.float32, device="cuda")
+            self.vel_ = torch.empty(3 * particle_count, dtype=torch.float32, device="cuda")
+
+    def cleanup(self):
+        self.pos_ = self.vel_ = None
+        self.is_mapped_ = self.is_velocity_mapped_ = False
+        self.particle_count_ = 0
+
+    def mapPositionBuffer(self):
+        self.is_mapped_ = self.pos_ is not None
+        return self.pos_
+
+    def mapVelocityBuffer(self):
+        self.is_velocity_mapped_ = self.vel_ is not None
+        return self.vel_
+
+    def unmapPositionBuffer(self):
+        self.is_mapped_ = False
+
+    def unmapVelocityBuffer(self):
+        self.is_velocity_mapped_ = False
+
+    def unmapAllBuffers(self):
+        self.is_mapped_ = self.is_velocity_mapped_ = False
+
+    def isMapped(self):
+        return self.is_mapped_
+
+    def isVelocityMapped(self):
+        return self.is_velocity_mapped_
+
+    def getPositionVBO(self):
+        return 0
+
+    def getVelocityVBO(self):
+        return 0
+
+    def getParticleCount(self):
+        return self.particle_count_
+
+    def _pack(self, d_particles, pos, vel):
+        if self.pos_ is None or d_particles.count != self.particle_count_:
+            raise ValidationException("interop buffers are not sized for these particles")
+        check(_lib.lib().nb_interop_pack(get_context().handle, C.byref(d_particles.c),
+                                         C.c_void_p(pos.data_ptr()) if pos is not None else None,
+                                         C.c_void_p(vel.data_ptr()) if vel is not None else None, _stream()))
+
+    def updatePositions(self, d_particles):
+        self._pack(d_particles, self.pos_, None)
+
+    def updateVelocities(self, d_particles):
+        self._pack(d_particles, None, self.vel_)
+
+    def verifyDataIntegrity(self, expected, count=None) -> bool:
+        """Bit-exact comparison of the position buffer with `count` floats of interleaved expected data."""
+        if self.pos_ is None:
+            return False
+        exp = np.ascontiguousarray(expected, dtype=np.float32).reshape(-1)
+        count = exp.size if count is None else int(count)
+        if count > 3 * self.particle_count_:
+            return False
+        return bool(np.array_equal(self.pos_[:count].cpu().numpy().view(np.uint32), exp[:count].view(np.uint32)))
+
+
 # ---- ParticleSystem facade ------------------------------------------------------------------------
 @dataclass
 class SimulationState:  # include/nbody/simulation_state.hpp
@@ -535,6 +615,7 @@ class ParticleSystem:
         self.force_method_ = ForceMethod.DIRECT_N2
         self.is_paused_ = False
         self.is_initialized_ = False
+        self.interop_ = None
         self.use_graph_ = False
         self.graph_, self.graph_key_, self.graph_warm_key_, self.graph_stream_ = None, None, None, None
         self.config_ = SimulationConfig()
@@ -561,6 +642,41 @@ class ParticleSystem:
             st = ics.disk(n, 10.0, 1.0, 0.5)
         self._install(st)
         self.simulation_time_ = 0.0
+        self._resize_interop()  # particle_system.cpp:96-99
+
+    def initializeWithDistribution(self, particle_count: int, dist: InitDistribution):  # :102-107
+        cfg = SimulationConfig()
+        cfg.particle_count = particle_count
+        cfg.init_distribution = dist
+        self.initialize(cfg)
+
+    # rendering interop (particle_system.cpp:320-345), headless: device buffers instead of GL buffer objects
+    def getInterop(self):
+        return self.interop_
+
+    def initializeInterop(self):
+        if not self.is_initialized_:
+            raise ValidationException("ParticleSystem is not initialized")
+        self.interop_ = CudaGLInterop()
+        self.interop_.initialize(self.particle_count_)
+        self.updateInteropBuffer()
+
+    def updateInteropBuffer(self):
+        if self.interop_ is None:
+            return
+        self.interop_.updatePositions(self.d_particles_)
+        self.interop_.updateVelocities(self.d_particles_)
+
+    def _resize_interop(self):
+        if self.interop_ is not None:
+            self.interop_.initialize(self.particle_count_)
+            self.updateInteropBuffer()
+
+    def getForceMethod(self):
+        return self.force_method_
+
+    def getTimeStep(self):
+        return self.dt_
 
     def _install(self, st: dict):
         n = st["pos_x"].size
@@ -587,6 +703,8 @@ class ParticleSystem:
         else:
             self.integrator_.integrate(self.d_particles_, self.force_calculator_, dt)
         self.simulation_time_ += dt
+        if self.interop_ is not None:
+            self.updateInteropBuffer()
 
     # ---- CUDA-graph replay of the steady-state step --------------------
     def setUseCudaGraph(self, on: bool):
@@ -730,6 +848,7 @@ class ParticleSystem:
         st = {k: np.ascontiguousarray(v, np.float32) for k, v in state.arrays.items()}
         self._install(st)  # accelerations zeroed then recomputed (particle_system.cpp:261, 283)
         self.is_paused_ = False
+        self._resize_interop()  # :288-291
 
     def saveState(self, filename):  # particle_system.cpp:294-297
         from .serialization import Serializer

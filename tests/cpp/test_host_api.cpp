@@ -182,6 +182,41 @@ static void checkpoint_round_trip_through_the_system() {  // tests/test_serializ
   std::remove(path);
 }
 
+static void headless_interop() {  // src/render/cuda_gl_interop.cpp + particle_system.cpp:320-345, without GL
+  ParticleSystem sys;
+  sys.initializeWithDistribution(1000, InitDistribution::DISK);
+  CHECK(sys.getParticleCount() == 1000 && sys.getInterop() == nullptr);
+  sys.initializeInterop();
+  CudaGLInterop* io = sys.getInterop();
+  CHECK(io != nullptr && io->getParticleCount() == 1000 && io->getPositionVBO() == 0);
+  SimulationState st = sys.getState();
+  std::vector<float> xyz(3000);
+  for (int i = 0; i < 1000; i++) { xyz[3 * i] = st.pos_x[i]; xyz[3 * i + 1] = st.pos_y[i]; xyz[3 * i + 2] = st.pos_z[i]; }
+  CHECK(io->verifyDataIntegrity(xyz.data(), xyz.size()));
+  sys.update(0.001f);  // update() refreshes the interop buffers (:123-126)
+  CHECK(!io->verifyDataIntegrity(xyz.data(), xyz.size()));
+  st = sys.getState();
+  for (int i = 0; i < 1000; i++) { xyz[3 * i] = st.pos_x[i]; xyz[3 * i + 1] = st.pos_y[i]; xyz[3 * i + 2] = st.pos_z[i]; }
+  CHECK(io->verifyDataIntegrity(xyz.data(), xyz.size()));
+  CHECK(io->mapPositionBuffer() != nullptr && io->isMapped());
+  io->unmapAllBuffers();
+  CHECK(!io->isMapped());
+  // the interop follows a re-initialisation to another size (:96-99)
+  sys.initializeWithDistribution(500, InitDistribution::UNIFORM);
+  CHECK(sys.getInterop() != nullptr && sys.getInterop()->getParticleCount() == 500);
+  // free-standing copy kernels into a caller's buffer
+  void* buf = nullptr;
+  CHECK(nb_device_alloc(Engine::get(), 500 * 3 * sizeof(float), &buf) == 0);
+  launchCopyVelocitiesToVBOKernel(static_cast<float*>(buf), sys.getDeviceData(), 256);
+  std::vector<float> v(1500, 1.0f);
+  CHECK(nb_device_download(Engine::get(), v.data(), buf, v.size() * sizeof(float), nullptr) == 0);
+  st = sys.getState();
+  bool same = true;
+  for (int i = 0; i < 500; i++) same = same && v[3 * i] == st.vel_x[i] && v[3 * i + 1] == st.vel_y[i] && v[3 * i + 2] == st.vel_z[i];
+  CHECK(same);
+  nb_device_free(Engine::get(), buf);
+}
+
 static void headless_renderer() {
   const int w = 64, h = 36;
   Renderer r;
@@ -213,6 +248,7 @@ int main() {
   particle_system_cases();
   validation_cases();
   graph_replay_matches_eager();
+  headless_interop();
   headless_renderer();
   checkpoint_round_trip_through_the_system();
   puts("cpp host api: all checks passed");

@@ -85,3 +85,33 @@ def test_interop_pack_matches_interleaving():
     torch.cuda.synchronize()
     assert np.array_equal(pos.cpu().numpy().reshape(-1, 3), np.stack([st["pos_x"], st["pos_y"], st["pos_z"]], 1))
     assert np.array_equal(vel.cpu().numpy().reshape(-1, 3), np.stack([st["vel_x"], st["vel_y"], st["vel_z"]], 1))
+
+
+def test_particle_system_interop_buffers_follow_the_state():
+    """CudaGLInterop headless (src/render/cuda_gl_interop.cpp, particle_system.cpp:96-99, 123-126, 320-345): the
+    interleaved xyz buffers are refreshed by update() and follow a re-initialisation."""
+    import nbody_b200 as nb
+    sys_ = nb.ParticleSystem()
+    sys_.initializeWithDistribution(3000, nb.InitDistribution.DISK)
+    assert sys_.getInterop() is None and sys_.getParticleCount() == 3000
+    sys_.initializeInterop()
+    io = sys_.getInterop()
+    assert io.getParticleCount() == 3000 and io.getPositionVBO() == 0 and not io.isMapped()
+
+    def xyz(prefix):
+        a = sys_.getState().arrays
+        return np.stack([a[prefix + "_x"], a[prefix + "_y"], a[prefix + "_z"]], axis=1).reshape(-1)
+
+    before = xyz("pos")
+    assert io.verifyDataIntegrity(before)
+    for _ in range(3):
+        sys_.update(1e-3)
+    assert not io.verifyDataIntegrity(before)
+    assert io.verifyDataIntegrity(xyz("pos"))
+    vel = io.mapVelocityBuffer()
+    assert io.isVelocityMapped() and np.array_equal(vel.cpu().numpy(), xyz("vel"))
+    io.unmapAllBuffers()
+    assert not io.isVelocityMapped()
+    sys_.initializeWithDistribution(1000, nb.InitDistribution.UNIFORM)
+    assert sys_.getInterop().getParticleCount() == 1000 and sys_.getInterop().verifyDataIntegrity(xyz("pos"))
+    assert sys_.getForceMethod() == nb.ForceMethod.DIRECT_N2 and sys_.getTimeStep() == nb.SimulationConfig().dt
