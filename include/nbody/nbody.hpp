@@ -32,6 +32,13 @@
 
 #include "../nbody_b200.h"
 
+#ifndef __CUDACC__  // include/nbody/types.hpp:20-35: host builds get the reference's stand-in, nvcc brings its own
+struct int3 {
+  int x, y, z;
+};
+inline constexpr int3 make_int3(int x, int y, int z) { return {x, y, z}; }
+#endif
+
 namespace nbody {
 
 // ---- enums / PODs (include/nbody/types.hpp:66-86, 123-198, 234-313, 343-382) -----------------------
@@ -317,11 +324,85 @@ class DirectForceCalculator : public ForceCalculator {
   int block_size_;
 };
 
-// What getTree() hands out: the device tree read back on demand (the reference exposes its host octree).
+// include/nbody/barnes_hut_tree.hpp:9-30.  The reference's node record, here filled from the device LBVH on request
+// (copyNodesToHost): a binary tree, so children[0] / children[1] are the left / right child and the other six are -1;
+// center / half_size are those of the node's Morton cell; node 0 is the root; leaves follow the n-1 internal nodes.
+struct OctreeNode {
+  Vec3 center;
+  float half_size = 0;
+  Vec3 center_of_mass;
+  float total_mass = 0;
+  int children[8] = {-1, -1, -1, -1, -1, -1, -1, -1};
+  int particle_index = -1;
+  bool is_leaf = true;
+  int particle_count = 0;
+};
+
+// include/nbody/barnes_hut_tree.hpp:36-78 -- same public surface; the tree itself lives on the device (nb_bh_build),
+// one per engine context, and is read back on demand.
 class BarnesHutTree {
  public:
+  explicit BarnesHutTree(std::size_t max_particles = 0) : max_particles_(max_particles) {}
+  void build(const ParticleData* d) {  // src/cuda/force_barnes_hut.cu:282-289
+    NB_CALL(nb_bh_build(Engine::get(), as_nb(d), Engine::stream()));
+    n_ = d->count;
+    h_nodes_.clear();
+  }
+  void computeForces(ParticleData* d, float theta, float G, float eps) {  // :488-498
+    NB_CALL(nb_bh_forces(Engine::get(), as_nb(d), theta, G, eps, Engine::stream()));
+  }
   int getNodeCount() const { int c = 0; NB_CALL(nb_bh_stats(Engine::get(), nullptr, &c)); return c; }
+  int getMaxDepth() const { return max_depth_; }  // octree levels spanned by the Morton prefixes; after copyNodesToHost
+  const OctreeNode* getNodes() const { return h_nodes_.data(); }
   std::uint64_t getInteractionCount() const { std::uint64_t v = 0; NB_CALL(nb_bh_stats(Engine::get(), &v, nullptr)); return v; }
+  void copyNodesToHost() {  // :500-503
+    const std::size_t n = bodies();
+    if (n == 0) { h_nodes_.clear(); return; }
+    std::vector<std::int32_t> perm(n), left(n > 1 ? n - 1 : 1), right(left.size()), prefix(left.size());
+    std::vector<float> com(4 * (2 * n - 1));
+    float bb[6];
+    NB_CALL(nb_bh_export(Engine::get(), nullptr, perm.data(), left.data(), right.data(), nullptr, prefix.data(), com.data(), bb));
+    h_nodes_.assign(2 * n - 1, OctreeNode());
+    const float side = std::max(std::max(bb[3] - bb[0], bb[4] - bb[1]), bb[5] - bb[2]) + 0.002f;  // :339-344
+    const Vec3 root_center((bb[0] + bb[3]) * 0.5f, (bb[1] + bb[4]) * 0.5f, (bb[2] + bb[5]) * 0.5f);
+    max_depth_ = 0;
+    for (std::size_t i = 0; i < 2 * n - 1; i++) {
+      OctreeNode& o = h_nodes_[i];
+      o.center_of_mass = Vec3(com[4 * i], com[4 * i + 1], com[4 * i + 2]);
+      o.total_mass = com[4 * i + 3];
+      o.center = root_center;
+      o.half_size = side * 0.5f;
+      if (n > 1 && i < n - 1) {
+        o.is_leaf = false;
+        o.children[0] = left[i];
+        o.children[1] = right[i];
+        const int level = (prefix[i] + 2) / 3;  // octree level of the node's common Morton prefix
+        o.half_size = side * 0.5f / static_cast<float>(1 << std::min(level, 30));
+        max_depth_ = std::max(max_depth_, level);
+      } else {
+        o.particle_index = perm[n > 1 ? i - (n - 1) : 0];
+        o.particle_count = 1;
+      }
+    }
+    if (n > 1) countBodies(0);  // particle_count of the internal nodes, bottom-up
+  }
+  bool verifyTreeStructure() const {  // :505-509, plus what it says it would check: every body exactly once
+    if (h_nodes_.empty()) return getNodeCount() > 0;
+    const std::size_t n = bodies();
+    std::vector<char> seen(n, 0);
+    for (const OctreeNode& o : h_nodes_)
+      if (o.is_leaf) {
+        if (o.particle_index < 0 || static_cast<std::size_t>(o.particle_index) >= n || seen[o.particle_index]) return false;
+        seen[o.particle_index] = 1;
+      }
+    return h_nodes_[0].particle_count == static_cast<int>(n);
+  }
+  bool verifyMassConservation(const ParticleData* h) const {  // :511-519
+    float total_mass = 0.0f;
+    for (std::size_t i = 0; i < h->count; i++) total_mass += h->mass[i];
+    const float root_mass = h_nodes_.empty() ? getRootMass(h->count) : h_nodes_[0].total_mass;
+    return std::fabs(total_mass - root_mass) < 0.001f * total_mass;
+  }
   // sorted Morton keys + permutation, LBVH topology, node centres of mass (x,y,z,m)
   void exportTree(std::size_t n, std::vector<std::uint32_t>& keys, std::vector<std::int32_t>& perm,
                   std::vector<std::int32_t>& left, std::vector<std::int32_t>& right, std::vector<float>& node_com) const {
@@ -334,15 +415,39 @@ class BarnesHutTree {
     NB_CALL(nb_bh_export(Engine::get(), nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, com.data(), nullptr));
     return com[3];
   }
+
+ private:
+  std::size_t bodies() const { return n_ ? n_ : static_cast<std::size_t>((getNodeCount() + 1) / 2); }
+  int countBodies(int i) {  // explicit stack: the LBVH of sorted duplicates can be deep
+    std::vector<std::pair<int, int>> st;  // (node, state)
+    st.emplace_back(i, 0);
+    while (!st.empty()) {
+      auto [node, state] = st.back();
+      OctreeNode& o = h_nodes_[node];
+      if (o.is_leaf) { st.pop_back(); continue; }
+      if (state == 0) {
+        st.back().second = 1;
+        st.emplace_back(o.children[0], 0);
+        st.emplace_back(o.children[1], 0);
+      } else {
+        o.particle_count = h_nodes_[o.children[0]].particle_count + h_nodes_[o.children[1]].particle_count;
+        st.pop_back();
+      }
+    }
+    return h_nodes_[i].particle_count;
+  }
+  std::size_t max_particles_ = 0, n_ = 0;
+  int max_depth_ = 0;
+  std::vector<OctreeNode> h_nodes_;
 };
 
 class BarnesHutCalculator : public ForceCalculator {
  public:
   explicit BarnesHutCalculator(float theta = 0.5f) : theta_(theta) {}
   void computeForces(ParticleData* d) override {  // src/cuda/force_barnes_hut.cu:526-532
-    if (!tree_) tree_ = std::make_unique<BarnesHutTree>();
-    NB_CALL(nb_bh_build(Engine::get(), as_nb(d), Engine::stream()));
-    NB_CALL(nb_bh_forces(Engine::get(), as_nb(d), theta_, G_, softening_eps_, Engine::stream()));
+    if (!tree_) tree_ = std::make_unique<BarnesHutTree>(d->count);
+    tree_->build(d);
+    tree_->computeForces(d, theta_, G_, softening_eps_);
   }
   ForceMethod getMethod() const noexcept override { return ForceMethod::BARNES_HUT; }
   void setTheta(float t) { theta_ = t; }
@@ -354,9 +459,30 @@ class BarnesHutCalculator : public ForceCalculator {
   float theta_;
 };
 
+// include/nbody/spatial_hash_grid.hpp:13-57 -- same public surface; the grid lives on the device (nb_sh_build), one
+// per engine context.
 class SpatialHashGrid {
  public:
+  explicit SpatialHashGrid(std::size_t max_particles = 0, float cell_size = 1.0f)
+      : max_particles_(max_particles), cell_size_(cell_size) {}
+  void build(const ParticleData* d) {  // src/cuda/force_spatial_hash.cu:235-303
+    NB_CALL(nb_sh_build(Engine::get(), as_nb(d), cell_size_, Engine::stream()));
+    n_ = d->count;
+    std::int32_t dims[3];
+    NB_CALL(nb_sh_export(Engine::get(), dims, bbox_, nullptr, nullptr, nullptr, nullptr));
+    grid_dims_ = make_int3(dims[0], dims[1], dims[2]);
+  }
+  void computeForces(ParticleData* d, float cutoff, float G, float eps) {  // :305-316
+    NB_CALL(nb_sh_forces(Engine::get(), as_nb(d), cutoff, G, eps, Engine::stream()));
+  }
+  void setCellSize(float s) { cell_size_ = s; }
+  int3 getGridDims() const { return grid_dims_; }
+  float getCellSize() const { return cell_size_; }
   int getTotalCells() const { int t = 0; NB_CALL(nb_sh_total_cells(Engine::get(), &t)); return t; }
+  void copyCellDataToHost(std::vector<int>& cell_start, std::vector<int>& cell_end, std::vector<int>& particle_cells,
+                          std::vector<int>& sorted_indices) const {  // :318-334
+    copyCellDataToHost(n_, cell_start, cell_end, particle_cells, sorted_indices);
+  }
   void copyCellDataToHost(std::size_t n, std::vector<int>& cell_start, std::vector<int>& cell_end,
                           std::vector<int>& particle_cells, std::vector<int>& sorted_indices) const {
     const int t = getTotalCells();
@@ -364,6 +490,35 @@ class SpatialHashGrid {
     NB_CALL(nb_sh_export(Engine::get(), nullptr, nullptr, particle_cells.data(), cell_start.data(), cell_end.data(),
                          sorted_indices.data()));
   }
+  bool verifyCellAssignment(const ParticleData* h) const {  // :336-362
+    for (std::size_t i = 0; i < h->count; i++) {
+      int3 c = getCellIndex(h->pos_x[i] - bbox_[0], h->pos_y[i] - bbox_[1], h->pos_z[i] - bbox_[2], cell_size_);
+      c.x = std::max(0, std::min(c.x, grid_dims_.x - 1));
+      c.y = std::max(0, std::min(c.y, grid_dims_.y - 1));
+      c.z = std::max(0, std::min(c.z, grid_dims_.z - 1));
+      const float lo[3] = {bbox_[0] + c.x * cell_size_, bbox_[1] + c.y * cell_size_, bbox_[2] + c.z * cell_size_};
+      const float p[3] = {h->pos_x[i], h->pos_y[i], h->pos_z[i]};
+      for (int a = 0; a < 3; a++)
+        if (p[a] < lo[a] || p[a] > lo[a] + cell_size_) return false;
+    }
+    return true;
+  }
+  static int3 getCellIndex(float x, float y, float z, float cell_size) {  // :14-17
+    return make_int3(static_cast<int>(std::floor(x / cell_size)), static_cast<int>(std::floor(y / cell_size)),
+                     static_cast<int>(std::floor(z / cell_size)));
+  }
+  static int hashCell(int3 cell, int3 grid_dims) {  // :19-25, wraps negative indices
+    const int cx = ((cell.x % grid_dims.x) + grid_dims.x) % grid_dims.x;
+    const int cy = ((cell.y % grid_dims.y) + grid_dims.y) % grid_dims.y;
+    const int cz = ((cell.z % grid_dims.z) + grid_dims.z) % grid_dims.z;
+    return cx + cy * grid_dims.x + cz * grid_dims.x * grid_dims.y;
+  }
+
+ private:
+  std::size_t max_particles_ = 0, n_ = 0;
+  float cell_size_ = 1.0f;
+  int3 grid_dims_ = {0, 0, 0};
+  float bbox_[6] = {0, 0, 0, 0, 0, 0};
 };
 
 class SpatialHashCalculator : public ForceCalculator {
@@ -371,9 +526,10 @@ class SpatialHashCalculator : public ForceCalculator {
   explicit SpatialHashCalculator(float cell_size = 1.0f, float cutoff_radius = 2.0f)
       : cell_size_(cell_size), cutoff_radius_(cutoff_radius) {}
   void computeForces(ParticleData* d) override {  // src/cuda/force_spatial_hash.cu:370-377
-    if (!grid_) grid_ = std::make_unique<SpatialHashGrid>();
-    NB_CALL(nb_sh_build(Engine::get(), as_nb(d), cell_size_, nullptr));
-    NB_CALL(nb_sh_forces(Engine::get(), as_nb(d), cutoff_radius_, G_, softening_eps_, nullptr));
+    if (!grid_) grid_ = std::make_unique<SpatialHashGrid>(d->count, cell_size_);
+    grid_->setCellSize(cell_size_);
+    grid_->build(d);
+    grid_->computeForces(d, cutoff_radius_, G_, softening_eps_);
   }
   ForceMethod getMethod() const noexcept override { return ForceMethod::SPATIAL_HASH; }
   void setCellSize(float s) { cell_size_ = s; }

@@ -182,6 +182,50 @@ static void checkpoint_round_trip_through_the_system() {  // tests/test_serializ
   std::remove(path);
 }
 
+static void standalone_tree_and_grid() {  // the call sites of tests/test_barnes_hut.cpp:14-62 and test_spatial_hash.cpp:15-130
+  const std::size_t n = 500;
+  ParticleData h, d;
+  ParticleDataManager::allocateHost(h, n);
+  ParticleDataManager::allocateDevice(d, n);
+  SphericalDistParams sp; sp.radius = 10.0f;
+  ParticleInitializer::initSpherical(h, sp);
+  ParticleDataManager::copyToDevice(d, h);
+  BarnesHutTree tree(n);
+  tree.build(&d);
+  CHECK(tree.getNodeCount() > 0);
+  tree.copyNodesToHost();
+  CHECK(tree.verifyMassConservation(&h));
+  CHECK(tree.verifyTreeStructure());
+  CHECK(tree.getMaxDepth() > 0 && tree.getMaxDepth() <= 11);
+  const OctreeNode* nodes = tree.getNodes();
+  CHECK(!nodes[0].is_leaf && nodes[0].particle_count == static_cast<int>(n) && nodes[0].children[2] == -1);
+  CHECK(std::fabs(nodes[0].total_mass - static_cast<float>(n)) < 0.5f);
+  tree.computeForces(&d, 0.5f, 1.0f, 0.01f);
+  CHECK(tree.getInteractionCount() > 0);
+
+  CHECK(SpatialHashGrid::getCellIndex(0.5f, 0.5f, 0.5f, 1.0f).x == 0);   // tests/test_spatial_hash.cpp:38-51
+  const int3 c = SpatialHashGrid::getCellIndex(2.5f, 3.5f, 4.5f, 1.0f);
+  CHECK(c.x == 2 && c.y == 3 && c.z == 4);
+  CHECK(SpatialHashGrid::hashCell(make_int3(-1, 0, 0), make_int3(4, 4, 4)) == 3);
+  SpatialHashGrid grid(n, 2.0f);
+  grid.build(&d);
+  CHECK(grid.getTotalCells() > 0 && grid.getCellSize() == 2.0f);
+  const int3 dims = grid.getGridDims();
+  CHECK(dims.x * dims.y * dims.z == grid.getTotalCells());
+  CHECK(grid.verifyCellAssignment(&h));
+  std::vector<int> cs, ce, pc, si;
+  grid.copyCellDataToHost(cs, ce, pc, si);   // :89-130: every particle in exactly one cell
+  std::vector<int> seen(n, 0);
+  for (int cell = 0; cell < grid.getTotalCells(); cell++)
+    for (int k = cs[cell]; k < ce[cell]; k++) { CHECK(pc[si[k]] == cell); seen[si[k]]++; }
+  bool once = true;
+  for (std::size_t i = 0; i < n; i++) once = once && seen[i] == 1;
+  CHECK(once);
+  grid.computeForces(&d, 4.0f, 1.0f, 0.01f);
+  ParticleDataManager::freeDevice(d);
+  ParticleDataManager::freeHost(h);
+}
+
 static void headless_interop() {  // src/render/cuda_gl_interop.cpp + particle_system.cpp:320-345, without GL
   ParticleSystem sys;
   sys.initializeWithDistribution(1000, InitDistribution::DISK);
@@ -248,6 +292,7 @@ int main() {
   particle_system_cases();
   validation_cases();
   graph_replay_matches_eager();
+  standalone_tree_and_grid();
   headless_interop();
   headless_renderer();
   checkpoint_round_trip_through_the_system();
