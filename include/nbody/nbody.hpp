@@ -862,6 +862,16 @@ struct Mat4 {
   float& at(int col, int row) { return m[col * 4 + row]; }
   float at(int col, int row) const { return m[col * 4 + row]; }
 };
+inline Mat4 operator*(const Mat4& a, const Mat4& b) {  // column-major product, like glm
+  Mat4 r;
+  for (int c = 0; c < 4; c++)
+    for (int row = 0; row < 4; row++) {
+      float v = 0.0f;
+      for (int k = 0; k < 4; k++) v += a.at(k, row) * b.at(c, k);
+      r.at(c, row) = v;
+    }
+  return r;
+}
 inline Vec3 cross(const Vec3& a, const Vec3& b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
 inline Mat4 lookAt(const Vec3& eye, const Vec3& center, const Vec3& up) {  // glm::lookAt, right-handed
   const Vec3 f = (center - eye).normalized(), s = cross(f, up).normalized(), u = cross(s, f);
@@ -888,6 +898,7 @@ class Camera {  // camera.hpp:9-88
       : fov_(fov), aspect_(aspect), near_(z_near), far_(z_far) {}
   Mat4 getViewMatrix() const { return lookAt(position_, target_, up_); }
   Mat4 getProjectionMatrix() const { return perspective(fov_ * 3.14159265358979323846f / 180.0f, aspect_, near_, far_); }
+  Mat4 getViewProjectionMatrix() const { return getProjectionMatrix() * getViewMatrix(); }  // camera.cpp:32-34
   void setPosition(const Vec3& p) { position_ = p; }
   void setTarget(const Vec3& t) { target_ = t; }
   void setUp(const Vec3& u) { up_ = u; }
@@ -984,6 +995,9 @@ class Renderer {  // renderer.hpp:20-80
   void setColorMode(ColorMode m) { color_mode_ = m; }
   ColorMode getColorMode() const { return color_mode_; }
   void setPointSize(float s) { point_size_ = s; }
+  float getPointSize() const { return point_size_; }
+  void setCamera(const Camera& c) { camera_ = c; }
+  unsigned int getShaderProgram() const { return 0; }  // no GL program object: the shader math is the CUDA kernels
   void setMaxDepth(float d) { max_depth_ = d; }
   void setMaxVelocity(float v) { max_velocity_ = v; }
   Camera& getCamera() { return camera_; }

@@ -75,6 +75,11 @@ class Camera:
     def getProjectionMatrix(self):
         return perspective(math.radians(self.fov_), self.aspect_, self.near_, self.far_)
 
+    def getViewProjectionMatrix(self):  # camera.cpp:32-34; flat column-major like the two factors
+        v = self.getViewMatrix().reshape(4, 4).T
+        p = self.getProjectionMatrix().reshape(4, 4).T
+        return (p @ v).T.reshape(16).astype(f32)
+
     def setPosition(self, p):
         self.position_ = np.asarray(p, f32)
 
@@ -89,6 +94,21 @@ class Camera:
 
     def getTarget(self):
         return self.target_
+
+    def getUp(self):
+        return self.up_
+
+    def getFOV(self):
+        return self.fov_
+
+    def getAspectRatio(self):
+        return self.aspect_
+
+    def getNear(self):
+        return self.near_
+
+    def getFar(self):
+        return self.far_
 
     def getForward(self):
         return _normalize(self.target_ - self.position_)
@@ -187,6 +207,10 @@ class Renderer:
         self.framebuffer_ = torch.zeros(self.height_ * self.width_ * 4, dtype=torch.uint8, device="cuda")
         self.is_initialized_ = True
 
+    def cleanup(self):                             # :123-140: drops the framebuffer (no GL objects to delete)
+        self.framebuffer_ = None
+        self.is_initialized_ = False
+
     def onResize(self, width, height):             # :233-238
         self.initialize(width, height) if self.framebuffer_ is None or (width, height) != (self.width_, self.height_) \
             else None
@@ -200,6 +224,15 @@ class Renderer:
 
     def setPointSize(self, size):
         self.point_size_ = float(size)
+
+    def getPointSize(self):
+        return self.point_size_
+
+    def setCamera(self, camera):
+        self.camera_ = camera
+
+    def getShaderProgram(self):
+        return 0  # no GL program object: the shader math is the CUDA kernels
 
     def setMaxDepth(self, d):
         self.max_depth_ = float(d)

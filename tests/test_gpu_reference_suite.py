@@ -1,7 +1,7 @@
 """The reference's OWN test sources for the hot path (tests/test_{force_calculation,integrator,barnes_hut,
-spatial_hash,particle_data,serialization,performance_observability,validation}.cpp, 58 cases incl. the RapidCheck
+spatial_hash,particle_data,serialization,performance_observability,validation,camera,color_mapping}.cpp, 71 cases incl. the RapidCheck
 properties at 100 cases each), compiled UNMODIFIED against this repo's drop-in headers and libnbody_b200.so by
-oracle/build_ref_tests.sh (GoogleTest / RapidCheck stand-ins: tests/cpp/shim), run on the GPU.
+oracle/build_ref_tests.sh (GoogleTest / RapidCheck / glm stand-ins: tests/cpp/shim), run on the GPU.
 
 One case cannot pass for any fp32 implementation, the reference's included: Integrator.EnergyConservationProperty
 starts a two-body system at v = sqrt(G m / 2r), for which KE = 0.1 and PE = -0.1 cancel to E0 ~ 5e-8 (the softening
@@ -30,7 +30,7 @@ def test_reference_test_sources_pass_against_the_drop_in():
     assert m, out[-2000:]
     ran, passed, failed = (int(x) for x in m.groups())
     bad = set(re.findall(r"^\[  FAILED  \] (\S+)$", out, flags=re.M))
-    assert ran >= 58, out[-2000:]
+    assert ran >= 71, out[-2000:]
     assert bad <= ILL_CONDITIONED, "reference tests failing against the drop-in: %s\n%s" % (sorted(bad), out[-3000:])
     assert passed >= ran - len(ILL_CONDITIONED)
 
