@@ -244,6 +244,19 @@ class ParticleDataManager {
   static void copyToHost(ParticleData& h, const ParticleData& d) {
     NB_CALL(nb_particles_download(Engine::get(), as_nb(&h), as_nb(&d), nullptr));
   }
+  // positions only (src/cuda/particle_init.cu:285-299)
+  static void copyPositionsToHost(float* h_pos_x, float* h_pos_y, float* h_pos_z, const ParticleData& d) {
+    const std::size_t bytes = d.count * sizeof(float);
+    NB_CALL(nb_device_download(Engine::get(), h_pos_x, d.pos_x, bytes, nullptr));
+    NB_CALL(nb_device_download(Engine::get(), h_pos_y, d.pos_y, bytes, nullptr));
+    NB_CALL(nb_device_download(Engine::get(), h_pos_z, d.pos_z, bytes, nullptr));
+  }
+  static void copyPositionsToDevice(ParticleData& d, const float* h_pos_x, const float* h_pos_y, const float* h_pos_z) {
+    const std::size_t bytes = d.count * sizeof(float);
+    NB_CALL(nb_device_upload(Engine::get(), d.pos_x, h_pos_x, bytes, nullptr));
+    NB_CALL(nb_device_upload(Engine::get(), d.pos_y, h_pos_y, bytes, nullptr));
+    NB_CALL(nb_device_upload(Engine::get(), d.pos_z, h_pos_z, bytes, nullptr));
+  }
 };
 
 class ParticleInitializer {

@@ -70,6 +70,7 @@ uint64_t nb_launch_count(const nb_context* ctx);
 int nb_device_alloc(nb_context* ctx, size_t bytes, void** out);   /* raw device buffer (e.g. a framebuffer) */
 int nb_device_free(nb_context* ctx, void* p);
 int nb_device_download(nb_context* ctx, void* host_dst, const void* device_src, size_t bytes, nb_stream s); /* synchronises */
+int nb_device_upload(nb_context* ctx, void* device_dst, const void* host_src, size_t bytes, nb_stream s);     /* synchronises */
 typedef struct nb_graph nb_graph;
 int nb_stream_create(nb_context* ctx, nb_stream* out);
 int nb_stream_destroy(nb_context* ctx, nb_stream s);

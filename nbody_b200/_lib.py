@@ -60,6 +60,7 @@ SYMBOLS = {
     "nb_device_alloc": (_i, [_vp, _sz, C.POINTER(_vp)]),
     "nb_device_free": (_i, [_vp, _vp]),
     "nb_device_download": (_i, [_vp, _vp, _vp, _sz, _vp]),
+    "nb_device_upload": (_i, [_vp, _vp, _vp, _sz, _vp]),
     "nb_stream_create": (_i, [_vp, C.POINTER(_vp)]),
     "nb_stream_destroy": (_i, [_vp, _vp]),
     "nb_graph_begin_capture": (_i, [_vp, _vp]),

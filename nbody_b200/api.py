@@ -247,6 +247,25 @@ class ParticleDataManager:
         ctx = get_context()
         check(_lib.lib().nb_particles_download(ctx.handle, C.byref(h_data.c), C.byref(d_data.c), _stream()))
 
+    @staticmethod
+    def copyPositionsToHost(h_pos_x, h_pos_y, h_pos_z, d_data: ParticleData):
+        """Positions only, device -> three host float32 arrays (particle_data.hpp:29-31)."""
+        ctx, nbytes = get_context(), d_data.count * 4
+        for dst, key in ((h_pos_x, "pos_x"), (h_pos_y, "pos_y"), (h_pos_z, "pos_z")):
+            assert dst.dtype == np.float32 and dst.flags["C_CONTIGUOUS"] and dst.size >= d_data.count
+            check(_lib.lib().nb_device_download(ctx.handle, dst.ctypes.data_as(C.c_void_p),
+                                                C.c_void_p(getattr(d_data.c, key)), nbytes, _stream()))
+
+    @staticmethod
+    def copyPositionsToDevice(d_data: ParticleData, h_pos_x, h_pos_y, h_pos_z):
+        """Positions only, three host float32 arrays -> device (particle_data.hpp:33-35)."""
+        ctx, nbytes = get_context(), d_data.count * 4
+        for src, key in ((h_pos_x, "pos_x"), (h_pos_y, "pos_y"), (h_pos_z, "pos_z")):
+            src = np.ascontiguousarray(src, np.float32)
+            assert src.size >= d_data.count
+            check(_lib.lib().nb_device_upload(ctx.handle, C.c_void_p(getattr(d_data.c, key)),
+                                              src.ctypes.data_as(C.c_void_p), nbytes, _stream()))
+
 
 # ---- force calculators ----------------------------------------------------------------------------
 class ForceCalculator:

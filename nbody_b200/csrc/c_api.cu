@@ -293,6 +293,17 @@ int nb_device_download(nb_context* ctx, void* host_dst, const void* device_src, 
   return NB_OK;
 }
 
+int nb_device_upload(nb_context* ctx, void* device_dst, const void* host_src, size_t bytes, nb_stream s) {
+  NB_ENTER(ctx);
+  if (bytes && (!host_src || !device_dst)) {
+    set_error("device upload: null argument");
+    return NB_ERR_INVALID;
+  }
+  NB_CUDA(cudaMemcpyAsync(device_dst, host_src, bytes, cudaMemcpyHostToDevice, (cudaStream_t)s));
+  NB_CUDA(cudaStreamSynchronize((cudaStream_t)s));  // the host buffer may be pageable and reused at once
+  return NB_OK;
+}
+
 int nb_stream_create(nb_context* ctx, nb_stream* out) {
   NB_ENTER(ctx);
   if (!out) {

@@ -190,6 +190,17 @@ static void standalone_tree_and_grid() {  // the call sites of tests/test_barnes
   SphericalDistParams sp; sp.radius = 10.0f;
   ParticleInitializer::initSpherical(h, sp);
   ParticleDataManager::copyToDevice(d, h);
+  {  // positions-only copies (particle_data.hpp:29-35)
+    std::vector<float> x(n), y(n), z(n);
+    ParticleDataManager::copyPositionsToHost(x.data(), y.data(), z.data(), d);
+    CHECK(x[7] == h.pos_x[7] && y[n - 1] == h.pos_y[n - 1] && z[0] == h.pos_z[0]);
+    x[7] += 1.0f;
+    ParticleDataManager::copyPositionsToDevice(d, x.data(), y.data(), z.data());
+    std::vector<float> x2(n), y2(n), z2(n);
+    ParticleDataManager::copyPositionsToHost(x2.data(), y2.data(), z2.data(), d);
+    CHECK(x2[7] == h.pos_x[7] + 1.0f);
+    ParticleDataManager::copyPositionsToDevice(d, h.pos_x, h.pos_y, h.pos_z);
+  }
   BarnesHutTree tree(n);
   tree.build(&d);
   CHECK(tree.getNodeCount() > 0);

@@ -295,3 +295,18 @@ def test_verlet_conserves_momentum_and_plummer_is_virialised():
     assert np.abs(b["angular_momentum"] - a["angular_momentum"]).max() <= 1e-5 * scale
     assert np.abs(b["center_of_mass"] - (a["center_of_mass"] + 0.05 * a["momentum"] / a["total_mass"])).max() <= 1e-6
     assert abs(b["total_energy"] - a["total_energy"]) <= 1e-5 * abs(a["total_energy"])
+
+
+def test_positions_only_copies():
+    """ParticleDataManager::copyPositionsToHost / copyPositionsToDevice (include/nbody/particle_data.hpp:29-35)."""
+    import nbody_b200 as nb
+    from nbody_b200 import ics
+    st = ics.uniform_box(1001, -3, 3, seed=9)
+    d = _device_data(st)
+    x, y, z = (np.zeros(1001, np.float32) for _ in range(3))
+    nb.ParticleDataManager.copyPositionsToHost(x, y, z, d)
+    assert np.array_equal(x, st["pos_x"]) and np.array_equal(y, st["pos_y"]) and np.array_equal(z, st["pos_z"])
+    nb.ParticleDataManager.copyPositionsToDevice(d, x + 1, y, z * 2)
+    out = d.numpy()
+    assert np.array_equal(out["pos_x"], st["pos_x"] + 1) and np.array_equal(out["pos_z"], st["pos_z"] * 2)
+    assert np.array_equal(out["vel_x"], st["vel_x"])
