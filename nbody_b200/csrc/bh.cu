@@ -184,6 +184,78 @@ __global__ void __launch_bounds__(256) bh_com_kernel(int n, const int4* __restri
   }
 }
 
+// The same bottom-up pass with the lower levels in shared memory.  A CTA owns COM_TILE consecutive leaves; the
+// internal nodes whose leaf range lies inside that tile (all but ~1 in COM_TILE of them; node i always lies inside
+// its own range, so their indices fall in the tile too) have their topology staged in shared memory, arrive on
+// shared-memory counters and hand their values up through shared memory; only nodes that span tiles go through the
+// global flags as above.  Every node is still combine(left child, right child) with the same operations, so the
+// result is bit-identical to bh_com_kernel's.
+constexpr int COM_TILE = 512;
+__device__ __forceinline__ float4 bh_combine(const float4& a, const float4& b) {
+  const float ms = __fadd_rn(a.w, b.w);
+  float4 c;
+  if (ms > 0.f) {
+    c.x = __fdiv_rn(__fadd_rn(__fmul_rn(a.x, a.w), __fmul_rn(b.x, b.w)), ms);
+    c.y = __fdiv_rn(__fadd_rn(__fmul_rn(a.y, a.w), __fmul_rn(b.y, b.w)), ms);
+    c.z = __fdiv_rn(__fadd_rn(__fmul_rn(a.z, a.w), __fmul_rn(b.z, b.w)), ms);
+  } else {
+    c.x = a.x; c.y = a.y; c.z = a.z;
+  }
+  c.w = ms;
+  return c;
+}
+__global__ void __launch_bounds__(COM_TILE) bh_com_tile_kernel(int n, const int4* __restrict__ meta,
+                                                               const int32_t* __restrict__ parent,
+                                                               const int2* __restrict__ range, int* __restrict__ flags,
+                                                               float4* node_com) {
+  __shared__ int4 s_meta[COM_TILE];
+  __shared__ int2 s_range[COM_TILE];
+  __shared__ int s_parent[COM_TILE];
+  __shared__ int s_cnt[COM_TILE];
+  __shared__ float4 s_com[COM_TILE];
+  const int tid = threadIdx.x;
+  const int t0 = blockIdx.x * COM_TILE, t1 = min(t0 + COM_TILE, n);  // this CTA's leaves [t0, t1)
+  const int leaf0 = n - 1;
+  if (t0 + tid < n - 1) {
+    s_meta[tid] = meta[t0 + tid];
+    s_range[tid] = range[t0 + tid];
+    s_parent[tid] = parent[t0 + tid];
+  }
+  s_cnt[tid] = 0;
+  __syncthreads();
+  const int k = t0 + tid;
+  if (k >= n) return;
+  int node = leaf0 + k;
+  int p = parent[node];
+  float4 cur = __ldcg(node_com + node);
+  while (p >= 0) {  // levels inside the tile
+    const int q = p - t0;
+    if (q < 0 || q >= COM_TILE) break;
+    const int2 r = s_range[q];
+    if (r.x < t0 || r.y >= t1) break;
+    __threadfence_block();
+    if (atomicAdd(&s_cnt[q], 1) == 0) return;  // the sibling's thread finishes this node
+    __threadfence_block();  // the sibling's value was published before its arrival: read it after ours
+    const int4 m = s_meta[q];
+    const bool left = (m.x == node);
+    const int sib = left ? m.y : m.x;
+    const float4 sv = (sib >= leaf0) ? __ldcg(node_com + sib) : s_com[sib - t0];
+    cur = left ? bh_combine(cur, sv) : bh_combine(sv, cur);
+    s_com[q] = cur;
+    __stcg(node_com + p, cur);
+    node = p;
+    p = s_parent[q];
+  }
+  while (p >= 0) {  // nodes spanning tiles: as bh_com_kernel
+    __threadfence();
+    if (atomicAdd(&flags[p], 1) == 0) return;
+    const int4 m = meta[p];
+    const float4 c = bh_combine(__ldcg(node_com + m.x), __ldcg(node_com + m.y));
+    __stcg(node_com + p, c);
+    p = parent[p];
+  }
+}
+
 // Traversal groups.  A "supergroup" is a maximal subtree with at most `smax` leaves: its bodies share
 // a Morton prefix, so it is as compact as its cell (a fixed run of consecutive sorted bodies can
 // straddle distant cells in sparse regions).  Each supergroup of c bodies is cut into
@@ -533,7 +605,11 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
     bh_karras_kernel<<<gi, 256, 0, st>>>(b->keys.as<uint32_t>(), (int)n, b->meta.as<int4>(), b->parent.as<int32_t>(),
                                          b->range.as<int2>());
     NB_LAUNCH_CHECK(ctx);
-    bh_com_kernel<<<gn, 256, 0, st>>>((int)n, b->meta.as<int4>(), b->parent.as<int32_t>(), b->flags.as<int>(), com);
+    if (getenv("NB_BH_COM_GLOBAL"))  // the all-global version, kept for A/B
+      bh_com_kernel<<<gn, 256, 0, st>>>((int)n, b->meta.as<int4>(), b->parent.as<int32_t>(), b->flags.as<int>(), com);
+    else
+      bh_com_tile_kernel<<<(unsigned)((n + COM_TILE - 1) / COM_TILE), COM_TILE, 0, st>>>(
+          (int)n, b->meta.as<int4>(), b->parent.as<int32_t>(), b->range.as<int2>(), b->flags.as<int>(), com);
     NB_LAUNCH_CHECK(ctx);
   }
   bh_groups_kernel<<<gn, 256, 0, st>>>((int)n, b->super, b->group, b->parent.as<int32_t>(), b->range.as<int2>(),
