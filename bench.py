@@ -141,6 +141,12 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def cpu_sample_targets(n: int, per_thread: int) -> int:
+    """Targets in the bounded CPU sample: per_thread targets for every host thread (one thread does
+    ~0.35 G-interactions/s, so 4096 targets x 1 Mi sources per thread is ~12 s of CPU work)."""
+    return min(n, per_thread * len(os.sched_getaffinity(0))) if n >= (1 << 20) else min(n, 4096)
+
+
 def cpu_sample_rate(state, n_targets: int, reps: int = 1):
     """Oracle port of the reference CPU loop on a bounded sample: the first n_targets targets of the
     workload against ALL sources.  Returns (G-interactions/s, threads, seconds)."""
@@ -165,7 +171,7 @@ def run_reference_arm(args):
     from nbody_b200 import ics
     n, wl = workload(args.gpus, args.bodies)
     st = ics.plummer(n, seed=42)
-    sample = 16384 if n >= (1 << 20) else min(n, 4096)
+    sample = cpu_sample_targets(n, 1024)  # ~3 s per step: the whole run stays within a few minutes
     for _ in range(max(args.warmup, 0)):
         cpu_sample_rate(st, max(sample // 8, 256))
     times = []
@@ -318,7 +324,7 @@ def main():
 
     cpu = None
     if not args.no_cpu_baseline and world == 1:   # rank 0 at N = 1 only
-        sample = 16384 if n >= (1 << 20) else min(n, 4096)
+        sample = cpu_sample_targets(n, 4096)
         rate, threads, sec = cpu_sample_rate(state, sample)
         cpu = {"value": rate, "unit": "G-interactions/s", "cores": threads, "kind": "port",
                "sample": f"first {sample} targets x all {n} sources of the same workload, {sec:.1f} s, "
