@@ -14,6 +14,7 @@
 // implies it passes for every body of the group, so each body's force is at least as accurate as
 // with its own per-body test.
 #include <cstdlib>
+#include <new>
 #include <cstring>
 
 #include "bh.cuh"
@@ -536,7 +537,7 @@ __global__ void __launch_bounds__(256) bh_shard_finish_kernel(const float4* __re
 }
 
 static BH* bh_get(nb_context* ctx) {
-  if (!ctx->bh) ctx->bh = new BH();
+  if (!ctx->bh) ctx->bh = new (std::nothrow) BH();
   return ctx->bh;
 }
 
@@ -552,6 +553,10 @@ void bh_destroy(nb_context* ctx) {
 
 int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
   BH* b = bh_get(ctx);
+  if (!b) {
+    set_error("out of host memory");
+    return NB_ERR_RESOURCE;
+  }
   const size_t n = d->count;
   b->built = false;
   if (n == 0) return NB_OK;
@@ -631,6 +636,10 @@ static int bh_check_overflow(BH* b) {
 int bh_forces(nb_context* ctx, const nb_particles* d, float theta, float G, float eps, cudaStream_t st,
               const BhShard* shard) {
   BH* b = bh_get(ctx);
+  if (!b) {
+    set_error("out of host memory");
+    return NB_ERR_RESOURCE;
+  }
   const size_t n = d->count;
   if (n == 0) return NB_OK;
   if (!b->built || b->n != n) {
@@ -696,6 +705,10 @@ int bh_shard_wait(nb_context* ctx, const unsigned* flags, int flag_base, unsigne
 int bh_shard_finish(nb_context* ctx, const float4* acc_sorted, const nb_particles* d, float dt, bool kick,
                     cudaStream_t st) {
   BH* b = bh_get(ctx);
+  if (!b) {
+    set_error("out of host memory");
+    return NB_ERR_RESOURCE;
+  }
   const size_t n = d->count;
   if (n == 0) return NB_OK;
   if (!b->built || b->n != n) {

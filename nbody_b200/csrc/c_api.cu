@@ -350,7 +350,13 @@ int nb_graph_end_capture(nb_context* ctx, nb_stream s, nb_graph** out) {
     cudaGraphDestroy(g);
     return cuda_fail(err, "cudaGraphInstantiate", __FILE__, __LINE__);
   }
-  nb_graph* h = new nb_graph();
+  nb_graph* h = new (std::nothrow) nb_graph();
+  if (!h) {
+    cudaGraphExecDestroy(e);
+    cudaGraphDestroy(g);
+    set_error("out of host memory");
+    return NB_ERR_RESOURCE;
+  }
   h->graph = g;
   h->exec = e;
   h->device = ctx->device;

@@ -6,6 +6,7 @@
 // nb_mgpu_pack_local and nb_mgpu_forces_remote; the local-source pass needs no remote data and
 // overlaps the gather.
 #include <cstring>
+#include <new>
 
 #include "bh.cuh"
 #include "direct.cuh"
@@ -143,7 +144,11 @@ static int peer_block_alloc(nb_context* ctx, PeerState*& slot, size_t payload_by
                             unsigned char handle_out[64]) {
   NB_CUDA(cudaSetDevice(ctx->device));
   peer_block_close(ctx, slot);
-  PeerState* ps = slot = new PeerState();
+  PeerState* ps = slot = new (std::nothrow) PeerState();
+  if (!ps) {
+    set_error("out of host memory");
+    return NB_ERR_RESOURCE;
+  }
   ps->block_bytes = kFlagBytes + payload_bytes;
   NB_CUDA(cudaMalloc(&ps->block, ps->block_bytes));
   NB_CUDA(cudaMemset(ps->block, 0, ps->block_bytes));

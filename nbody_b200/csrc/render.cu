@@ -18,6 +18,7 @@
 // Every fp32 operation is an explicit round-to-nearest intrinsic in the order oracle/render.c spells
 // out, so the framebuffer is bit-exact with the oracle.
 #include <cstring>
+#include <new>
 
 #include "common.cuh"
 
@@ -294,7 +295,7 @@ __global__ void __launch_bounds__(256) interleave3_kernel(const float* __restric
 namespace nb {
 
 static RenderState* render_get(nb_context* ctx) {
-  if (!ctx->render) ctx->render = new RenderState();
+  if (!ctx->render) ctx->render = new (std::nothrow) RenderState();
   return ctx->render;
 }
 
@@ -332,6 +333,10 @@ int nb_render_splats(nb_context* ctx, const nb_particles* d, const nb_render_par
   NB_CUDA(cudaSetDevice(ctx->device));
   cudaStream_t st = (cudaStream_t)s;
   RenderState* r = render_get(ctx);
+  if (!r) {
+    set_error("out of host memory");
+    return NB_ERR_RESOURCE;
+  }
   const size_t n = d->count, pixels = (size_t)p->width * p->height;
   auto u8 = [](float c) { return (uint32_t)lrintf(fminf(fmaxf(c, 0.f), 1.f) * 255.0f); };
   const uint32_t clear = u8(p->clear_color[0]) | (u8(p->clear_color[1]) << 8) | (u8(p->clear_color[2]) << 16) |

@@ -12,6 +12,7 @@
 // interactions: pairs are counted from each cell's first slot (a cell with an odd count ends in a
 // single), and the build lists the pair leaders' slots (flag + scan over the cell-ordered bodies).
 #include <cmath>
+#include <new>
 #include <cstring>
 
 #include "common.cuh"
@@ -270,7 +271,7 @@ __global__ void __launch_bounds__(128) sh_force_kernel(size_t n, const float4* _
 }
 
 static SH* sh_get(nb_context* ctx) {
-  if (!ctx->sh) ctx->sh = new SH();
+  if (!ctx->sh) ctx->sh = new (std::nothrow) SH();
   return ctx->sh;
 }
 
@@ -286,6 +287,10 @@ void sh_destroy(nb_context* ctx) {
 
 int sh_build(nb_context* ctx, const nb_particles* d, float cell, cudaStream_t st) {
   SH* s = sh_get(ctx);
+  if (!s) {
+    set_error("out of host memory");
+    return NB_ERR_RESOURCE;
+  }
   const size_t n = d->count;
   s->built = false;
   if (!(cell > 0.f) || std::isnan(cell) || std::isinf(cell)) {
@@ -350,6 +355,10 @@ int sh_build(nb_context* ctx, const nb_particles* d, float cell, cudaStream_t st
 
 int sh_forces(nb_context* ctx, const nb_particles* d, float cutoff, float G, float eps, cudaStream_t st) {
   SH* s = sh_get(ctx);
+  if (!s) {
+    set_error("out of host memory");
+    return NB_ERR_RESOURCE;
+  }
   const size_t n = d->count;
   if (n == 0) return NB_OK;
   if (!s->built || s->n != n) {

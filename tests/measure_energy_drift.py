@@ -3,7 +3,7 @@
 (dt 1e-3, eps 0.01, Plummer seed 42) at 65 536 and 262 144 bodies, ours and -- same initial conditions -- the
 reference's own kernels (oracle/_ref/libnbody_ref.so), E in fp64 by our diagnostic for both.  A measurement
 script, not a test (the 8192-body version of the same check is tests/test_gpu_vs_reference.py): run on a B200,
-one JSON line per case.  usage: python tests/measure_energy_drift.py [n ...]"""
+one JSON line per case.  usage: python tests/measure_energy_drift.py [--steps K] [n ...]"""
 import json
 import sys
 import time
@@ -17,8 +17,14 @@ def main():
     from nbody_b200 import ics
     from oracle import ref_bindings as ref
 
-    sizes = [int(a) for a in sys.argv[1:]] or [65536, 262144]
-    steps, dt, eps = 1000, 1e-3, 0.01
+    argv = sys.argv[1:]
+    steps = 1000
+    if "--steps" in argv:  # fewer steps for the sizes where 1000 do not fit the GPU budget (1 Mi: 0.43 s per step)
+        k = argv.index("--steps")
+        steps = int(argv[k + 1])
+        del argv[k:k + 2]
+    sizes = [int(a) for a in argv] or [65536, 262144]
+    dt, eps = 1e-3, 0.01
     for n in sizes:
         st = ics.plummer(n, seed=42)
 
