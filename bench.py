@@ -290,6 +290,30 @@ def main():
 
     exchange = system.exchange
     system.close()
+
+    # ---- the same bodies through the general pair loop -------------------------------------------
+    # The workload's masses are all 1/N (as in every initial condition of the reference), so every full
+    # source tile takes the one-mass pair loop.  For the record, the same step with the last
+    # mantissa bit of every 512th mass flipped, which sends every tile through the general loop.
+    mixed = None
+    if world == 1:
+        st2 = {k: v.copy() for k, v in state.items()}
+        st2["mass"].view(np.uint32)[::512] ^= 1
+        sys2 = ShardedDirectSystem(st2, n, 0, 1, G_CONST, SOFTENING)
+        sys2.compute_forces()
+        sys2.update(DT)
+        torch.cuda.synchronize()
+        k2 = max(1, min(args.steps, 3))
+        e0.record()
+        for _ in range(k2):
+            sys2.update(DT)
+        e1.record()
+        torch.cuda.synchronize()
+        ms2 = e0.elapsed_time(e1) / k2
+        sys2.close()
+        mixed = {"value": interactions_per_step / (ms2 * 1e-3) / 1e9, "unit": "G-interactions/s", "ms_per_step": ms2,
+                 "steps": k2, "what": "same bodies, one mass in every 512 differs in its last bit: general pair loop "
+                                      "(3 packed multiplies per pair instead of 2) for every source tile"}
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -316,10 +340,10 @@ def main():
         "flop_per_interaction": FLOP_PER_INTERACTION, "kernel_ms": kernel_ms,
         "kernel_share_of_step": (kms.value / args.steps) / ms_per_step if ms_per_step > 0 else None,
         # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the ncu --set full capture of this
-        # command (profiles/r01_direct_force_1mi_ncu_full.txt): 34.8 MB read (the 16 MiB packed sources, once,
-        # + target tiles) + 261.7 MB written (302 MB of per-chunk partials, part still in L2 at kernel end)
-        "traffic": 296489216 if (n == (1 << 20) and world == 1) else None,
-        "traffic_unit": "bytes per launch (compute-bound kernel: 3.7e3 flop per DRAM byte)",
+        # command (profiles/r01_direct_force_1mi_ncu_full_v2.txt): 109.0 MB read (the 16 MiB packed sources + target
+        # tiles) + 428.5 MB written (349 MB of per-chunk partials, 888 CTAs x 64 chunks x 6 KiB, + write-backs)
+        "traffic": 537492736 if (n == (1 << 20) and world == 1) else None,
+        "traffic_unit": "bytes per launch (compute-bound kernel: 4.1e4 flop per DRAM byte)",
     }
 
     cpu = None
@@ -354,13 +378,15 @@ def main():
                    "exchange": ("peer-memory push fused into the pack kernel, flag wait between the local and remote pass (no NCCL in the step)"
                                 if exchange == "peer" else "NCCL all_gather_into_tensor overlapped with the local pass")
                    if world > 1 else "none",
+                   "masses": "all equal (1/N): source tiles of one mass take the one-mass pair loop, decided per tile "
+                             "on the device from the data; see mixed_mass_path for the general loop",
                    "cache": "positions (16 MiB+ packed) are rewritten every step; compute bound, L2 state irrelevant"},
         "tflops_20flop": value * 1e9 * FLOP_PER_INTERACTION / 1e12,
         "pct_fp32_peak_datasheet": 100.0 * value * 1e9 * FLOP_PER_INTERACTION / 1e12 / (FP32_PEAK_DATASHEET_TF * args.gpus),
         "e2e": {"value": e2e_value, "unit": "G-interactions/s", "ms_per_step": e2e_ms,
                 "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": d2h * world},
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
-        "reference_gpu": ref_gpu,
+        "reference_gpu": ref_gpu, "mixed_mass_path": mixed,
     }
     emit(line)
 

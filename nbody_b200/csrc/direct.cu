@@ -9,7 +9,7 @@
 //     with Blackwell FFMA2/FADD2/FMUL2 (12 packed instructions + 2 MUFU.RSQ per two pairs), the
 //     source being a warp-broadcast LDS.128;
 //   * source tiles are staged by 1-D TMA bulk copies (cp.async.bulk + mbarrier), double buffered;
-//   * the (target tile x source tile) unit space is cut into chunks that a persistent grid (5 CTAs per
+//   * the (target tile x source tile) unit space is cut into chunks that a persistent grid (6 CTAs per
 //     SM) claims from a global counter, so all 148 SMs and all resident CTAs finish together for any
 //     N; chunk c writes fp32 partials to slot c, and a reduce kernel adds a tile's chunks in chunk
 //     order (deterministic, no float atomics) and applies the kick;
@@ -18,6 +18,7 @@
 #include "direct.cuh"
 
 #include <cstdlib>
+#include <type_traits>
 
 namespace nb {
 
@@ -147,7 +148,7 @@ int launch_peer_wait(nb_context* ctx, const unsigned* flags, int flag_base, unsi
 // ---------------------------------------------------------------------------------------------
 // build-time tuning knobs (A/B builds through tools/ab_direct.sh)
 #ifndef NB_DIRECT_THREADS_PER_SM
-#define NB_DIRECT_THREADS_PER_SM 1280  // 5 CTAs of 256 threads: caps the kernel at 48 registers
+#define NB_DIRECT_THREADS_PER_SM 1536  // 6 CTAs of 256 threads at 40 registers (5 at 48: 404.8 ms per 1 Mi step, 6: 387.7)
 #endif
 #ifndef NB_DIRECT_UNROLL
 #define NB_DIRECT_UNROLL 64  // sources per trip of the pair loop (8: 440.5 ms per 1 Mi step, 32: 430.9, 64: 429.4)
@@ -160,6 +161,9 @@ int launch_peer_wait(nb_context* ctx, const unsigned* flags, int flag_base, unsi
 #endif
 #ifndef NB_DIRECT_BIG_JT
 #define NB_DIRECT_BIG_JT 1024  // sources per shared-memory tile of the large-N configuration
+#endif
+#ifndef NB_DIRECT_BIG_I
+#define NB_DIRECT_BIG_I 2  // targets per thread of the large-N configuration (even: packed pairs)
 #endif
 #define NB_PRAGMA_(x) _Pragma(#x)
 #define NB_PRAGMA_UNROLL(n) NB_PRAGMA_(unroll n)
@@ -186,6 +190,7 @@ __global__ void __launch_bounds__(T, NB_DIRECT_THREADS_PER_SM / T) direct_force_
   constexpr int IT = T * I;
   constexpr uint32_t TILE_BYTES = JT * sizeof(float4);
   static_assert(I % 2 == 0, "targets per thread must be even (packed fp32x2)");
+  static_assert(JT % T == 0, "the one-mass test reads JT / T sources per thread");
   __shared__ __align__(128) float4 tile[2][JT];
   __shared__ __align__(8) uint64_t full[2];
   __shared__ int claimed[2];
@@ -267,29 +272,56 @@ __global__ void __launch_bounds__(T, NB_DIRECT_THREADS_PER_SM / T) direct_force_
 #pragma unroll
       for (int p = 0; p < P; p++) ax[p] = ay[p] = az[p] = zero2;
       const float4* tj = &tile[st][0];
-      NB_PRAGMA_UNROLL(NB_DIRECT_UNROLL)
-      for (int jj = 0; jj < JT; jj++) {
-        const float4 s = tj[jj];  // warp-broadcast LDS.128
-        const f2 px = pk(s.x, s.x), py = pk(s.y, s.y), pz = pk(s.z, s.z), pm = pk(s.w, s.w);
+      // Sources of one mass: when every body of the tile carries the same G*m (bit pattern), the factor
+      // leaves the pair loop -- w = 1/r^3 costs two packed multiplies instead of three -- and is applied
+      // once to the tile's sums.  Decided per tile from the data itself (all the reference's initial
+      // conditions are equal-mass, particle_init.cu:290-357; mixed tiles, e.g. the zero-mass padding of
+      // the last tile, take the general loop), so it holds for every caller of this kernel.
+      const float gm0 = tj[0].w;
+      bool mixed = false;
+#pragma unroll
+      for (int q = 0; q < JT / T; q++) mixed |= (__float_as_uint(tj[q * T + tid].w) != __float_as_uint(gm0));
+      const bool one_mass = !__syncthreads_or(mixed);
+      auto pair_loop = [&](auto uniform_tag) {
+        constexpr bool ONE_MASS = decltype(uniform_tag)::value;
+        NB_PRAGMA_UNROLL(NB_DIRECT_UNROLL)
+        for (int jj = 0; jj < JT; jj++) {
+          const float4 s = tj[jj];  // warp-broadcast LDS.128
+          const f2 px = pk(s.x, s.x), py = pk(s.y, s.y), pz = pk(s.z, s.z);
+#pragma unroll
+          for (int p = 0; p < P; p++) {
+            const f2 dx = sub2(px, xi[p]), dy = sub2(py, yi[p]), dz = sub2(pz, zi[p]);
+            f2 r2 = fma2(dx, dx, e2);
+            r2 = fma2(dy, dy, r2);
+            r2 = fma2(dz, dz, r2);
+            float r0, r1;
+            upk(r2, r0, r1);
+            float i0 = rsq(r0), i1 = rsq(r1);
+            if (EPS0) {  // eps == 0: the self pair (and exact coincidences) must contribute 0, not NaN
+              i0 = (r0 > 0.f) ? i0 : 0.f;
+              i1 = (r1 > 0.f) ? i1 : 0.f;
+            }
+            const f2 ri = pk(i0, i1);
+            f2 w;
+            if (ONE_MASS) w = mul2(mul2(ri, ri), ri);                      // 1 / r^3
+            else w = mul2(mul2(ri, ri), mul2(pk(s.w, s.w), ri));           // (G m_j) / r^3
+            ax[p] = fma2(w, dx, ax[p]);
+            ay[p] = fma2(w, dy, ay[p]);
+            az[p] = fma2(w, dz, az[p]);
+          }
+        }
+      };
+      if (one_mass) {
+        pair_loop(std::true_type{});
+        const f2 gm = pk(gm0, gm0);
 #pragma unroll
         for (int p = 0; p < P; p++) {
-          const f2 dx = sub2(px, xi[p]), dy = sub2(py, yi[p]), dz = sub2(pz, zi[p]);
-          f2 r2 = fma2(dx, dx, e2);
-          r2 = fma2(dy, dy, r2);
-          r2 = fma2(dz, dz, r2);
-          float r0, r1;
-          upk(r2, r0, r1);
-          float i0 = rsq(r0), i1 = rsq(r1);
-          if (EPS0) {  // eps == 0: the self pair (and exact coincidences) must contribute 0, not NaN
-            i0 = (r0 > 0.f) ? i0 : 0.f;
-            i1 = (r1 > 0.f) ? i1 : 0.f;
-          }
-          const f2 ri = pk(i0, i1);
-          const f2 w = mul2(mul2(ri, ri), mul2(pm, ri));  // (G m_j) / r^3
-          ax[p] = fma2(w, dx, ax[p]);
-          ay[p] = fma2(w, dy, ay[p]);
-          az[p] = fma2(w, dz, az[p]);
+          ax[p] = mul2(ax[p], gm);
+          ay[p] = mul2(ay[p], gm);
+          az[p] = mul2(az[p], gm);
         }
+      } else {
+        pair_loop(std::false_type{});
       }
       // fold the tile's sums into the compensated running sums
 #pragma unroll
@@ -375,7 +407,7 @@ __global__ void __launch_bounds__(256) reduce_kernel(const float* __restrict__ p
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
-static const DirectCfg kCfgBig = {NB_DIRECT_BIG_T, 2, NB_DIRECT_BIG_JT};
+static const DirectCfg kCfgBig = {NB_DIRECT_BIG_T, NB_DIRECT_BIG_I, NB_DIRECT_BIG_JT};
 static const DirectCfg kCfgSmall = {128, 2, 256};
 static const size_t kSmallN = 32768;
 
@@ -424,7 +456,7 @@ int launch_direct_pass(nb_context* ctx, const DirectCfg& cfg, const float4* src,
   const bool big = (&cfg == &kCfgBig);
   const bool eps0 = !(eps2 > 0.f);
   int& occ = ctx->direct_occ[(big ? 0 : 2) + (eps0 ? 1 : 0)];
-  if (occ == 0) occ = big ? occupancy<NB_DIRECT_BIG_T, 2, NB_DIRECT_BIG_JT>(eps0) : occupancy<128, 2, 256>(eps0);
+  if (occ == 0) occ = big ? occupancy<NB_DIRECT_BIG_T, NB_DIRECT_BIG_I, NB_DIRECT_BIG_JT>(eps0) : occupancy<128, 2, 256>(eps0);
   int use_occ = occ;
   if (const char* e = getenv("NB_DIRECT_OCC")) {  // tuning knob: resident CTAs per SM
     const int v = atoi(e);
@@ -450,8 +482,8 @@ int launch_direct_pass(nb_context* ctx, const DirectCfg& cfg, const float4* src,
                                                             jb0, eps2, (unsigned long long)ps.slot_base)
   ProfScope prof(ctx, st);
   if (big) {
-    if (eps0) NB_LAUNCH_DIRECT(NB_DIRECT_BIG_T, 2, NB_DIRECT_BIG_JT, true);
-    else NB_LAUNCH_DIRECT(NB_DIRECT_BIG_T, 2, NB_DIRECT_BIG_JT, false);
+    if (eps0) NB_LAUNCH_DIRECT(NB_DIRECT_BIG_T, NB_DIRECT_BIG_I, NB_DIRECT_BIG_JT, true);
+    else NB_LAUNCH_DIRECT(NB_DIRECT_BIG_T, NB_DIRECT_BIG_I, NB_DIRECT_BIG_JT, false);
   } else {
     if (eps0) NB_LAUNCH_DIRECT(128, 2, 256, true);
     else NB_LAUNCH_DIRECT(128, 2, 256, false);
@@ -471,8 +503,8 @@ int launch_reduce(nb_context* ctx, const DirectCfg& cfg, const nb_particles* d, 
   const float* part = ctx->partial.as<float>();
   const bool big = (&cfg == &kCfgBig);
   if (big) {
-    if (kick) reduce_kernel<2 * NB_DIRECT_BIG_T, true><<<grid, 256, 0, st>>>(part, ra, *d, n, dt);
-    else reduce_kernel<2 * NB_DIRECT_BIG_T, false><<<grid, 256, 0, st>>>(part, ra, *d, n, dt);
+    if (kick) reduce_kernel<NB_DIRECT_BIG_I * NB_DIRECT_BIG_T, true><<<grid, 256, 0, st>>>(part, ra, *d, n, dt);
+    else reduce_kernel<NB_DIRECT_BIG_I * NB_DIRECT_BIG_T, false><<<grid, 256, 0, st>>>(part, ra, *d, n, dt);
   } else {
     if (kick) reduce_kernel<256, true><<<grid, 256, 0, st>>>(part, ra, *d, n, dt);
     else reduce_kernel<256, false><<<grid, 256, 0, st>>>(part, ra, *d, n, dt);

@@ -82,6 +82,72 @@ def test_direct_G_and_eps(orc):
     assert rel_err((out["acc_x"], out["acc_y"], out["acc_z"]), ref).max() <= TOL
 
 
+def _forces(st, eps=0.01, G=1.0):
+    import nbody_b200 as nb
+    d = _device_data(st)
+    calc = nb.DirectForceCalculator()
+    calc.setSofteningParameter(eps)
+    calc.setGravitationalConstant(G)
+    calc.computeForces(d)
+    out = d.numpy()
+    return out["acc_x"], out["acc_y"], out["acc_z"]
+
+
+@pytest.mark.parametrize("n", [5000, 40000, 70001])
+@pytest.mark.parametrize("masses", ["random", "two_blocks", "one_odd_body", "equal"])
+def test_direct_mass_patterns(orc, n, masses):
+    """The force kernel takes a source tile whose bodies all carry one mass through a shorter pair loop
+    (factor applied once per tile) and every other tile through the general loop: both, their mix inside one
+    launch, and a tile boundary that does not coincide with the change of mass must meet the same bound.
+    Both kernel configurations (n below / above 32768)."""
+    from nbody_b200 import ics
+    st = ics.plummer(n, seed=13)
+    rng = np.random.default_rng(5)
+    if masses == "random":
+        st["mass"][:] = (10.0 ** rng.uniform(-3, 1, n) / n).astype(np.float32)
+    elif masses == "two_blocks":
+        st["mass"][: n // 3] = np.float32(2.5 / n)
+        st["mass"][n // 3:] = np.float32(0.25 / n)
+    elif masses == "one_odd_body":
+        st["mass"][n // 2] = np.float32(100.0 / n)
+    got = _forces(st)
+    ref = orc.direct_f64(st["pos_x"], st["pos_y"], st["pos_z"], st["mass"], 1.0, 1e-4)
+    e = rel_err(got, ref)
+    assert e.max() <= TOL, f"{masses} n={n}: max rel err {e.max():.3e}"
+
+
+def test_direct_one_mass_loop_agrees_with_general_loop():
+    """Same bodies twice: equal masses (every full tile takes the one-mass loop), and the same masses with the
+    last bit of every 97th body flipped (every tile takes the general loop).  The two answers differ by the
+    perturbation and the rounding of one multiplication, far below the parity bound."""
+    from nbody_b200 import ics
+    n = 66000
+    st = ics.plummer(n, seed=21)
+    a = _forces(st, G=2.0)                        # a power of two: G*m keeps the flipped bit
+    st2 = {k: v.copy() for k, v in st.items()}
+    m = st2["mass"].view(np.uint32)
+    m[::97] ^= 1
+    b = _forces(st2, G=2.0)
+    e = rel_err(a, tuple(np.asarray(x, np.float64) for x in b))
+    assert 0 < e.max() <= 2e-6, e.max()
+
+
+def test_direct_one_mass_loop_eps0_coincident_bodies():
+    from nbody_b200 import ics
+    n = 40000
+    st = ics.uniform_box(n, -1, 1, seed=9)
+    for k in ("pos_x", "pos_y", "pos_z"):
+        st[k][1::2000] = st[k][0::2000]          # exact coincidences, r = 0 with eps = 0
+    got = _forces(st, eps=0.0)
+    assert all(np.isfinite(g).all() for g in got)
+    # fp64 truth: eps^2 = 1e-200 leaves every separated pair unchanged and makes the r = 0 pairs contribute
+    # (finite weight) x 0 = 0, which is what the kernels define for them
+    ref = __import__("oracle.bindings", fromlist=["x"]).direct_f64(st["pos_x"], st["pos_y"], st["pos_z"], st["mass"],
+                                                                   1.0, 1e-200)
+    # eps = 0 and random points: a few close pairs dominate their bodies' sums, nothing cancels
+    assert rel_err(got, ref).max() <= TOL
+
+
 @pytest.mark.parametrize("fuse", [True, False])
 def test_verlet_steps_vs_oracle(orc, fuse):
     """10 steps, fused and 4-call paths, against the fp32 oracle step (integrator.cu:224-238)."""

@@ -9,7 +9,7 @@ s = sys.stdin.read()
 ins = [(int(a, 16), t) for a, t in re.findall(r"/\*([0-9a-f]{4})\*/\s+(.*?);", s)]
 print(len(ins), "instructions")
 for a, txt in ins:
-    m = re.search(r"BRA\s+0x([0-9a-f]+)", txt)
+    m = re.search(r"BRA(?:\.\w+)*\s+(?:!?UP\d+,\s*)?0x([0-9a-f]+)", txt)  # also BRA.U UP0, 0x... (uniform loop counter)
     if not m or int(m.group(1), 16) >= a:
         continue
     t = int(m.group(1), 16)
