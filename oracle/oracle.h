@@ -9,12 +9,15 @@
  * reference checkout).  Built with -ffp-contract=off so fp32 arithmetic is the same
  * sequence of IEEE operations the reference source spells out.
  *
- * Parity pinning: the reference holds no golden vectors for this path, only analytic
- * anchors (tests/test_force_calculation.cpp:13-60, tests/test_integrator.cpp:15-84,
- * tests/test_spatial_hash.cpp:38-51); tests/test_oracle_anchors.py checks the oracle
- * against all of them.  Where oracle/_ref (the reference's own CUDA sources compiled for
- * sm_100, see oracle/build_ref.sh) is present, tests/test_gpu_vs_reference.py also runs
- * the reference kernels on the GPU box on the same inputs.
+ * Parity pinning (PINNED): the reference's own tests hold no golden vectors for this path, only
+ * analytic anchors (tests/test_force_calculation.cpp:13-60, tests/test_integrator.cpp:15-84,
+ * tests/test_spatial_hash.cpp:38-51); tests/test_oracle_golden.py checks the oracle against all of
+ * them, against tests/golden/ref_host_helpers.json (outputs of the reference's own host-callable
+ * functions) and against tests/golden/ref_gpu_n4096.npz (outputs of the reference's own CUDA kernels,
+ * compiled unmodified by oracle/build_ref.sh and run on a B200 by tests/golden/make_golden.py).  Where
+ * oracle/_ref is present, tests/test_gpu_vs_reference.py also runs the reference kernels live on the
+ * GPU box on the same inputs.  Only oracle/render.c is unpinned against a GL implementation
+ * (graphics: unavailable on this box); it is pinned by the shader source alone.
  */
 #ifndef NBODY_ORACLE_H
 #define NBODY_ORACLE_H
