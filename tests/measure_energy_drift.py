@@ -3,7 +3,9 @@
 (dt 1e-3, eps 0.01, Plummer seed 42) at 65 536 and 262 144 bodies, ours and -- same initial conditions -- the
 reference's own kernels (oracle/_ref/libnbody_ref.so), E in fp64 by our diagnostic for both.  A measurement
 script, not a test (the 8192-body version of the same check is tests/test_gpu_vs_reference.py): run on a B200,
-one JSON line per case.  usage: python tests/measure_energy_drift.py [--steps K] [n ...]"""
+one JSON line per case.  usage: python tests/measure_energy_drift.py [--steps K] [--every S] [n ...]
+--every S also samples the energy every S steps on both arms and records the largest excursion along the trajectory
+(the end-point value alone is one sample of a rounding-noise random walk)."""
 import json
 import sys
 import time
@@ -22,6 +24,11 @@ def main():
     if "--steps" in argv:  # fewer steps for the sizes where 1000 do not fit the GPU budget (1 Mi: 0.43 s per step)
         k = argv.index("--steps")
         steps = int(argv[k + 1])
+        del argv[k:k + 2]
+    every = 0
+    if "--every" in argv:
+        k = argv.index("--every")
+        every = int(argv[k + 1])
         del argv[k:k + 2]
     sizes = [int(a) for a in argv] or [65536, 262144]
     dt, eps = 1e-3, 0.01
@@ -43,16 +50,32 @@ def main():
         e0 = integ.computeTotalEnergy(d, 1.0, eps)
         torch.cuda.synchronize()
         t0 = time.time()
-        for _ in range(steps):
+        samples_ours = []
+        for k in range(steps):
             integ.integrate(d, calc, dt)
+            if every and (k + 1) % every == 0 and k + 1 < steps:
+                samples_ours.append(integ.computeTotalEnergy(d, 1.0, eps))
         e1 = integ.computeTotalEnergy(d, 1.0, eps)
         t_ours = time.time() - t0
+        samples_ours.append(e1)
         rec = {"bodies": n, "steps": steps, "dt": dt, "softening": eps, "E0": e0, "E_ours": e1,
                "drift_ours": abs(e1 - e0) / abs(e0), "seconds_ours": t_ours}
+        if every:
+            rec.update({"sample_every": every,
+                        "max_excursion_ours": max(abs(e - e0) for e in samples_ours) / abs(e0)})
         if ref.available():
             r = {k: v.copy() for k, v in st.items()}
             t0 = time.time()
-            ref.run(r, 0, dt, 1.0, eps, steps=steps, initial_forces=True)
+            if every:  # the same trajectory in segments: the state (accelerations included) round-trips through the host
+                samples_ref, done = [], 0
+                while done < steps:
+                    seg = min(every, steps - done)
+                    ref.run(r, 0, dt, 1.0, eps, steps=seg, initial_forces=(done == 0))
+                    done += seg
+                    samples_ref.append(integ.computeTotalEnergy(device(r), 1.0, eps))
+                rec["max_excursion_reference"] = max(abs(e - e0) for e in samples_ref) / abs(e0)
+            else:
+                ref.run(r, 0, dt, 1.0, eps, steps=steps, initial_forces=True)
             rec["seconds_reference"] = time.time() - t0
             er = integ.computeTotalEnergy(device(r), 1.0, eps)
             rec.update({"E_reference": er, "drift_reference": abs(er - e0) / abs(e0)})
