@@ -187,8 +187,13 @@ __global__ void __launch_bounds__(256) sh_pair_fill_kernel(const uint32_t* __res
 // run: its own term is G m * rsqrt(eps^2)^3 * 0 = 0 exactly for eps > 0 and is zeroed by a select for eps = 0
 // (as are exact coincidences).  Candidates are accumulated in run order, i.e. cell order z, y, x then slot
 // (:104-150).
+#ifdef NB_SH_MIN_BLOCKS  // build-time tuning knob: resident CTAs per SM asked of ptxas (register cap)
+#define NB_SH_BOUNDS __launch_bounds__(128, NB_SH_MIN_BLOCKS)
+#else
+#define NB_SH_BOUNDS __launch_bounds__(128)
+#endif
 template <bool EPS0>
-__global__ void __launch_bounds__(128) sh_force_kernel(size_t n, const float4* __restrict__ spos,
+__global__ void NB_SH_BOUNDS sh_force_kernel(size_t n, const float4* __restrict__ spos,
                                                        const uint32_t* __restrict__ keys,
                                                        const int32_t* __restrict__ sidx,
                                                        const int32_t* __restrict__ pair_slot,
