@@ -5,9 +5,12 @@ INTENDED octree algorithm (per-body test, src/cuda/force_barnes_hut.cu:154-196 w
 eps.  A measurement script, not a test (tests/test_gpu_sort_tree.py asserts the relation at theta = 0.5).
 usage: python tests/measure_bh_accuracy.py [n]   -> one JSON line per (distribution, theta)"""
 import json
+import os
 import sys
 
 import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))  # run from anywhere
 
 
 def main():

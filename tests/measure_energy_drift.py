@@ -7,10 +7,13 @@ one JSON line per case.  usage: python tests/measure_energy_drift.py [--steps K]
 --every S also samples the energy every S steps on both arms and records the largest excursion along the trajectory
 (the end-point value alone is one sample of a rounding-noise random walk)."""
 import json
+import os
 import sys
 import time
 
 import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))  # run from anywhere
 
 
 def main():
