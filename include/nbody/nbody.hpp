@@ -1284,7 +1284,11 @@ class ParticleSystem {
     int method = -1;
     std::size_t count = 0;
     const void *pos = nullptr, *calc = nullptr;
-    bool operator==(const GraphKey&) const = default;
+    // spelled out (not "= default") so that the headers also compile as C++17, the reference's own standard
+    bool operator==(const GraphKey& o) const {
+      return dt == o.dt && G == o.G && eps == o.eps && theta == o.theta && method == o.method && count == o.count &&
+             pos == o.pos && calc == o.calc;
+    }
   };
   GraphKey graphKey(float dt) const {
     GraphKey k;

@@ -144,3 +144,18 @@ def test_shard_layout_properties():
     with pytest.raises(ValueError):
         shard_layout(10, 2, 2)
 
+
+
+@pytest.mark.parametrize("std", ["c++17", "c++20"])
+def test_host_headers_compile_as_the_reference_standard_and_as_cxx20(std):
+    """The reference builds as C++17 (CMakeLists.txt:25); the host layer is written for C++20 and must stay usable
+    from both, warning-free."""
+    import shutil
+    import subprocess
+    if shutil.which("g++") is None:
+        pytest.skip("no g++")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    for src in ("tests/cpp/test_host_api.cpp", "examples/benchmark_main.cpp"):
+        r = subprocess.run(["g++", f"-std={std}", "-O0", "-Wall", "-Wextra", "-Werror", "-fsyntax-only",
+                            "-I" + os.path.join(root, "include"), os.path.join(root, src)], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr[:2000]
