@@ -294,7 +294,8 @@ int sort_pairs(nb_context* ctx, uint32_t* d_keys, int32_t* d_vals, size_t n, int
     set_error("sort: too many elements");
     return NB_ERR_INVALID;
   }
-  static bool attr_set = false;
+  static bool attr_set_dev[64] = {};  // function attributes are per device: a process may hold a context on several
+  bool& attr_set = attr_set_dev[ctx->device & 63];
   if (!attr_set) {
     NB_CUDA(cudaFuncSetAttribute(rs_onesweep_kernel<8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * RS_WARP_KEYS * 8));
     NB_CUDA(cudaFuncSetAttribute(rs_onesweep_kernel<16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16 * RS_WARP_KEYS * 8));
