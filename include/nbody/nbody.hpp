@@ -1304,6 +1304,9 @@ class ParticleSystem {
   }
   void updateGraphed(float dt) {
     const GraphKey key = graphKey(dt);
+    // a stale graph (context scratch reallocated since capture, e.g. by a renderer frame with more fragments or a
+    // larger second system) must not be replayed: drop it, run this step eagerly, capture again
+    if (graph_ && nb_graph_is_stale(graph_)) dropGraph();
     if (graph_ && graph_valid_ && key == graph_key_) {
       NB_CALL(nb_graph_launch(graph_, Engine::stream()));
       return;

@@ -31,9 +31,13 @@ extern "C" {
 #define NB_ERR_GRID_TOO_LARGE (-4) /* spatial hash > 1e8 cells: src/cuda/force_spatial_hash.cu:252-254 (std::runtime_error) */
 #define NB_ERR_NCCL (-5)        /* NCCL failure in the multi-GPU path                                  */
 #define NB_ERR_INTERNAL (-6)
+#define NB_ERR_STALE_GRAPH (-7) /* nb_graph_launch: scratch the graph points into was reallocated; capture again */
 
 typedef struct nb_context nb_context; /* one per device; owns all scratch; NOT thread-safe
-                                         (same contract as include/nbody/force_calculator.hpp:8-20) */
+                                         (same contract as include/nbody/force_calculator.hpp:8-20).  The scratch
+                                         is shared by every entry point: keep ONE stream's work in flight per
+                                         context (nb_host_* run on the context's own stream and synchronise
+                                         before returning); use a second context for concurrent streams. */
 typedef void* nb_stream;              /* cudaStream_t */
 
 /* Same layout as nbody::ParticleData (include/nbody/types.hpp:234-276): 13 float* then count,
@@ -76,7 +80,15 @@ int nb_stream_create(nb_context* ctx, nb_stream* out);
 int nb_stream_destroy(nb_context* ctx, nb_stream s);
 int nb_graph_begin_capture(nb_context* ctx, nb_stream s);
 int nb_graph_end_capture(nb_context* ctx, nb_stream s, nb_graph** out);
+/* A captured step holds raw pointers into context-owned scratch (packed sources, partials, tree and sort
+ * buffers).  Any later call on the context that needs MORE scratch (a renderer frame with more fragments, a
+ * second system with more bodies) reallocates it; nb_graph_launch then refuses with NB_ERR_STALE_GRAPH instead
+ * of replaying on freed memory, and nb_graph_is_stale says so beforehand: run one eager step and re-capture.
+ * nb_graph_launch and nb_synchronize also report device-side failures flagged by earlier (replayed) work:
+ * Barnes-Hut traversal stack overflow, sort look-back timeout, multi-GPU exchange timeout. */
 int nb_graph_launch(nb_graph* g, nb_stream s);
+int nb_graph_is_stale(const nb_graph* g);
+uint64_t nb_scratch_generation(const nb_context* ctx);
 int nb_graph_node_count(const nb_graph* g, size_t* nodes);
 int nb_graph_destroy(nb_graph* g);
 
@@ -85,6 +97,19 @@ int nb_graph_destroy(nb_graph* g);
  * summed kernel milliseconds and launch count since the last read, and resets them. */
 int nb_profile_enable(nb_context* ctx, int on);
 int nb_profile_read(nb_context* ctx, double* kernel_ms, uint64_t* kernel_launches);
+/* per-stage device timing (bench.py `paths`): with on != 0 every stage of a path (bbox, morton, sort, tree,
+ * traversal, assign, ranges, ...) is bracketed by CUDA events on the launching stream.
+ * nb_profile_stages_read synchronises, writes one line "name total_ms launches\n" per stage seen since the
+ * last read (first-seen order) into buf, and resets.  Not capturable into a graph. */
+int nb_profile_stages_enable(nb_context* ctx, int on);
+int nb_profile_stages_read(nb_context* ctx, char* buf, size_t cap);
+/* device bytes held by the library's own scratch buffers (packed sources, partials, tree, grid, sort and
+ * renderer buffers) in this process; the caller's 13 particle arrays are not counted */
+size_t nb_scratch_bytes(const nb_context* ctx);
+/* FP32 pipe rate of this device, measured now: independent chains of scalar FFMA (packed = 0) or packed
+ * fma.rn.f32x2 (packed = 1) for a few tens of milliseconds, CUDA events on stream s; TFLOP/s with 2 flop per
+ * FMA lane.  bench.py quotes the direct-N^2 kernel against these next to the datasheet figure. */
+int nb_probe_fp32(nb_context* ctx, int packed, double* tflops, double* ms, nb_stream s);
 
 /* ---- ParticleDataManager (src/cuda/particle_init.cu:143-283) ------------------------------ */
 int nb_particles_alloc_device(nb_particles* d, size_t count); /* :143-168, acc/acc_old zeroed   */
@@ -158,6 +183,8 @@ int nb_sh_stats(nb_context* ctx, uint64_t* pairs);
 /* stable LSD radix sort of (u32 key, i32 value) pairs on device; replaces thrust::sort_by_key
  * (src/cuda/force_barnes_hut.cu:276-280).  end_bit <= 32, begin_bit = 0. */
 int nb_sort_pairs(nb_context* ctx, uint32_t* d_keys, int32_t* d_vals, size_t n, int end_bit, nb_stream s);
+/* number of read/write sweeps nb_sort_pairs makes over the pairs for keys of end_bit significant bits */
+int nb_sort_passes(int end_bit);
 /* bbox kernel (src/cuda/force_barnes_hut.cu:218-258); out = 6 host floats; synchronises. */
 int nb_bounding_box(nb_context* ctx, const nb_particles* d, float out[6], nb_stream s);
 

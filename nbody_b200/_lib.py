@@ -31,6 +31,7 @@ class NoDeviceError(RuntimeError):
 
 
 NB_ERR_INVALID, NB_ERR_NO_DEVICE, NB_ERR_RESOURCE, NB_ERR_GRID_TOO_LARGE, NB_ERR_NCCL, NB_ERR_INTERNAL = -1, -2, -3, -4, -5, -6
+NB_ERR_STALE_GRAPH = -7
 
 
 class NbParticles(C.Structure):
@@ -66,6 +67,12 @@ SYMBOLS = {
     "nb_graph_begin_capture": (_i, [_vp, _vp]),
     "nb_graph_end_capture": (_i, [_vp, _vp, C.POINTER(_vp)]),
     "nb_graph_launch": (_i, [_vp, _vp]),
+    "nb_graph_is_stale": (_i, [_vp]),
+    "nb_scratch_generation": (C.c_uint64, [_vp]),
+    "nb_scratch_bytes": (_sz, [_vp]),
+    "nb_probe_fp32": (_i, [_vp, _i, C.POINTER(C.c_double), C.POINTER(C.c_double), _vp]),
+    "nb_profile_stages_enable": (_i, [_vp, _i]),
+    "nb_profile_stages_read": (_i, [_vp, C.c_char_p, _sz]),
     "nb_graph_node_count": (_i, [_vp, C.POINTER(_sz)]),
     "nb_graph_destroy": (_i, [_vp]),
     "nb_profile_enable": (_i, [_vp, _i]),
@@ -98,6 +105,7 @@ SYMBOLS = {
     "nb_render_stats": (_i, [_vp, C.POINTER(C.c_uint64)]),
     "nb_interop_pack": (_i, [_vp, _pp, _vp, _vp, _vp]),
     "nb_sort_pairs": (_i, [_vp, _vp, _vp, _sz, _i, _vp]),
+    "nb_sort_passes": (_i, [_i]),
     "nb_bounding_box": (_i, [_vp, _pp, _vp, _vp]),
     "nb_mgpu_layout": (_i, [_vp, _sz, _i, _i, C.POINTER(_sz), C.POINTER(_sz), C.POINTER(_sz), C.POINTER(_sz)]),
     "nb_mgpu_pack_local": (_i, [_vp, _pp, _vp, _f, _f, _i, _vp]),

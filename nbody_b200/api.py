@@ -748,6 +748,10 @@ class ParticleSystem:
         import torch
         L, ctx = _lib.lib(), get_context()
         key = self._graph_key(dt)
+        # a stale graph (context scratch reallocated since capture, e.g. by a renderer frame with more fragments or
+        # a larger second system) must not be replayed: drop it, run this step eagerly, capture again
+        if self.graph_ and L.nb_graph_is_stale(self.graph_):
+            self._drop_graph()
         if self.graph_ and self.graph_key_ == key:
             check(L.nb_graph_launch(self.graph_, _stream()))
             return

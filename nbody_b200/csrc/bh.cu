@@ -592,24 +592,40 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
     b->super = sg;
   }
   float* misc = b->misc.as<float>();
-  if (int rc = bbox_device(ctx, d, st)) return rc;
-  bh_prepare_kernel<<<1, 32, 0, st>>>(ctx->bbox_dev.as<int>(), misc);
-  NB_LAUNCH_CHECK(ctx);
+  {
+    NB_STAGE(ctx, st, "bh.bbox");
+    if (int rc = bbox_device(ctx, d, st)) return rc;
+    bh_prepare_kernel<<<1, 32, 0, st>>>(ctx->bbox_dev.as<int>(), misc);
+    NB_LAUNCH_CHECK(ctx);
+  }
   const unsigned gn = (unsigned)((n + 255) / 256);
-  bh_morton_kernel<<<gn, 256, 0, st>>>(d->pos_x, d->pos_y, d->pos_z, d->mass, n, misc, b->keys.as<uint32_t>(),
-                                       b->perm.as<int32_t>(), b->packed.as<float4>());
-  NB_LAUNCH_CHECK(ctx);
-  if (int rc = sort_pairs(ctx, b->keys.as<uint32_t>(), b->perm.as<int32_t>(), n, 30, st)) return rc;
+  {
+    NB_STAGE(ctx, st, "bh.morton");
+    bh_morton_kernel<<<gn, 256, 0, st>>>(d->pos_x, d->pos_y, d->pos_z, d->mass, n, misc, b->keys.as<uint32_t>(),
+                                         b->perm.as<int32_t>(), b->packed.as<float4>());
+    NB_LAUNCH_CHECK(ctx);
+  }
+  {
+    NB_STAGE(ctx, st, "bh.sort");
+    if (int rc = sort_pairs(ctx, b->keys.as<uint32_t>(), b->perm.as<int32_t>(), n, 30, st)) return rc;
+  }
   float4* com = b->node_com.as<float4>();
-  bh_gather_kernel<<<gn, 256, 0, st>>>(b->packed.as<float4>(), n, b->perm.as<int32_t>(), com + (n - 1));
-  NB_LAUNCH_CHECK(ctx);
+  {
+    NB_STAGE(ctx, st, "bh.gather");
+    bh_gather_kernel<<<gn, 256, 0, st>>>(b->packed.as<float4>(), n, b->perm.as<int32_t>(), com + (n - 1));
+    NB_LAUNCH_CHECK(ctx);
+  }
   NB_CUDA(cudaMemsetAsync(b->parent.p, 0xff, sizeof(int32_t), st));  // parent[0] = -1 (also when n == 1)
   if (n > 1) {
-    NB_CUDA(cudaMemsetAsync(b->flags.p, 0, (n - 1) * 4, st));
-    const unsigned gi = (unsigned)((n - 1 + 255) / 256);
-    bh_karras_kernel<<<gi, 256, 0, st>>>(b->keys.as<uint32_t>(), (int)n, b->meta.as<int4>(), b->parent.as<int32_t>(),
-                                         b->range.as<int2>());
-    NB_LAUNCH_CHECK(ctx);
+    {
+      NB_STAGE(ctx, st, "bh.karras");
+      NB_CUDA(cudaMemsetAsync(b->flags.p, 0, (n - 1) * 4, st));
+      const unsigned gi = (unsigned)((n - 1 + 255) / 256);
+      bh_karras_kernel<<<gi, 256, 0, st>>>(b->keys.as<uint32_t>(), (int)n, b->meta.as<int4>(),
+                                           b->parent.as<int32_t>(), b->range.as<int2>());
+      NB_LAUNCH_CHECK(ctx);
+    }
+    NB_STAGE(ctx, st, "bh.com");
     if (getenv("NB_BH_COM_GLOBAL"))  // the all-global version, kept for A/B
       bh_com_kernel<<<gn, 256, 0, st>>>((int)n, b->meta.as<int4>(), b->parent.as<int32_t>(), b->flags.as<int>(), com);
     else
@@ -617,9 +633,12 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
           (int)n, b->meta.as<int4>(), b->parent.as<int32_t>(), b->range.as<int2>(), b->flags.as<int>(), com);
     NB_LAUNCH_CHECK(ctx);
   }
-  bh_groups_kernel<<<gn, 256, 0, st>>>((int)n, b->super, b->group, b->parent.as<int32_t>(), b->range.as<int2>(),
-                                       b->groups.as<int2>(), reinterpret_cast<int*>(misc) + 44);
-  NB_LAUNCH_CHECK(ctx);
+  {
+    NB_STAGE(ctx, st, "bh.groups");
+    bh_groups_kernel<<<gn, 256, 0, st>>>((int)n, b->super, b->group, b->parent.as<int32_t>(), b->range.as<int2>(),
+                                         b->groups.as<int2>(), reinterpret_cast<int*>(misc) + 44);
+    NB_LAUNCH_CHECK(ctx);
+  }
   b->built = true;
   return NB_OK;
 }
@@ -632,6 +651,9 @@ static int bh_check_overflow(BH* b) {
   }
   return NB_OK;
 }
+
+// host-visible error state of launches that have already run (graph replays included): c_api.cu polls it
+int bh_poll_error(nb_context* ctx) { return ctx->bh ? bh_check_overflow(ctx->bh) : NB_OK; }
 
 int bh_forces(nb_context* ctx, const nb_particles* d, float theta, float G, float eps, cudaStream_t st,
               const BhShard* shard) {
@@ -671,6 +693,7 @@ int bh_forces(nb_context* ctx, const nb_particles* d, float theta, float G, floa
   long long cap = (long long)b->occ * ctx->sm_count;
   const unsigned grid = (unsigned)(want < cap ? want : cap);
   ProfScope prof(ctx, st);
+  NB_STAGE(ctx, st, "bh.traversal");
   BhShard none{};
   const BhShard shv = shard ? *shard : none;
 #define NB_BH_LAUNCH_S(BPL_, E_, S_)                                                                               \

@@ -1,9 +1,12 @@
 // c_api.cu -- the extern "C" boundary declared in include/nbody_b200.h: context, error plumbing,
 // ParticleDataManager equivalents, and the direct / integrator / host-buffer / multi-GPU entry
 // points.  Barnes-Hut, spatial hash, sort and bbox entry points live next to their kernels.
+#include <atomic>
 #include <cstdarg>
 #include <cstring>
+#include <map>
 #include <new>
+#include <string>
 
 #include "common.cuh"
 
@@ -24,10 +27,18 @@ int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
   return (int)e;
 }
 
+// Every reallocation of a live scratch buffer invalidates the pointers baked into captured graphs: a
+// process-wide generation counter, compared by nb_graph_launch against the value at capture time.
+static std::atomic<uint64_t> g_scratch_generation{0};
+uint64_t scratch_generation() { return g_scratch_generation.load(std::memory_order_relaxed); }
+static std::atomic<size_t> g_scratch_bytes{0};  // live DevBuf bytes of this process (nb_scratch_bytes)
+
 int DevBuf::ensure(size_t bytes) {
   if (bytes <= cap) return NB_OK;
   if (p) {
+    g_scratch_generation.fetch_add(1, std::memory_order_relaxed);
     cudaError_t e = cudaFree(p);
+    g_scratch_bytes.fetch_sub(cap, std::memory_order_relaxed);
     p = nullptr;
     cap = 0;
     if (e != cudaSuccess) return cuda_fail(e, "cudaFree", __FILE__, __LINE__);
@@ -41,11 +52,16 @@ int DevBuf::ensure(size_t bytes) {
     return NB_ERR_RESOURCE;
   }
   cap = want;
+  g_scratch_bytes.fetch_add(cap, std::memory_order_relaxed);
   return NB_OK;
 }
 
 void DevBuf::release() {
-  if (p) cudaFree(p);
+  if (p) {
+    g_scratch_generation.fetch_add(1, std::memory_order_relaxed);
+    g_scratch_bytes.fetch_sub(cap, std::memory_order_relaxed);
+    cudaFree(p);
+  }
   p = nullptr;
   cap = 0;
 }
@@ -71,6 +87,17 @@ ProfScope::~ProfScope() {
   cudaEventRecord(e1, st);
   ctx->prof_ev.emplace_back(e0, e1);
 }
+StageScope::StageScope(nb_context* c, cudaStream_t s, const char* n) : ctx(c), st(s), name(n) {
+  if (!ctx->prof_stages || ctx->stage_ev.size() >= 262144) return;
+  e0 = prof_get_event(ctx);
+  e1 = prof_get_event(ctx);
+  cudaEventRecord(e0, st);
+}
+StageScope::~StageScope() {
+  if (!e0) return;
+  cudaEventRecord(e1, st);
+  ctx->stage_ev.push_back({name, e0, e1});
+}
 
 // implemented in the kernel files
 int direct_run(nb_context* ctx, const nb_particles* d, float dt, float G, float eps2, bool step, cudaStream_t st);
@@ -81,6 +108,11 @@ int kinetic_energy(nb_context* ctx, const nb_particles* d, double* ke, cudaStrea
 int potential_energy(nb_context* ctx, const nb_particles* d, float G, float eps, double* pe, cudaStream_t st);
 int moments(nb_context* ctx, const nb_particles* d, double* out11, cudaStream_t st);
 void bh_destroy(nb_context* ctx);
+int bh_poll_error(nb_context* ctx);
+int peer_poll_error(nb_context* ctx);
+int sort_poll_error(nb_context* ctx);
+int sort_init_device(nb_context* ctx);
+void sort_destroy(nb_context* ctx);
 void sh_destroy(nb_context* ctx);
 void render_destroy(nb_context* ctx);
 
@@ -179,6 +211,11 @@ int nb_context_create(int device, size_t max_bodies_hint, nb_context** out) {
     delete ctx;
     return NB_ERR_RESOURCE;
   }
+  if (int rc = sort_init_device(ctx)) {  // per-device kernel attributes, set once here (not lazily from a sort)
+    ctx->direct_work.release();
+    delete ctx;
+    return rc;
+  }
   *out = ctx;
   return NB_OK;
 }
@@ -192,6 +229,7 @@ int nb_context_destroy(nb_context* ctx) {
   render_destroy(ctx);
   bh_destroy(ctx);
   sh_destroy(ctx);
+  sort_destroy(ctx);
   ctx->src.release();
   ctx->partial.release();
   ctx->direct_work.release();
@@ -239,10 +277,68 @@ int nb_profile_read(nb_context* ctx, double* kernel_ms, uint64_t* kernel_launche
   return NB_OK;
 }
 
+int nb_profile_stages_enable(nb_context* ctx, int on) {
+  NB_ENTER(ctx);
+  ctx->prof_stages = on != 0;
+  return NB_OK;
+}
+
+int nb_profile_stages_read(nb_context* ctx, char* buf, size_t cap) {
+  NB_ENTER(ctx);
+  if (!buf || cap == 0) {
+    set_error("stage profile: null buffer");
+    return NB_ERR_INVALID;
+  }
+  std::vector<std::string> order;
+  std::map<std::string, std::pair<double, uint64_t>> sum;
+  for (auto& r : ctx->stage_ev) {
+    NB_CUDA(cudaEventSynchronize(r.e1));
+    float ms = 0.f;
+    NB_CUDA(cudaEventElapsedTime(&ms, r.e0, r.e1));
+    auto it = sum.find(r.name);
+    if (it == sum.end()) {
+      order.push_back(r.name);
+      sum[r.name] = {ms, 1};
+    } else {
+      it->second.first += ms;
+      it->second.second += 1;
+    }
+    ctx->prof_pool.push_back(r.e0);
+    ctx->prof_pool.push_back(r.e1);
+  }
+  ctx->stage_ev.clear();
+  std::string out;
+  char line[160];
+  for (auto& nme : order) {
+    snprintf(line, sizeof line, "%s %.6f %llu\n", nme.c_str(), sum[nme].first, (unsigned long long)sum[nme].second);
+    out += line;
+  }
+  if (out.size() + 1 > cap) {
+    set_error("stage profile: buffer too small (%zu bytes needed)", out.size() + 1);
+    return NB_ERR_INVALID;
+  }
+  memcpy(buf, out.c_str(), out.size() + 1);
+  return NB_OK;
+}
+
+size_t nb_scratch_bytes(const nb_context* ctx) {
+  (void)ctx;
+  return g_scratch_bytes.load(std::memory_order_relaxed);
+}
+
+uint64_t nb_scratch_generation(const nb_context* ctx) {
+  (void)ctx;
+  return scratch_generation();
+}
+
 int nb_synchronize(nb_context* ctx, nb_stream stream) {
   NB_ENTER(ctx);
   NB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
-  return NB_OK;
+  // device-side failures of work that has now finished (eager or replayed from a graph): Barnes-Hut traversal
+  // stack overflow, radix-sort look-back timeout, multi-GPU exchange timeout
+  if (int rc = bh_poll_error(ctx)) return rc;
+  if (int rc = sort_poll_error(ctx)) return rc;
+  return peer_poll_error(ctx);
 }
 
 // ---- CUDA graphs: the steady-state step as one replayable launch -----------------------------------
@@ -256,6 +352,8 @@ struct nb_graph {
   cudaGraph_t graph = nullptr;
   cudaGraphExec_t exec = nullptr;
   int device = 0;
+  nb_context* ctx = nullptr;
+  uint64_t generation = 0;  // scratch generation the captured launches' pointers belong to
 };
 
 // raw device buffers for host code without CUDA headers (the renderer's framebuffer)
@@ -328,10 +426,11 @@ int nb_graph_begin_capture(nb_context* ctx, nb_stream s) {
     set_error("graph capture needs a non-default stream (nb_stream_create)");
     return NB_ERR_INVALID;
   }
-  if (ctx->prof) {
-    set_error("graph capture with nb_profile_enable on is not supported");
+  if (ctx->prof || ctx->prof_stages) {
+    set_error("graph capture with nb_profile_enable / nb_profile_stages_enable on is not supported");
     return NB_ERR_INVALID;
   }
+  ctx->capture_generation = scratch_generation();
   NB_CUDA(cudaStreamBeginCapture((cudaStream_t)s, cudaStreamCaptureModeThreadLocal));
   return NB_OK;
 }
@@ -344,6 +443,12 @@ int nb_graph_end_capture(nb_context* ctx, nb_stream s, nb_graph** out) {
   }
   cudaGraph_t g = nullptr;
   NB_CUDA(cudaStreamEndCapture((cudaStream_t)s, &g));
+  if (scratch_generation() != ctx->capture_generation) {
+    // a scratch buffer grew while the step was being captured: earlier nodes hold the freed pointer
+    cudaGraphDestroy(g);
+    set_error("graph capture: scratch was reallocated during capture (run one eager step first)");
+    return NB_ERR_INVALID;
+  }
   cudaGraphExec_t e = nullptr;
   cudaError_t err = cudaGraphInstantiate(&e, g, 0);
   if (err != cudaSuccess) {
@@ -360,6 +465,8 @@ int nb_graph_end_capture(nb_context* ctx, nb_stream s, nb_graph** out) {
   h->graph = g;
   h->exec = e;
   h->device = ctx->device;
+  h->ctx = ctx;
+  h->generation = ctx->capture_generation;
   *out = h;
   return NB_OK;
 }
@@ -369,10 +476,22 @@ int nb_graph_launch(nb_graph* g, nb_stream s) {
     set_error("graph launch: null graph");
     return NB_ERR_INVALID;
   }
+  if (g->generation != scratch_generation()) {
+    // context scratch (sort buffers, partials, tree arrays ...) was reallocated by another user of the context
+    // after the capture: the graph's kernels would read and write freed memory
+    set_error("graph launch: stale graph (context scratch was reallocated since capture); re-capture");
+    return NB_ERR_STALE_GRAPH;
+  }
   NB_CUDA(cudaSetDevice(g->device));
+  // a replay runs no host-side checks of its own: report what earlier replays flagged (host-mapped flags)
+  if (int rc = bh_poll_error(g->ctx)) return rc;
+  if (int rc = sort_poll_error(g->ctx)) return rc;
+  if (int rc = peer_poll_error(g->ctx)) return rc;
   NB_CUDA(cudaGraphLaunch(g->exec, (cudaStream_t)s));
   return NB_OK;
 }
+
+int nb_graph_is_stale(const nb_graph* g) { return (!g || g->generation != scratch_generation()) ? 1 : 0; }
 
 int nb_graph_node_count(const nb_graph* g, size_t* nodes) {
   if (!g || !g->graph || !nodes) {
@@ -421,7 +540,17 @@ int nb_particles_alloc_device(nb_particles* d, size_t count) {
       return NB_ERR_RESOURCE;
     }
   }
-  for (int k = 6; k < 12; k++) NB_CUDA(cudaMemset(*f[k], 0, bytes));  // acc, acc_old (particle_init.cu:161-167)
+  for (int k = 6; k < 12; k++) {  // acc, acc_old (particle_init.cu:161-167)
+    cudaError_t e = cudaMemset(*f[k], 0, bytes);
+    if (e != cudaSuccess) {
+      for (int j = 0; j < 13; j++) {
+        cudaFree(*f[j]);
+        *f[j] = nullptr;
+      }
+      d->count = 0;
+      return cuda_fail(e, "cudaMemset", __FILE__, __LINE__);
+    }
+  }
   return NB_OK;
 }
 

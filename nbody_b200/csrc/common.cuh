@@ -14,6 +14,7 @@ namespace nb {
 
 // ---- error plumbing -----------------------------------------------------------------------
 void set_error(const char* fmt, ...);
+uint64_t scratch_generation();  // counts reallocations of live scratch buffers (stale-graph detection)
 int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
 
 #define NB_CUDA(call)                                                       \
@@ -142,7 +143,24 @@ struct ProfScope {
   ProfScope(nb_context* c, cudaStream_t s);
   ~ProfScope();
 };
+// Named stage timer (nb_profile_stages_enable): CUDA events on the launching stream around one stage of a
+// path (bbox, morton, sort, ...); bench.py's `paths` block reads the per-stage sums.  Off: no events, no cost.
+struct StageScope {
+  nb_context* ctx;
+  cudaStream_t st;
+  const char* name;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  StageScope(nb_context* c, cudaStream_t s, const char* n);
+  ~StageScope();
+};
+struct StageRec {
+  const char* name;
+  cudaEvent_t e0, e1;
+};
 }  // namespace nb
+#define NB_STAGE_CAT2_(a, b) a##b
+#define NB_STAGE_CAT_(a, b) NB_STAGE_CAT2_(a, b)
+#define NB_STAGE(ctx, st, name) nb::StageScope NB_STAGE_CAT_(nb_stage_scope_, __LINE__)(ctx, st, name)
 
 // One pass of the direct kernel (see direct.cu): n_itiles target tiles x UJ source tiles, cut into
 // `chunks` = n_itiles * C chunks that G CTAs claim dynamically; chunk c writes partial slot slot_base + c.
@@ -164,6 +182,9 @@ struct nb_context {
   bool prof = false;  // nb_profile_enable
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_ev;
   std::vector<cudaEvent_t> prof_pool;
+  bool prof_stages = false;  // nb_profile_stages_enable
+  std::vector<nb::StageRec> stage_ev;
+  uint64_t capture_generation = 0;  // scratch generation (c_api.cu) when the running stream capture began
   // direct N^2
   nb::DevBuf src;       // packed float4 (x,y,z,G*m), tile padded
   nb::DevBuf partial;   // per-chunk partial accelerations
@@ -186,6 +207,8 @@ struct nb_context {
   struct RenderState* render = nullptr;
   // radix sort scratch
   nb::DevBuf sort_keys2, sort_vals2, sort_hist;
+  int* h_sort_err = nullptr;  // host-mapped: a look-back wait gave up (sort.cu)
+  int* d_sort_err = nullptr;
   // bbox scratch (6 ordered ints) + pinned readback
   nb::DevBuf bbox_dev;
   float* h_bbox = nullptr;

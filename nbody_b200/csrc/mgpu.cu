@@ -120,6 +120,21 @@ struct PeerState {
 };
 static const size_t kFlagBytes = 4096;
 
+extern "C++" {
+namespace nb {
+// a peer's slice / accelerations did not arrive (peer_flags_wait_kernel gave up): polled by c_api.cu after
+// synchronisation and before graph replays, so the failure is reported by the call that observes it
+int peer_poll_error(nb_context* ctx) {
+  for (PeerState* ps : {ctx->peer, ctx->peer_bh})
+    if (ps && ps->h_timeout && *ps->h_timeout) {
+      set_error("multi-GPU exchange: a peer's data did not arrive within 20 s (peer process gone?)");
+      return NB_ERR_INTERNAL;
+    }
+  return NB_OK;
+}
+}  // namespace nb
+}  // extern "C++"
+
 static int peer_block_close(nb_context* ctx, PeerState*& slot) {
   if (!slot) return NB_OK;
   PeerState* ps = slot;

@@ -319,9 +319,12 @@ int sh_build(nb_context* ctx, const nb_particles* d, float cell, cudaStream_t st
   if (int rc = s->misc.ensure(sizeof(SHMisc))) return rc;
   if (!s->h_misc) NB_CUDA(cudaMallocHost(&s->h_misc, sizeof(SHMisc)));
   SHMisc* misc = s->misc.as<SHMisc>();
-  if (int rc = bbox_device(ctx, d, st)) return rc;
-  sh_prepare_kernel<<<1, 32, 0, st>>>(ctx->bbox_dev.as<int>(), cell, misc);
-  NB_LAUNCH_CHECK(ctx);
+  {
+    NB_STAGE(ctx, st, "sh.bbox");
+    if (int rc = bbox_device(ctx, d, st)) return rc;
+    sh_prepare_kernel<<<1, 32, 0, st>>>(ctx->bbox_dev.as<int>(), cell, misc);
+    NB_LAUNCH_CHECK(ctx);
+  }
   // the grid size decides the allocation: one small readback (the reference does 12 here)
   NB_CUDA(cudaMemcpyAsync(s->h_misc, misc, sizeof(SHMisc), cudaMemcpyDeviceToHost, st));
   NB_CUDA(cudaStreamSynchronize(st));
@@ -335,17 +338,27 @@ int sh_build(nb_context* ctx, const nb_particles* d, float cell, cudaStream_t st
   if (int rc = s->cell_start.ensure((size_t)s->total_cells * 4)) return rc;
   if (int rc = s->cell_end.ensure((size_t)s->total_cells * 4)) return rc;
   const unsigned gn = (unsigned)((n + 255) / 256);
-  sh_assign_kernel<<<gn, 256, 0, st>>>(d->pos_x, d->pos_y, d->pos_z, d->mass, n, cell, misc,
-                                       s->particle_cell.as<int32_t>(), s->keys.as<uint32_t>(),
-                                       s->sorted_idx.as<int32_t>(), s->packed.as<float4>());
-  NB_LAUNCH_CHECK(ctx);
+  {
+    NB_STAGE(ctx, st, "sh.assign");
+    sh_assign_kernel<<<gn, 256, 0, st>>>(d->pos_x, d->pos_y, d->pos_z, d->mass, n, cell, misc,
+                                         s->particle_cell.as<int32_t>(), s->keys.as<uint32_t>(),
+                                         s->sorted_idx.as<int32_t>(), s->packed.as<float4>());
+    NB_LAUNCH_CHECK(ctx);
+  }
   int bits = 1;
   while (bits < 32 && (1ll << bits) < (long long)s->total_cells) bits++;
-  if (int rc = sort_pairs(ctx, s->keys.as<uint32_t>(), s->sorted_idx.as<int32_t>(), n, bits, st)) return rc;
-  sh_ranges_gather_kernel<<<(unsigned)((n + 1 + 255) / 256), 256, 0, st>>>(
-      s->keys.as<uint32_t>(), n, s->total_cells, s->cell_start.as<int32_t>(), s->cell_end.as<int32_t>(),
-      s->sorted_idx.as<int32_t>(), s->packed.as<float4>(), s->spos.as<float4>());
-  NB_LAUNCH_CHECK(ctx);
+  {
+    NB_STAGE(ctx, st, "sh.sort");
+    if (int rc = sort_pairs(ctx, s->keys.as<uint32_t>(), s->sorted_idx.as<int32_t>(), n, bits, st)) return rc;
+  }
+  {
+    NB_STAGE(ctx, st, "sh.ranges_gather");
+    sh_ranges_gather_kernel<<<(unsigned)((n + 1 + 255) / 256), 256, 0, st>>>(
+        s->keys.as<uint32_t>(), n, s->total_cells, s->cell_start.as<int32_t>(), s->cell_end.as<int32_t>(),
+        s->sorted_idx.as<int32_t>(), s->packed.as<float4>(), s->spos.as<float4>());
+    NB_LAUNCH_CHECK(ctx);
+  }
+  NB_STAGE(ctx, st, "sh.pair_list");
   const int ntiles = (int)((n + SH_TILE - 1) / SH_TILE);
   unsigned long long* tile_sum = s->tile_sum.as<unsigned long long>();
   sh_pair_sums_kernel<<<ntiles, 256, 0, st>>>(s->keys.as<uint32_t>(), s->cell_start.as<int32_t>(), n, tile_sum);
@@ -374,6 +387,7 @@ int sh_forces(nb_context* ctx, const nb_particles* d, float cutoff, float G, flo
   NB_CUDA(cudaMemsetAsync(&misc->pairs, 0, sizeof(unsigned long long), st));
   const float eps2 = eps * eps;
   ProfScope prof(ctx, st);
+  NB_STAGE(ctx, st, "sh.force");
   // pairs = sum over cells of ceil(count / 2) <= (n + non-empty cells) / 2; threads past the device-side count exit
   size_t nonempty_bound = n;
   if ((size_t)s->total_cells < nonempty_bound) nonempty_bound = (size_t)s->total_cells;

@@ -1,10 +1,12 @@
 // sort.cu -- bounding box reduction and a CUB-free stable LSD radix sort of (u32 key, i32 value)
 // pairs.  Replaces computeBoundingBoxKernel + its 6 malloc / 12 memcpy wrapper
 // (reference src/cuda/force_barnes_hut.cu:66-110, 218-258) and thrust::sort_by_key (:276-280).
-// Both are HBM-bound: bbox reads 12 B/body; the sort reads the keys once for all digit histograms
-// and then moves 16 B/pair per 8-bit pass.
+// Both are HBM-side kernels: bbox reads 12 B/body; the sort reads the keys once for all digit histograms
+// and then moves 16 B/pair per pass, with digits of up to 11 bits (3 passes for 30-bit Morton keys, 2 for
+// the 20/21-bit cell ids of the spatial hash and the renderer's pixel ids).
 #include <cstdlib>
 #include <cstring>
+#include <type_traits>
 
 #include "common.cuh"
 
@@ -93,38 +95,72 @@ int bbox_to_host(nb_context* ctx, float out[6], cudaStream_t st) {
   return NB_OK;
 }
 
-// ---- radix sort ("onesweep": one histogram read + one read/write sweep per 8-bit digit) ---------------
-// Stable LSD.  rs_hist_all reads the keys once and builds the digit histograms of every pass.  Each
-// pass is ONE kernel: a block takes the next 4096/8192-key tile (ticket order), ranks its keys per
-// digit (each warp owns 512 consecutive keys and ranks them 32 at a time with __match_any_sync, so
-// equal digits keep input order), publishes its per-digit counts and resolves the counts of all
-// earlier tiles by decoupled look-back over a per-tile status word (2 flag bits + 30-bit count, one
-// thread per digit), then moves keys and values through shared memory in digit order so that every
-// global store is a run of consecutive addresses.  Algorithmic traffic: 4 + 16 x passes B/pair
-// (68 B for 30-bit Morton keys) against 80 B for the histogram/scan/scatter-per-pass design it replaces.
+// ---- radix sort ("onesweep": one histogram read + one read/write sweep per digit of up to 11 bits) ------
+// Stable LSD.  rs_hist_kernel reads the keys once and builds the digit histograms of every pass,
+// rs_scan_kernel turns them into global digit offsets.  Each pass is ONE kernel: a block takes the next
+// 8192-key tile (ticket order), ranks its keys per digit -- each warp owns 512 consecutive keys and ranks
+// them 32 at a time: peers (lanes with the same digit) come from one ballot per digit bit, the lowest
+// peer adds the group size to the warp's digit counter with one shared-memory atomic and hands the old
+// value to its peers by shuffle, so equal digits keep input order -- publishes its per-digit counts and
+// resolves the counts of all earlier tiles by decoupled look-back over a per-tile status word (2 flag bits
+// + 30-bit count), then moves keys and values through shared memory in digit order so that global stores
+// are runs of consecutive addresses.
+//
+// Round 1 used 8-bit digits (4 passes for 30 bits, 0.60 ms for 16 Mi pairs = 29 % of the measured HBM
+// bandwidth) and was bound by integer issue, not by DRAM (ncu: ALU pipe 58 %, DRAM 18 %): most of the
+// ~140 thread-instructions per key and pass are per-pass work (loads, slot computation, two trips
+// through shared memory, 64-bit addressing), only ~4 per digit BIT are ranking.  So: fewer, wider passes
+// (the ranking cost per key bit stays, everything else drops by the pass count), per-warp digit counters
+// packed two to a 32-bit word (a warp holds 512 keys, a count fits 16 bits) and aliased with the
+// digit-ordered staging buffer, which keeps two 512-thread CTAs resident per SM with 2048 bins, and 32-bit
+// index arithmetic inside a tile.  Algorithmic traffic: 4 + 16 x passes B/pair (52 B for 30-bit keys); a
+// sort whose values are the identity permutation (tree and grid builds) generates them in the first pass
+// instead of reading them (-4 B), and internal callers take the result from whichever buffer the last pass
+// wrote (no copy back; nb_sort_pairs, which sorts in place, copies after an odd number of passes).
 constexpr int RS_ITEMS = 16;
-constexpr int RS_WARP_KEYS = RS_ITEMS * 32;  // 512 consecutive keys per warp
+constexpr int RS_WARPS = 16;
+constexpr int RS_THREADS = RS_WARPS * 32;
+constexpr int RS_WARP_KEYS = RS_ITEMS * 32;      // 512 consecutive keys per warp
+constexpr int RS_TILE = RS_WARPS * RS_WARP_KEYS;  // 8192 keys per tile
 constexpr uint32_t RS_FLAG_AGG = 1u << 30, RS_FLAG_INC = 2u << 30, RS_VAL_MASK = (1u << 30) - 1u;
-constexpr int RS_MAX_PASSES = 4;
+constexpr int RS_MAX_PASSES = 3;   // ceil(32 / 11)
+constexpr int RS_MAX_BITS = 11;
+constexpr int RS_MAX_BINS = 1 << RS_MAX_BITS;
+
+struct RsPlan {
+  int passes;
+  int shift[RS_MAX_PASSES];
+  int bits[RS_MAX_PASSES];
+};
+
+// digits of (almost) equal width, at most 11 bits each, low digit first
+static RsPlan rs_plan(int end_bit) {
+  RsPlan p{};
+  p.passes = (end_bit + RS_MAX_BITS - 1) / RS_MAX_BITS;
+  int done = 0;
+  for (int k = 0; k < p.passes; k++) {
+    const int left = p.passes - k;
+    const int b = (end_bit - done + left - 1) / left;
+    p.shift[k] = done;
+    p.bits[k] = b;
+    done += b;
+  }
+  return p;
+}
 
 // hist[p][d] += number of keys whose pass-p digit is d
-__global__ void __launch_bounds__(512) rs_hist_all_kernel(const uint32_t* __restrict__ keys, size_t n, int passes,
-                                                          int end_bit, uint32_t* __restrict__ hist) {
-  __shared__ uint32_t sh[RS_MAX_PASSES][256];
-  for (int k = threadIdx.x; k < RS_MAX_PASSES * 256; k += blockDim.x) (&sh[0][0])[k] = 0;
+__global__ void __launch_bounds__(512) rs_hist_kernel(const uint32_t* __restrict__ keys, size_t n, RsPlan plan,
+                                                      uint32_t* __restrict__ hist) {
+  extern __shared__ uint32_t rs_hsh[];  // [passes][RS_MAX_BINS]
+  const int total = plan.passes * RS_MAX_BINS;
+  for (int k = threadIdx.x; k < total; k += blockDim.x) rs_hsh[k] = 0;
   __syncthreads();
-  const uint32_t last_mask = (1u << (end_bit - 8 * (passes - 1))) - 1u;
   const size_t n4 = n / 4;
   const uint4* k4 = reinterpret_cast<const uint4*>(keys);
   auto add = [&](uint32_t k) {
 #pragma unroll
-    for (int p = 0; p < RS_MAX_PASSES; p++) {
-      if (p < passes) {
-        uint32_t d = (k >> (8 * p)) & 0xffu;
-        if (p == passes - 1) d &= last_mask;
-        atomicAdd(&sh[p][d], 1u);
-      }
-    }
+    for (int p = 0; p < RS_MAX_PASSES; p++)
+      if (p < plan.passes) atomicAdd(&rs_hsh[p * RS_MAX_BINS + ((k >> plan.shift[p]) & ((1u << plan.bits[p]) - 1u))], 1u);
   };
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
     const uint4 v = k4[i];
@@ -132,194 +168,318 @@ __global__ void __launch_bounds__(512) rs_hist_all_kernel(const uint32_t* __rest
   }
   if (blockIdx.x == 0 && threadIdx.x < (int)(n - n4 * 4)) add(keys[n4 * 4 + threadIdx.x]);
   __syncthreads();
-  for (int k = threadIdx.x; k < passes * 256; k += blockDim.x) {
-    const uint32_t c = (&sh[0][0])[k];
+  for (int k = threadIdx.x; k < total; k += blockDim.x) {
+    const uint32_t c = rs_hsh[k];
     if (c) atomicAdd(&hist[k], c);
   }
 }
 
-__device__ __forceinline__ uint32_t ld_status(const uint32_t* p) {
-  uint32_t v;
-  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_status(uint32_t* p, uint32_t v) {
-  asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+// in place: hist[p][d] -> number of keys whose pass-p digit is < d.  One block per pass, 2 bins per thread.
+__global__ void __launch_bounds__(RS_MAX_BINS / 2) rs_scan_kernel(uint32_t* __restrict__ hist) {
+  __shared__ uint32_t ws[32];
+  uint32_t* h = hist + (size_t)blockIdx.x * RS_MAX_BINS;
+  const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+  const uint32_t a = h[2 * t], b = h[2 * t + 1];
+  uint32_t x = a + b;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+    if (lane >= o) x += y;
+  }
+  if (lane == 31) ws[w] = x;
+  __syncthreads();
+  if (w == 0) {
+    uint32_t v = ws[lane];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t y = __shfl_up_sync(0xffffffffu, v, o);
+      if (lane >= o) v += y;
+    }
+    ws[lane] = v;
+  }
+  __syncthreads();
+  const uint32_t excl = x - (a + b) + (w ? ws[w - 1] : 0u);
+  h[2 * t] = excl;
+  h[2 * t + 1] = excl + a;
 }
 
-// one pass.  status: tiles x 256 words, zeroed; ticket: zeroed; hist: this pass's 256 global digit counts
-template <int WARPS, bool MATCH>
-__global__ void __launch_bounds__(WARPS * 32, 1024 / (WARPS * 32)) rs_onesweep_kernel(const uint32_t* __restrict__ keys_in,
+__device__ __forceinline__ unsigned long long ld_status2(const uint32_t* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_status2(uint32_t* p, uint32_t lo, uint32_t hi) {
+  asm volatile("st.relaxed.gpu.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(lo), "r"(hi) : "memory");
+}
+
+// One pass.  RB: digit capacity of this instantiation (bins = 2^RB sizes the shared memory), `bits` <= RB
+// the digit width of this pass.  gexcl: global exclusive digit offsets; status: tiles x 2^bits words,
+// zeroed; ticket: zeroed.  IDENT: the values are the identity permutation (value = index) and not read.
+template <int RB, bool IDENT>
+__global__ void __launch_bounds__(RS_THREADS, 2) rs_pass_kernel(const uint32_t* __restrict__ keys_in,
                                                                  const int32_t* __restrict__ vals_in,
                                                                  uint32_t* __restrict__ keys_out,
                                                                  int32_t* __restrict__ vals_out, size_t n, int shift,
-                                                                 uint32_t mask, const uint32_t* __restrict__ hist,
+                                                                 int bits, const uint32_t* __restrict__ gexcl,
                                                                  uint32_t* __restrict__ status,
-                                                                 uint32_t* __restrict__ ticket) {
-  constexpr int THREADS = WARPS * 32;
-  constexpr int TILE = WARPS * RS_WARP_KEYS;
-  __shared__ uint32_t cnt[WARPS][256];  // per-warp digit counts, then exclusive offsets across warps
-  __shared__ uint32_t lstart[256];      // first slot of the digit inside the tile's digit-ordered buffer
-  __shared__ uint32_t gbase[256];       // global position of the tile's first key of the digit
-  extern __shared__ __align__(16) uint32_t rs_buf[];  // keys then values of the tile in digit order
-  uint32_t* buf_k = rs_buf;
-  uint32_t* buf_v = rs_buf + TILE;
-  __shared__ uint32_t wsum[8];
+                                                                 uint32_t* __restrict__ ticket,
+                                                                 int* __restrict__ err_flag) {
+  constexpr int BINS = 1 << RB;
+  constexpr int CW = BINS / 2;  // packed counter words per warp: digits 2j (low half) and 2j + 1 (high half)
+  constexpr int CNT_WORDS = RS_WARPS * CW;
+  constexpr int STAGE_WORDS = 2 * RS_TILE;
+  constexpr int UNION_WORDS = CNT_WORDS > STAGE_WORDS ? CNT_WORDS : STAGE_WORDS;
+  extern __shared__ __align__(16) uint32_t rs_sm[];
+  uint32_t* cntw = rs_sm;                 // [RS_WARPS][CW], live until every key knows its slot
+  uint32_t* buf_k = rs_sm;                // then: keys and values of the tile in digit order
+  uint32_t* buf_v = rs_sm + RS_TILE;
+  uint32_t* lstart = rs_sm + UNION_WORDS;  // [BINS] first slot of the digit inside the tile
+  uint32_t* gbase2 = lstart + BINS;        // [BINS] global position of the digit's first key of this tile - lstart
+  __shared__ uint32_t wsum[RS_WARPS];
   __shared__ uint32_t tile_s;
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const uint32_t mask = (1u << bits) - 1u;
   if (tid == 0) tile_s = atomicAdd(ticket, 1u);
-  for (int k = tid; k < WARPS * 256; k += THREADS) (&cnt[0][0])[k] = 0;
+  {
+    uint4* z = reinterpret_cast<uint4*>(cntw);
+    for (int k = tid; k < CNT_WORDS / 4; k += RS_THREADS) z[k] = make_uint4(0u, 0u, 0u, 0u);
+  }
   __syncthreads();
   const uint32_t tile = tile_s;
-  const size_t tbase = (size_t)tile * TILE;
-  const uint32_t tcount = (uint32_t)((n - tbase) < (size_t)TILE ? (n - tbase) : (size_t)TILE);
+  const size_t tbase = (size_t)tile * RS_TILE;
+  const uint32_t tcount = (uint32_t)((n - tbase) < (size_t)RS_TILE ? (n - tbase) : (size_t)RS_TILE);
 
   // ---- load + rank inside the warp's 512 consecutive keys -----------------------------------------
-  // peers = lanes holding the same digit, from 8 independent ballots (pipelined over the 16 keys; the
-  // MATCH instruction serialises over the distinct values in the warp).  The lowest peer adds the
-  // group's size to the warp's digit counter with one shared-memory atomic -- a warp's atomics retire in
-  // issue order, so key k sees the counts of keys < k without any warp synchronisation -- and hands the
-  // old value to its peers by shuffle.
-  const size_t wbase = tbase + (size_t)w * RS_WARP_KEYS;
+  const uint32_t wofs = (uint32_t)w * RS_WARP_KEYS + lane;  // offset of this lane's first key inside the tile
   uint32_t key[RS_ITEMS];
-  uint32_t pos[RS_ITEMS];  // rank among the warp's keys of the same digit
+  uint32_t pos[RS_ITEMS];  // rank among the warp's keys of the same digit; later the key's slot in the tile
   const uint32_t lt = (1u << lane) - 1u;
+  uint32_t* mycnt = cntw + w * CW;
+  const bool full = (uint32_t)w * RS_WARP_KEYS + RS_WARP_KEYS <= tcount;  // warp-uniform
+  {
+    const uint32_t* kin = keys_in + tbase + wofs;
+    if (full) {
 #pragma unroll
-  for (int k = 0; k < RS_ITEMS; k++) {
-    const size_t i = wbase + (size_t)k * 32 + lane;
-    key[k] = (i < n) ? keys_in[i] : 0xffffffffu;
-  }
-  const uint32_t full_valid = (wbase + RS_WARP_KEYS <= n) ? 1u : 0u;
-#pragma unroll
-  for (int k = 0; k < RS_ITEMS; k++) {
-    const size_t i = wbase + (size_t)k * 32 + lane;
-    const bool ok = full_valid || (i < n);
-    const uint32_t dgt = (key[k] >> shift) & mask;
-    uint32_t peers;
-    if (MATCH) {
-      peers = __match_any_sync(0xffffffffu, ok ? dgt : 0x100u);  // padding forms its own group
+      for (int k = 0; k < RS_ITEMS; k++) key[k] = kin[k * 32];
     } else {
-      peers = __ballot_sync(0xffffffffu, ok);  // padding lanes are nobody's peer
 #pragma unroll
-      for (int b = 0; b < 8; b++) {
-        if ((mask >> b) & 1u) {  // warp-uniform: a 6-bit last pass needs 6 ballots
-          const uint32_t v = __ballot_sync(0xffffffffu, (dgt >> b) & 1u);
-          peers &= ((dgt >> b) & 1u) ? v : ~v;
+      for (int k = 0; k < RS_ITEMS; k++) key[k] = (wofs + k * 32 < tcount) ? kin[k * 32] : 0xffffffffu;
+    }
+  }
+  auto rank = [&](auto full_tag) {
+    constexpr bool FULL = decltype(full_tag)::value;
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; k++) {
+      const bool ok = FULL || (wofs + k * 32 < tcount);
+      const uint32_t dgt = (key[k] >> shift) & mask;
+      uint32_t peers = FULL ? 0xffffffffu : __ballot_sync(0xffffffffu, ok);  // padding lanes are nobody's peer
+#pragma unroll
+      for (int b = 0; b < RB; b++) {
+        if (b < bits) {  // warp-uniform
+          const bool bit = (dgt >> b) & 1u;
+          const uint32_t v = __ballot_sync(0xffffffffu, bit);
+          peers &= bit ? v : ~v;
         }
       }
+      const int leader = FULL ? (__ffs(peers) - 1) : max(__ffs(peers) - 1, 0);
+      const uint32_t sh16 = (dgt & 1u) * 16u;
+      uint32_t old = 0;
+      // a warp's shared-memory atomics retire in issue order: key k sees the counts of keys < k
+      if (ok && lane == leader) old = atomicAdd(&mycnt[dgt >> 1], (uint32_t)__popc(peers) << sh16);
+      old = __shfl_sync(0xffffffffu, old, leader);
+      pos[k] = ((old >> sh16) & 0xffffu) + __popc(peers & lt);
     }
-    const int leader = __ffs(peers) - 1;
-    uint32_t before = 0;
-    if (ok && lane == leader) before = atomicAdd(&cnt[w][dgt], (uint32_t)__popc(peers));
-    before = __shfl_sync(0xffffffffu, before, leader < 0 ? 0 : leader);
-    pos[k] = before + __popc(peers & lt);
-  }
+  };
+  if (full) rank(std::true_type{});
+  else rank(std::false_type{});
   __syncthreads();
 
   // ---- per digit: offsets across warps, tile count; publish, look back -----------------------------
-  uint32_t my_total = 0;
-  if (tid < 256) {
+  // thread t owns the packed words [t * WPT, (t + 1) * WPT) = digits [2 t WPT, 2 (t + 1) WPT)
+  constexpr int WPT = (CW + RS_THREADS - 1) / RS_THREADS;
+  const int nwords = (int)((mask + 1u + 1u) >> 1);  // words in use (a 1-bit digit still uses one word)
+  uint32_t tot[WPT];                     // packed tile counts of my words
+  uint32_t mysum = 0;
 #pragma unroll
-    for (int k = 0; k < WARPS; k++) {
-      const uint32_t c = cnt[k][tid];
-      cnt[k][tid] = my_total;
-      my_total += c;
-    }
-    uint32_t* mine = status + (size_t)tile * 256 + tid;
-    if (tile == 0) st_status(mine, RS_FLAG_INC | my_total);
-    else st_status(mine, RS_FLAG_AGG | my_total);
-  }
-  // exclusive scan of the 256 tile counts (slot of each digit in buf) and of the global histogram
-  {
-    uint32_t x = (tid < 256) ? my_total : 0u, g = (tid < 256) ? hist[tid] : 0u;
-    const uint32_t x0 = x, g0 = g;
+  for (int j = 0; j < WPT; j++) {
+    const int wd = tid * WPT + j;
+    uint32_t run = 0;
+    if (wd < nwords) {
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const uint32_t y = __shfl_up_sync(0xffffffffu, x, o), h = __shfl_up_sync(0xffffffffu, g, o);
-      if (lane >= o) { x += y; g += h; }
-    }
-    __shared__ uint32_t gsum[8];
-    if (tid < 256 && lane == 31) { wsum[w] = x; gsum[w] = g; }
-    __syncthreads();
-    if (tid < 256) {
-      uint32_t px = 0, pg = 0;
-      for (int k = 0; k < w; k++) { px += wsum[k]; pg += gsum[k]; }
-      lstart[tid] = px + x - x0;
-      uint32_t excl = 0;  // keys of this digit in earlier tiles
-      if (tile > 0) {
-        const uint32_t* look = status + (size_t)(tile - 1) * 256 + tid;
-        for (;;) {
-          const uint32_t s = ld_status(look);
-          if (s & RS_FLAG_INC) { excl += s & RS_VAL_MASK; break; }
-          if (s & RS_FLAG_AGG) { excl += s & RS_VAL_MASK; look -= 256; }
-        }
-        st_status(status + (size_t)tile * 256 + tid, RS_FLAG_INC | (excl + my_total));
+      for (int k = 0; k < RS_WARPS; k++) {
+        const uint32_t c = cntw[k * CW + wd];
+        cntw[k * CW + wd] = run;  // exclusive over warps; the halves cannot carry (<= 8192 keys per tile)
+        run += c;
       }
-      gbase[tid] = pg + g - g0 + excl;
+    }
+    tot[j] = run;
+    mysum += (run & 0xffffu) + (run >> 16);
+  }
+  uint32_t x = mysum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+    if (lane >= o) x += y;
+  }
+  if (lane == 31) wsum[w] = x;
+  __syncthreads();
+  {
+    uint32_t before = x - mysum;
+    for (int k = 0; k < w; k++) before += wsum[k];
+#pragma unroll
+    for (int j = 0; j < WPT; j++) {
+      const int wd = tid * WPT + j;
+      if (wd < nwords) {
+        const uint32_t t0 = tot[j] & 0xffffu, t1 = tot[j] >> 16;
+        const uint32_t l0 = before, l1 = before + t0;
+        before += t0 + t1;
+        lstart[2 * wd] = l0;
+        lstart[2 * wd + 1] = l1;
+        uint32_t e0 = 0, e1 = 0;  // keys of these digits in earlier tiles
+        uint32_t* mine = status + ((size_t)tile << bits) + 2 * wd;
+        if (bits == 0 || tile == 0) {
+          st_status2(mine, RS_FLAG_INC | t0, RS_FLAG_INC | t1);
+        } else {
+          st_status2(mine, RS_FLAG_AGG | t0, RS_FLAG_AGG | t1);
+          const uint32_t* look = mine - ((size_t)1 << bits);
+          unsigned long long t_start = 0;
+          for (unsigned spins = 1;; spins++) {
+            // both words of a pair are always published together: the flags of the low word decide
+            const unsigned long long s2 = ld_status2(look);
+            const uint32_t s_lo = (uint32_t)s2, s_hi = (uint32_t)(s2 >> 32);
+            if (s_lo & RS_FLAG_INC) {
+              e0 += s_lo & RS_VAL_MASK;
+              e1 += s_hi & RS_VAL_MASK;
+              break;
+            }
+            if (s_lo & RS_FLAG_AGG) {
+              e0 += s_lo & RS_VAL_MASK;
+              e1 += s_hi & RS_VAL_MASK;
+              look -= ((size_t)1 << bits);
+              continue;
+            }
+            if ((spins & 4095u) == 0u) {  // a faulted predecessor must not hang the device: give up after ~2 s
+              unsigned long long now;
+              asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+              if (t_start == 0) t_start = now;
+              else if (now - t_start > 2000000000ull) {
+                *err_flag = 1;
+                break;
+              }
+            }
+          }
+          st_status2(mine, RS_FLAG_INC | (e0 + t0), RS_FLAG_INC | (e1 + t1));
+        }
+        gbase2[2 * wd] = gexcl[2 * wd] + e0 - l0;
+        if (2 * wd + 1 <= (int)mask) gbase2[2 * wd + 1] = gexcl[2 * wd + 1] + e1 - l1;
+      }
     }
   }
-  __syncthreads();
-
-  // ---- registers -> buf (digit order) -> global (runs of consecutive addresses) ---------------------------
+  // every key's slot in the digit-ordered staging buffer (the last use of the per-warp counters)
 #pragma unroll
   for (int k = 0; k < RS_ITEMS; k++) {
-    const size_t i = wbase + (size_t)k * 32 + lane;
     const uint32_t dgt = (key[k] >> shift) & mask;
-    if (i < n) {
-      const uint32_t slot = lstart[dgt] + cnt[w][dgt] + pos[k];
-      buf_k[slot] = key[k];
-      buf_v[slot] = (uint32_t)vals_in[i];
+    pos[k] += ((mycnt[dgt >> 1] >> ((dgt & 1u) * 16u)) & 0xffffu);
+  }
+  __syncthreads();  // lstart complete, counters dead: the staging buffer may overwrite them
+#pragma unroll
+  for (int k = 0; k < RS_ITEMS; k++) pos[k] += lstart[(key[k] >> shift) & mask];
+  // ---- registers -> staging buffer (digit order) -> global (runs of consecutive addresses) -----------
+  if (IDENT) {
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; k++) {
+      if (full || wofs + k * 32 < tcount) {
+        buf_k[pos[k]] = key[k];
+        buf_v[pos[k]] = (uint32_t)(tbase + wofs + k * 32);
+      }
+    }
+  } else {
+    const int32_t* vin = vals_in + tbase + wofs;
+    uint32_t val[RS_ITEMS];
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; k++) val[k] = (full || wofs + k * 32 < tcount) ? (uint32_t)vin[k * 32] : 0u;
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; k++) {
+      if (full || wofs + k * 32 < tcount) {
+        buf_k[pos[k]] = key[k];
+        buf_v[pos[k]] = val[k];
+      }
     }
   }
   __syncthreads();
 #pragma unroll
   for (int k = 0; k < RS_ITEMS; k++) {
-    const uint32_t p = (uint32_t)k * THREADS + tid;
+    const uint32_t p = (uint32_t)k * RS_THREADS + tid;
     if (p < tcount) {
       const uint32_t kk = buf_k[p];
-      const uint32_t dgt = (kk >> shift) & mask;
-      const uint32_t g = gbase[dgt] + (p - lstart[dgt]);
+      const uint32_t g = gbase2[(kk >> shift) & mask] + p;
       keys_out[g] = kk;
       vals_out[g] = (int32_t)buf_v[p];
     }
   }
 }
 
-// sorts in place (result in d_keys/d_vals); bits [0, end_bit) are significant
-int sort_pairs(nb_context* ctx, uint32_t* d_keys, int32_t* d_vals, size_t n, int end_bit, cudaStream_t st) {
-  if (n < 2) return NB_OK;
+template <int RB>
+static constexpr size_t rs_smem_bytes() {
+  constexpr size_t cnt = (size_t)RS_WARPS * ((1 << RB) / 2), stage = 2 * (size_t)RS_TILE;
+  return ((cnt > stage ? cnt : stage) + 2 * ((size_t)1 << RB)) * sizeof(uint32_t);
+}
+
+// per-device kernel attributes (opt-in shared memory), set once when a context is created on the device
+int sort_init_device(nb_context* ctx) {
+  (void)ctx;
+  NB_CUDA(cudaFuncSetAttribute(rs_pass_kernel<8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rs_smem_bytes<8>()));
+  NB_CUDA(cudaFuncSetAttribute(rs_pass_kernel<8, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rs_smem_bytes<8>()));
+  NB_CUDA(cudaFuncSetAttribute(rs_pass_kernel<RS_MAX_BITS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rs_smem_bytes<RS_MAX_BITS>()));
+  NB_CUDA(cudaFuncSetAttribute(rs_pass_kernel<RS_MAX_BITS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rs_smem_bytes<RS_MAX_BITS>()));
+  return NB_OK;
+}
+
+void sort_destroy(nb_context* ctx) {
+  if (ctx->h_sort_err) cudaFreeHost(ctx->h_sort_err);
+  ctx->h_sort_err = nullptr;
+}
+
+int sort_poll_error(nb_context* ctx) {
+  if (ctx->h_sort_err && *ctx->h_sort_err) {
+    *ctx->h_sort_err = 0;
+    set_error("radix sort: a tile waited more than 2 s for its predecessors (device fault?); result invalid");
+    return NB_ERR_INTERNAL;
+  }
+  return NB_OK;
+}
+
+// Sorts (keys, vals) by bits [0, end_bit) of the keys.  The passes ping-pong between the caller's arrays and
+// context scratch; *out_keys / *out_vals say where the result is (no copy).  identity_vals: vals need not be
+// initialised -- the first pass writes value = index.
+int sort_pairs_db(nb_context* ctx, uint32_t* d_keys, int32_t* d_vals, size_t n, int end_bit, bool identity_vals,
+                  uint32_t** out_keys, int32_t** out_vals, cudaStream_t st) {
+  *out_keys = d_keys;
+  *out_vals = d_vals;
   if (end_bit < 1) end_bit = 1;
   if (end_bit > 32) end_bit = 32;
   if (n > (size_t)RS_VAL_MASK) {
     set_error("sort: too many elements");
     return NB_ERR_INVALID;
   }
-  static bool attr_set_dev[64] = {};  // function attributes are per device: a process may hold a context on several
-  bool& attr_set = attr_set_dev[ctx->device & 63];
-  if (!attr_set) {
-    NB_CUDA(cudaFuncSetAttribute(rs_onesweep_kernel<8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * RS_WARP_KEYS * 8));
-    NB_CUDA(cudaFuncSetAttribute(rs_onesweep_kernel<16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16 * RS_WARP_KEYS * 8));
-    NB_CUDA(cudaFuncSetAttribute(rs_onesweep_kernel<8, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * RS_WARP_KEYS * 8));
-    NB_CUDA(cudaFuncSetAttribute(rs_onesweep_kernel<16, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16 * RS_WARP_KEYS * 8));
-    attr_set = true;
+  if (n == 0) return NB_OK;
+  if (!ctx->h_sort_err) {
+    NB_CUDA(cudaHostAlloc(&ctx->h_sort_err, sizeof(int), cudaHostAllocMapped));
+    *ctx->h_sort_err = 0;
+    NB_CUDA(cudaHostGetDevicePointer(&ctx->d_sort_err, ctx->h_sort_err, 0));
   }
-  const char* e = getenv("NB_SORT_WARPS");  // tuning knob: 8 (4096-key tiles) or 16 (8192-key tiles)
-  const int warps_cfg = (e && atoi(e) == 8) ? 8 : 16;
-  const char* me = getenv("NB_SORT_MATCH");  // tuning knob: 1 = MATCH.ANY instruction, 0 = eight ballots
-  const bool use_match = me && atoi(me) == 1;
-  const int warps = warps_cfg;
-  const int tile = warps * RS_WARP_KEYS;
-  const size_t smem = (size_t)tile * 8;
-  const int passes = (end_bit + 7) / 8;
-  const size_t ntiles = (n + tile - 1) / tile;
+  if (int rc = sort_poll_error(ctx)) return rc;
+  const RsPlan plan = rs_plan(end_bit);
+  const size_t ntiles = (n + RS_TILE - 1) / RS_TILE;
   if (int rc = ctx->sort_keys2.ensure(n * sizeof(uint32_t))) return rc;
   if (int rc = ctx->sort_vals2.ensure(n * sizeof(int32_t))) return rc;
-  // scratch: [passes][256] histograms, [passes] tickets (padded to 64 words), [passes][ntiles][256] status
-  const size_t head = (size_t)RS_MAX_PASSES * 256 + 64;
-  const size_t words = head + (size_t)passes * ntiles * 256;
+  // scratch: [passes][2048] histograms, [passes] tickets (padded to 64 words), per pass [ntiles][2^bits] status
+  const size_t head = (size_t)RS_MAX_PASSES * RS_MAX_BINS + 64;
+  size_t words = head;
+  for (int p = 0; p < plan.passes; p++) words += ntiles << plan.bits[p];
   if (int rc = ctx->sort_hist.ensure(words * sizeof(uint32_t))) return rc;
   uint32_t* hist = ctx->sort_hist.as<uint32_t>();
-  uint32_t* ticket = hist + RS_MAX_PASSES * 256;
+  uint32_t* ticket = hist + RS_MAX_PASSES * RS_MAX_BINS;
   uint32_t* status = hist + head;
   NB_CUDA(cudaMemsetAsync(hist, 0, words * sizeof(uint32_t), st));
   {
@@ -327,34 +487,45 @@ int sort_pairs(nb_context* ctx, uint32_t* d_keys, int32_t* d_vals, size_t n, int
     const size_t cap = (size_t)ctx->sm_count * 4;
     if (g > cap) g = cap;
     if (g < 1) g = 1;
-    rs_hist_all_kernel<<<(unsigned)g, 512, 0, st>>>(d_keys, n, passes, end_bit, hist);
+    rs_hist_kernel<<<(unsigned)g, 512, (size_t)plan.passes * RS_MAX_BINS * sizeof(uint32_t), st>>>(d_keys, n, plan, hist);
+    NB_LAUNCH_CHECK(ctx);
+    rs_scan_kernel<<<plan.passes, RS_MAX_BINS / 2, 0, st>>>(hist);
     NB_LAUNCH_CHECK(ctx);
   }
   uint32_t *ka = d_keys, *kb = ctx->sort_keys2.as<uint32_t>();
   int32_t *va = d_vals, *vb = ctx->sort_vals2.as<int32_t>();
-  for (int p = 0; p < passes; p++) {
-    const int shift = p * 8;
-    const int bits = (end_bit - shift) < 8 ? (end_bit - shift) : 8;
-    const uint32_t mask = (1u << bits) - 1u;
-    uint32_t* stp = status + (size_t)p * ntiles * 256;
-#define NB_RS_LAUNCH(W_, M_)                                                                                   \
-  rs_onesweep_kernel<W_, M_><<<(unsigned)ntiles, W_ * 32, smem, st>>>(ka, va, kb, vb, n, shift, mask, hist + p * 256, \
-                                                                      stp, ticket + p)
-    if (warps == 8) {
-      if (use_match) NB_RS_LAUNCH(8, true);
+  for (int p = 0; p < plan.passes; p++) {
+    const bool ident = identity_vals && p == 0;
+#define NB_RS_LAUNCH(RB_, ID_)                                                                                        \
+  rs_pass_kernel<RB_, ID_><<<(unsigned)ntiles, RS_THREADS, rs_smem_bytes<RB_>(), st>>>(                               \
+      ka, va, kb, vb, n, plan.shift[p], plan.bits[p], hist + p * RS_MAX_BINS, status, ticket + p, ctx->d_sort_err)
+    if (plan.bits[p] <= 8) {
+      if (ident) NB_RS_LAUNCH(8, true);
       else NB_RS_LAUNCH(8, false);
     } else {
-      if (use_match) NB_RS_LAUNCH(16, true);
-      else NB_RS_LAUNCH(16, false);
+      if (ident) NB_RS_LAUNCH(RS_MAX_BITS, true);
+      else NB_RS_LAUNCH(RS_MAX_BITS, false);
     }
 #undef NB_RS_LAUNCH
     NB_LAUNCH_CHECK(ctx);
+    status += ntiles << plan.bits[p];
     uint32_t* tk = ka; ka = kb; kb = tk;
     int32_t* tv = va; va = vb; vb = tv;
   }
-  if (ka != d_keys) {
-    NB_CUDA(cudaMemcpyAsync(d_keys, ka, n * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
-    NB_CUDA(cudaMemcpyAsync(d_vals, va, n * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+  *out_keys = ka;
+  *out_vals = va;
+  return NB_OK;
+}
+
+// sorts in place (result in d_keys/d_vals); bits [0, end_bit) are significant
+int sort_pairs(nb_context* ctx, uint32_t* d_keys, int32_t* d_vals, size_t n, int end_bit, cudaStream_t st) {
+  if (n < 2) return NB_OK;
+  uint32_t* ko;
+  int32_t* vo;
+  if (int rc = sort_pairs_db(ctx, d_keys, d_vals, n, end_bit, false, &ko, &vo, st)) return rc;
+  if (ko != d_keys) {
+    NB_CUDA(cudaMemcpyAsync(d_keys, ko, n * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+    NB_CUDA(cudaMemcpyAsync(d_vals, vo, n * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
   }
   return NB_OK;
 }
@@ -372,6 +543,12 @@ int nb_sort_pairs(nb_context* ctx, uint32_t* d_keys, int32_t* d_vals, size_t n, 
   }
   NB_CUDA(cudaSetDevice(ctx->device));
   return sort_pairs(ctx, d_keys, d_vals, n, end_bit, (cudaStream_t)s);
+}
+
+int nb_sort_passes(int end_bit) {
+  if (end_bit < 1) end_bit = 1;
+  if (end_bit > 32) end_bit = 32;
+  return rs_plan(end_bit).passes;
 }
 
 int nb_bounding_box(nb_context* ctx, const nb_particles* d, float out[6], nb_stream s) {
