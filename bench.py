@@ -14,6 +14,17 @@ Integrator::integrate of the reference (src/cuda/integrator.cu:224-238) = N^2 pa
 (nb_host_step_direct / ShardedDirectSystem.host_update): pinned host state in, one step, host state
 out, copies inside the timed region.  The CPU legs (cpu_baseline, --impl reference) run the oracle
 port of the reference's CPU loop (examples/example_force_methods.cpp:44-66) on a bounded sample.
+
+After the timed regions (never inside them) the line also carries
+  parity        every N: max relative error of >= 256 sampled targets per rank of the system that was just timed,
+                against the fp64 oracle over ALL sources (all-reduced MAX); bound 1e-5;
+  exchange_nccl N > 1: the same step with the NCCL all_gather_into_tensor exchange, 3 steps, next to the peer push;
+  t1_4mi        N = 1: the 4 Mi-body workload of configs[2] on ONE GPU, so that strong-scaling efficiency can be
+                stated as T1 / (G * T_G) (SURVEY.md sec. 8(d) config 3);
+  paths         N = 1: configs[3] and [4] -- Barnes-Hut theta = 0.5 at 1 Mi and 16 Mi bodies, spatial hash at 10 M,
+                the radix sort at 16 Mi x 30 bits -- per stage: CUDA-event ms, algorithmic bytes, achieved GB/s and
+                the fraction of the measured HBM bandwidth (tools/bench_paths.py; the reference benchmarks all
+                three methods from one program too, benchmarks/benchmark_main.cpp:170-233).
 """
 from __future__ import annotations
 
@@ -67,6 +78,8 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--bodies", type=int, default=0, help="override the body count (parity/debug only)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-paths", action="store_true", help="skip the Barnes-Hut / spatial-hash / sort / 4 Mi legs")
+    ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--no-reference-gpu", action="store_true")
     return ap.parse_args()
 
@@ -160,6 +173,64 @@ def cpu_sample_rate(state, n_targets: int, reps: int = 1):
                        float(np.float32(SOFTENING) ** 2), 0, n_targets)
     dt = (time.perf_counter() - t0) / reps
     return n_targets * float(n) / dt / 1e9, orc.num_threads(), dt
+
+
+def parity_check(system, state, n, begin, count, rank, world, dist, torch):
+    """Accelerations of the system that was just timed against the fp64 oracle: the CURRENT positions of all bodies
+    (gathered from the ranks), one more force evaluation (collective), >= 256 targets of this rank's slice against
+    ALL sources.  Returns the all-reduced maximum of |a - a_ref| / |a_ref|."""
+    from oracle import bindings as orc
+    keys = ("pos_x", "pos_y", "pos_z")
+    local = {k: system.d.arrays[k].detach().cpu().numpy().copy() for k in keys}
+    if world > 1:
+        parts = [None] * world
+        dist.all_gather_object(parts, local)
+        full = {k: np.concatenate([p[k] for p in parts]) for k in keys}
+    else:
+        full = local
+    assert full["pos_x"].size == n
+    system.compute_forces()
+    torch.cuda.synchronize()
+    acc = {k: system.d.arrays[k].detach().cpu().numpy() for k in ("acc_x", "acc_y", "acc_z")}
+    m = max(256, 1)
+    idx_local = np.unique(np.concatenate([np.linspace(0, count - 1, m).astype(np.int64), [0, count - 1]]))
+    idx = (idx_local + begin).astype(np.int32)
+    orc.set_num_threads(max(1, len(os.sched_getaffinity(0)) // world))
+    ref = orc.direct_f64(full["pos_x"], full["pos_y"], full["pos_z"], state["mass"], G_CONST,
+                         float(np.float32(SOFTENING) ** 2), idx)
+    err = np.sqrt(sum((acc[k][idx_local].astype(np.float64) - r) ** 2 for k, r in zip(("acc_x", "acc_y", "acc_z"), ref)))
+    rel = float((err / np.sqrt(sum(r ** 2 for r in ref))).max())
+    if world > 1:
+        t = torch.tensor([rel], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        rel = float(t.item())
+    return {"max_rel_err": rel, "bound": 1e-5, "ok": bool(rel <= 1e-5), "targets_per_rank": int(idx.size),
+            "sources": n, "oracle": "oracle/direct.c orc_direct_f64 (fp64, all sources), on the positions the timed "
+                                    "steps left behind"}
+
+
+def partial_slots_bytes(ctx, L):
+    """Bytes the library's scratch holds right now (packed sources + per-chunk partials dominate after a direct run)."""
+    try:
+        return int(L.nb_scratch_bytes(ctx.handle))
+    except Exception:
+        return None
+
+
+def direct_traffic(n, world, scratch_bytes):
+    """roofline.traffic: dram__bytes_read.sum + dram__bytes_write.sum of ONE force-kernel launch from the ncu --set
+    full capture of this command, kept in profiles/direct_traffic.json by tools/ncu_summary.py (null when no capture
+    of the current build exists); scratch_bytes is what the library held during THIS run."""
+    out = {"traffic": None, "traffic_unit": "bytes per launch (compute-bound kernel)", "scratch_bytes": scratch_bytes}
+    try:
+        with open(os.path.join(ROOT, "profiles", "direct_traffic.json")) as f:
+            rec = json.load(f)
+        if rec.get("bodies") == n and world == 1:
+            out["traffic"] = rec["dram_bytes_per_launch"]
+            out["traffic_source"] = rec.get("source")
+    except Exception:
+        pass
+    return out
 
 
 def run_reference_arm(args):
@@ -288,8 +359,43 @@ def main():
     h2d = 10 * 4 * count
     d2h = 12 * 4 * count
 
+    # ---- parity of the system that was just timed (after timing): fp64 oracle on sampled targets ------
+    parity = None
+    if not args.no_parity:
+        parity = parity_check(system, state, n, begin, count, rank, world, dist if world > 1 else None, torch)
+
     exchange = system.exchange
+    partial_bytes = partial_slots_bytes(ctx, L)
     system.close()
+
+    # ---- N > 1: the collective north_star names (NCCL all-gather overlapped with the local pass) ------
+    exchange_nccl = None
+    if world > 1 and exchange != "nccl":
+        sys_n = ShardedDirectSystem(slice_state(state, begin, count), n, rank, world, G_CONST, SOFTENING, exchange="nccl")
+        sys_n.compute_forces()
+        sys_n.update(DT)
+        barrier()
+        k3 = 3
+        e0.record()
+        for _ in range(k3):
+            sys_n.update(DT)
+        e1.record()
+        barrier()
+        ms_n = max_over_ranks(e0.elapsed_time(e1)) / k3
+        sys_n.host_update(DT, 1)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(k3):
+            sys_n.host_update(DT, 1)
+        barrier()
+        e2e_n = max_over_ranks((time.perf_counter() - t0) * 1e3) / k3
+        sys_n.close()
+        exchange_nccl = {"ms_per_step": ms_n, "value": interactions_per_step / (ms_n * 1e-3) / 1e9,
+                         "e2e_ms_per_step": e2e_n, "e2e_value": interactions_per_step / (e2e_n * 1e-3) / 1e9,
+                         "unit": "G-interactions/s", "steps": k3,
+                         "what": "same workload, exchange = NCCL all_gather_into_tensor of the packed slices on NCCL's "
+                                 "stream, overlapped with the local-source pass (nbody_b200/dist.py)",
+                         "peer_over_nccl": ms_n / ms_per_step}
 
     # ---- the same bodies through the general pair loop -------------------------------------------
     # The workload's masses are all 1/N (as in every initial condition of the reference), so every full
@@ -314,6 +420,40 @@ def main():
         mixed = {"value": interactions_per_step / (ms2 * 1e-3) / 1e9, "unit": "G-interactions/s", "ms_per_step": ms2,
                  "steps": k2, "what": "same bodies, one mass in every 512 differs in its last bit: general pair loop "
                                       "(3 packed multiplies per pair instead of 2) for every source tile"}
+    t1_4mi, paths, probe = None, None, None
+    if world == 1 and not args.no_paths and not args.bodies:
+        # FP32 pipe rates of THIS device, measured now (replaces constants copied from an earlier capture)
+        probe = {}
+        for name, packed in (("ffma", 0), ("ffma2", 1)):
+            tf, pms = C.c_double(0), C.c_double(0)
+            _lib.check(L.nb_probe_fp32(ctx.handle, packed, C.byref(tf), C.byref(pms), None))
+            probe[name] = {"tflops": tf.value, "ms": pms.value}
+        # configs[2]'s workload on one GPU: T1 of the strong-scaling efficiency
+        n4 = 1 << 22
+        st4 = ics.plummer(n4, seed=42)
+        sys4 = ShardedDirectSystem(st4, n4, 0, 1, G_CONST, SOFTENING)
+        sys4.update(DT)
+        torch.cuda.synchronize()
+        k4 = 2
+        e0.record()
+        for _ in range(k4):
+            sys4.update(DT)
+        e1.record()
+        torch.cuda.synchronize()
+        ms4 = e0.elapsed_time(e1) / k4
+        sys4.close()
+        del sys4, st4
+        t1_4mi = {"ms_per_step": ms4, "value": float(n4) * n4 / (ms4 * 1e-3) / 1e9, "unit": "G-interactions/s",
+                  "steps": k4, "warmup": 1, "bodies": n4, "workload": "direct_n2_4Mi_plummer on ONE GPU",
+                  "what": "T1 for strong-scaling efficiency T1 / (G * T_G) of the N > 1 runs (SURVEY.md 8(d) config 3)"}
+        scratch_direct = int(L.nb_scratch_bytes(ctx.handle))
+        # configs[3], configs[4] and the sort, per stage (tools/bench_paths.py)
+        from tools import bench_paths as bp
+        paths = {"bh_1mi": bp.bench_bh(1 << 20), "bh_16mi": bp.bench_bh(1 << 24), "sh_10m": bp.bench_sh(10_000_000),
+                 "sort_16mi": bp.bench_sort(1 << 24, 30), "sort_10m_21bit": bp.bench_sort(10_000_000, 21),
+                 "scratch_bytes_after_direct_legs": scratch_direct,
+                 "scratch_bytes_after_all_legs": int(L.nb_scratch_bytes(ctx.handle))}
+        torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -335,15 +475,13 @@ def main():
         "frac": (achieved_tf / FP32_PEAK_DATASHEET_TF) if achieved_tf else None,
         "peak_source": "B200 datasheet FP32 (BASELINE.json target denominator); MEASURED_PEAKS.json holds no FP32 figure",
         "peak_clock_derived": clock_peak_tf, "frac_of_clock_peak": (achieved_tf / clock_peak_tf) if achieved_tf else None,
-        "peak_measured_ffma": 71.8, "peak_measured_ffma2": 64.3,
-        "frac_of_measured_ffma2": (achieved_tf / 64.3) if achieved_tf else None,
+        # scalar FFMA / packed FFMA2 rates measured by THIS run (nb_probe_fp32), null when the legs are skipped
+        "peak_measured_ffma": probe["ffma"]["tflops"] if probe else None,
+        "peak_measured_ffma2": probe["ffma2"]["tflops"] if probe else None,
+        "frac_of_measured_ffma2": (achieved_tf / probe["ffma2"]["tflops"]) if (achieved_tf and probe) else None,
         "flop_per_interaction": FLOP_PER_INTERACTION, "kernel_ms": kernel_ms,
         "kernel_share_of_step": (kms.value / args.steps) / ms_per_step if ms_per_step > 0 else None,
-        # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the ncu --set full capture of this
-        # command (profiles/r01_direct_force_1mi_ncu_full_v2.txt): 109.0 MB read (the 16 MiB packed sources + target
-        # tiles) + 428.5 MB written (349 MB of per-chunk partials, 888 CTAs x 64 chunks x 6 KiB, + write-backs)
-        "traffic": 537492736 if (n == (1 << 20) and world == 1) else None,
-        "traffic_unit": "bytes per launch (compute-bound kernel: 4.1e4 flop per DRAM byte)",
+        **direct_traffic(n, world, partial_bytes),
     }
 
     cpu = None
@@ -386,7 +524,8 @@ def main():
         "e2e": {"value": e2e_value, "unit": "G-interactions/s", "ms_per_step": e2e_ms,
                 "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": d2h * world},
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
-        "reference_gpu": ref_gpu, "mixed_mass_path": mixed,
+        "reference_gpu": ref_gpu, "mixed_mass_path": mixed, "parity": parity, "exchange_nccl": exchange_nccl,
+        "t1_4mi": t1_4mi, "paths": paths,
     }
     emit(line)
 

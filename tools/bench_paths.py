@@ -1,6 +1,11 @@
 #!/usr/bin/env python
-"""Per-stage timings of the Barnes-Hut and spatial-hash paths (CUDA events), configs 4 and 5 of
-BASELINE.json.  usage: tools/bench_paths.py bh 1048576 [plummer|sphere]  |  sh 10000000"""
+"""Per-stage timings of the Barnes-Hut, spatial-hash and sort paths (CUDA events), configs 4 and 5 of
+BASELINE.json.  bench.py imports the functions below for its `paths` block; stand-alone:
+  tools/bench_paths.py bh 1048576 [plummer|sphere] | sh 10000000 | sort 16777216 [bits] | energy N | graph N [bh] | render N
+
+Every HBM-side stage is reported with its ALGORITHMIC bytes (what the stage has to move with our layouts,
+DESIGN.md 7.1), the achieved GB/s over its CUDA-event time, and the fraction of the measured copy bandwidth
+(MEASURED_PEAKS.json hbm_gbs, else the B200_PROFILING.md fallback)."""
 import ctypes as C
 import json
 import os
@@ -8,11 +13,34 @@ import sys
 
 import numpy as np
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
 import torch  # noqa: E402
 
 import nbody_b200 as nb  # noqa: E402
 from nbody_b200 import _lib, ics  # noqa: E402
+
+HBM_FALLBACK_GBS = 6400.0  # B200_PROFILING.md: measured copy bandwidth to use when MEASURED_PEAKS.json is absent
+
+# algorithmic bytes per body of each stage, with the layouts of DESIGN.md sec. 2
+ALGO_BYTES = {
+    "bh.bbox": 12,            # x, y, z read once
+    "bh.morton": 16 + 4 + 4 + 16,  # x,y,z,m read; key, identity value and packed {x,y,z,m} written
+    "bh.gather": 4 + 16 + 16, "bh.karras": 4 + 16 + 8 + 8, "bh.com": 76, "bh.groups": 16,  # round-1 kernels
+    "bh.tree": 4 + 4 + 16 + 16 + 32,  # keys + perm read, packed float4 gathered, leaf record + 32-B node record written
+    "sh.bbox": 12,
+    "sh.assign": 16 + 4 + 4 + 4 + 16,  # x,y,z,m read; particle_cell, key, identity value and packed written
+    "sh.ranges_gather": 4 + 4 + 16 + 16,  # sorted key + index read, packed gathered, cell-ordered float4 written (+ cell ranges)
+    "sh.pair_list": 2 * 8 + 4,     # sorted key + cell_start read twice (flag pass, fill pass), pair slot written
+}
+
+
+def hbm_peak_gbs():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs"
+    except Exception:
+        return HBM_FALLBACK_GBS, "B200_PROFILING.md fallback"
 
 
 def timed(fn, reps=5, warm=2):
@@ -28,38 +56,154 @@ def timed(fn, reps=5, warm=2):
     return e0.elapsed_time(e1) / reps
 
 
+def sort_passes(bits):
+    return int(_lib.lib().nb_sort_passes(bits))
+
+
+def sort_algo_bytes(n, bits, identity_values=False):
+    """keys read once for all digit histograms, then 16 B per pair and pass (8 read + 8 written); a sort whose
+    values are the identity (the tree and grid builds) does not read them in the first pass."""
+    return (4 + 16 * sort_passes(bits) - (4 if identity_values else 0)) * n
+
+
+def stages(fn, reps, n, sort_bits=None, identity_values=False):
+    """Run fn reps times under the library's stage timers; returns {stage: {ms, algorithmic_bytes, gbs, frac}}."""
+    L, ctx = _lib.lib(), nb.get_context()
+    peak, _ = hbm_peak_gbs()
+    buf = C.create_string_buffer(1 << 16)
+    torch.cuda.synchronize()
+    _lib.check(L.nb_profile_stages_enable(ctx.handle, 1))
+    _lib.check(L.nb_profile_stages_read(ctx.handle, buf, len(buf)))  # drop anything older
+    for _ in range(reps):
+        fn()
+    _lib.check(L.nb_profile_stages_read(ctx.handle, buf, len(buf)))
+    _lib.check(L.nb_profile_stages_enable(ctx.handle, 0))
+    out = {}
+    for ln in buf.value.decode().splitlines():
+        name, ms, cnt = ln.split()
+        ms = float(ms) / reps
+        rec = {"ms": ms, "launches_per_call": int(cnt) / reps}
+        b = None
+        if name.endswith(".sort") and sort_bits:
+            b = sort_algo_bytes(n, sort_bits, identity_values)
+        elif name in ALGO_BYTES:
+            b = ALGO_BYTES[name] * n
+        if b is not None and ms > 0:
+            rec.update(algorithmic_bytes=int(b), achieved_gbs=b / ms / 1e6, frac=b / ms / 1e6 / peak)
+        out[name] = rec
+    return out
+
+
+def device_data(st):
+    h = nb.ParticleDataManager.fromState(st)
+    d = nb.ParticleData()
+    nb.ParticleDataManager.allocateDevice(d, h.count)
+    nb.ParticleDataManager.copyToDevice(d, h)
+    return d
+
+
+def bench_bh(n, ic="plummer", theta=0.5, reps=5):
+    L, ctx = _lib.lib(), nb.get_context()
+    st = ics.plummer(n, seed=42) if ic == "plummer" else ics.uniform_sphere(n, 1.0, 1.0 / n, seed=42)
+    d = device_data(st)
+    s = None
+    build = timed(lambda: _lib.check(L.nb_bh_build(ctx.handle, C.byref(d.c), s)), reps)
+    force = timed(lambda: _lib.check(L.nb_bh_forces(ctx.handle, C.byref(d.c), theta, 1.0, 0.01, s)), reps, warm=1)
+
+    def step():
+        _lib.check(L.nb_bh_build(ctx.handle, C.byref(d.c), s))
+        _lib.check(L.nb_bh_forces(ctx.handle, C.byref(d.c), theta, 1.0, 0.01, s))
+    step_ms = timed(step, reps, warm=1)
+    stg = stages(step, 3, n, sort_bits=30, identity_values=IDENTITY_SORT)
+    inter, cnt = C.c_uint64(0), C.c_int(0)
+    _lib.check(L.nb_bh_stats(ctx.handle, C.byref(inter), C.byref(cnt)))
+    deep, cap = C.c_int(0), C.c_int(0)
+    _lib.check(L.nb_bh_max_stack(ctx.handle, C.byref(deep), C.byref(cap)))
+    peak, src = hbm_peak_gbs()
+    build_bytes = sum(r.get("algorithmic_bytes", 0) for k, r in stg.items() if k != "bh.traversal")
+    return dict(path="barnes_hut", n=n, ic=ic, theta=theta, build_ms=build, force_ms=force, step_ms=step_ms,
+                build_algorithmic_bytes=int(build_bytes), build_gbs=build_bytes / build / 1e6,
+                build_frac=build_bytes / build / 1e6 / peak, hbm_peak_gbs=peak, hbm_peak_source=src,
+                interactions=inter.value, interactions_per_body=inter.value / n,
+                g_interactions_per_s=inter.value / force / 1e6,
+                tflops_20flop=inter.value * 20.0 / force / 1e9, stack_deepest=deep.value, stack_cap=cap.value,
+                stages=stg, timing="CUDA events, mean of %d calls after warm-up; stages under the library's stage "
+                                   "timers (events between the kernels of one call)" % reps)
+
+
+IDENTITY_SORT = False  # set when the builds stop writing / reading the identity permutation
+
+
+def bench_sh(n, reps=5):
+    L, ctx = _lib.lib(), nb.get_context()
+    side = (n / 8.0) ** (1.0 / 3.0)     # ~8 bodies per unit cell (SURVEY.md config 5)
+    st = ics.uniform_box(n, 0.0, side, seed=42)
+    d = device_data(st)
+    build = timed(lambda: _lib.check(L.nb_sh_build(ctx.handle, C.byref(d.c), 1.0, None)), reps)
+    force = timed(lambda: _lib.check(L.nb_sh_forces(ctx.handle, C.byref(d.c), 2.0, 1.0, 0.01, None)), reps)
+    t, pairs = C.c_int(0), C.c_uint64(0)
+    L.nb_sh_total_cells(ctx.handle, C.byref(t))
+    _lib.check(L.nb_sh_stats(ctx.handle, C.byref(pairs)))
+    bits = max(1, int(np.ceil(np.log2(max(t.value, 2)))))
+
+    def step():
+        _lib.check(L.nb_sh_build(ctx.handle, C.byref(d.c), 1.0, None))
+        _lib.check(L.nb_sh_forces(ctx.handle, C.byref(d.c), 2.0, 1.0, 0.01, None))
+    stg = stages(step, 3, n, sort_bits=bits, identity_values=IDENTITY_SORT)
+    peak, src = hbm_peak_gbs()
+    build_bytes = sum(r.get("algorithmic_bytes", 0) for k, r in stg.items() if k != "sh.force")
+    return dict(path="spatial_hash", n=n, side=side, cell_size=1.0, cutoff=2.0, cells=t.value, key_bits=bits,
+                build_ms=build, force_ms=force, step_ms=build + force,
+                build_algorithmic_bytes=int(build_bytes), build_gbs=build_bytes / build / 1e6,
+                build_frac=build_bytes / build / 1e6 / peak, hbm_peak_gbs=peak, hbm_peak_source=src,
+                pairs_in_cutoff=pairs.value, pairs_per_body=pairs.value / n, g_pairs_per_s=pairs.value / force / 1e6,
+                stages=stg)
+
+
+def bench_sort(n, bits=30, reps=7):
+    """(key, value) pairs with `bits`-bit keys in random order (what the Morton sort sees), restored before every
+    repetition; nb_sort_pairs sorts in place."""
+    L, ctx = _lib.lib(), nb.get_context()
+    g = torch.Generator(device="cuda").manual_seed(42)
+    k0 = torch.randint(0, 1 << bits, (n,), device="cuda", dtype=torch.int64, generator=g).to(torch.int32)
+    v0 = torch.arange(n, device="cuda", dtype=torch.int32)
+    k, v = k0.clone(), v0.clone()
+    ms = []
+    for rep in range(reps):
+        k.copy_(k0); v.copy_(v0)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        _lib.check(L.nb_sort_pairs(ctx.handle, k.data_ptr(), v.data_ptr(), n, bits, None))
+        e1.record()
+        torch.cuda.synchronize()
+        ms.append(e0.elapsed_time(e1))
+    best, mean = min(ms[2:]), float(np.mean(ms[2:]))
+    passes = sort_passes(bits)
+    algo = sort_algo_bytes(n, bits) + (16 * n if passes % 2 else 0)  # in place: odd pass counts copy back
+    assert bool((k[1:] >= k[:-1]).all())
+    assert bool((k0[v.long()] == k).all())
+    peak, src = hbm_peak_gbs()
+    return dict(path="radix_sort_pairs", n=n, bits=bits, passes=passes, ms=mean, ms_best=best, ms_all=ms,
+                algorithmic_bytes=int(algo), achieved_gbs=algo / mean / 1e6, frac=algo / mean / 1e6 / peak,
+                hbm_peak_gbs=peak, hbm_peak_source=src, gkeys_per_s=n / mean / 1e6,
+                what="nb_sort_pairs in place: keys read once for the histograms, 16 B per pair and pass, and after an "
+                     "odd number of passes 16 B per pair for the copy back into the caller's arrays (the tree and "
+                     "grid builds take the result from the scratch buffer instead: see paths.*.stages['*.sort'])")
+
+
 def main():
     kind, n = sys.argv[1], int(sys.argv[2])
-    L, ctx = _lib.lib(), nb.get_context()
     if kind == "bh":
-        ic = sys.argv[3] if len(sys.argv) > 3 else "plummer"
-        st = ics.plummer(n, seed=42) if ic == "plummer" else ics.uniform_sphere(n, 1.0, 1.0 / n, seed=42)
-        h = nb.ParticleDataManager.fromState(st)
-        d = nb.ParticleData()
-        nb.ParticleDataManager.allocateDevice(d, n)
-        nb.ParticleDataManager.copyToDevice(d, h)
-        s = None
-        build = timed(lambda: _lib.check(L.nb_bh_build(ctx.handle, C.byref(d.c), s)))
-        force = timed(lambda: _lib.check(L.nb_bh_forces(ctx.handle, C.byref(d.c), 0.5, 1.0, 0.01, s)))
-        _lib.check(L.nb_bh_build(ctx.handle, C.byref(d.c), s))
-        _lib.check(L.nb_bh_forces(ctx.handle, C.byref(d.c), 0.5, 1.0, 0.01, s))
-        inter, cnt = C.c_uint64(0), C.c_int(0)
-        _lib.check(L.nb_bh_stats(ctx.handle, C.byref(inter), C.byref(cnt)))
-        deep, cap = C.c_int(0), C.c_int(0)
-        _lib.check(L.nb_bh_max_stack(ctx.handle, C.byref(deep), C.byref(cap)))
-        print(json.dumps(dict(path="barnes_hut", n=n, ic=ic, theta=0.5, group=os.environ.get("NB_BH_GROUP", "64"),
-                              stack_deepest=deep.value, stack_cap=cap.value,
-                              super=os.environ.get("NB_BH_SUPER", "default"), build_ms=build, force_ms=force,
-                              step_ms=build + force, interactions=inter.value, per_body=inter.value / n,
-                              g_interactions_per_s=inter.value / force / 1e6)))
+        print(json.dumps(bench_bh(n, sys.argv[3] if len(sys.argv) > 3 else "plummer")))
+    elif kind == "sh":
+        print(json.dumps(bench_sh(n)))
+    elif kind == "sort":
+        print(json.dumps(bench_sort(n, int(sys.argv[3]) if len(sys.argv) > 3 else 30)))
     elif kind == "energy":
         # potential-energy diagnostic (O(N^2)) and the one-pass moments, wall clock around the synchronising calls
         import time
         st = ics.plummer(n, seed=42)
-        h = nb.ParticleDataManager.fromState(st)
-        d = nb.ParticleData()
-        nb.ParticleDataManager.allocateDevice(d, n)
-        nb.ParticleDataManager.copyToDevice(d, h)
+        d = device_data(st)
         integ = nb.Integrator()
         integ.computePotentialEnergy(d, 1.0, 0.01)
         torch.cuda.synchronize()
@@ -98,57 +242,18 @@ def main():
         st = ics.plummer(n, seed=42)
         for k in ("pos_x", "pos_y", "pos_z"):
             st[k] = (st[k] * np.float32(8.0)).astype(np.float32)
-        hd = nb.ParticleDataManager.fromState(st)
-        d = nb.ParticleData()
-        nb.ParticleDataManager.allocateDevice(d, n)
-        nb.ParticleDataManager.copyToDevice(d, hd)
+        d = device_data(st)
         r = nb.Renderer()
         r.initialize(w, h)
         ms = timed(lambda: r.render(d))
         frags = r.fragments()
         img = r.readPixels()
-        r.savePPM(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out",
-                               f"render_{n}.ppm")) if os.path.isdir("gpurun_out") and n <= (1 << 20) else None
+        if os.path.isdir(os.path.join(ROOT, "gpurun_out")) and n <= (1 << 20):
+            r.savePPM(os.path.join(ROOT, "gpurun_out", f"render_{n}.ppm"))
         print(json.dumps(dict(path="splat_render", n=n, width=w, height=h, ms=ms, fragments=frags,
                               lit_pixels=int((img != img[0, 0]).any(axis=2).sum()), gbodies_per_s=n / ms / 1e6)))
-    elif kind == "sort":
-        # 30-bit keys in random order (what the Morton sort sees), restored before every repetition
-        bits = int(sys.argv[3]) if len(sys.argv) > 3 else 30
-        g = torch.Generator(device="cuda").manual_seed(42)
-        k0 = torch.randint(0, 1 << bits, (n,), device="cuda", dtype=torch.int64, generator=g).to(torch.int32)
-        v0 = torch.arange(n, device="cuda", dtype=torch.int32)
-        k, v = k0.clone(), v0.clone()
-        ms = []
-        for rep in range(7):
-            k.copy_(k0); v.copy_(v0)
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            _lib.check(L.nb_sort_pairs(ctx.handle, k.data_ptr(), v.data_ptr(), n, bits, None))
-            e1.record()
-            torch.cuda.synchronize()
-            ms.append(e0.elapsed_time(e1))
-        best = min(ms[2:])
-        passes = (bits + 7) // 8
-        algo = (4 + 16 * passes) * n
-        assert bool((k[1:] >= k[:-1]).all())
-        print(json.dumps(dict(path="radix_sort_pairs", n=n, bits=bits, passes=passes, ms=best, ms_all=ms,
-                              warps=os.environ.get("NB_SORT_WARPS", "16"), algorithmic_bytes=algo,
-                              gbs=algo / best / 1e6, gkeys_per_s=n / best / 1e6)))
     else:
-        side = (n / 8.0) ** (1.0 / 3.0)     # ~8 bodies per unit cell
-        st = ics.uniform_box(n, 0.0, side, seed=42)
-        h = nb.ParticleDataManager.fromState(st)
-        d = nb.ParticleData()
-        nb.ParticleDataManager.allocateDevice(d, n)
-        nb.ParticleDataManager.copyToDevice(d, h)
-        build = timed(lambda: _lib.check(L.nb_sh_build(ctx.handle, C.byref(d.c), 1.0, None)))
-        force = timed(lambda: _lib.check(L.nb_sh_forces(ctx.handle, C.byref(d.c), 2.0, 1.0, 0.01, None)))
-        t, pairs = C.c_int(0), C.c_uint64(0)
-        L.nb_sh_total_cells(ctx.handle, C.byref(t))
-        _lib.check(L.nb_sh_stats(ctx.handle, C.byref(pairs)))
-        print(json.dumps(dict(path="spatial_hash", n=n, side=side, cells=t.value, build_ms=build, force_ms=force,
-                              step_ms=build + force, build_gbs=136.0 * n / build / 1e6, pairs_in_cutoff=pairs.value,
-                              pairs_per_body=pairs.value / n, g_pairs_per_s=pairs.value / force / 1e6)))
+        raise SystemExit(__doc__)
 
 
 if __name__ == "__main__":
