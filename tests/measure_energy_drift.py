@@ -3,7 +3,9 @@
 (dt 1e-3, eps 0.01, Plummer seed 42) at 65 536 and 262 144 bodies, ours and -- same initial conditions -- the
 reference's own kernels (oracle/_ref/libnbody_ref.so), E in fp64 by our diagnostic for both.  A measurement
 script, not a test (the 8192-body version of the same check is tests/test_gpu_vs_reference.py): run on a B200,
-one JSON line per case.  usage: python tests/measure_energy_drift.py [--steps K] [--every S] [n ...]
+one JSON line per case.  usage: python tests/measure_energy_drift.py [--steps K] [--every S] [--seeds a,b,c] [n ...]
+--seeds runs every size once per seed (an ENSEMBLE: the end-point drift of one run is one sample of a rounding walk)
+and appends one summary line per size with the median and maximum over the seeds for both arms.
 --every S also samples the energy every S steps on both arms and records the largest excursion along the trajectory
 (the end-point value alone is one sample of a rounding-noise random walk)."""
 import json
@@ -33,10 +35,16 @@ def main():
         k = argv.index("--every")
         every = int(argv[k + 1])
         del argv[k:k + 2]
+    seeds = [42]
+    if "--seeds" in argv:
+        k = argv.index("--seeds")
+        seeds = [int(x) for x in argv[k + 1].split(",")]
+        del argv[k:k + 2]
     sizes = [int(a) for a in argv] or [65536, 262144]
     dt, eps = 1e-3, 0.01
-    for n in sizes:
-        st = ics.plummer(n, seed=42)
+    records = []
+    for n, seed in [(n, sd) for n in sizes for sd in seeds]:
+        st = ics.plummer(n, seed=seed)
 
         def device(state):
             h = nb.ParticleDataManager.fromState(state)
@@ -61,7 +69,7 @@ def main():
         e1 = integ.computeTotalEnergy(d, 1.0, eps)
         t_ours = time.time() - t0
         samples_ours.append(e1)
-        rec = {"bodies": n, "steps": steps, "dt": dt, "softening": eps, "E0": e0, "E_ours": e1,
+        rec = {"bodies": n, "seed": seed, "steps": steps, "dt": dt, "softening": eps, "E0": e0, "E_ours": e1,
                "drift_ours": abs(e1 - e0) / abs(e0), "seconds_ours": t_ours}
         if every:
             rec.update({"sample_every": every,
@@ -87,6 +95,22 @@ def main():
             dx = np.sqrt((o["pos_x"] - r["pos_x"]) ** 2 + (o["pos_y"] - r["pos_y"]) ** 2 + (o["pos_z"] - r["pos_z"]) ** 2)
             rec["max_position_difference"] = float(dx.max())
         print(json.dumps(rec), flush=True)
+        records.append(rec)
+    if len(seeds) > 1:
+        for n in sizes:
+            rs = [r for r in records if r["bodies"] == n]
+            summ = {"summary": True, "bodies": n, "seeds": [r["seed"] for r in rs], "steps": steps}
+            for key in ("drift_ours", "drift_reference", "max_excursion_ours", "max_excursion_reference"):
+                v = [r[key] for r in rs if key in r]
+                if v:
+                    summ["median_" + key], summ["max_" + key], summ["min_" + key] = (float(np.median(v)), float(max(v)),
+                                                                                     float(min(v)))
+            if all("drift_reference" in r for r in rs):
+                summ["seeds_where_ours_is_lower"] = int(sum(r["drift_ours"] <= r["drift_reference"] for r in rs))
+                if all("max_excursion_reference" in r for r in rs):
+                    summ["seeds_where_our_excursion_is_lower"] = int(
+                        sum(r["max_excursion_ours"] <= r["max_excursion_reference"] for r in rs))
+            print(json.dumps(summ), flush=True)
 
 
 if __name__ == "__main__":

@@ -19,12 +19,13 @@ def _device_data(state):
     return d
 
 
-@pytest.mark.parametrize("warps", [16, 8])
 @pytest.mark.parametrize("n,bits", [(1, 32), (2, 32), (33, 8), (4096, 32), (4097, 30), (8191, 32), (8192, 30), (8193, 13),
-                                    (16385, 1), (100003, 30), (1 << 20, 21), (3000017, 32)])
-def test_radix_sort_stable_bit_exact(orc, n, bits, warps, monkeypatch):
+                                    (16385, 1), (100003, 30), (1 << 20, 21), (3000017, 32),
+                                    # every digit plan of the pass kernel: 1 x 9/10/11 bits, 2 x (6..11), 3 x (8..11)
+                                    (50000, 9), (50000, 10), (70001, 11), (70001, 12), (123457, 16), (123457, 20),
+                                    (123457, 22), (200003, 23), (200003, 24), (200003, 31), (20000, 2), (20000, 7)])
+def test_radix_sort_stable_bit_exact(orc, n, bits):
     import torch
-    monkeypatch.setenv("NB_SORT_WARPS", str(warps))  # both tile shapes of the onesweep kernel
     import nbody_b200 as nb
     from nbody_b200 import _lib
     rng = np.random.default_rng(n)
