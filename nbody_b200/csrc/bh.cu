@@ -23,14 +23,21 @@
 namespace nb {
 
 int bbox_device(nb_context* ctx, const nb_particles* d, cudaStream_t st);
-int sort_pairs(nb_context* ctx, uint32_t* d_keys, int32_t* d_vals, size_t n, int end_bit, cudaStream_t st);
+int sort_pairs_db(nb_context* ctx, uint32_t* d_keys, int32_t* d_vals, uint32_t* keys_alt, int32_t* vals_alt, size_t n,
+                  int end_bit, bool identity_vals, uint32_t** out_keys, int32_t** out_vals, cudaStream_t st);
 
 }  // namespace nb
 
 struct BH {
   size_t n = 0;
-  nb::DevBuf keys, perm, packed, node_com, meta, parent, flags, misc;  // misc: size2 table[32] + counter + bbox floats
-  nb::DevBuf range, groups;  // int2 {first,last} per internal node; int2 {first,count} per traversal group
+  // keys/perm: two buffers each, the radix passes ping-pong between them (the result stays in BH-owned memory, so
+  // a later sort on the same context cannot clobber the permutation the traversal scatters through)
+  nb::DevBuf keys, perm, keys_alt, perm_alt, packed, node_com, meta, misc;  // misc: size2 table[32] + counter + bbox floats
+  nb::DevBuf slot;    // int per split position: meeting point of the two children of a node that spans tiles
+  nb::DevBuf parent;  // filled on export only
+  nb::DevBuf groups;  // int2 {first,count} per traversal group
+  uint32_t* keys_sorted = nullptr;  // where the last build's sorted keys / permutation live
+  int32_t* perm_sorted = nullptr;
   float h_bbox[6] = {0, 0, 0, 0, 0, 0};
   int* h_flag = nullptr;  // host-mapped: traversal stack overflow
   int* d_flag = nullptr;
@@ -85,7 +92,7 @@ __global__ void __launch_bounds__(256) bh_morton_kernel(const float* __restrict_
                                                         const float* __restrict__ pz,
                                                         const float* __restrict__ mass, size_t n,
                                                         const float* __restrict__ misc, uint32_t* __restrict__ keys,
-                                                        int32_t* __restrict__ perm, float4* __restrict__ packed) {
+                                                        float4* __restrict__ packed) {
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const float x = px[i], y = py[i], z = pz[i];
@@ -104,94 +111,42 @@ __global__ void __launch_bounds__(256) bh_morton_kernel(const float* __restrict_
   const unsigned uy = min(__float2uint_rz(__fmul_rn(ny, 1024.0f)), 1023u);
   const unsigned uz = min(__float2uint_rz(__fmul_rn(nz, 1024.0f)), 1023u);
   keys[i] = (expand_bits(ux) << 2) | (expand_bits(uy) << 1) | expand_bits(uz);
-  perm[i] = (int32_t)i;
+  // the identity permutation is not written: the first radix pass generates value = index itself
 }
 
-// leaves of the tree = bodies in sorted order, packed {x,y,z,m}
-__global__ void __launch_bounds__(256) bh_gather_kernel(const float4* __restrict__ packed, size_t n,
-                                                        const int32_t* __restrict__ perm,
-                                                        float4* __restrict__ leaves) {
-  const size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (k >= n) return;
-  leaves[k] = __ldg(packed + perm[k]);
-}
+// ---- tree build: ONE kernel for leaf gather + radix-tree topology + centres of mass + traversal groups -----
+// Round 1 built the tree in four kernels -- leaf gather, Karras' per-node binary searches, a bottom-up
+// centre-of-mass pass (one thread per leaf climbing, second arriver combines) and a group pass -- 1.84 ms of
+// the 2.6 ms build at 16 Mi bodies, all of them bound by instruction issue at low lane occupancy (the climbing
+// passes lose half their lanes per level, ncu: 22 % / 22 % / 17 % of the HBM bandwidth).  This kernel builds the
+// same tree bottom-up instead (Apetrei 2014): a complete subtree [l, r] is a left child iff
+// delta(r) > delta(l-1) (delta(k) = common prefix of sorted keys k, k+1, with Karras' index tie-break for equal
+// keys); two adjacent complete subtrees [l, g], [g+1, r] are siblings iff delta(g) exceeds both outer deltas.
+// Node numbering stays Karras' (a left child is node r, a right child node l, the root node 0; children of a
+// node split at g are g and g+1, or leaves), so left/right/prefix and the centres of mass are bit-identical to
+// the per-node searches and to oracle/lbvh.c.  Schedule, per CTA tile of 4096 consecutive leaves in shared
+// memory:
+//   phase 0  leaves: one random 16-B read per body through the sort permutation (the round-1 gather kernel),
+//            stored coalesced as leaf records and kept in shared memory; delta of every adjacent pair;
+//   phase 1  every thread merges inside its OWN 16 consecutive leaves with the sequential stack algorithm (the
+//            stack is implicit: a current subtree [a, b] keeps its value at slot a and its ends at slots a
+//            and b), one action -- merge the top two subtrees or push the next leaf -- per trip, so all lanes
+//            work until their own leaves run out: ~5 warp-instructions per leaf where the climbing passes
+//            spent ~37;
+//   phase 2  log2(256) rounds: thread j joins blocks 2j and 2j+1 of the previous round across their common
+//            boundary (only subtrees touching the boundary can newly merge), dense thread indices;
+//   phase 3  the few subtrees whose sibling lies in another tile (the two spines of the tile, ~0.6 % of the
+//            nodes) climb with one global exchange per level: the first child to arrive leaves its far end
+//            in slot[split], the second takes it, reads the sibling's record and goes on.
+// The thread that completes a node writes its record, and emits the traversal groups of a child that is a
+// maximal subtree of <= smax leaves (the round-1 group pass).
+constexpr int TB_THREADS = 256;
+constexpr int TB_K = 16;                        // consecutive leaves per thread in phase 1
+constexpr int TB_TILE = TB_THREADS * TB_K;      // 4096 leaves per CTA
+constexpr int TB_PADDED = TB_TILE + TB_TILE / 16 + 2;
+constexpr int TB_MAX_ROOTS = 512;               // subtrees left per tile: two spines of <= 62 levels each
+__device__ __forceinline__ int tb_pad(int q) { return q + (q >> 4); }  // thread j's leaf i at 17 j + i: no bank conflicts
 
-__device__ __forceinline__ int bh_delta(const uint32_t* __restrict__ k, int n, int i, int j) {
-  if (j < 0 || j >= n) return -1;
-  const uint32_t a = k[i], b = k[j];
-  if (a == b) return 32 + __clz((unsigned)i ^ (unsigned)j);
-  return __clz(a ^ b);
-}
-
-// Karras 2012, sec. 4: one thread per internal node.  meta[i] = {left, right, prefix, 0}.
-__global__ void __launch_bounds__(256) bh_karras_kernel(const uint32_t* __restrict__ keys, int n,
-                                                        int4* __restrict__ meta, int32_t* __restrict__ parent,
-                                                        int2* __restrict__ range) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n - 1) return;
-  const int leaf0 = n - 1;
-  const int d = (bh_delta(keys, n, i, i + 1) - bh_delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
-  const int dmin = bh_delta(keys, n, i, i - d);
-  int lmax = 2;
-  while (bh_delta(keys, n, i, i + lmax * d) > dmin) lmax <<= 1;
-  int l = 0;
-  for (int t = lmax >> 1; t >= 1; t >>= 1)
-    if (bh_delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
-  const int j = i + l * d;
-  const int dnode = bh_delta(keys, n, i, j);
-  int s = 0, t = l;
-  do {
-    t = (t + 1) >> 1;
-    if (bh_delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
-  } while (t > 1);
-  const int gamma = i + s * d + (d < 0 ? d : 0);
-  const int lo = min(i, j), hi = max(i, j);
-  const int lc = (lo == gamma) ? leaf0 + gamma : gamma;
-  const int rc = (hi == gamma + 1) ? leaf0 + gamma + 1 : gamma + 1;
-  int p = dnode - 2;
-  if (p > 30) p = 30;
-  meta[i] = make_int4(lc, rc, p, 0);
-  range[i] = make_int2(lo, hi);
-  parent[lc] = i;
-  parent[rc] = i;
-  if (i == 0) parent[0] = -1;
-}
-
-// bottom-up centres of mass: the second thread to reach a node combines its two children.
-// c = (ca*ma + cb*mb) / (ma+mb), a = left child, b = right child: order-independent of arrival.
-__global__ void __launch_bounds__(256) bh_com_kernel(int n, const int4* __restrict__ meta,
-                                                     const int32_t* __restrict__ parent, int* __restrict__ flags,
-                                                     float4* node_com) {
-  const int k = blockIdx.x * blockDim.x + threadIdx.x;
-  if (k >= n) return;
-  int p = parent[n - 1 + k];
-  while (p >= 0) {
-    __threadfence();
-    if (atomicAdd(&flags[p], 1) == 0) return;
-    const int4 m = meta[p];
-    const float4 a = __ldcg(node_com + m.x), b = __ldcg(node_com + m.y);
-    const float ms = __fadd_rn(a.w, b.w);
-    float4 c;
-    if (ms > 0.f) {
-      c.x = __fdiv_rn(__fadd_rn(__fmul_rn(a.x, a.w), __fmul_rn(b.x, b.w)), ms);
-      c.y = __fdiv_rn(__fadd_rn(__fmul_rn(a.y, a.w), __fmul_rn(b.y, b.w)), ms);
-      c.z = __fdiv_rn(__fadd_rn(__fmul_rn(a.z, a.w), __fmul_rn(b.z, b.w)), ms);
-    } else {
-      c.x = a.x; c.y = a.y; c.z = a.z;
-    }
-    c.w = ms;
-    __stcg(node_com + p, c);
-    p = parent[p];
-  }
-}
-
-// The same bottom-up pass with the lower levels in shared memory.  A CTA owns COM_TILE consecutive leaves; the
-// internal nodes whose leaf range lies inside that tile (all but ~1 in COM_TILE of them; node i always lies inside
-// its own range, so their indices fall in the tile too) have their topology staged in shared memory, arrive on
-// shared-memory counters and hand their values up through shared memory; only nodes that span tiles go through the
-// global flags as above.  Every node is still combine(left child, right child) with the same operations, so the
-// result is bit-identical to bh_com_kernel's.
-constexpr int COM_TILE = 512;
 __device__ __forceinline__ float4 bh_combine(const float4& a, const float4& b) {
   const float ms = __fadd_rn(a.w, b.w);
   float4 c;
@@ -205,86 +160,214 @@ __device__ __forceinline__ float4 bh_combine(const float4& a, const float4& b) {
   c.w = ms;
   return c;
 }
-__global__ void __launch_bounds__(COM_TILE) bh_com_tile_kernel(int n, const int4* __restrict__ meta,
-                                                               const int32_t* __restrict__ parent,
-                                                               const int2* __restrict__ range, int* __restrict__ flags,
-                                                               float4* node_com) {
-  __shared__ int4 s_meta[COM_TILE];
-  __shared__ int2 s_range[COM_TILE];
-  __shared__ int s_parent[COM_TILE];
-  __shared__ int s_cnt[COM_TILE];
-  __shared__ float4 s_com[COM_TILE];
-  const int tid = threadIdx.x;
-  const int t0 = blockIdx.x * COM_TILE, t1 = min(t0 + COM_TILE, n);  // this CTA's leaves [t0, t1)
-  const int leaf0 = n - 1;
-  if (t0 + tid < n - 1) {
-    s_meta[tid] = meta[t0 + tid];
-    s_range[tid] = range[t0 + tid];
-    s_parent[tid] = parent[t0 + tid];
-  }
-  s_cnt[tid] = 0;
-  __syncthreads();
-  const int k = t0 + tid;
-  if (k >= n) return;
-  int node = leaf0 + k;
-  int p = parent[node];
-  float4 cur = __ldcg(node_com + node);
-  while (p >= 0) {  // levels inside the tile
-    const int q = p - t0;
-    if (q < 0 || q >= COM_TILE) break;
-    const int2 r = s_range[q];
-    if (r.x < t0 || r.y >= t1) break;
-    __threadfence_block();
-    if (atomicAdd(&s_cnt[q], 1) == 0) return;  // the sibling's thread finishes this node
-    __threadfence_block();  // the sibling's value was published before its arrival: read it after ours
-    const int4 m = s_meta[q];
-    const bool left = (m.x == node);
-    const int sib = left ? m.y : m.x;
-    const float4 sv = (sib >= leaf0) ? __ldcg(node_com + sib) : s_com[sib - t0];
-    cur = left ? bh_combine(cur, sv) : bh_combine(sv, cur);
-    s_com[q] = cur;
-    __stcg(node_com + p, cur);
-    node = p;
-    p = s_parent[q];
-  }
-  while (p >= 0) {  // nodes spanning tiles: as bh_com_kernel
-    __threadfence();
-    if (atomicAdd(&flags[p], 1) == 0) return;
-    const int4 m = meta[p];
-    const float4 c = bh_combine(__ldcg(node_com + m.x), __ldcg(node_com + m.y));
-    __stcg(node_com + p, c);
-    p = parent[p];
+
+// common prefix of sorted keys k and k+1 (Karras 2012 sec. 4: equal keys fall back to the positions); -1 outside
+__device__ __forceinline__ int bh_delta_adj(const uint32_t* __restrict__ keys, int n, int k) {
+  if (k < 0 || k >= n - 1) return -1;
+  const uint32_t a = keys[k], b = keys[k + 1];
+  if (a == b) return 32 + __clz((unsigned)k ^ (unsigned)(k + 1));
+  return __clz(a ^ b);
+}
+
+struct TreeOut {
+  float4* node_com;  // [2n-1]: internal nodes 0..n-2, leaf k of the sorted order at n-1+k
+  int4* meta;        // [n-1] {left, right, prefix, 0}
+  int2* groups;
+  int* ngroups;
+  int n, leaf0, smax, gmax;
+};
+
+// Traversal groups of a supergroup (a maximal subtree [cl, cr] of <= smax leaves): ceil(c / gmax) runs of
+// consecutive bodies of (almost) equal length, run i starting at floor(i * c / runs).  With smax == gmax the
+// groups are the subtrees themselves (mean fill 69 % of gmax), with smax = 8 * gmax the runs are 89-100 % full
+// and still confined to one cell.
+__device__ __forceinline__ void tb_emit(int cl, int cr, const TreeOut& o) {
+  const int c = cr - cl + 1;
+  const int runs = (c + o.gmax - 1) / o.gmax;
+  const int base = atomicAdd(o.ngroups, runs);
+  for (int i = 0; i < runs; i++) {
+    const int s0 = (int)(((long long)i * c) / runs), s1 = (int)(((long long)(i + 1) * c) / runs);
+    o.groups[base + i] = make_int2(cl + s0, s1 - s0);
   }
 }
 
-// Traversal groups.  A "supergroup" is a maximal subtree with at most `smax` leaves: its bodies share
-// a Morton prefix, so it is as compact as its cell (a fixed run of consecutive sorted bodies can
-// straddle distant cells in sparse regions).  Each supergroup of c bodies is cut into
-// ceil(c / gmax) runs of consecutive bodies of (almost) equal length <= gmax, run i starting at
-// floor(i * c / runs): with smax == gmax the groups are the subtrees themselves (mean fill 69 % of
-// gmax), with smax = 8 * gmax the runs are 89-100 % full and still confined to one cell.
-// One thread per leaf climbs to its supergroup's root; the leaf that starts a run publishes it.
-__global__ void __launch_bounds__(256) bh_groups_kernel(int n, int smax, int gmax, const int32_t* __restrict__ parent,
-                                                        const int2* __restrict__ range, int2* __restrict__ groups,
-                                                        int* __restrict__ ngroups) {
-  const int k = blockIdx.x * blockDim.x + threadIdx.x;
-  if (k >= n) return;
-  int first = k, count = 1;
-  int p = parent[n - 1 + k];
-  while (p >= 0) {
-    const int2 r = range[p];
-    if (r.y - r.x + 1 > smax) break;
-    first = r.x;
-    count = r.y - r.x + 1;
-    p = parent[p];
+// Completes node [l, r] split at g (all global leaf indices) from its children's values; dL = delta(l-1),
+// dR = delta(r), dS = delta(g).  Writes the node's record and emits the groups of supergroup children.
+__device__ __forceinline__ float4 tb_form(int l, int g, int r, int dL, int dR, int dS, const float4& a, const float4& b,
+                                          const TreeOut& o) {
+  const float4 c = bh_combine(a, b);
+  const int id = (dR > dL) ? r : l;  // a left child is numbered by its last leaf, a right child (and the root) by its first
+  const int lc = (l == g) ? o.leaf0 + g : g;
+  const int rc = (r == g + 1) ? o.leaf0 + g + 1 : g + 1;
+  int p = dS - 2;  // key bits start at bit 29
+  if (p > 30) p = 30;
+  o.meta[id] = make_int4(lc, rc, p, 0);
+  o.node_com[id] = c;
+  if (r - l + 1 > o.smax) {
+    if (g - l + 1 <= o.smax) tb_emit(l, g, o);
+    if (r - g <= o.smax) tb_emit(g + 1, r, o);
+  } else if (l == 0 && r == o.n - 1) {
+    tb_emit(l, r, o);  // the whole tree is one supergroup
   }
-  const int runs = (count + gmax - 1) / gmax;
-  const int r = k - first;
-  const int i = (int)(((long long)r * runs + count - 1) / count);  // first run starting at or after r
-  if (i < runs && (int)(((long long)i * count) / runs) == r) {
-    const int next = (int)(((long long)(i + 1) * count) / runs);
-    groups[atomicAdd(ngroups, 1)] = make_int2(k, next - r);
+  return c;
+}
+
+__global__ void __launch_bounds__(TB_THREADS, 2) bh_tree_kernel(const uint32_t* __restrict__ keys,
+                                                                 const int32_t* __restrict__ perm,
+                                                                 const float4* __restrict__ packed,
+                                                                 int* __restrict__ slot, TreeOut o) {
+  extern __shared__ __align__(16) unsigned char tb_smem[];
+  float4* s_com = reinterpret_cast<float4*>(tb_smem);            // value of the current subtree starting here
+  int* s_d = reinterpret_cast<int*>(s_com + TB_PADDED);          // s_d[q]: delta between local leaves q-1 and q
+  short* s_lo = reinterpret_cast<short*>(s_d + TB_PADDED);       // s_lo[b]: first leaf of the current subtree ending at b
+  short* s_hi = s_lo + TB_PADDED;                                // s_hi[a]: last leaf of the current subtree starting at a
+  __shared__ int s_roots[TB_MAX_ROOTS];
+  __shared__ int s_nroots;
+  const int tid = threadIdx.x;
+  const int n = o.n;
+  const int t0 = blockIdx.x * TB_TILE;
+  const int tcount = min(TB_TILE, n - t0);
+
+  // ---- phase 0: leaves and deltas ---------------------------------------------------------------------
+  {
+    int idx[TB_K];
+#pragma unroll
+    for (int i = 0; i < TB_K; i++) {
+      const int q = tid + i * TB_THREADS;
+      idx[i] = (q < tcount) ? perm[t0 + q] : -1;
+    }
+#pragma unroll
+    for (int i = 0; i < TB_K; i++) {
+      const int q = tid + i * TB_THREADS;
+      if (q < tcount) {
+        const float4 v = __ldg(packed + idx[i]);
+        s_com[tb_pad(q)] = v;
+        o.node_com[o.leaf0 + t0 + q] = v;
+        s_lo[tb_pad(q)] = (short)q;
+        s_hi[tb_pad(q)] = (short)q;
+        s_d[tb_pad(q + 1)] = bh_delta_adj(keys, n, t0 + q);
+      }
+    }
+    if (tid == 0) s_d[0] = bh_delta_adj(keys, n, t0 - 1);
   }
+  __syncthreads();
+  if (n == 1) {  // a single leaf: no internal node, one group
+    if (tid == 0) tb_emit(0, 0, o);
+    return;
+  }
+
+  // ---- phase 1: every thread merges inside its own TB_K consecutive leaves ---------------------------------
+  {
+    const int blk0 = tid * TB_K, blk1 = min(blk0 + TB_K, tcount);
+    int q = blk0;  // the top subtree ends at leaf q
+    while (q < blk1) {
+      const int a_top = s_lo[tb_pad(q)];
+      bool merged = false;
+      if (a_top > blk0) {
+        const int g = a_top - 1;          // the subtree below the top is [a, g]
+        const int a = s_lo[tb_pad(g)];
+        const int dS = s_d[tb_pad(g + 1)], dL = s_d[tb_pad(a)], dR = s_d[tb_pad(q + 1)];
+        if (dS > dL && dS > dR) {
+          const float4 c = tb_form(t0 + a, t0 + g, t0 + q, dL, dR, dS, s_com[tb_pad(a)], s_com[tb_pad(a_top)], o);
+          s_com[tb_pad(a)] = c;
+          s_hi[tb_pad(a)] = (short)q;
+          s_lo[tb_pad(q)] = (short)a;
+          merged = true;
+        }
+      }
+      if (!merged) q++;  // push the next leaf (its one-leaf subtree is already in place)
+    }
+  }
+  __syncthreads();
+
+  // ---- phase 2: join neighbouring blocks across their common boundary, doubling the block size ---------------
+  for (int half = TB_K; half < TB_TILE; half <<= 1) {
+    const int p = (2 * tid + 1) * half;  // boundary between local leaves p-1 and p
+    if (p < tcount) {
+      const int lo_lim = p - half, hi_lim = min(p + half, tcount);
+      int a = s_lo[tb_pad(p - 1)], b = s_hi[tb_pad(p)];
+      int dL = s_d[tb_pad(a)], dR = s_d[tb_pad(b + 1)];
+      const int dS = s_d[tb_pad(p)];
+      if (dS > dL && dS > dR) {
+        float4 c = tb_form(t0 + a, t0 + p - 1, t0 + b, dL, dR, dS, s_com[tb_pad(a)], s_com[tb_pad(p)], o);
+        for (;;) {  // the new subtree [a, b] may now be the sibling of its left or of its right neighbour
+          if (a > lo_lim) {
+            const int a2 = s_lo[tb_pad(a - 1)];
+            const int d2 = s_d[tb_pad(a2)];
+            if (dL > d2 && dL > dR) {
+              c = tb_form(t0 + a2, t0 + a - 1, t0 + b, d2, dR, dL, s_com[tb_pad(a2)], c, o);
+              a = a2;
+              dL = d2;
+              continue;
+            }
+          }
+          if (b + 1 < hi_lim) {
+            const int b2 = s_hi[tb_pad(b + 1)];
+            const int d2 = s_d[tb_pad(b2 + 1)];
+            if (dR > dL && dR > d2) {
+              c = tb_form(t0 + a, t0 + b, t0 + b2, dL, d2, dR, c, s_com[tb_pad(b + 1)], o);
+              b = b2;
+              dR = d2;
+              continue;
+            }
+          }
+          break;
+        }
+        s_com[tb_pad(a)] = c;
+        s_hi[tb_pad(a)] = (short)b;
+        s_lo[tb_pad(b)] = (short)a;
+      }
+    }
+    __syncthreads();
+  }
+  if (gridDim.x == 1) return;  // the tile holds the whole tree: its root is complete
+
+  // ---- phase 3: subtrees whose sibling lies in another tile climb through global memory ------------------------
+  if (tid == 0) {
+    int nr = 0;
+    for (int q = 0; q < tcount && nr < TB_MAX_ROOTS; q = s_hi[tb_pad(q)] + 1) s_roots[nr++] = q;
+    s_nroots = nr;
+  }
+  __syncthreads();
+  for (int i = tid; i < s_nroots; i += TB_THREADS) {
+    const int a = s_roots[i], b = s_hi[tb_pad(a)];
+    int l = t0 + a, r = t0 + b;
+    int dL = s_d[tb_pad(a)], dR = s_d[tb_pad(b + 1)];
+    float4 cur = s_com[tb_pad(a)];
+    while (!(l == 0 && r == n - 1)) {
+      const bool is_left = dR > dL;
+      const int g = is_left ? r : l - 1;  // split of the parent: where the two children meet
+      __threadfence();                    // this subtree's record is visible before its arrival
+      const int old = atomicExch(&slot[g], (is_left ? l : r) + 1);
+      if (old == 0) break;  // first to arrive: the sibling's thread completes the parent
+      slot[g] = 0;          // both children have arrived: the slot is clean for the next build
+      __threadfence();
+      const int far = old - 1;
+      const int dS = is_left ? dR : dL;
+      float4 sib;
+      if (is_left) {
+        sib = __ldcg(o.node_com + ((far == g + 1) ? o.leaf0 + g + 1 : g + 1));
+        r = far;
+        dR = bh_delta_adj(keys, n, r);
+        cur = tb_form(l, g, r, dL, dR, dS, cur, sib, o);
+      } else {
+        sib = __ldcg(o.node_com + ((far == g) ? o.leaf0 + g : g));
+        l = far;
+        dL = bh_delta_adj(keys, n, l - 1);
+        cur = tb_form(l, g, r, dL, dR, dS, sib, cur, o);
+      }
+    }
+  }
+}
+
+// parent[] is needed by nb_bh_export only (parity tests): derived from the children on demand
+__global__ void __launch_bounds__(256) bh_parent_kernel(int n, const int4* __restrict__ meta, int32_t* __restrict__ parent) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i == 0) parent[0] = -1;
+  if (i >= n - 1) return;
+  const int4 m = meta[i];
+  parent[m.x] = i;
+  parent[m.y] = i;
 }
 
 // ---- traversal ---------------------------------------------------------------------------------------
@@ -536,6 +619,15 @@ __global__ void __launch_bounds__(256) bh_shard_finish_kernel(const float4* __re
   }
 }
 
+constexpr size_t kTreeSmem = (size_t)TB_PADDED * (sizeof(float4) + sizeof(int) + 2 * sizeof(short));
+
+// per-device kernel attribute (opt-in shared memory), set when a context is created on the device
+int bh_init_device(nb_context* ctx) {
+  (void)ctx;
+  NB_CUDA(cudaFuncSetAttribute(bh_tree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTreeSmem));
+  return NB_OK;
+}
+
 static BH* bh_get(nb_context* ctx) {
   if (!ctx->bh) ctx->bh = new (std::nothrow) BH();
   return ctx->bh;
@@ -544,8 +636,9 @@ static BH* bh_get(nb_context* ctx) {
 void bh_destroy(nb_context* ctx) {
   if (!ctx->bh) return;
   BH* b = ctx->bh;
-  b->keys.release(); b->perm.release(); b->packed.release(); b->node_com.release(); b->meta.release();
-  b->parent.release(); b->flags.release(); b->misc.release(); b->range.release(); b->groups.release();
+  b->keys.release(); b->perm.release(); b->keys_alt.release(); b->perm_alt.release(); b->packed.release();
+  b->node_com.release(); b->meta.release(); b->parent.release(); b->slot.release(); b->misc.release();
+  b->groups.release();
   if (b->h_flag) cudaFreeHost(b->h_flag);
   delete b;
   ctx->bh = nullptr;
@@ -567,14 +660,19 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
   b->n = n;
   if (int rc = b->keys.ensure(n * 4)) return rc;
   if (int rc = b->perm.ensure(n * 4)) return rc;
+  if (int rc = b->keys_alt.ensure(n * 4)) return rc;
+  if (int rc = b->perm_alt.ensure(n * 4)) return rc;
   if (int rc = b->packed.ensure(n * sizeof(float4))) return rc;
   if (int rc = b->node_com.ensure((2 * n) * sizeof(float4))) return rc;
   if (int rc = b->meta.ensure(n * sizeof(int4))) return rc;
-  if (int rc = b->parent.ensure(2 * n * 4)) return rc;
-  if (int rc = b->flags.ensure(n * 4)) return rc;
   if (int rc = b->misc.ensure(64 * 4)) return rc;
-  if (int rc = b->range.ensure(n * sizeof(int2))) return rc;
   if (int rc = b->groups.ensure(n * sizeof(int2))) return rc;
+  if (b->slot.cap < n * 4) {
+    // meeting slots of the tree build: zero when idle (the second child to arrive cleans its slot), so they
+    // are cleared only when (re)allocated
+    if (int rc = b->slot.ensure(n * 4)) return rc;
+    NB_CUDA(cudaMemsetAsync(b->slot.p, 0, b->slot.cap, st));
+  }
   {
     const char* e = getenv("NB_BH_GROUP");
     const int g = (e && atoi(e) == 32) ? 32 : 64;
@@ -602,41 +700,28 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
   {
     NB_STAGE(ctx, st, "bh.morton");
     bh_morton_kernel<<<gn, 256, 0, st>>>(d->pos_x, d->pos_y, d->pos_z, d->mass, n, misc, b->keys.as<uint32_t>(),
-                                         b->perm.as<int32_t>(), b->packed.as<float4>());
+                                         b->packed.as<float4>());
     NB_LAUNCH_CHECK(ctx);
   }
   {
     NB_STAGE(ctx, st, "bh.sort");
-    if (int rc = sort_pairs(ctx, b->keys.as<uint32_t>(), b->perm.as<int32_t>(), n, 30, st)) return rc;
-  }
-  float4* com = b->node_com.as<float4>();
-  {
-    NB_STAGE(ctx, st, "bh.gather");
-    bh_gather_kernel<<<gn, 256, 0, st>>>(b->packed.as<float4>(), n, b->perm.as<int32_t>(), com + (n - 1));
-    NB_LAUNCH_CHECK(ctx);
-  }
-  NB_CUDA(cudaMemsetAsync(b->parent.p, 0xff, sizeof(int32_t), st));  // parent[0] = -1 (also when n == 1)
-  if (n > 1) {
-    {
-      NB_STAGE(ctx, st, "bh.karras");
-      NB_CUDA(cudaMemsetAsync(b->flags.p, 0, (n - 1) * 4, st));
-      const unsigned gi = (unsigned)((n - 1 + 255) / 256);
-      bh_karras_kernel<<<gi, 256, 0, st>>>(b->keys.as<uint32_t>(), (int)n, b->meta.as<int4>(),
-                                           b->parent.as<int32_t>(), b->range.as<int2>());
-      NB_LAUNCH_CHECK(ctx);
-    }
-    NB_STAGE(ctx, st, "bh.com");
-    if (getenv("NB_BH_COM_GLOBAL"))  // the all-global version, kept for A/B
-      bh_com_kernel<<<gn, 256, 0, st>>>((int)n, b->meta.as<int4>(), b->parent.as<int32_t>(), b->flags.as<int>(), com);
-    else
-      bh_com_tile_kernel<<<(unsigned)((n + COM_TILE - 1) / COM_TILE), COM_TILE, 0, st>>>(
-          (int)n, b->meta.as<int4>(), b->parent.as<int32_t>(), b->range.as<int2>(), b->flags.as<int>(), com);
-    NB_LAUNCH_CHECK(ctx);
+    if (int rc = sort_pairs_db(ctx, b->keys.as<uint32_t>(), b->perm.as<int32_t>(), b->keys_alt.as<uint32_t>(),
+                               b->perm_alt.as<int32_t>(), n, 30, true, &b->keys_sorted, &b->perm_sorted, st))
+      return rc;
   }
   {
-    NB_STAGE(ctx, st, "bh.groups");
-    bh_groups_kernel<<<gn, 256, 0, st>>>((int)n, b->super, b->group, b->parent.as<int32_t>(), b->range.as<int2>(),
-                                         b->groups.as<int2>(), reinterpret_cast<int*>(misc) + 44);
+    NB_STAGE(ctx, st, "bh.tree");
+    TreeOut o;
+    o.node_com = b->node_com.as<float4>();
+    o.meta = b->meta.as<int4>();
+    o.groups = b->groups.as<int2>();
+    o.ngroups = reinterpret_cast<int*>(misc) + 44;
+    o.n = (int)n;
+    o.leaf0 = (int)n - 1;
+    o.smax = b->super;
+    o.gmax = b->group;
+    bh_tree_kernel<<<(unsigned)((n + TB_TILE - 1) / TB_TILE), TB_THREADS, kTreeSmem, st>>>(
+        b->keys_sorted, b->perm_sorted, b->packed.as<float4>(), b->slot.as<int>(), o);
     NB_LAUNCH_CHECK(ctx);
   }
   b->built = true;
@@ -698,7 +783,7 @@ int bh_forces(nb_context* ctx, const nb_particles* d, float theta, float G, floa
   const BhShard shv = shard ? *shard : none;
 #define NB_BH_LAUNCH_S(BPL_, E_, S_)                                                                               \
   bh_force_kernel<BPL_, E_, S_><<<grid, BH_WARPS * 32, smem, st>>>(                                                \
-      (int)n, b->node_com.as<float4>(), b->meta.as<int4>(), b->perm.as<int32_t>(), misc, theta * theta, G, eps2,  \
+      (int)n, b->node_com.as<float4>(), b->meta.as<int4>(), b->perm_sorted, misc, theta * theta, G, eps2,         \
       d->acc_x, d->acc_y, d->acc_z, reinterpret_cast<unsigned long long*>(misc + 40), b->d_flag,                   \
       b->groups.as<int2>(), reinterpret_cast<const int*>(misc) + 44, cursor, b->stack_cap,                        \
       reinterpret_cast<int*>(misc) + 46, shv)
@@ -739,8 +824,8 @@ int bh_shard_finish(nb_context* ctx, const float4* acc_sorted, const nb_particle
     return NB_ERR_INVALID;
   }
   const unsigned gn = (unsigned)((n + 255) / 256);
-  if (kick) bh_shard_finish_kernel<true><<<gn, 256, 0, st>>>(acc_sorted, b->perm.as<int32_t>(), *d, n, dt);
-  else bh_shard_finish_kernel<false><<<gn, 256, 0, st>>>(acc_sorted, b->perm.as<int32_t>(), *d, n, dt);
+  if (kick) bh_shard_finish_kernel<true><<<gn, 256, 0, st>>>(acc_sorted, b->perm_sorted, *d, n, dt);
+  else bh_shard_finish_kernel<false><<<gn, 256, 0, st>>>(acc_sorted, b->perm_sorted, *d, n, dt);
   NB_LAUNCH_CHECK(ctx);
   return NB_OK;
 }
@@ -779,9 +864,14 @@ int nb_bh_export(nb_context* ctx, uint32_t* keys, int32_t* perm, int32_t* left, 
   NB_CUDA(cudaDeviceSynchronize());
   BH* b = ctx->bh;
   const size_t n = b->n;
-  if (keys) NB_CUDA(cudaMemcpy(keys, b->keys.p, n * 4, cudaMemcpyDeviceToHost));
-  if (perm) NB_CUDA(cudaMemcpy(perm, b->perm.p, n * 4, cudaMemcpyDeviceToHost));
-  if (parent) NB_CUDA(cudaMemcpy(parent, b->parent.p, (2 * n - 1) * 4, cudaMemcpyDeviceToHost));
+  if (keys) NB_CUDA(cudaMemcpy(keys, b->keys_sorted, n * 4, cudaMemcpyDeviceToHost));
+  if (perm) NB_CUDA(cudaMemcpy(perm, b->perm_sorted, n * 4, cudaMemcpyDeviceToHost));
+  if (parent) {
+    if (int rc = b->parent.ensure(2 * n * 4)) return rc;
+    bh_parent_kernel<<<(unsigned)((n + 255) / 256), 256>>>((int)n, b->meta.as<int4>(), b->parent.as<int32_t>());
+    NB_CUDA(cudaGetLastError());
+    NB_CUDA(cudaMemcpy(parent, b->parent.p, (2 * n - 1) * 4, cudaMemcpyDeviceToHost));
+  }
   if (node_com) NB_CUDA(cudaMemcpy(node_com, b->node_com.p, (2 * n - 1) * sizeof(float4), cudaMemcpyDeviceToHost));
   if ((left || right || prefix) && n > 1) {
     int4* h = (int4*)malloc((n - 1) * sizeof(int4));

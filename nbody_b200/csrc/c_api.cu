@@ -112,6 +112,7 @@ int bh_poll_error(nb_context* ctx);
 int peer_poll_error(nb_context* ctx);
 int sort_poll_error(nb_context* ctx);
 int sort_init_device(nb_context* ctx);
+int bh_init_device(nb_context* ctx);
 void sort_destroy(nb_context* ctx);
 void sh_destroy(nb_context* ctx);
 void render_destroy(nb_context* ctx);
@@ -211,7 +212,9 @@ int nb_context_create(int device, size_t max_bodies_hint, nb_context** out) {
     delete ctx;
     return NB_ERR_RESOURCE;
   }
-  if (int rc = sort_init_device(ctx)) {  // per-device kernel attributes, set once here (not lazily from a sort)
+  int rc_init = sort_init_device(ctx);  // per-device kernel attributes, set once here (not lazily from a sort)
+  if (!rc_init) rc_init = bh_init_device(ctx);
+  if (int rc = rc_init) {
     ctx->direct_work.release();
     delete ctx;
     return rc;

@@ -449,11 +449,11 @@ int sort_poll_error(nb_context* ctx) {
   return NB_OK;
 }
 
-// Sorts (keys, vals) by bits [0, end_bit) of the keys.  The passes ping-pong between the caller's arrays and
-// context scratch; *out_keys / *out_vals say where the result is (no copy).  identity_vals: vals need not be
+// Sorts (keys, vals) by bits [0, end_bit) of the keys.  The passes ping-pong between (d_keys, d_vals) and the
+// caller's second pair of buffers (keys_alt, vals_alt); *out_keys / *out_vals say where the result is (no copy).  identity_vals: vals need not be
 // initialised -- the first pass writes value = index.
-int sort_pairs_db(nb_context* ctx, uint32_t* d_keys, int32_t* d_vals, size_t n, int end_bit, bool identity_vals,
-                  uint32_t** out_keys, int32_t** out_vals, cudaStream_t st) {
+int sort_pairs_db(nb_context* ctx, uint32_t* d_keys, int32_t* d_vals, uint32_t* keys_alt, int32_t* vals_alt, size_t n,
+                  int end_bit, bool identity_vals, uint32_t** out_keys, int32_t** out_vals, cudaStream_t st) {
   *out_keys = d_keys;
   *out_vals = d_vals;
   if (end_bit < 1) end_bit = 1;
@@ -471,8 +471,6 @@ int sort_pairs_db(nb_context* ctx, uint32_t* d_keys, int32_t* d_vals, size_t n, 
   if (int rc = sort_poll_error(ctx)) return rc;
   const RsPlan plan = rs_plan(end_bit);
   const size_t ntiles = (n + RS_TILE - 1) / RS_TILE;
-  if (int rc = ctx->sort_keys2.ensure(n * sizeof(uint32_t))) return rc;
-  if (int rc = ctx->sort_vals2.ensure(n * sizeof(int32_t))) return rc;
   // scratch: [passes][2048] histograms, [passes] tickets (padded to 64 words), per pass [ntiles][2^bits] status
   const size_t head = (size_t)RS_MAX_PASSES * RS_MAX_BINS + 64;
   size_t words = head;
@@ -492,8 +490,8 @@ int sort_pairs_db(nb_context* ctx, uint32_t* d_keys, int32_t* d_vals, size_t n, 
     rs_scan_kernel<<<plan.passes, RS_MAX_BINS / 2, 0, st>>>(hist);
     NB_LAUNCH_CHECK(ctx);
   }
-  uint32_t *ka = d_keys, *kb = ctx->sort_keys2.as<uint32_t>();
-  int32_t *va = d_vals, *vb = ctx->sort_vals2.as<int32_t>();
+  uint32_t *ka = d_keys, *kb = keys_alt;
+  int32_t *va = d_vals, *vb = vals_alt;
   for (int p = 0; p < plan.passes; p++) {
     const bool ident = identity_vals && p == 0;
 #define NB_RS_LAUNCH(RB_, ID_)                                                                                        \
@@ -522,7 +520,11 @@ int sort_pairs(nb_context* ctx, uint32_t* d_keys, int32_t* d_vals, size_t n, int
   if (n < 2) return NB_OK;
   uint32_t* ko;
   int32_t* vo;
-  if (int rc = sort_pairs_db(ctx, d_keys, d_vals, n, end_bit, false, &ko, &vo, st)) return rc;
+  if (int rc = ctx->sort_keys2.ensure(n * sizeof(uint32_t))) return rc;
+  if (int rc = ctx->sort_vals2.ensure(n * sizeof(int32_t))) return rc;
+  if (int rc = sort_pairs_db(ctx, d_keys, d_vals, ctx->sort_keys2.as<uint32_t>(), ctx->sort_vals2.as<int32_t>(), n,
+                             end_bit, false, &ko, &vo, st))
+    return rc;
   if (ko != d_keys) {
     NB_CUDA(cudaMemcpyAsync(d_keys, ko, n * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
     NB_CUDA(cudaMemcpyAsync(d_vals, vo, n * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));

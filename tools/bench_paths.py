@@ -25,9 +25,9 @@ HBM_FALLBACK_GBS = 6400.0  # B200_PROFILING.md: measured copy bandwidth to use w
 # algorithmic bytes per body of each stage, with the layouts of DESIGN.md sec. 2
 ALGO_BYTES = {
     "bh.bbox": 12,            # x, y, z read once
-    "bh.morton": 16 + 4 + 4 + 16,  # x,y,z,m read; key, identity value and packed {x,y,z,m} written
-    "bh.gather": 4 + 16 + 16, "bh.karras": 4 + 16 + 8 + 8, "bh.com": 76, "bh.groups": 16,  # round-1 kernels
-    "bh.tree": 4 + 4 + 16 + 16 + 32,  # keys + perm read, packed float4 gathered, leaf record + 32-B node record written
+    "bh.morton": 16 + 4 + 16,  # x,y,z,m read; key and packed {x,y,z,m} written (the sort generates the identity values)
+    # keys + perm read, packed float4 gathered, leaf record written; per internal node {left,right,prefix} + centre of mass
+    "bh.tree": 4 + 4 + 16 + 16 + 16 + 16,
     "sh.bbox": 12,
     "sh.assign": 16 + 4 + 4 + 4 + 16,  # x,y,z,m read; particle_cell, key, identity value and packed written
     "sh.ranges_gather": 4 + 4 + 16 + 16,  # sorted key + index read, packed gathered, cell-ordered float4 written (+ cell ranges)
@@ -114,7 +114,7 @@ def bench_bh(n, ic="plummer", theta=0.5, reps=5):
         _lib.check(L.nb_bh_build(ctx.handle, C.byref(d.c), s))
         _lib.check(L.nb_bh_forces(ctx.handle, C.byref(d.c), theta, 1.0, 0.01, s))
     step_ms = timed(step, reps, warm=1)
-    stg = stages(step, 3, n, sort_bits=30, identity_values=IDENTITY_SORT)
+    stg = stages(step, 3, n, sort_bits=30, identity_values=True)
     inter, cnt = C.c_uint64(0), C.c_int(0)
     _lib.check(L.nb_bh_stats(ctx.handle, C.byref(inter), C.byref(cnt)))
     deep, cap = C.c_int(0), C.c_int(0)
@@ -129,9 +129,6 @@ def bench_bh(n, ic="plummer", theta=0.5, reps=5):
                 tflops_20flop=inter.value * 20.0 / force / 1e9, stack_deepest=deep.value, stack_cap=cap.value,
                 stages=stg, timing="CUDA events, mean of %d calls after warm-up; stages under the library's stage "
                                    "timers (events between the kernels of one call)" % reps)
-
-
-IDENTITY_SORT = False  # set when the builds stop writing / reading the identity permutation
 
 
 def bench_sh(n, reps=5):
@@ -149,7 +146,7 @@ def bench_sh(n, reps=5):
     def step():
         _lib.check(L.nb_sh_build(ctx.handle, C.byref(d.c), 1.0, None))
         _lib.check(L.nb_sh_forces(ctx.handle, C.byref(d.c), 2.0, 1.0, 0.01, None))
-    stg = stages(step, 3, n, sort_bits=bits, identity_values=IDENTITY_SORT)
+    stg = stages(step, 3, n, sort_bits=bits, identity_values=False)
     peak, src = hbm_peak_gbs()
     build_bytes = sum(r.get("algorithmic_bytes", 0) for k, r in stg.items() if k != "sh.force")
     return dict(path="spatial_hash", n=n, side=side, cell_size=1.0, cutoff=2.0, cells=t.value, key_bits=bits,
