@@ -100,6 +100,8 @@ def lib():
     L.orc_lbvh_cell_size.restype = f
     L.orc_lbvh_forces.argtypes = [i, i32p, i32p, i32p, i32p, i32p, f32p, f32p, f32p, f32p, f32p, f, f, f, i, i,
                                   f32p, f32p, f32p, C.POINTER(C.c_uint64)]
+    L.orc_lbvh_forces_ex.argtypes = [i, i32p, i32p, i32p, i32p, i32p, f32p, f32p, f32p, f32p, f32p, f, f, f, i, i, i, f,
+                                     f32p, f32p, f32p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     L.orc_cell_index.argtypes = [f, f, f, f, i32p]
     L.orc_grid_dims.argtypes = [f32p, f, i32p]
     L.orc_assign_cells.argtypes = [i, f32p, f32p, f32p, f32p, f, i32p, i32p]
@@ -282,6 +284,19 @@ def lbvh_forces(tree, com, sx, sy, sz, bb, theta, G, eps, group=32, super_=None)
                           _f32(sx), _f32(sy), _f32(sz), _f32(bb), theta, G, eps, group,
                           8 * group if super_ is None else super_, ax, ay, az, C.byref(cnt))
     return ax, ay, az, cnt.value
+
+
+def lbvh_forces_ex(tree, com, sx, sy, sz, bb, theta, G, eps, group=64, super_=None, mode=0, alpha=0.0):
+    """lbvh_forces with the grouping / acceptance variants (see oracle/lbvh.c); returns also (groups, list entries)."""
+    n = sx.size
+    ax, ay, az = (np.zeros(n, np.float32) for _ in range(3))
+    cnt = C.c_uint64(0)
+    stats = (C.c_uint64 * 2)()
+    lib().orc_lbvh_forces_ex(n, tree["left"], tree["right"], tree["prefix"], tree["first"], tree["last"],
+                             np.ascontiguousarray(com).reshape(-1), _f32(sx), _f32(sy), _f32(sz), _f32(bb), theta, G,
+                             eps, group, 8 * group if super_ is None else super_, mode, alpha, ax, ay, az,
+                             C.byref(cnt), stats)
+    return ax, ay, az, cnt.value, int(stats[0]), int(stats[1])
 
 
 # ---- spatial hash ------------------------------------------------------------------------

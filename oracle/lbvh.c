@@ -115,10 +115,52 @@ float orc_lbvh_cell_size(int L, const float bbox[6]) {
   return fmaxf(ex, fmaxf(ey, ez));
 }
 
+/* hybrid grouping (mode bit 0): inside a supergroup, follow the tree split whenever that costs no extra warp
+ * (ceil(a / group) + ceil(b / group) == ceil(c / group)), else cut equal runs */
+static void hybrid_groups(int ni, int leaf0, int group, const int32_t* left, const int32_t* right,
+                          const int32_t* range_first, const int32_t* range_last, int32_t* gfirst, int32_t* gcount,
+                          int* ngroups) {
+  if (ni >= leaf0) {
+    gfirst[*ngroups] = ni - leaf0;
+    gcount[(*ngroups)++] = 1;
+    return;
+  }
+  const int first = range_first[ni], c = range_last[ni] - range_first[ni] + 1;
+  if (c <= group) {
+    gfirst[*ngroups] = first;
+    gcount[(*ngroups)++] = c;
+    return;
+  }
+  const int l = left[ni], r = right[ni];
+  const int a = l >= leaf0 ? 1 : range_last[l] - range_first[l] + 1, b = c - a;
+  const int need = (c + group - 1) / group;
+  if ((a + group - 1) / group + (b + group - 1) / group == need) {
+    hybrid_groups(l, leaf0, group, left, right, range_first, range_last, gfirst, gcount, ngroups);
+    hybrid_groups(r, leaf0, group, left, right, range_first, range_last, gfirst, gcount, ngroups);
+    return;
+  }
+  for (int i = 0; i < need; i++) {
+    const int b0 = (int)(((long long)i * c) / need), b1 = (int)(((long long)(i + 1) * c) / need);
+    gfirst[*ngroups] = first + b0;
+    gcount[(*ngroups)++] = b1 - b0;
+  }
+}
+
 void orc_lbvh_forces(int n, const int32_t* left, const int32_t* right, const int32_t* prefix,
                      const int32_t* range_first, const int32_t* range_last, const float* node_com,
                      const float* sx, const float* sy, const float* sz, const float bbox[6], float theta, float G,
                      float eps, int group, int super, float* ax, float* ay, float* az, uint64_t* interactions) {
+  orc_lbvh_forces_ex(n, left, right, prefix, range_first, range_last, node_com, sx, sy, sz, bbox, theta, G, eps, group,
+                     super, 0, 0.0f, ax, ay, az, interactions, 0);
+}
+
+/* mode bit 0: hybrid grouping; alpha: acceptance distance^2 = (1 - alpha) * dmin^2 + alpha * dcentre^2 (alpha = 0: the
+ * conservative group-box test).  stats[0] = groups, stats[1] = sum over groups of accepted list entries. */
+void orc_lbvh_forces_ex(int n, const int32_t* left, const int32_t* right, const int32_t* prefix,
+                        const int32_t* range_first, const int32_t* range_last, const float* node_com,
+                        const float* sx, const float* sy, const float* sz, const float bbox[6], float theta, float G,
+                        float eps, int group, int super, int mode, float alpha, float* ax, float* ay, float* az,
+                        uint64_t* interactions, uint64_t* stats) {
   /* Sequential restatement of nbody_b200/csrc/bh.cu: bh_groups_kernel + bh_force_kernel.  A
    * supergroup is a maximal subtree with at most `super` (>= group) leaves (a lone leaf whose parent
    * is larger is a supergroup of one); its c bodies are cut into ceil(c / group) runs of consecutive
@@ -143,7 +185,7 @@ void orc_lbvh_forces(int n, const int32_t* left, const int32_t* right, const int
     size2_of[L] = s * s;
   }
   size2_of[31] = 0.0f;
-  uint64_t total = 0;
+  uint64_t total = 0, entries = 0;
   /* groups: top-down, a node whose leaf range fits becomes a group */
   int32_t* gfirst = (int32_t*)malloc(sizeof(int32_t) * (size_t)n);
   int32_t* gcount = (int32_t*)malloc(sizeof(int32_t) * (size_t)n);
@@ -157,6 +199,8 @@ void orc_lbvh_forces(int n, const int32_t* left, const int32_t* right, const int
       if (ni >= leaf0) {
         gfirst[ngroups] = ni - leaf0;
         gcount[ngroups++] = 1;
+      } else if ((mode & 1) && range_last[ni] - range_first[ni] + 1 <= super) {
+        hybrid_groups(ni, leaf0, group, left, right, range_first, range_last, gfirst, gcount, &ngroups);
       } else if (range_last[ni] - range_first[ni] + 1 <= super) {
         const int first = range_first[ni], c = range_last[ni] - range_first[ni] + 1;
         const int runs = (c + group - 1) / group;
@@ -172,7 +216,7 @@ void orc_lbvh_forces(int n, const int32_t* left, const int32_t* right, const int
     }
     free(st);
   }
-#pragma omp parallel for schedule(dynamic, 16) reduction(+ : total)
+#pragma omp parallel for schedule(dynamic, 16) reduction(+ : total, entries)
   for (int g = 0; g < ngroups; g++) {
     const int k0 = gfirst[g], cnt = gcount[g];
     float accx[64], accy[64], accz[64];
@@ -204,6 +248,12 @@ void orc_lbvh_forces(int n, const int32_t* left, const int32_t* right, const int
           float ddy = fmaxf(fmaxf(lo[1] - c[1], c[1] - hi[1]), 0.0f);
           float ddz = fmaxf(fmaxf(lo[2] - c[2], c[2] - hi[2]), 0.0f);
           float d2 = fmaf(ddz, ddz, fmaf(ddy, ddy, fmaf(ddx, ddx, eps2)));
+          if (alpha != 0.0f) {
+            const float cx = 0.5f * (lo[0] + hi[0]) - c[0], cy = 0.5f * (lo[1] + hi[1]) - c[1],
+                        cz = 0.5f * (lo[2] + hi[2]) - c[2];
+            const float dc2 = cx * cx + cy * cy + cz * cz + eps2;
+            d2 = (1.0f - alpha) * d2 + alpha * dc2;
+          }
           accept = size2_of[prefix[ni]] < theta2 * d2;
         }
         if (accept) {
@@ -233,6 +283,7 @@ void orc_lbvh_forces(int n, const int32_t* left, const int32_t* right, const int
           }
         }
         total += (uint64_t)ne * (uint64_t)cnt;
+        entries += (uint64_t)ne;
         for (int e = ne; e < nl; e++) list[e - ne] = list[e];
         nl -= ne;
       }
@@ -246,4 +297,8 @@ void orc_lbvh_forces(int n, const int32_t* left, const int32_t* right, const int
   free(gfirst);
   free(gcount);
   if (interactions) *interactions = total;
+  if (stats) {
+    stats[0] = (uint64_t)ngroups;
+    stats[1] = entries;
+  }
 }
