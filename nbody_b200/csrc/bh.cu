@@ -177,17 +177,49 @@ struct TreeOut {
   int n, leaf0, smax, gmax;
 };
 
-// Traversal groups of a supergroup (a maximal subtree [cl, cr] of <= smax leaves): ceil(c / gmax) runs of
-// consecutive bodies of (almost) equal length, run i starting at floor(i * c / runs).  With smax == gmax the
-// groups are the subtrees themselves (mean fill 69 % of gmax), with smax = 8 * gmax the runs are 89-100 % full
-// and still confined to one cell.
-__device__ __forceinline__ void tb_emit(int cl, int cr, const TreeOut& o) {
-  const int c = cr - cl + 1;
-  const int runs = (c + o.gmax - 1) / o.gmax;
+// Traversal groups of a supergroup (a maximal subtree of <= smax leaves, node `id` with leaves [cl, cr]).
+// Wanted: as few groups as possible (a warp costs the same whether its 64 lane-slots are full or not) that are as
+// compact as possible (a group opens every node its bounding box is close to).  ceil(c / gmax) groups is the
+// minimum; cutting the c bodies into that many runs of (almost) equal length, run i starting at
+// floor(i * c / runs), achieves it but ignores the tree, following the tree all the way down to subtrees of
+// <= gmax leaves is compact but needs ~45 % more groups (mean fill 69 %).  So: descend the tree as long as that
+// costs no extra group -- ceil(a / gmax) + ceil(b / gmax) == ceil(c / gmax) for the children's leaf counts a, b --
+// and cut equal runs where it would (3296 instead of 3429 list entries x lane-slots per body on a 262 144-body
+// Plummer sphere, same number of groups, same error: oracle/lbvh.c counts it on the CPU).  The subtree's nodes are
+// complete when this runs; the ones written by other thread blocks are read through L2.
+__device__ __forceinline__ void tb_emit_runs(int cl, int c, int runs, const TreeOut& o) {
   const int base = atomicAdd(o.ngroups, runs);
   for (int i = 0; i < runs; i++) {
     const int s0 = (int)(((long long)i * c) / runs), s1 = (int)(((long long)(i + 1) * c) / runs);
     o.groups[base + i] = make_int2(cl + s0, s1 - s0);
+  }
+}
+__device__ __noinline__ void tb_emit(int id, int cl, int cr, const TreeOut& o) {
+  constexpr int CAP = 32;
+  int sid[CAP], sl[CAP], sr[CAP];
+  int sp = 0;
+  sid[0] = id; sl[0] = cl; sr[0] = cr;
+  sp = 1;
+  while (sp > 0) {
+    sp--;
+    const int ni = sid[sp], l = sl[sp], r = sr[sp];
+    const int c = r - l + 1;
+    const int need = (c + o.gmax - 1) / o.gmax;
+    if (need == 1) {
+      tb_emit_runs(l, c, 1, o);
+      continue;
+    }
+    const int4 m = __ldcg(o.meta + ni);
+    const int g = (m.x >= o.leaf0) ? m.x - o.leaf0 : m.x;  // the left child ends at the split
+    const int a = g - l + 1, b = r - g;
+    if ((a + o.gmax - 1) / o.gmax + (b + o.gmax - 1) / o.gmax == need && sp + 2 <= CAP) {
+      sid[sp] = m.y; sl[sp] = g + 1; sr[sp] = r;
+      sp++;
+      sid[sp] = m.x; sl[sp] = l; sr[sp] = g;
+      sp++;
+    } else {
+      tb_emit_runs(l, c, need, o);
+    }
   }
 }
 
@@ -204,10 +236,10 @@ __device__ __forceinline__ float4 tb_form(int l, int g, int r, int dL, int dR, i
   o.meta[id] = make_int4(lc, rc, p, 0);
   o.node_com[id] = c;
   if (r - l + 1 > o.smax) {
-    if (g - l + 1 <= o.smax) tb_emit(l, g, o);
-    if (r - g <= o.smax) tb_emit(g + 1, r, o);
+    if (g - l + 1 <= o.smax) tb_emit(lc, l, g, o);
+    if (r - g <= o.smax) tb_emit(rc, g + 1, r, o);
   } else if (l == 0 && r == o.n - 1) {
-    tb_emit(l, r, o);  // the whole tree is one supergroup
+    tb_emit(id, l, r, o);  // the whole tree is one supergroup
   }
   return c;
 }
@@ -252,7 +284,7 @@ __global__ void __launch_bounds__(TB_THREADS, 2) bh_tree_kernel(const uint32_t* 
   }
   __syncthreads();
   if (n == 1) {  // a single leaf: no internal node, one group
-    if (tid == 0) tb_emit(0, 0, o);
+    if (tid == 0) tb_emit(0, 0, 0, o);
     return;
   }
 
@@ -460,19 +492,28 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
   unsigned visits = 0;
   if (lane == 0) stack[0] = 0;
   __syncwarp();
-  for (;;) {
+  // The node fetches are software-pipelined: the next round's nodes are popped and their loads issued BEFORE the
+  // current interaction list is evaluated, so the (L2 / DRAM) latency of the walk hides under the pair arithmetic.
+  int ni;
+  bool have;
+  float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+  int4 mt = make_int4(0, 0, 31, 0);
+  auto pop_and_fetch = [&]() {
     const int m = min(sp, 32);
-    const bool have = lane < m;
-    const int ni = have ? stack[sp - m + lane] : 0;
+    have = lane < m;
+    ni = have ? stack[sp - m + lane] : 0;
     sp -= m;
     __syncwarp();
-    float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
-    int4 mt = make_int4(0, 0, 31, 0);
-    const bool leaf = ni >= leaf0;
+    c = make_float4(0.f, 0.f, 0.f, 0.f);
+    mt = make_int4(0, 0, 31, 0);
     if (have) {  // both fetches issue together (no dependence of the second on the first's data)
       c = node_com[ni];
-      if (!leaf) mt = meta[ni];
+      if (ni < leaf0) mt = meta[ni];
     }
+  };
+  pop_and_fetch();
+  for (;;) {
+    const bool leaf = ni >= leaf0;
     const bool valid = have && c.w != 0.f;  // total_mass == 0 -> skipped (:157-158)
     bool acc = leaf;
     if (valid && !leaf) {
@@ -500,6 +541,7 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
     sp += npush;
     __syncwarp();
     const bool done = (sp == 0);
+    if (!done) pop_and_fetch();  // in flight while the list is evaluated
     while (nl >= 32 || (done && nl > 0)) {
       const int ne = min(nl, 32);
       auto body = [&](int e) {
@@ -512,9 +554,9 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
           float r0, r1;
           upk(d2, r0, r1);
           float i0 = rsq(r0), i1 = rsq(r1);
-          if (EPS0) {  // own leaf / exact coincidence at eps = 0
-            i0 = (r0 > 0.f) ? i0 : 0.f;
-            i1 = (r1 > 0.f) ? i1 : 0.f;
+          if (EPS0) {  // own leaf / exact coincidence at eps ~ 0
+            i0 = (r0 > eps2) ? i0 : 0.f;
+            i1 = (r1 > eps2) ? i1 : 0.f;
           }
           const f2 ri = pk(i0, i1);
           const f2 f = mul2(pk(gm, gm), mul2(mul2(ri, ri), ri));
@@ -527,7 +569,7 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
             const float dx = p.x - me[b].x, dy = p.y - me[b].y, dz = p.z - me[b].z;
             const float d2 = fmaf(dz, dz, fmaf(dy, dy, fmaf(dx, dx, eps2)));
             float inv = rsq(d2);
-            if (EPS0) inv = (d2 > 0.f) ? inv : 0.f;  // own leaf / exact coincidence at eps = 0
+            if (EPS0) inv = (d2 > eps2) ? inv : 0.f;  // own leaf / exact coincidence at eps ~ 0
             const float f = gm * (inv * inv * inv);
             sx[b] = fmaf(f, dx, sx[b]);
             sy[b] = fmaf(f, dy, sy[b]);
@@ -764,7 +806,7 @@ int bh_forces(nb_context* ctx, const nb_particles* d, float theta, float G, floa
   NB_CUDA(cudaMemsetAsync(cursor, 0, sizeof(int), st));
   const size_t smem = (size_t)BH_WARPS * ((size_t)b->stack_cap * 4 + BH_LIST * 16);
   const float eps2 = eps * eps;
-  const bool eps0 = !(eps2 > 0.f);
+  const bool eps0 = !(eps2 >= NB_EPS2_GUARD);
   if (!b->occ) {
     int o = 0;
     if (b->group == 64)

@@ -70,6 +70,12 @@ __device__ __forceinline__ float rsq(float x) {
   return r;
 }
 
+// Softening below which the force kernels use their guarded instantiation (EPS0): the un-guarded pair body relies
+// on w * d == w * 0 == 0 for the self pair, which needs w = G m (eps^2)^-3/2 finite -- eps^2 = 1e-12 keeps it below
+// 1e18 * G m; under that, a pair whose r^2 + eps^2 does not exceed eps^2 (the body itself, an exact coincidence)
+// contributes 0 by a select, as at eps = 0 (the reference skips j == i by index, force_direct.cu:60).
+constexpr float NB_EPS2_GUARD = 1e-12f;
+
 // ---- mbarrier + 1-D TMA bulk copy (cp.async.bulk, SASS UBLKCP) --------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));

@@ -297,9 +297,9 @@ __global__ void __launch_bounds__(T, NB_DIRECT_THREADS_PER_SM / T) direct_force_
             float r0, r1;
             upk(r2, r0, r1);
             float i0 = rsq(r0), i1 = rsq(r1);
-            if (EPS0) {  // eps == 0: the self pair (and exact coincidences) must contribute 0, not NaN
-              i0 = (r0 > 0.f) ? i0 : 0.f;
-              i1 = (r1 > 0.f) ? i1 : 0.f;
+            if (EPS0) {  // eps ~ 0: the self pair (and exact coincidences) must contribute 0, not NaN
+              i0 = (r0 > eps2) ? i0 : 0.f;
+              i1 = (r1 > eps2) ? i1 : 0.f;
             }
             const f2 ri = pk(i0, i1);
             f2 w;
@@ -454,7 +454,7 @@ int launch_direct_pass(nb_context* ctx, const DirectCfg& cfg, const float4* src,
     return NB_OK;
   }
   const bool big = (&cfg == &kCfgBig);
-  const bool eps0 = !(eps2 > 0.f);
+  const bool eps0 = !(eps2 >= NB_EPS2_GUARD);
   int& occ = ctx->direct_occ[(big ? 0 : 2) + (eps0 ? 1 : 0)];
   if (occ == 0) occ = big ? occupancy<NB_DIRECT_BIG_T, NB_DIRECT_BIG_I, NB_DIRECT_BIG_JT>(eps0) : occupancy<128, 2, 256>(eps0);
   int use_occ = occ;

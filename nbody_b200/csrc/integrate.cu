@@ -212,7 +212,7 @@ int potential_energy(nb_context* ctx, const nb_particles* d, float G, float eps,
   if (int rc = ctx->red.ensure(sizeof(double) * (size_t)nt * (size_t)gy)) return rc;
   dim3 grid((unsigned)nt, (unsigned)gy);
   const float eps2 = eps * eps;
-  if (eps2 > 0.f) potential_kernel<false><<<grid, PE_T, 0, st>>>(*d, n, eps2, (int)nt, (int)chunk, ctx->red.as<double>());
+  if (eps2 >= 1.17549435e-38f) potential_kernel<false><<<grid, PE_T, 0, st>>>(*d, n, eps2, (int)nt, (int)chunk, ctx->red.as<double>());
   else potential_kernel<true><<<grid, PE_T, 0, st>>>(*d, n, eps2, (int)nt, (int)chunk, ctx->red.as<double>());
   NB_LAUNCH_CHECK(ctx);
   double s = 0.0;
@@ -308,7 +308,7 @@ int potential_partial(nb_context* ctx, const float4* src, size_t n_src, size_t t
   if (int rc = ctx->red.ensure(sizeof(double) * (size_t)gi * (size_t)gy)) return rc;
   dim3 grid((unsigned)gi, (unsigned)gy);
   const float eps2 = eps * eps;
-  if (eps2 > 0.f)
+  if (eps2 >= 1.17549435e-38f)  // rsqrt.approx.ftz flushes a denormal eps^2 to 0
     potential_rect_kernel<false><<<grid, PE_T, 0, st>>>(src, n_src, tgt_off, n_tgt, mass_local, eps2, (int)nt, (int)chunk,
                                                         ctx->red.as<double>());
   else

@@ -212,8 +212,9 @@ __device__ __forceinline__ void st_status2(uint32_t* p, uint32_t lo, uint32_t hi
   asm volatile("st.relaxed.gpu.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(lo), "r"(hi) : "memory");
 }
 
-// One pass.  RB: digit capacity of this instantiation (bins = 2^RB sizes the shared memory), `bits` <= RB
-// the digit width of this pass.  gexcl: global exclusive digit offsets; status: tiles x 2^bits words,
+// One pass.  RB: digit capacity of this instantiation (bins = 2^RB sizes the shared memory and RB ballots rank a
+// key -- a run-time ballot count costs a branch per ballot), `bits` <= RB the digit width of this pass (the
+// ballots of the unused high bits see zeros and change nothing).  gexcl: global exclusive digit offsets; status: tiles x 2^bits words,
 // zeroed; ticket: zeroed.  IDENT: the values are the identity permutation (value = index) and not read.
 template <int RB, bool IDENT>
 __global__ void __launch_bounds__(RS_THREADS, 2) rs_pass_kernel(const uint32_t* __restrict__ keys_in,
@@ -266,32 +267,39 @@ __global__ void __launch_bounds__(RS_THREADS, 2) rs_pass_kernel(const uint32_t* 
       for (int k = 0; k < RS_ITEMS; k++) key[k] = (wofs + k * 32 < tcount) ? kin[k * 32] : 0xffffffffu;
     }
   }
-  auto rank = [&](auto full_tag) {
-    constexpr bool FULL = decltype(full_tag)::value;
+  // ranking runs at the top level of the kernel (no enclosing branch: the ballots need no divergence checks);
+  // a partial last tile is handled by one extra ballot per key (padding lanes are nobody's peer)
 #pragma unroll
-    for (int k = 0; k < RS_ITEMS; k++) {
-      const bool ok = FULL || (wofs + k * 32 < tcount);
-      const uint32_t dgt = (key[k] >> shift) & mask;
-      uint32_t peers = FULL ? 0xffffffffu : __ballot_sync(0xffffffffu, ok);  // padding lanes are nobody's peer
+  for (int k = 0; k < RS_ITEMS; k++) {
+    const bool ok = wofs + k * 32 < tcount;
+    const uint32_t dgt = (key[k] >> shift) & mask;
+    uint32_t peers = __ballot_sync(0xffffffffu, ok);
 #pragma unroll
-      for (int b = 0; b < RB; b++) {
-        if (b < bits) {  // warp-uniform
-          const bool bit = (dgt >> b) & 1u;
-          const uint32_t v = __ballot_sync(0xffffffffu, bit);
-          peers &= bit ? v : ~v;
-        }
-      }
-      const int leader = FULL ? (__ffs(peers) - 1) : max(__ffs(peers) - 1, 0);
-      const uint32_t sh16 = (dgt & 1u) * 16u;
-      uint32_t old = 0;
-      // a warp's shared-memory atomics retire in issue order: key k sees the counts of keys < k
-      if (ok && lane == leader) old = atomicAdd(&mycnt[dgt >> 1], (uint32_t)__popc(peers) << sh16);
-      old = __shfl_sync(0xffffffffu, old, leader);
-      pos[k] = ((old >> sh16) & 0xffffu) + __popc(peers & lt);
+    for (int b = 0; b < RB; b++) {
+      // v = lanes whose bit b is set, x = 0 if mine is set else ~0: peers &= ~(v ^ x) ... written as v ^ ~x below.
+      // PTX on purpose: the compiler's own sequence tests the bit twice and shifts first (6 instructions per bit).
+      uint32_t v, x;
+      asm volatile(
+          "{\n"
+          ".reg .pred p;\n"
+          ".reg .b32 t;\n"
+          "and.b32 t, %2, %3;\n"
+          "setp.ne.u32 p, t, 0;\n"
+          "vote.sync.ballot.b32 %0, p, 0xffffffff;\n"
+          "selp.b32 %1, 0, 0xffffffff, p;\n"
+          "}"
+          : "=r"(v), "=r"(x)
+          : "r"(dgt), "r"(1u << b));
+      peers &= v ^ x;
     }
-  };
-  if (full) rank(std::true_type{});
-  else rank(std::false_type{});
+    const int leader = max(__ffs(peers) - 1, 0);
+    const uint32_t sh16 = (dgt & 1u) * 16u;
+    uint32_t old = 0;
+    // a warp's shared-memory atomics retire in issue order: key k sees the counts of keys < k
+    if (ok && lane == leader) old = atomicAdd(&mycnt[dgt >> 1], (uint32_t)__popc(peers) << sh16);
+    old = __shfl_sync(0xffffffffu, old, leader);
+    pos[k] = ((old >> sh16) & 0xffffu) + __popc(peers & lt);
+  }
   __syncthreads();
 
   // ---- per digit: offsets across warps, tile count; publish, look back -----------------------------
@@ -428,10 +436,16 @@ static constexpr size_t rs_smem_bytes() {
 // per-device kernel attributes (opt-in shared memory), set once when a context is created on the device
 int sort_init_device(nb_context* ctx) {
   (void)ctx;
-  NB_CUDA(cudaFuncSetAttribute(rs_pass_kernel<8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rs_smem_bytes<8>()));
-  NB_CUDA(cudaFuncSetAttribute(rs_pass_kernel<8, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rs_smem_bytes<8>()));
-  NB_CUDA(cudaFuncSetAttribute(rs_pass_kernel<RS_MAX_BITS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rs_smem_bytes<RS_MAX_BITS>()));
-  NB_CUDA(cudaFuncSetAttribute(rs_pass_kernel<RS_MAX_BITS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rs_smem_bytes<RS_MAX_BITS>()));
+#define NB_RS_ATTR(RB_)                                                                                    \
+  NB_CUDA(cudaFuncSetAttribute(rs_pass_kernel<RB_, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,   \
+                               (int)rs_smem_bytes<RB_>()));                                               \
+  NB_CUDA(cudaFuncSetAttribute(rs_pass_kernel<RB_, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,    \
+                               (int)rs_smem_bytes<RB_>()))
+  NB_RS_ATTR(4);
+  NB_RS_ATTR(8);
+  NB_RS_ATTR(10);
+  NB_RS_ATTR(11);
+#undef NB_RS_ATTR
   return NB_OK;
 }
 
@@ -497,12 +511,18 @@ int sort_pairs_db(nb_context* ctx, uint32_t* d_keys, int32_t* d_vals, uint32_t* 
 #define NB_RS_LAUNCH(RB_, ID_)                                                                                        \
   rs_pass_kernel<RB_, ID_><<<(unsigned)ntiles, RS_THREADS, rs_smem_bytes<RB_>(), st>>>(                               \
       ka, va, kb, vb, n, plan.shift[p], plan.bits[p], hist + p * RS_MAX_BINS, status, ticket + p, ctx->d_sort_err)
-    if (plan.bits[p] <= 8) {
+    if (plan.bits[p] <= 4) {
+      if (ident) NB_RS_LAUNCH(4, true);
+      else NB_RS_LAUNCH(4, false);
+    } else if (plan.bits[p] <= 8) {
       if (ident) NB_RS_LAUNCH(8, true);
       else NB_RS_LAUNCH(8, false);
+    } else if (plan.bits[p] <= 10) {
+      if (ident) NB_RS_LAUNCH(10, true);
+      else NB_RS_LAUNCH(10, false);
     } else {
-      if (ident) NB_RS_LAUNCH(RS_MAX_BITS, true);
-      else NB_RS_LAUNCH(RS_MAX_BITS, false);
+      if (ident) NB_RS_LAUNCH(11, true);
+      else NB_RS_LAUNCH(11, false);
     }
 #undef NB_RS_LAUNCH
     NB_LAUNCH_CHECK(ctx);

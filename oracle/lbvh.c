@@ -115,8 +115,9 @@ float orc_lbvh_cell_size(int L, const float bbox[6]) {
   return fmaxf(ex, fmaxf(ey, ez));
 }
 
-/* hybrid grouping (mode bit 0): inside a supergroup, follow the tree split whenever that costs no extra warp
- * (ceil(a / group) + ceil(b / group) == ceil(c / group)), else cut equal runs */
+/* Groups of a supergroup, as nbody_b200/csrc/bh.cu tb_emit forms them (mode bit 0; mode 0 = equal runs only, kept for
+ * the comparison): follow the tree split whenever that costs no extra warp
+ * (ceil(a / group) + ceil(b / group) == ceil(c / group)), else cut equal runs. */
 static void hybrid_groups(int ni, int leaf0, int group, const int32_t* left, const int32_t* right,
                           const int32_t* range_first, const int32_t* range_last, int32_t* gfirst, int32_t* gcount,
                           int* ngroups) {
@@ -151,7 +152,7 @@ void orc_lbvh_forces(int n, const int32_t* left, const int32_t* right, const int
                      const float* sx, const float* sy, const float* sz, const float bbox[6], float theta, float G,
                      float eps, int group, int super, float* ax, float* ay, float* az, uint64_t* interactions) {
   orc_lbvh_forces_ex(n, left, right, prefix, range_first, range_last, node_com, sx, sy, sz, bbox, theta, G, eps, group,
-                     super, 0, 0.0f, ax, ay, az, interactions, 0);
+                     super, 1, 0.0f, ax, ay, az, interactions, 0);
 }
 
 /* mode bit 0: hybrid grouping; alpha: acceptance distance^2 = (1 - alpha) * dmin^2 + alpha * dcentre^2 (alpha = 0: the

@@ -68,6 +68,32 @@ def test_direct_eps0_coincident_and_zero_mass():
     assert rel_err((out["acc_x"], out["acc_y"], out["acc_z"]), ref).max() <= TOL
 
 
+@pytest.mark.parametrize("eps", [1e-20, 1e-14, 1e-7])
+@pytest.mark.parametrize("method", ["direct", "barnes_hut", "spatial_hash"])
+def test_tiny_softening_stays_finite(orc, eps, method):
+    """Softening so small that G m (eps^2)^-3/2 overflows fp32 (or eps^2 is a denormal that rsqrt.approx.ftz flushes):
+    the un-guarded pair body would turn every body's self term into inf * 0 = NaN.  The reference skips j == i by
+    index (src/cuda/force_direct.cu:60) and validateSoftening accepts any eps >= 0; ours switches to the guarded
+    kernel below eps^2 = 1e-12."""
+    import nbody_b200 as nb
+    from nbody_b200 import ics
+    st = ics.uniform_box(3000, -1, 1, seed=5)
+    d = _device_data(st)
+    if method == "direct":
+        calc = nb.DirectForceCalculator()
+    elif method == "barnes_hut":
+        calc = nb.BarnesHutCalculator(0.0)   # theta = 0: every leaf is opened, the sum is the direct sum
+    else:
+        calc = nb.SpatialHashCalculator(4.0, 4.0)  # cutoff larger than the box diagonal: all pairs
+    calc.setSofteningParameter(eps)
+    calc.computeForces(d)
+    out = d.numpy()
+    for k in ("acc_x", "acc_y", "acc_z"):
+        assert np.isfinite(out[k]).all(), (method, eps, k)
+    ref = orc.direct_f64(st["pos_x"], st["pos_y"], st["pos_z"], st["mass"], 1.0, float(np.float32(eps)) ** 2)
+    assert rel_err((out["acc_x"], out["acc_y"], out["acc_z"]), ref).max() <= (TOL if method == "direct" else 2e-5)
+
+
 def test_direct_G_and_eps(orc):
     import nbody_b200 as nb
     from nbody_b200 import ics
