@@ -33,6 +33,9 @@ struct BH {
   // keys/perm: two buffers each, the radix passes ping-pong between them (the result stays in BH-owned memory, so
   // a later sort on the same context cannot clobber the permutation the traversal scatters through)
   nb::DevBuf keys, perm, keys_alt, perm_alt, packed, node_com, meta, misc;  // misc: size2 table[32] + counter + bbox floats
+  nb::DevBuf roots;   // int2 {first, last} of the subtrees the tiles hand to the top pass
+  int hybrid = 1;     // NB_BH_HYBRID=0: equal runs only (A/B)
+  int pipeline = 1;   // NB_BH_PIPELINE=0: fetch the next round's nodes after the list evaluation (A/B)
   nb::DevBuf slot;    // int per split position: meeting point of the two children of a node that spans tiles
   nb::DevBuf parent;  // filled on export only
   nb::DevBuf groups;  // int2 {first,count} per traversal group
@@ -63,7 +66,7 @@ __device__ __forceinline__ unsigned expand_bits(unsigned v) {
 
 // misc layout (floats): [0..31] size2 table by prefix length, [32..37] bbox, [40..41] u64 counter,
 // [44] int number of traversal groups, [45] int work-queue cursor of the traversal kernel,
-// [46] int deepest traversal stack of the last force evaluation
+// [46] int deepest traversal stack of the last force evaluation, [47] int subtrees left to bh_tree_top_kernel
 __global__ void bh_prepare_kernel(const int* __restrict__ bb_ord, float* __restrict__ misc) {
   const int t = threadIdx.x;
   __shared__ float bb[6];
@@ -74,6 +77,7 @@ __global__ void bh_prepare_kernel(const int* __restrict__ bb_ord, float* __restr
   if (t == 6) *reinterpret_cast<unsigned long long*>(misc + 40) = 0ull;
   if (t == 7) reinterpret_cast<int*>(misc)[44] = 0;  // number of traversal groups
   if (t == 8) reinterpret_cast<int*>(misc)[46] = 0;  // deepest traversal stack seen
+  if (t == 9) reinterpret_cast<int*>(misc)[47] = 0;  // subtrees handed to the top pass of the tree build
   __syncthreads();
   if (t <= 30) {
     // side of the Morton cell at prefix length L: x is split first, then y, then z
@@ -135,12 +139,14 @@ __global__ void __launch_bounds__(256) bh_morton_kernel(const float* __restrict_
 //            spent ~37;
 //   phase 2  log2(256) rounds: thread j joins blocks 2j and 2j+1 of the previous round across their common
 //            boundary (only subtrees touching the boundary can newly merge), dense thread indices;
-//   phase 3  the few subtrees whose sibling lies in another tile (the two spines of the tile, ~0.6 % of the
-//            nodes) climb with one global exchange per level: the first child to arrive leaves its far end
-//            in slot[split], the second takes it, reads the sibling's record and goes on.
+// and then bh_tree_top_kernel: the few subtrees whose sibling lies in another tile (the two spines of a tile,
+// ~0.6 % of the nodes) climb with one global exchange per level, one thread per subtree.
 // The thread that completes a node writes its record, and emits the traversal groups of a child that is a
 // maximal subtree of <= smax leaves (the round-1 group pass).
-constexpr int TB_THREADS = 256;
+#ifndef NB_TB_THREADS
+#define NB_TB_THREADS 256  // build-time knob: 128 -> 2048-leaf tiles, four CTAs per SM instead of two
+#endif
+constexpr int TB_THREADS = NB_TB_THREADS;
 constexpr int TB_K = 16;                        // consecutive leaves per thread in phase 1
 constexpr int TB_TILE = TB_THREADS * TB_K;      // 4096 leaves per CTA
 constexpr int TB_PADDED = TB_TILE + TB_TILE / 16 + 2;
@@ -175,6 +181,9 @@ struct TreeOut {
   int2* groups;
   int* ngroups;
   int n, leaf0, smax, gmax;
+  int hybrid;  // 1: descend the tree inside a supergroup while that costs no extra group (default); 0: equal runs only
+  int2* roots;  // subtrees whose sibling lies in another tile: {first, last} leaf, joined by bh_tree_top_kernel
+  int* nroots;
 };
 
 // Traversal groups of a supergroup (a maximal subtree of <= smax leaves, node `id` with leaves [cl, cr]).
@@ -212,7 +221,7 @@ __device__ __noinline__ void tb_emit(int id, int cl, int cr, const TreeOut& o) {
     const int4 m = __ldcg(o.meta + ni);
     const int g = (m.x >= o.leaf0) ? m.x - o.leaf0 : m.x;  // the left child ends at the split
     const int a = g - l + 1, b = r - g;
-    if ((a + o.gmax - 1) / o.gmax + (b + o.gmax - 1) / o.gmax == need && sp + 2 <= CAP) {
+    if (o.hybrid && (a + o.gmax - 1) / o.gmax + (b + o.gmax - 1) / o.gmax == need && sp + 2 <= CAP) {
       sid[sp] = m.y; sl[sp] = g + 1; sr[sp] = r;
       sp++;
       sid[sp] = m.x; sl[sp] = l; sr[sp] = g;
@@ -244,17 +253,16 @@ __device__ __forceinline__ float4 tb_form(int l, int g, int r, int dL, int dR, i
   return c;
 }
 
-__global__ void __launch_bounds__(TB_THREADS, 2) bh_tree_kernel(const uint32_t* __restrict__ keys,
+__global__ void __launch_bounds__(TB_THREADS, 512 / TB_THREADS) bh_tree_kernel(const uint32_t* __restrict__ keys,
                                                                  const int32_t* __restrict__ perm,
-                                                                 const float4* __restrict__ packed,
-                                                                 int* __restrict__ slot, TreeOut o) {
+                                                                 const float4* __restrict__ packed, TreeOut o) {
   extern __shared__ __align__(16) unsigned char tb_smem[];
   float4* s_com = reinterpret_cast<float4*>(tb_smem);            // value of the current subtree starting here
   int* s_d = reinterpret_cast<int*>(s_com + TB_PADDED);          // s_d[q]: delta between local leaves q-1 and q
   short* s_lo = reinterpret_cast<short*>(s_d + TB_PADDED);       // s_lo[b]: first leaf of the current subtree ending at b
   short* s_hi = s_lo + TB_PADDED;                                // s_hi[a]: last leaf of the current subtree starting at a
   __shared__ int s_roots[TB_MAX_ROOTS];
-  __shared__ int s_nroots;
+  __shared__ int s_nroots, s_base;
   const int tid = threadIdx.x;
   const int n = o.n;
   const int t0 = blockIdx.x * TB_TILE;
@@ -354,40 +362,56 @@ __global__ void __launch_bounds__(TB_THREADS, 2) bh_tree_kernel(const uint32_t* 
   }
   if (gridDim.x == 1) return;  // the tile holds the whole tree: its root is complete
 
-  // ---- phase 3: subtrees whose sibling lies in another tile climb through global memory ------------------------
+  // ---- the subtrees left over (the tile's two spines: their siblings lie in other tiles) go to the top pass -----
   if (tid == 0) {
     int nr = 0;
     for (int q = 0; q < tcount && nr < TB_MAX_ROOTS; q = s_hi[tb_pad(q)] + 1) s_roots[nr++] = q;
     s_nroots = nr;
+    s_base = atomicAdd(o.nroots, nr);
   }
   __syncthreads();
   for (int i = tid; i < s_nroots; i += TB_THREADS) {
-    const int a = s_roots[i], b = s_hi[tb_pad(a)];
-    int l = t0 + a, r = t0 + b;
-    int dL = s_d[tb_pad(a)], dR = s_d[tb_pad(b + 1)];
-    float4 cur = s_com[tb_pad(a)];
-    while (!(l == 0 && r == n - 1)) {
-      const bool is_left = dR > dL;
-      const int g = is_left ? r : l - 1;  // split of the parent: where the two children meet
-      __threadfence();                    // this subtree's record is visible before its arrival
-      const int old = atomicExch(&slot[g], (is_left ? l : r) + 1);
-      if (old == 0) break;  // first to arrive: the sibling's thread completes the parent
-      slot[g] = 0;          // both children have arrived: the slot is clean for the next build
-      __threadfence();
-      const int far = old - 1;
-      const int dS = is_left ? dR : dL;
-      float4 sib;
-      if (is_left) {
-        sib = __ldcg(o.node_com + ((far == g + 1) ? o.leaf0 + g + 1 : g + 1));
-        r = far;
-        dR = bh_delta_adj(keys, n, r);
-        cur = tb_form(l, g, r, dL, dR, dS, cur, sib, o);
-      } else {
-        sib = __ldcg(o.node_com + ((far == g) ? o.leaf0 + g : g));
-        l = far;
-        dL = bh_delta_adj(keys, n, l - 1);
-        cur = tb_form(l, g, r, dL, dR, dS, sib, cur, o);
-      }
+    const int a = s_roots[i];
+    o.roots[s_base + i] = make_int2(t0 + a, t0 + s_hi[tb_pad(a)]);
+  }
+}
+
+// Top of the tree: every subtree a tile could not finish climbs through global memory, one thread each.  A
+// subtree [l, r] is a left child iff delta(r) > delta(l-1); the two children of a node meet at its split g:
+// the first to arrive leaves its far end in slot[g] and stops, the second takes it, reads the sibling's record
+// and completes the node.  This used to be the tail of the tile kernel, where each of the ~20 dependent global
+// round trips of a spine held a whole 100 KB tile resident (1.9 ms for 16 Mi leaves, 14 of every 15 issue
+// slots stalled); as a kernel of its own it is ~100 000 independent threads deep.
+__global__ void __launch_bounds__(256) bh_tree_top_kernel(const uint32_t* __restrict__ keys, int* __restrict__ slot,
+                                                          TreeOut o) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= *o.nroots) return;
+  const int n = o.n;
+  const int2 rt = o.roots[i];
+  int l = rt.x, r = rt.y;
+  int dL = bh_delta_adj(keys, n, l - 1), dR = bh_delta_adj(keys, n, r);
+  // the subtree's own record: a leaf, or node r (left child) / node l (right child)
+  float4 cur = __ldcg(o.node_com + ((l == r) ? o.leaf0 + l : ((dR > dL) ? r : l)));
+  while (!(l == 0 && r == n - 1)) {
+    const bool is_left = dR > dL;
+    const int g = is_left ? r : l - 1;  // split of the parent: where the two children meet
+    __threadfence();                    // this subtree's record is visible before its arrival
+    const int old = atomicExch(&slot[g], (is_left ? l : r) + 1);
+    if (old == 0) break;  // first to arrive: the sibling's thread completes the parent
+    slot[g] = 0;          // both children have arrived: the slot is clean for the next build
+    __threadfence();
+    const int far = old - 1;
+    const int dS = is_left ? dR : dL;
+    if (is_left) {
+      const float4 sib = __ldcg(o.node_com + ((far == g + 1) ? o.leaf0 + g + 1 : g + 1));
+      r = far;
+      dR = bh_delta_adj(keys, n, r);
+      cur = tb_form(l, g, r, dL, dR, dS, cur, sib, o);
+    } else {
+      const float4 sib = __ldcg(o.node_com + ((far == g) ? o.leaf0 + g : g));
+      l = far;
+      dL = bh_delta_adj(keys, n, l - 1);
+      cur = tb_form(l, g, r, dL, dR, dS, sib, cur, o);
     }
   }
 }
@@ -438,7 +462,8 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
                                                                   const int2* __restrict__ groups,
                                                                   const int* __restrict__ ngroups,
                                                                   int* __restrict__ cursor, int stack_cap,
-                                                                  int* __restrict__ max_stack, BhShard sh) {
+                                                                  int* __restrict__ max_stack, int pipeline,
+                                                                  BhShard sh) {
   extern __shared__ __align__(16) unsigned char bh_smem[];
   __shared__ float size2_tab[32];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -541,7 +566,7 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
     sp += npush;
     __syncwarp();
     const bool done = (sp == 0);
-    if (!done) pop_and_fetch();  // in flight while the list is evaluated
+    if (!done && pipeline) pop_and_fetch();  // in flight while the list is evaluated
     while (nl >= 32 || (done && nl > 0)) {
       const int ne = min(nl, 32);
       auto body = [&](int e) {
@@ -594,6 +619,7 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
       nl = rest;
     }
     if (done) break;
+    if (!pipeline) pop_and_fetch();
   }
   if constexpr (BPL == 2) {
     upk(sx2, sx[0], sx[1]);
@@ -680,6 +706,7 @@ void bh_destroy(nb_context* ctx) {
   BH* b = ctx->bh;
   b->keys.release(); b->perm.release(); b->keys_alt.release(); b->perm_alt.release(); b->packed.release();
   b->node_com.release(); b->meta.release(); b->parent.release(); b->slot.release(); b->misc.release();
+  b->roots.release();
   b->groups.release();
   if (b->h_flag) cudaFreeHost(b->h_flag);
   delete b;
@@ -709,6 +736,7 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
   if (int rc = b->meta.ensure(n * sizeof(int4))) return rc;
   if (int rc = b->misc.ensure(64 * 4)) return rc;
   if (int rc = b->groups.ensure(n * sizeof(int2))) return rc;
+  if (int rc = b->roots.ensure(((n + TB_TILE - 1) / TB_TILE) * 128 * sizeof(int2))) return rc;
   if (b->slot.cap < n * 4) {
     // meeting slots of the tree build: zero when idle (the second child to arrive cleans its slot), so they
     // are cleared only when (re)allocated
@@ -726,6 +754,8 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
       if (c != b->stack_cap) b->occ = 0;
       b->stack_cap = c;
     }
+    if (const char* he = getenv("NB_BH_HYBRID")) b->hybrid = atoi(he) != 0;
+    if (const char* pe = getenv("NB_BH_PIPELINE")) b->pipeline = atoi(pe) != 0;
     const char* se = getenv("NB_BH_SUPER");
     int sg = se ? atoi(se) : 8 * g;
     if (sg < g) sg = g;
@@ -762,9 +792,17 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
     o.leaf0 = (int)n - 1;
     o.smax = b->super;
     o.gmax = b->group;
-    bh_tree_kernel<<<(unsigned)((n + TB_TILE - 1) / TB_TILE), TB_THREADS, kTreeSmem, st>>>(
-        b->keys_sorted, b->perm_sorted, b->packed.as<float4>(), b->slot.as<int>(), o);
+    o.hybrid = b->hybrid;
+    o.roots = b->roots.as<int2>();
+    o.nroots = reinterpret_cast<int*>(misc) + 47;
+    const unsigned tiles = (unsigned)((n + TB_TILE - 1) / TB_TILE);
+    bh_tree_kernel<<<tiles, TB_THREADS, kTreeSmem, st>>>(b->keys_sorted, b->perm_sorted, b->packed.as<float4>(), o);
     NB_LAUNCH_CHECK(ctx);
+    if (tiles > 1) {  // at most 2 x 62 subtrees per tile are left (one per level of each spine)
+      const unsigned max_roots = tiles * 128u;
+      bh_tree_top_kernel<<<(max_roots + 255) / 256, 256, 0, st>>>(b->keys_sorted, b->slot.as<int>(), o);
+      NB_LAUNCH_CHECK(ctx);
+    }
   }
   b->built = true;
   return NB_OK;
@@ -828,7 +866,7 @@ int bh_forces(nb_context* ctx, const nb_particles* d, float theta, float G, floa
       (int)n, b->node_com.as<float4>(), b->meta.as<int4>(), b->perm_sorted, misc, theta * theta, G, eps2,         \
       d->acc_x, d->acc_y, d->acc_z, reinterpret_cast<unsigned long long*>(misc + 40), b->d_flag,                   \
       b->groups.as<int2>(), reinterpret_cast<const int*>(misc) + 44, cursor, b->stack_cap,                        \
-      reinterpret_cast<int*>(misc) + 46, shv)
+      reinterpret_cast<int*>(misc) + 46, b->pipeline, shv)
 #define NB_BH_LAUNCH(BPL_, E_)               \
   do {                                       \
     if (shard) NB_BH_LAUNCH_S(BPL_, E_, true); \

@@ -3,6 +3,7 @@
 // points.  Barnes-Hut, spatial hash, sort and bbox entry points live next to their kernels.
 #include <atomic>
 #include <cstdarg>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <new>
@@ -193,6 +194,10 @@ int nb_context_create(int device, size_t max_bodies_hint, nb_context** out) {
     return NB_ERR_NO_DEVICE;
   }
   NB_CUDA(cudaSetDevice(device));
+  if (const char* e = getenv("NB_L2_FETCH_GRANULARITY")) {  // experiment knob: 32 / 64 / 128 bytes fetched per L2 miss
+    const int v = atoi(e);
+    if (v == 32 || v == 64 || v == 128) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)v);
+  }
   nb_context* ctx = new (std::nothrow) nb_context();
   if (!ctx) {
     set_error("out of host memory");
