@@ -80,6 +80,9 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-paths", action="store_true", help="skip the Barnes-Hut / spatial-hash / sort / 4 Mi legs")
     ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--path", default="direct", choices=["direct", "bh"],
+                    help="direct: the headline direct-N^2 metric (default); bh: the Barnes-Hut step of configs[3], 16 Mi "
+                         "bodies, theta 0.5, traversal target-sharded over replicated state at N > 1")
     ap.add_argument("--no-reference-gpu", action="store_true")
     return ap.parse_args()
 
@@ -233,6 +236,93 @@ def direct_traffic(n, world, scratch_bytes):
     return out
 
 
+def run_bh_path(args):
+    """--path bh: configs[3] as a timed step -- store-acc + drift, tree rebuild (bbox, Morton keys, radix sort, tree +
+    centres of mass + groups), group traversal, kick -- for 16 Mi Plummer bodies, theta 0.5.  At N > 1 every rank holds
+    all bodies and rebuilds the tree, traverses only the groups dealt to it and pushes the accelerations to every
+    replica over NVLink peer memory (nbody_b200/dist.py ShardedBarnesHutSystem).  Strong scaling (total work fixed).
+    Parity: the replicas after the timed steps against the single-GPU step on the same inputs, bit for bit."""
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    import nbody_b200 as nb
+    from nbody_b200 import ics
+    from nbody_b200.dist import ShardedBarnesHutSystem
+    n = args.bodies or (1 << 24)
+    theta = 0.5
+    st = ics.plummer(n, seed=42)
+    ctx = nb.get_context(local_rank)
+    sysm = ShardedBarnesHutSystem(st, rank, world, G_CONST, SOFTENING, theta)
+    sysm.compute_forces()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    for _ in range(args.warmup):
+        sysm.update(DT)
+    barrier()
+    launches0 = ctx.launch_count
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        sysm.update(DT)
+    e1.record()
+    barrier()
+    ms = max_over_ranks(e0.elapsed_time(e1)) / args.steps
+    launches = ctx.launch_count - launches0
+    clocks = sampler.stop() if rank == 0 else None
+    got = sysm.arrays()
+    sysm.close()
+    parity = None
+    if not args.no_parity:
+        single = nb.ParticleSystem()
+        single.config_ = nb.SimulationConfig(particle_count=n, softening=SOFTENING, dt=DT, G=G_CONST,
+                                             barnes_hut_theta=theta, force_method=nb.ForceMethod.BARNES_HUT)
+        single.setState(nb.SimulationState(n, 0.0, DT, G_CONST, SOFTENING, nb.ForceMethod.BARNES_HUT,
+                                           {k: st[k] for k in ("pos_x", "pos_y", "pos_z", "vel_x", "vel_y", "vel_z", "mass")}))
+        for _ in range(args.warmup + args.steps):
+            single.update(DT)
+        torch.cuda.synchronize()
+        want = single.getDeviceData().numpy()
+        same = all(np.array_equal(got[k], want[k]) for k in ("pos_x", "pos_y", "pos_z", "vel_x", "vel_y", "vel_z",
+                                                             "acc_x", "acc_y", "acc_z"))
+        ok = max_over_ranks(0.0 if same else 1.0) == 0.0
+        parity = {"replicas_bit_identical_to_single_gpu_step": bool(ok), "ok": bool(ok),
+                  "steps_compared": args.warmup + args.steps}
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank != 0:
+        return
+    emit({"metric": "barnes_hut_mbody_steps_per_s", "value": n / (ms * 1e-3) / 1e6, "unit": "M body-steps/s",
+          "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+          "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+          "config": {"workload": f"barnes_hut_theta0.5_{n}_plummer", "bodies": n, "theta": theta, "softening": SOFTENING,
+                     "dt": DT, "parallelism": f"replicated_state_traversal_sharded_x{world}" if world > 1 else "single_gpu",
+                     "exchange": "accelerations pushed to every replica from the traversal kernel's epilogue (peer memory)"
+                     if world > 1 else "none"},
+          "gpu_launches": int(launches), "clocks": clocks, "parity": parity})
+
+
 def run_reference_arm(args):
     """--impl reference: the reference has no CPU force path of its own; the timed
     CPU implementation is the oracle port of its example loop, all host threads, bounded sample."""
@@ -272,6 +362,9 @@ def main():
     quiet_stdout()
     if args.impl == "reference":
         run_reference_arm(args)
+        return
+    if args.path == "bh":
+        run_bh_path(args)
         return
 
     import torch

@@ -24,7 +24,8 @@ namespace nb {
 
 int bbox_device(nb_context* ctx, const nb_particles* d, cudaStream_t st);
 int sort_pairs_db(nb_context* ctx, uint32_t* d_keys, int32_t* d_vals, uint32_t* keys_alt, int32_t* vals_alt, size_t n,
-                  int end_bit, bool identity_vals, uint32_t** out_keys, int32_t** out_vals, cudaStream_t st);
+                  int end_bit, bool identity_vals, uint32_t** out_keys, int32_t** out_vals, cudaStream_t st,
+                  const uint32_t* copy_keys = nullptr, const int32_t* copy_vals = nullptr);
 
 }  // namespace nb
 
@@ -34,6 +35,7 @@ struct BH {
   // a later sort on the same context cannot clobber the permutation the traversal scatters through)
   nb::DevBuf keys, perm, keys_alt, perm_alt, packed, node_com, meta, misc;  // misc: size2 table[32] + counter + bbox floats
   nb::DevBuf roots;   // int2 {first, last} of the subtrees the tiles hand to the top pass
+  nb::DevBuf supers;  // int4 {node, first, last, -} per supergroup
   int hybrid = 1;     // NB_BH_HYBRID=0: equal runs only (A/B)
   int pipeline = 1;   // NB_BH_PIPELINE=0: fetch the next round's nodes after the list evaluation (A/B)
   nb::DevBuf slot;    // int per split position: meeting point of the two children of a node that spans tiles
@@ -78,6 +80,7 @@ __global__ void bh_prepare_kernel(const int* __restrict__ bb_ord, float* __restr
   if (t == 7) reinterpret_cast<int*>(misc)[44] = 0;  // number of traversal groups
   if (t == 8) reinterpret_cast<int*>(misc)[46] = 0;  // deepest traversal stack seen
   if (t == 9) reinterpret_cast<int*>(misc)[47] = 0;  // subtrees handed to the top pass of the tree build
+  if (t == 10) reinterpret_cast<int*>(misc)[48] = 0;  // supergroups recorded by the tree passes
   __syncthreads();
   if (t <= 30) {
     // side of the Morton cell at prefix length L: x is split first, then y, then z
@@ -144,13 +147,16 @@ __global__ void __launch_bounds__(256) bh_morton_kernel(const float* __restrict_
 // The thread that completes a node writes its record, and emits the traversal groups of a child that is a
 // maximal subtree of <= smax leaves (the round-1 group pass).
 #ifndef NB_TB_THREADS
-#define NB_TB_THREADS 256  // build-time knob: 128 -> 2048-leaf tiles, four CTAs per SM instead of two
+#define NB_TB_THREADS 64  // build-time knob: leaves per tile / 16.  Small tiles on purpose: the phases of a tile are
+                          // latency chains (random gather, then serial merges along the tile's spines), so the SM
+                          // needs many independent tiles in different phases: 256 threads (2 tiles per SM, all in the
+                          // same phase) built 16 Mi leaves in 1.79 ms, 128 threads in 1.49 ms
 #endif
 constexpr int TB_THREADS = NB_TB_THREADS;
 constexpr int TB_K = 16;                        // consecutive leaves per thread in phase 1
 constexpr int TB_TILE = TB_THREADS * TB_K;      // 4096 leaves per CTA
 constexpr int TB_PADDED = TB_TILE + TB_TILE / 16 + 2;
-constexpr int TB_MAX_ROOTS = 512;               // subtrees left per tile: two spines of <= 62 levels each
+constexpr int TB_MAX_ROOTS = 128;               // subtrees left per tile: two spines of <= 62 levels each
 __device__ __forceinline__ int tb_pad(int q) { return q + (q >> 4); }  // thread j's leaf i at 17 j + i: no bank conflicts
 
 __device__ __forceinline__ float4 bh_combine(const float4& a, const float4& b) {
@@ -184,6 +190,8 @@ struct TreeOut {
   int hybrid;  // 1: descend the tree inside a supergroup while that costs no extra group (default); 0: equal runs only
   int2* roots;  // subtrees whose sibling lies in another tile: {first, last} leaf, joined by bh_tree_top_kernel
   int* nroots;
+  int4* supers;  // supergroups {node, first leaf, last leaf, -}: cut into traversal groups by bh_groups_kernel
+  int* nsupers;
 };
 
 // Traversal groups of a supergroup (a maximal subtree of <= smax leaves, node `id` with leaves [cl, cr]).
@@ -203,31 +211,40 @@ __device__ __forceinline__ void tb_emit_runs(int cl, int c, int runs, const Tree
     o.groups[base + i] = make_int2(cl + s0, s1 - s0);
   }
 }
-__device__ __noinline__ void tb_emit(int id, int cl, int cr, const TreeOut& o) {
+// The tree passes only RECORD the supergroups (node, first and last leaf); bh_groups_kernel cuts them into groups
+// afterwards, one thread per supergroup: the descent reads nodes through L2 (~1 us per level) and used to run
+// inside the tile pass, where it stalled a whole tile each time.
+__device__ __forceinline__ void tb_emit(int id, int cl, int cr, const TreeOut& o) {
+  o.supers[atomicAdd(o.nsupers, 1)] = make_int4(id, cl, cr, 0);
+}
+__global__ void __launch_bounds__(128) bh_groups_kernel(TreeOut o) {
+  const int nsup = *o.nsupers;
   constexpr int CAP = 32;
-  int sid[CAP], sl[CAP], sr[CAP];
-  int sp = 0;
-  sid[0] = id; sl[0] = cl; sr[0] = cr;
-  sp = 1;
-  while (sp > 0) {
-    sp--;
-    const int ni = sid[sp], l = sl[sp], r = sr[sp];
-    const int c = r - l + 1;
-    const int need = (c + o.gmax - 1) / o.gmax;
-    if (need == 1) {
-      tb_emit_runs(l, c, 1, o);
-      continue;
-    }
-    const int4 m = __ldcg(o.meta + ni);
-    const int g = (m.x >= o.leaf0) ? m.x - o.leaf0 : m.x;  // the left child ends at the split
-    const int a = g - l + 1, b = r - g;
-    if (o.hybrid && (a + o.gmax - 1) / o.gmax + (b + o.gmax - 1) / o.gmax == need && sp + 2 <= CAP) {
-      sid[sp] = m.y; sl[sp] = g + 1; sr[sp] = r;
-      sp++;
-      sid[sp] = m.x; sl[sp] = l; sr[sp] = g;
-      sp++;
-    } else {
-      tb_emit_runs(l, c, need, o);
+  for (int sidx = blockIdx.x * blockDim.x + threadIdx.x; sidx < nsup; sidx += gridDim.x * blockDim.x) {
+    const int4 sg = o.supers[sidx];
+    int sid[CAP], sl[CAP], sr[CAP];
+    int sp = 1;
+    sid[0] = sg.x; sl[0] = sg.y; sr[0] = sg.z;
+    while (sp > 0) {
+      sp--;
+      const int ni = sid[sp], l = sl[sp], r = sr[sp];
+      const int c = r - l + 1;
+      const int need = (c + o.gmax - 1) / o.gmax;
+      if (need == 1) {
+        tb_emit_runs(l, c, 1, o);
+        continue;
+      }
+      const int4 m = __ldcg(o.meta + ni);
+      const int g = (m.x >= o.leaf0) ? m.x - o.leaf0 : m.x;  // the left child ends at the split
+      const int a = g - l + 1, b = r - g;
+      if (o.hybrid && (a + o.gmax - 1) / o.gmax + (b + o.gmax - 1) / o.gmax == need && sp + 2 <= CAP) {
+        sid[sp] = m.y; sl[sp] = g + 1; sr[sp] = r;
+        sp++;
+        sid[sp] = m.x; sl[sp] = l; sr[sp] = g;
+        sp++;
+      } else {
+        tb_emit_runs(l, c, need, o);
+      }
     }
   }
 }
@@ -384,9 +401,9 @@ __global__ void __launch_bounds__(TB_THREADS, 512 / TB_THREADS) bh_tree_kernel(c
 // slots stalled); as a kernel of its own it is ~100 000 independent threads deep.
 __global__ void __launch_bounds__(256) bh_tree_top_kernel(const uint32_t* __restrict__ keys, int* __restrict__ slot,
                                                           TreeOut o) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= *o.nroots) return;
   const int n = o.n;
+  const int nroots = *o.nroots;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nroots; i += gridDim.x * blockDim.x) {
   const int2 rt = o.roots[i];
   int l = rt.x, r = rt.y;
   int dL = bh_delta_adj(keys, n, l - 1), dR = bh_delta_adj(keys, n, r);
@@ -414,6 +431,7 @@ __global__ void __launch_bounds__(256) bh_tree_top_kernel(const uint32_t* __rest
       cur = tb_form(l, g, r, dL, dR, dS, sib, cur, o);
     }
   }
+  }  // next subtree
 }
 
 // parent[] is needed by nb_bh_export only (parity tests): derived from the children on demand
@@ -707,6 +725,7 @@ void bh_destroy(nb_context* ctx) {
   b->keys.release(); b->perm.release(); b->keys_alt.release(); b->perm_alt.release(); b->packed.release();
   b->node_com.release(); b->meta.release(); b->parent.release(); b->slot.release(); b->misc.release();
   b->roots.release();
+  b->supers.release();
   b->groups.release();
   if (b->h_flag) cudaFreeHost(b->h_flag);
   delete b;
@@ -736,7 +755,8 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
   if (int rc = b->meta.ensure(n * sizeof(int4))) return rc;
   if (int rc = b->misc.ensure(64 * 4)) return rc;
   if (int rc = b->groups.ensure(n * sizeof(int2))) return rc;
-  if (int rc = b->roots.ensure(((n + TB_TILE - 1) / TB_TILE) * 128 * sizeof(int2))) return rc;
+  if (int rc = b->roots.ensure(((n + TB_TILE - 1) / TB_TILE) * TB_MAX_ROOTS * sizeof(int2))) return rc;
+  // supergroups: children (<= smax leaves) of the nodes with more: those nodes number < 2 n / (smax + 1)
   if (b->slot.cap < n * 4) {
     // meeting slots of the tree build: zero when idle (the second child to arrive cleans its slot), so they
     // are cleared only when (re)allocated
@@ -761,6 +781,7 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
     if (sg < g) sg = g;
     b->super = sg;
   }
+  if (int rc = b->supers.ensure((4 * n / ((size_t)b->super + 1) + 16) * sizeof(int4))) return rc;
   float* misc = b->misc.as<float>();
   {
     NB_STAGE(ctx, st, "bh.bbox");
@@ -795,14 +816,17 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
     o.hybrid = b->hybrid;
     o.roots = b->roots.as<int2>();
     o.nroots = reinterpret_cast<int*>(misc) + 47;
+    o.supers = b->supers.as<int4>();
+    o.nsupers = reinterpret_cast<int*>(misc) + 48;
     const unsigned tiles = (unsigned)((n + TB_TILE - 1) / TB_TILE);
     bh_tree_kernel<<<tiles, TB_THREADS, kTreeSmem, st>>>(b->keys_sorted, b->perm_sorted, b->packed.as<float4>(), o);
     NB_LAUNCH_CHECK(ctx);
-    if (tiles > 1) {  // at most 2 x 62 subtrees per tile are left (one per level of each spine)
-      const unsigned max_roots = tiles * 128u;
-      bh_tree_top_kernel<<<(max_roots + 255) / 256, 256, 0, st>>>(b->keys_sorted, b->slot.as<int>(), o);
+    if (tiles > 1) {  // the subtrees the tiles left over (at most 2 x 62 each: one per level of each spine)
+      bh_tree_top_kernel<<<ctx->sm_count * 8, 256, 0, st>>>(b->keys_sorted, b->slot.as<int>(), o);
       NB_LAUNCH_CHECK(ctx);
     }
+    bh_groups_kernel<<<ctx->sm_count * 8, 128, 0, st>>>(o);
+    NB_LAUNCH_CHECK(ctx);
   }
   b->built = true;
   return NB_OK;

@@ -20,7 +20,8 @@
 namespace nb {
 int bbox_device(nb_context* ctx, const nb_particles* d, cudaStream_t st);
 int sort_pairs_db(nb_context* ctx, uint32_t* d_keys, int32_t* d_vals, uint32_t* keys_alt, int32_t* vals_alt, size_t n,
-                  int end_bit, bool identity_vals, uint32_t** out_keys, int32_t** out_vals, cudaStream_t st);
+                  int end_bit, bool identity_vals, uint32_t** out_keys, int32_t** out_vals, cudaStream_t st,
+                  const uint32_t* copy_keys = nullptr, const int32_t* copy_vals = nullptr);
 int launch_scan_tiles(nb_context* ctx, unsigned long long* tile_sum, int ntiles, unsigned long long* total,
                       cudaStream_t st);  // render.cu
 }  // namespace nb

@@ -4,6 +4,7 @@
 // Both are HBM-side kernels: bbox reads 12 B/body; the sort reads the keys once for all digit histograms
 // and then moves 16 B/pair per pass, with digits of up to 11 bits (3 passes for 30-bit Morton keys, 2 for
 // the 20/21-bit cell ids of the spatial hash and the renderer's pixel ids).
+#include <cstdint>
 #include <cstdlib>
 #include <cstring>
 #include <type_traits>
@@ -126,6 +127,7 @@ constexpr uint32_t RS_FLAG_AGG = 1u << 30, RS_FLAG_INC = 2u << 30, RS_VAL_MASK =
 constexpr int RS_MAX_PASSES = 3;   // ceil(32 / 11)
 constexpr int RS_MAX_BITS = 11;
 constexpr int RS_MAX_BINS = 1 << RS_MAX_BITS;
+constexpr int RS_LOOK = 4;         // predecessors examined per look-back round trip
 
 struct RsPlan {
   int passes;
@@ -148,9 +150,13 @@ static RsPlan rs_plan(int end_bit) {
   return p;
 }
 
-// hist[p][d] += number of keys whose pass-p digit is d
+// hist[p][d] += number of keys whose pass-p digit is d.  COPY: the pairs are also copied to (keys_to, vals_to) on
+// the way -- an in-place sort with an odd number of passes starts from the scratch copy, so that its last pass
+// lands in the caller's arrays (12 B per pair more here instead of a 16 B per pair copy back at the end).
+template <bool COPY>
 __global__ void __launch_bounds__(512) rs_hist_kernel(const uint32_t* __restrict__ keys, size_t n, RsPlan plan,
-                                                      uint32_t* __restrict__ hist) {
+                                                      uint32_t* __restrict__ hist, const int32_t* __restrict__ vals,
+                                                      uint32_t* __restrict__ keys_to, int32_t* __restrict__ vals_to) {
   extern __shared__ uint32_t rs_hsh[];  // [passes][RS_MAX_BINS]
   const int total = plan.passes * RS_MAX_BINS;
   for (int k = threadIdx.x; k < total; k += blockDim.x) rs_hsh[k] = 0;
@@ -164,9 +170,21 @@ __global__ void __launch_bounds__(512) rs_hist_kernel(const uint32_t* __restrict
   };
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
     const uint4 v = k4[i];
+    if (COPY) {
+      reinterpret_cast<uint4*>(keys_to)[i] = v;
+      reinterpret_cast<int4*>(vals_to)[i] = reinterpret_cast<const int4*>(vals)[i];
+    }
     add(v.x); add(v.y); add(v.z); add(v.w);
   }
-  if (blockIdx.x == 0 && threadIdx.x < (int)(n - n4 * 4)) add(keys[n4 * 4 + threadIdx.x]);
+  if (blockIdx.x == 0 && threadIdx.x < (int)(n - n4 * 4)) {
+    const size_t i = n4 * 4 + threadIdx.x;
+    const uint32_t k = keys[i];
+    if (COPY) {
+      keys_to[i] = k;
+      vals_to[i] = vals[i];
+    }
+    add(k);
+  }
   __syncthreads();
   for (int k = threadIdx.x; k < total; k += blockDim.x) {
     const uint32_t c = rs_hsh[k];
@@ -349,24 +367,35 @@ __global__ void __launch_bounds__(RS_THREADS, 2) rs_pass_kernel(const uint32_t* 
           st_status2(mine, RS_FLAG_INC | t0, RS_FLAG_INC | t1);
         } else {
           st_status2(mine, RS_FLAG_AGG | t0, RS_FLAG_AGG | t1);
-          const uint32_t* look = mine - ((size_t)1 << bits);
+          // Decoupled look-back, RS_LOOK predecessors per round trip: the status words of tiles t-1 .. t-RS_LOOK are
+          // loaded together and consumed in order (aggregate: add and go on; inclusive: add and stop; not yet
+          // published: poll again from there).  One predecessor per trip left every tile waiting ~13 dependent L2
+          // round trips in this phase (ncu: a quarter of the pass's instructions and stall samples were this loop).
+          const size_t stride = (size_t)1 << bits;
+          const uint32_t* look = mine - stride;
+          uint32_t left = tile;  // predecessors not yet consumed (tile 0 always publishes an inclusive count)
           unsigned long long t_start = 0;
           for (unsigned spins = 1;; spins++) {
-            // both words of a pair are always published together: the flags of the low word decide
-            const unsigned long long s2 = ld_status2(look);
-            const uint32_t s_lo = (uint32_t)s2, s_hi = (uint32_t)(s2 >> 32);
-            if (s_lo & RS_FLAG_INC) {
-              e0 += s_lo & RS_VAL_MASK;
-              e1 += s_hi & RS_VAL_MASK;
-              break;
+            unsigned long long s2[RS_LOOK];
+#pragma unroll
+            for (int q = 0; q < RS_LOOK; q++) s2[q] = ((uint32_t)q < left) ? ld_status2(look - (size_t)q * stride) : 0ull;
+            bool finished = false;
+            int consumed = 0;
+#pragma unroll
+            for (int q = 0; q < RS_LOOK; q++) {
+              // both words of a pair are always published together: the flags of the low word decide
+              const uint32_t s_lo = (uint32_t)s2[q], s_hi = (uint32_t)(s2[q] >> 32);
+              if (!finished && consumed == q && (s_lo & (RS_FLAG_INC | RS_FLAG_AGG))) {
+                e0 += s_lo & RS_VAL_MASK;
+                e1 += s_hi & RS_VAL_MASK;
+                consumed++;
+                finished = (s_lo & RS_FLAG_INC) != 0u;
+              }
             }
-            if (s_lo & RS_FLAG_AGG) {
-              e0 += s_lo & RS_VAL_MASK;
-              e1 += s_hi & RS_VAL_MASK;
-              look -= ((size_t)1 << bits);
-              continue;
-            }
-            if ((spins & 4095u) == 0u) {  // a faulted predecessor must not hang the device: give up after ~2 s
+            if (finished) break;
+            look -= (size_t)consumed * stride;
+            left -= (uint32_t)consumed;
+            if ((spins & 1023u) == 0u) {  // a faulted predecessor must not hang the device: give up after ~2 s
               unsigned long long now;
               asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
               if (t_start == 0) t_start = now;
@@ -464,10 +493,12 @@ int sort_poll_error(nb_context* ctx) {
 }
 
 // Sorts (keys, vals) by bits [0, end_bit) of the keys.  The passes ping-pong between (d_keys, d_vals) and the
-// caller's second pair of buffers (keys_alt, vals_alt); *out_keys / *out_vals say where the result is (no copy).  identity_vals: vals need not be
-// initialised -- the first pass writes value = index.
+// caller's second pair of buffers (keys_alt, vals_alt); *out_keys / *out_vals say where the result is (no copy).
+// identity_vals: vals need not be initialised -- the first pass writes value = index.  copy_keys / copy_vals
+// (optional): the pairs are there, not in (d_keys, d_vals) yet; the histogram sweep copies them over.
 int sort_pairs_db(nb_context* ctx, uint32_t* d_keys, int32_t* d_vals, uint32_t* keys_alt, int32_t* vals_alt, size_t n,
-                  int end_bit, bool identity_vals, uint32_t** out_keys, int32_t** out_vals, cudaStream_t st) {
+                  int end_bit, bool identity_vals, uint32_t** out_keys, int32_t** out_vals, cudaStream_t st,
+                  const uint32_t* copy_keys = nullptr, const int32_t* copy_vals = nullptr) {
   *out_keys = d_keys;
   *out_vals = d_vals;
   if (end_bit < 1) end_bit = 1;
@@ -499,7 +530,17 @@ int sort_pairs_db(nb_context* ctx, uint32_t* d_keys, int32_t* d_vals, uint32_t* 
     const size_t cap = (size_t)ctx->sm_count * 4;
     if (g > cap) g = cap;
     if (g < 1) g = 1;
-    rs_hist_kernel<<<(unsigned)g, 512, (size_t)plan.passes * RS_MAX_BINS * sizeof(uint32_t), st>>>(d_keys, n, plan, hist);
+    const size_t hsm = (size_t)plan.passes * RS_MAX_BINS * sizeof(uint32_t);
+    const bool aligned = (((uintptr_t)d_keys | (uintptr_t)d_vals | (uintptr_t)copy_keys | (uintptr_t)copy_vals) & 15u) == 0;
+    if (copy_keys && aligned) {
+      rs_hist_kernel<true><<<(unsigned)g, 512, hsm, st>>>(copy_keys, n, plan, hist, copy_vals, d_keys, d_vals);
+    } else {
+      if (copy_keys) {  // odd alignment: plain copies, then the histogram
+        NB_CUDA(cudaMemcpyAsync(d_keys, copy_keys, n * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+        NB_CUDA(cudaMemcpyAsync(d_vals, copy_vals, n * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+      }
+      rs_hist_kernel<false><<<(unsigned)g, 512, hsm, st>>>(d_keys, n, plan, hist, nullptr, nullptr, nullptr);
+    }
     NB_LAUNCH_CHECK(ctx);
     rs_scan_kernel<<<plan.passes, RS_MAX_BINS / 2, 0, st>>>(hist);
     NB_LAUNCH_CHECK(ctx);
@@ -542,10 +583,18 @@ int sort_pairs(nb_context* ctx, uint32_t* d_keys, int32_t* d_vals, size_t n, int
   int32_t* vo;
   if (int rc = ctx->sort_keys2.ensure(n * sizeof(uint32_t))) return rc;
   if (int rc = ctx->sort_vals2.ensure(n * sizeof(int32_t))) return rc;
-  if (int rc = sort_pairs_db(ctx, d_keys, d_vals, ctx->sort_keys2.as<uint32_t>(), ctx->sort_vals2.as<int32_t>(), n,
-                             end_bit, false, &ko, &vo, st))
-    return rc;
-  if (ko != d_keys) {
+  uint32_t* k2 = ctx->sort_keys2.as<uint32_t>();
+  int32_t* v2 = ctx->sort_vals2.as<int32_t>();
+  if (end_bit < 1) end_bit = 1;
+  if (end_bit > 32) end_bit = 32;
+  if (rs_plan(end_bit).passes % 2) {
+    // odd number of passes: start from the scratch copy (made by the histogram sweep) so that the last pass
+    // writes the caller's arrays
+    if (int rc = sort_pairs_db(ctx, k2, v2, d_keys, d_vals, n, end_bit, false, &ko, &vo, st, d_keys, d_vals)) return rc;
+  } else {
+    if (int rc = sort_pairs_db(ctx, d_keys, d_vals, k2, v2, n, end_bit, false, &ko, &vo, st)) return rc;
+  }
+  if (ko != d_keys) {  // not reached with the plans above
     NB_CUDA(cudaMemcpyAsync(d_keys, ko, n * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
     NB_CUDA(cudaMemcpyAsync(d_vals, vo, n * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
   }
