@@ -172,7 +172,7 @@ struct StageRec {
 // row of UJ source tiles is cut at the same places into C chunks of DESCENDING length (start[k] .. start[k+1]);
 // chunk c = k * n_itiles + itile, so the G CTAs, claiming chunk indices in ascending order, take the long chunks
 // of all rows first and the short ones last; chunk c writes partial slot slot_base + c.
-constexpr int NB_MAX_ROW_CHUNKS = 24;
+constexpr int NB_MAX_ROW_CHUNKS = 32;
 struct nb_chunk_tab {
   int start[NB_MAX_ROW_CHUNKS + 1];
 };

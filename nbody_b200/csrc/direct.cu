@@ -452,6 +452,17 @@ static int plan_row_chunks(int n_itiles, int UJ, long long ctas, nb_chunk_tab& t
   if (min_len < 1) min_len = 1;
   int k = 0, at = 0;
   tab.start[0] = 0;
+  if (const char* e = getenv("NB_DIRECT_PLAN")) {  // A/B knob: 0 = equal chunks (per_cta of them per CTA), as in round 1
+    if (atoi(e) == 0) {
+      long long c = (per_cta * ctas + n_itiles - 1) / n_itiles;
+      if (c > UJ) c = UJ;
+      if (c > NB_MAX_ROW_CHUNKS) c = NB_MAX_ROW_CHUNKS;
+      if (c < 1) c = 1;
+      for (long long q = 1; q <= c; q++) tab.start[q] = (int)((long long)UJ * q / c);
+      for (int q = (int)c + 1; q <= NB_MAX_ROW_CHUNKS; q++) tab.start[q] = UJ;
+      return (int)c;
+    }
+  }
   while (at < UJ) {
     const long long rest = UJ - at;
     long long len = (rest + 2) / 3;
