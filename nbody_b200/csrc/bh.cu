@@ -23,6 +23,8 @@
 namespace nb {
 
 int bbox_device(nb_context* ctx, const nb_particles* d, cudaStream_t st);
+int launch_scan_tiles(nb_context* ctx, unsigned long long* tile_sum, int ntiles, unsigned long long* total,
+                      cudaStream_t st);  // render.cu
 int sort_pairs_db(nb_context* ctx, uint32_t* d_keys, int32_t* d_vals, uint32_t* keys_alt, int32_t* vals_alt, size_t n,
                   int end_bit, bool identity_vals, uint32_t** out_keys, int32_t** out_vals, cudaStream_t st,
                   const uint32_t* copy_keys = nullptr, const int32_t* copy_vals = nullptr);
@@ -36,6 +38,8 @@ struct BH {
   nb::DevBuf keys, perm, keys_alt, perm_alt, packed, node_com, meta, misc;  // misc: size2 table[32] + counter + bbox floats
   nb::DevBuf roots;   // int2 {first, last} of the subtrees the tiles hand to the top pass
   nb::DevBuf supers;  // int4 {node, first, last, -} per supergroup
+  nb::DevBuf glen;    // group length at the group's first leaf, compacted into `groups` in leaf order
+  nb::DevBuf gtiles;  // per-block counts / offsets of that compaction
   int hybrid = 1;     // NB_BH_HYBRID=0: equal runs only (A/B)
   int pipeline = 1;   // NB_BH_PIPELINE=0: fetch the next round's nodes after the list evaluation (A/B)
   nb::DevBuf slot;    // int per split position: meeting point of the two children of a node that spans tiles
@@ -68,7 +72,8 @@ __device__ __forceinline__ unsigned expand_bits(unsigned v) {
 
 // misc layout (floats): [0..31] size2 table by prefix length, [32..37] bbox, [40..41] u64 counter,
 // [44] int number of traversal groups, [45] int work-queue cursor of the traversal kernel,
-// [46] int deepest traversal stack of the last force evaluation, [47] int subtrees left to bh_tree_top_kernel
+// [46] int deepest traversal stack of the last force evaluation, [47] int subtrees left to bh_tree_top_kernel,
+// [48] int supergroups recorded, [50..51] u64 number of groups (the compaction's total)
 __global__ void bh_prepare_kernel(const int* __restrict__ bb_ord, float* __restrict__ misc) {
   const int t = threadIdx.x;
   __shared__ float bb[6];
@@ -152,12 +157,16 @@ __global__ void __launch_bounds__(256) bh_morton_kernel(const float* __restrict_
                           // needs many independent tiles in different phases: 256 threads (2 tiles per SM, all in the
                           // same phase) built 16 Mi leaves in 1.79 ms, 128 threads in 1.49 ms
 #endif
+#ifndef NB_TB_K
+#define NB_TB_K 8  // build-time knob: consecutive leaves per thread in phase 1 (a power of two)
+#endif
 constexpr int TB_THREADS = NB_TB_THREADS;
-constexpr int TB_K = 16;                        // consecutive leaves per thread in phase 1
-constexpr int TB_TILE = TB_THREADS * TB_K;      // 4096 leaves per CTA
-constexpr int TB_PADDED = TB_TILE + TB_TILE / 16 + 2;
+constexpr int TB_K = NB_TB_K;                   // consecutive leaves per thread in phase 1
+constexpr int TB_TILE = TB_THREADS * TB_K;      // leaves per CTA
+constexpr int TB_PADDED = TB_TILE + TB_TILE / TB_K + 2;
 constexpr int TB_MAX_ROOTS = 128;               // subtrees left per tile: two spines of <= 62 levels each
-__device__ __forceinline__ int tb_pad(int q) { return q + (q >> 4); }  // thread j's leaf i at 17 j + i: no bank conflicts
+// thread j's leaf i sits at (TB_K + 1) j + i: an odd stride, no shared-memory bank conflicts in phase 1
+__device__ __forceinline__ int tb_pad(int q) { return q + q / TB_K; }
 
 __device__ __forceinline__ float4 bh_combine(const float4& a, const float4& b) {
   const float ms = __fadd_rn(a.w, b.w);
@@ -186,6 +195,7 @@ struct TreeOut {
   int4* meta;        // [n-1] {left, right, prefix, 0}
   int2* groups;
   int* ngroups;
+  unsigned char* glen;  // [n rounded up to GC_TILE] group length at the group's first leaf, else 0
   int n, leaf0, smax, gmax;
   int hybrid;  // 1: descend the tree inside a supergroup while that costs no extra group (default); 0: equal runs only
   int2* roots;  // subtrees whose sibling lies in another tile: {first, last} leaf, joined by bh_tree_top_kernel
@@ -204,11 +214,14 @@ struct TreeOut {
 // and cut equal runs where it would (3296 instead of 3429 list entries x lane-slots per body on a 262 144-body
 // Plummer sphere, same number of groups, same error: oracle/lbvh.c counts it on the CPU).  The subtree's nodes are
 // complete when this runs; the ones written by other thread blocks are read through L2.
+// A group is recorded as its length at its first leaf (glen[], zero elsewhere); bh_group_fill_kernel compacts
+// the marks into the group list in LEAF ORDER.  Appending with an atomic counter instead left the list in whatever
+// order the supergroups were finished, and the traversal -- whose warps take groups in list order, so that
+// neighbouring warps walk neighbouring parts of the tree and share its nodes in L2 -- ran 10 % slower.
 __device__ __forceinline__ void tb_emit_runs(int cl, int c, int runs, const TreeOut& o) {
-  const int base = atomicAdd(o.ngroups, runs);
   for (int i = 0; i < runs; i++) {
     const int s0 = (int)(((long long)i * c) / runs), s1 = (int)(((long long)(i + 1) * c) / runs);
-    o.groups[base + i] = make_int2(cl + s0, s1 - s0);
+    o.glen[cl + s0] = (unsigned char)(s1 - s0);
   }
 }
 // The tree passes only RECORD the supergroups (node, first and last leaf); bh_groups_kernel cuts them into groups
@@ -249,6 +262,55 @@ __global__ void __launch_bounds__(128) bh_groups_kernel(TreeOut o) {
   }
 }
 
+constexpr int GC_TILE = 4096;  // leaves per block of the group compaction: 256 threads x 16 marks
+__device__ __forceinline__ unsigned gc_count16(const uint4& v) {
+  return (__popc(__vcmpne4(v.x, 0u)) + __popc(__vcmpne4(v.y, 0u)) + __popc(__vcmpne4(v.z, 0u)) +
+          __popc(__vcmpne4(v.w, 0u))) >> 3;
+}
+__global__ void __launch_bounds__(256) bh_group_count_kernel(const unsigned char* __restrict__ glen,
+                                                             unsigned long long* __restrict__ tile_sum) {
+  __shared__ unsigned ws[8];
+  const uint4 v = reinterpret_cast<const uint4*>(glen)[(size_t)blockIdx.x * 256 + threadIdx.x];
+  unsigned c = gc_count16(v);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = c;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned t = 0;
+    for (int w = 0; w < 8; w++) t += ws[w];
+    tile_sum[blockIdx.x] = t;
+  }
+}
+__global__ void __launch_bounds__(256) bh_group_fill_kernel(const unsigned char* __restrict__ glen,
+                                                            const unsigned long long* __restrict__ tile_off,
+                                                            const unsigned long long* __restrict__ total,
+                                                            int2* __restrict__ groups, int* __restrict__ ngroups) {
+  __shared__ unsigned ws[8];
+  const size_t base = ((size_t)blockIdx.x * 256 + threadIdx.x) * 16;
+  const uint4 v = reinterpret_cast<const uint4*>(glen)[(size_t)blockIdx.x * 256 + threadIdx.x];
+  const unsigned mine = gc_count16(v);
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  unsigned x = mine;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const unsigned y = __shfl_up_sync(0xffffffffu, x, o);
+    if (lane >= o) x += y;
+  }
+  if (lane == 31) ws[w] = x;
+  __syncthreads();
+  unsigned before = x - mine;
+  for (int k = 0; k < w; k++) before += ws[k];
+  size_t at = (size_t)tile_off[blockIdx.x] + before;
+  const unsigned words[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+  for (int q = 0; q < 16; q++) {
+    const unsigned len = (words[q >> 2] >> ((q & 3) * 8)) & 0xffu;
+    if (len) groups[at++] = make_int2((int)(base + q), (int)len);
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) *ngroups = (int)*total;
+}
+
 // Completes node [l, r] split at g (all global leaf indices) from its children's values; dL = delta(l-1),
 // dR = delta(r), dS = delta(g).  Writes the node's record and emits the groups of supergroup children.
 __device__ __forceinline__ float4 tb_form(int l, int g, int r, int dL, int dR, int dS, const float4& a, const float4& b,
@@ -270,7 +332,7 @@ __device__ __forceinline__ float4 tb_form(int l, int g, int r, int dL, int dR, i
   return c;
 }
 
-__global__ void __launch_bounds__(TB_THREADS, 512 / TB_THREADS) bh_tree_kernel(const uint32_t* __restrict__ keys,
+__global__ void __launch_bounds__(TB_THREADS, 1024 / TB_THREADS) bh_tree_kernel(const uint32_t* __restrict__ keys,
                                                                  const int32_t* __restrict__ perm,
                                                                  const float4* __restrict__ packed, TreeOut o) {
   extern __shared__ __align__(16) unsigned char tb_smem[];
@@ -317,22 +379,32 @@ __global__ void __launch_bounds__(TB_THREADS, 512 / TB_THREADS) bh_tree_kernel(c
   {
     const int blk0 = tid * TB_K, blk1 = min(blk0 + TB_K, tcount);
     int q = blk0;  // the top subtree ends at leaf q
+    int a_top, g, a, dS, dL, dR;
+    // can the top subtree [a_top, q] and the one below it [a, g] be joined?
+    auto siblings = [&]() -> bool {
+      a_top = s_lo[tb_pad(q)];
+      if (a_top <= blk0) return false;
+      g = a_top - 1;
+      a = s_lo[tb_pad(g)];
+      dS = s_d[tb_pad(g + 1)];
+      dL = s_d[tb_pad(a)];
+      dR = s_d[tb_pad(q + 1)];
+      return dS > dL && dS > dR;
+    };
+    // One trip = at most one push (cheap) and one merge (expensive, ONE site): a warp's lanes alternate between the
+    // two at different times, and a trip that did only one of them would cost every lane the other as well.
     while (q < blk1) {
-      const int a_top = s_lo[tb_pad(q)];
-      bool merged = false;
-      if (a_top > blk0) {
-        const int g = a_top - 1;          // the subtree below the top is [a, g]
-        const int a = s_lo[tb_pad(g)];
-        const int dS = s_d[tb_pad(g + 1)], dL = s_d[tb_pad(a)], dR = s_d[tb_pad(q + 1)];
-        if (dS > dL && dS > dR) {
-          const float4 c = tb_form(t0 + a, t0 + g, t0 + q, dL, dR, dS, s_com[tb_pad(a)], s_com[tb_pad(a_top)], o);
-          s_com[tb_pad(a)] = c;
-          s_hi[tb_pad(a)] = (short)q;
-          s_lo[tb_pad(q)] = (short)a;
-          merged = true;
-        }
+      bool can = siblings();
+      if (!can) {  // push the next leaf (its one-leaf subtree is already in place) and look again
+        if (++q >= blk1) break;
+        can = siblings();
       }
-      if (!merged) q++;  // push the next leaf (its one-leaf subtree is already in place)
+      if (can) {
+        const float4 c = tb_form(t0 + a, t0 + g, t0 + q, dL, dR, dS, s_com[tb_pad(a)], s_com[tb_pad(a_top)], o);
+        s_com[tb_pad(a)] = c;
+        s_hi[tb_pad(a)] = (short)q;
+        s_lo[tb_pad(q)] = (short)a;
+      }
     }
   }
   __syncthreads();
@@ -342,34 +414,34 @@ __global__ void __launch_bounds__(TB_THREADS, 512 / TB_THREADS) bh_tree_kernel(c
     const int p = (2 * tid + 1) * half;  // boundary between local leaves p-1 and p
     if (p < tcount) {
       const int lo_lim = p - half, hi_lim = min(p + half, tcount);
-      int a = s_lo[tb_pad(p - 1)], b = s_hi[tb_pad(p)];
-      int dL = s_d[tb_pad(a)], dR = s_d[tb_pad(b + 1)];
-      const int dS = s_d[tb_pad(p)];
-      if (dS > dL && dS > dR) {
-        float4 c = tb_form(t0 + a, t0 + p - 1, t0 + b, dL, dR, dS, s_com[tb_pad(a)], s_com[tb_pad(p)], o);
-        for (;;) {  // the new subtree [a, b] may now be the sibling of its left or of its right neighbour
-          if (a > lo_lim) {
-            const int a2 = s_lo[tb_pad(a - 1)];
-            const int d2 = s_d[tb_pad(a2)];
-            if (dL > d2 && dL > dR) {
-              c = tb_form(t0 + a2, t0 + a - 1, t0 + b, d2, dR, dL, s_com[tb_pad(a2)], c, o);
-              a = a2;
-              dL = d2;
-              continue;
-            }
-          }
-          if (b + 1 < hi_lim) {
-            const int b2 = s_hi[tb_pad(b + 1)];
-            const int d2 = s_d[tb_pad(b2 + 1)];
-            if (dR > dL && dR > d2) {
-              c = tb_form(t0 + a, t0 + b, t0 + b2, dL, d2, dR, c, s_com[tb_pad(b + 1)], o);
-              b = b2;
-              dR = d2;
-              continue;
-            }
-          }
-          break;
+      // start from the subtree that ends at the boundary; every trip joins it with its left or its right neighbour
+      // if the two are siblings (ONE merge site for both directions: the lanes of a warp stay together)
+      int a = s_lo[tb_pad(p - 1)], b = p - 1;
+      int dL = s_d[tb_pad(a)], dR = s_d[tb_pad(p)];
+      float4 c = s_com[tb_pad(a)];
+      bool changed = false;
+      for (;;) {
+        bool left = false, right = false;
+        int o2 = 0, d2 = 0;
+        if (a > lo_lim) {
+          o2 = s_lo[tb_pad(a - 1)];
+          d2 = s_d[tb_pad(o2)];
+          left = dL > d2 && dL > dR;
         }
+        if (!left && b + 1 < hi_lim) {
+          o2 = s_hi[tb_pad(b + 1)];
+          d2 = s_d[tb_pad(o2 + 1)];
+          right = dR > dL && dR > d2;
+        }
+        if (!left && !right) break;
+        const float4 other = s_com[tb_pad(left ? o2 : b + 1)];
+        const int nl = left ? o2 : a, ng = left ? a - 1 : b, nr = left ? b : o2;
+        const int ndL = left ? d2 : dL, ndR = left ? dR : d2, dS = left ? dL : dR;
+        c = tb_form(t0 + nl, t0 + ng, t0 + nr, ndL, ndR, dS, left ? other : c, left ? c : other, o);
+        a = nl; b = nr; dL = ndL; dR = ndR;
+        changed = true;
+      }
+      if (changed) {
         s_com[tb_pad(a)] = c;
         s_hi[tb_pad(a)] = (short)b;
         s_lo[tb_pad(b)] = (short)a;
@@ -726,6 +798,8 @@ void bh_destroy(nb_context* ctx) {
   b->node_com.release(); b->meta.release(); b->parent.release(); b->slot.release(); b->misc.release();
   b->roots.release();
   b->supers.release();
+  b->glen.release();
+  b->gtiles.release();
   b->groups.release();
   if (b->h_flag) cudaFreeHost(b->h_flag);
   delete b;
@@ -782,6 +856,9 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
     b->super = sg;
   }
   if (int rc = b->supers.ensure((4 * n / ((size_t)b->super + 1) + 16) * sizeof(int4))) return rc;
+  const size_t gc_tiles = (n + GC_TILE - 1) / GC_TILE;
+  if (int rc = b->glen.ensure(gc_tiles * GC_TILE)) return rc;
+  if (int rc = b->gtiles.ensure(gc_tiles * sizeof(unsigned long long))) return rc;
   float* misc = b->misc.as<float>();
   {
     NB_STAGE(ctx, st, "bh.bbox");
@@ -816,6 +893,8 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
     o.hybrid = b->hybrid;
     o.roots = b->roots.as<int2>();
     o.nroots = reinterpret_cast<int*>(misc) + 47;
+    o.glen = b->glen.as<unsigned char>();
+    NB_CUDA(cudaMemsetAsync(o.glen, 0, gc_tiles * GC_TILE, st));
     o.supers = b->supers.as<int4>();
     o.nsupers = reinterpret_cast<int*>(misc) + 48;
     const unsigned tiles = (unsigned)((n + TB_TILE - 1) / TB_TILE);
@@ -826,6 +905,13 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
       NB_LAUNCH_CHECK(ctx);
     }
     bh_groups_kernel<<<ctx->sm_count * 8, 128, 0, st>>>(o);
+    NB_LAUNCH_CHECK(ctx);
+    unsigned long long* gt = b->gtiles.as<unsigned long long>();
+    unsigned long long* gtotal = reinterpret_cast<unsigned long long*>(misc + 50);
+    bh_group_count_kernel<<<(unsigned)gc_tiles, 256, 0, st>>>(o.glen, gt);
+    NB_LAUNCH_CHECK(ctx);
+    if (int rc = launch_scan_tiles(ctx, gt, (int)gc_tiles, gtotal, st)) return rc;
+    bh_group_fill_kernel<<<(unsigned)gc_tiles, 256, 0, st>>>(o.glen, gt, gtotal, o.groups, o.ngroups);
     NB_LAUNCH_CHECK(ctx);
   }
   b->built = true;

@@ -90,9 +90,10 @@ def test_graph_is_dropped_when_another_user_reallocates_the_context_scratch():
         g = __import__("ctypes").c_void_p()
         _lib.check(L.nb_graph_end_capture(ctx.handle, s, __import__("ctypes").byref(g)))
     assert L.nb_graph_is_stale(g) == 0
-    big = torch.empty(1 << 22, dtype=torch.int32, device="cuda")
-    keys = torch.randint(0, 1 << 20, (1 << 22,), device="cuda", dtype=torch.int32)
-    _lib.check(L.nb_sort_pairs(ctx.handle, keys.data_ptr(), big.data_ptr(), 1 << 22, 20, None))  # outgrows the scratch
+    m = 2 * max(int(r.fragments()), 1 << 22)   # more pairs than any sort on this context so far: the scratch must grow
+    big = torch.zeros(m, dtype=torch.int32, device="cuda")
+    keys = torch.randint(0, 1 << 20, (m,), device="cuda", dtype=torch.int32)
+    _lib.check(L.nb_sort_pairs(ctx.handle, keys.data_ptr(), big.data_ptr(), m, 20, None))
     torch.cuda.synchronize()
     assert L.nb_graph_is_stale(g) == 1
     assert L.nb_graph_launch(g, None) == _lib.NB_ERR_STALE_GRAPH
