@@ -152,13 +152,13 @@ __global__ void __launch_bounds__(256) bh_morton_kernel(const float* __restrict_
 // The thread that completes a node writes its record, and emits the traversal groups of a child that is a
 // maximal subtree of <= smax leaves (the round-1 group pass).
 #ifndef NB_TB_THREADS
-#define NB_TB_THREADS 64  // build-time knob: leaves per tile / 16.  Small tiles on purpose: the phases of a tile are
+#define NB_TB_THREADS 128  // build-time knob: leaves per tile / 16.  Small tiles on purpose: the phases of a tile are
                           // latency chains (random gather, then serial merges along the tile's spines), so the SM
                           // needs many independent tiles in different phases: 256 threads (2 tiles per SM, all in the
                           // same phase) built 16 Mi leaves in 1.79 ms, 128 threads in 1.49 ms
 #endif
 #ifndef NB_TB_K
-#define NB_TB_K 8  // build-time knob: consecutive leaves per thread in phase 1 (a power of two)
+#define NB_TB_K 4  // build-time knob: consecutive leaves per thread in phase 1 (a power of two)
 #endif
 constexpr int TB_THREADS = NB_TB_THREADS;
 constexpr int TB_K = NB_TB_K;                   // consecutive leaves per thread in phase 1

@@ -168,14 +168,8 @@ struct StageRec {
 #define NB_STAGE_CAT_(a, b) NB_STAGE_CAT2_(a, b)
 #define NB_STAGE(ctx, st, name) nb::StageScope NB_STAGE_CAT_(nb_stage_scope_, __LINE__)(ctx, st, name)
 
-// One pass of the direct kernel (see direct.cu): n_itiles target tiles x UJ source tiles.  Every target tile's
-// row of UJ source tiles is cut at the same places into C chunks of DESCENDING length (start[k] .. start[k+1]);
-// chunk c = k * n_itiles + itile, so the G CTAs, claiming chunk indices in ascending order, take the long chunks
-// of all rows first and the short ones last; chunk c writes partial slot slot_base + c.
-constexpr int NB_MAX_ROW_CHUNKS = 32;
-struct nb_chunk_tab {
-  int start[NB_MAX_ROW_CHUNKS + 1];
-};
+// One pass of the direct kernel (see direct.cu): n_itiles target tiles x UJ source tiles, cut into
+// `chunks` = n_itiles * C chunks that G CTAs claim dynamically; chunk c writes partial slot slot_base + c.
 struct nb_pass {
   long long U;       // work units = n_itiles * UJ
   long long chunks;  // n_itiles * C
@@ -184,7 +178,6 @@ struct nb_pass {
   int G;             // gridDim.x of that launch
   int n_itiles;
   size_t slot_base;  // first partial slot of this pass
-  nb_chunk_tab tab;
 };
 
 struct nb_context {

@@ -173,25 +173,24 @@ __device__ unsigned long long nb_direct_trace_buf[3 * 4096];
 #endif
 
 // Work distribution: the (target tile x source tile) unit space is cut into n_chunks CHUNKS, chunk c =
-// target tile c % n_itiles, source tiles [tab.start[k], tab.start[k+1]) with k = c / n_itiles, and CTAs claim
-// chunks from a global counter (work[0]) until none are left.  The cuts of a row are of descending length
-// (guided self-scheduling with fixed cut points: about a third of what is left of the row, never less than
-// 1/64 of a CTA's share of the launch), and chunk indices run over all rows' first chunks, then all second
-// chunks, ...: the launch starts with long chunks and ends with short ones, so its tail is as short as with 64
-// equal chunks per CTA while only ~1/3 as many chunks -- and per-chunk partial slots -- exist (1 Mi bodies:
-// 350 MB of partials with equal chunks, ~120 MB now).  A static equal split is not balanced on this machine:
+// target tile c / C, source tiles [jc*UJ/C, (jc+1)*UJ/C) with jc = c % C, and CTAs claim chunks from a
+// global counter (work[0]) until none are left.  A static equal split is not balanced on this machine:
 // with 5 CTAs resident per SM the warp schedulers favour some CTAs, equal shares finished between 151
 // and 457 ms of a 457 ms launch (profiles/r01_direct_cta_trace.log) and the SM ran under-occupied for
 // most of it.  Which CTA computes a chunk does not affect its result, and chunk c always lands in
 // partial slot c, so the sums stay reproducible.  The last CTA to leave re-arms the counters (work[1]
 // counts leavers), which keeps the launch replayable from a CUDA graph.
+// Tried in round 2 and dropped (profiles/r02_direct_chunk_plans_ab.jsonl): rows cut into chunks of DESCENDING length
+// claimed class by class (all rows' long chunks first, the short ones last), which needs a third of the partial slots
+// for the same tail: 394.1 ms per 1 Mi step against 387.9; the same equal chunks claimed class-major instead of
+// row-major: 391.0 ms.  With row-major claiming the CTAs in flight cover ~32 target tiles x ALL source ranges, so the
+// whole packed source array stays in use at once; class-major makes all 888 CTAs stream the same few source tiles.
 template <int T, int I, int JT, bool EPS0>
 __global__ void __launch_bounds__(T, NB_DIRECT_THREADS_PER_SM / T) direct_force_kernel(const float4* __restrict__ src,
                                                           const float4* __restrict__ tgt,
                                                           float* __restrict__ partial, unsigned* __restrict__ work,
-                                                          int n_chunks, int n_itiles, const nb_chunk_tab tab,
-                                                          int ja0, int na, int jb0, float eps2,
-                                                          unsigned long long slot_base) {
+                                                          int n_chunks, int C, int UJ, int ja0, int na, int jb0,
+                                                          float eps2, unsigned long long slot_base) {
   constexpr int P = I / 2;
   constexpr int IT = T * I;
   constexpr uint32_t TILE_BYTES = JT * sizeof(float4);
@@ -206,15 +205,7 @@ __global__ void __launch_bounds__(T, NB_DIRECT_THREADS_PER_SM / T) direct_force_
     const int g = (j < na) ? (ja0 + j) : (jb0 + (j - na));
     return src + (size_t)g * JT;
   };
-  // start[k] by compile-time indices only (a run-time index into the parameter struct would make ptxas copy the
-  // table to local memory); once or twice per chunk
-  auto tab_at = [&](int k) -> int {
-    int v = tab.start[0];
-#pragma unroll
-    for (int q = 1; q <= NB_MAX_ROW_CHUNKS; q++) v = (k >= q) ? tab.start[q] : v;
-    return v;
-  };
-  auto first_jtile = [&](int c) -> int { return tab_at(c / n_itiles); };
+  auto first_jtile = [&](int c) -> int { return (int)(((long long)(c % C) * UJ) / C); };
   if (tid == 0) {
     mbar_init(&full[0], 1);
     mbar_init(&full[1], 1);
@@ -247,9 +238,9 @@ __global__ void __launch_bounds__(T, NB_DIRECT_THREADS_PER_SM / T) direct_force_
   int chunk = claimed[0];
   unsigned n = 0;  // tiles this CTA has consumed: buffer and mbarrier parity
   for (unsigned k = 0; chunk < n_chunks; k++) {
-    const int kc = chunk / n_itiles, itile = chunk - kc * n_itiles;
-    int j = tab_at(kc);
-    const int jend = tab_at(kc + 1);
+    const int itile = chunk / C, jc = chunk - itile * C;
+    int j = (int)(((long long)jc * UJ) / C);
+    const int jend = (int)(((long long)(jc + 1) * UJ) / C);
     {
       const float4* base = tgt + (size_t)itile * IT + tid;
 #pragma unroll
@@ -399,9 +390,8 @@ __global__ void __launch_bounds__(256) reduce_kernel(const float* __restrict__ p
   float ax = 0.f, ay = 0.f, az = 0.f, ex = 0.f, ey = 0.f, ez = 0.f;
   for (int ps = 0; ps < ra.npass; ps++) {
     const int C = ra.pass[ps].C;
-    const size_t stride = (size_t)ra.pass[ps].n_itiles * (size_t)(3 * IT);  // chunk k of tile t is slot k * n_itiles + t
-    const float* p = partial + (ra.pass[ps].slot_base + (size_t)t) * (size_t)(3 * IT) + r;
-    for (int c = 0; c < C; c++, p += stride) {
+    const float* p = partial + (ra.pass[ps].slot_base + (size_t)t * C) * (size_t)(3 * IT) + r;
+    for (int c = 0; c < C; c++, p += 3 * IT) {
       float y, s;
       y = __fsub_rn(p[0], ex); s = __fadd_rn(ax, y); ex = __fsub_rn(__fsub_rn(s, ax), y); ax = s;
       y = __fsub_rn(p[IT], ey); s = __fadd_rn(ay, y); ey = __fsub_rn(__fsub_rn(s, ay), y); ay = s;
@@ -438,48 +428,20 @@ static int occupancy(bool eps0) {
   return occ > 0 ? occ : 1;
 }
 
-// Cut points of a row of UJ source tiles (see the kernel's comment): next chunk = a third of what is left,
-// at least `min_len` = 1/per_cta of a CTA's share of the launch (NB_DIRECT_CHUNKS, default 64: the tail of a
-// launch is at most one such chunk long), a short remainder joins the last chunk.  Returns the chunk count.
-static int plan_row_chunks(int n_itiles, int UJ, long long ctas, nb_chunk_tab& tab) {
-  long long per_cta = 64;
-  if (const char* e = getenv("NB_DIRECT_CHUNKS")) {  // tuning knob: shortest chunk = share / per_cta
+// Chunks per target tile: enough chunks that every CTA claims about `per_cta` of them (the tail of a launch is at
+// most one chunk long), never more than one chunk per source tile.  per_cta = 32: round 1 used 64, whose per-chunk
+// partial slots came to 350 MB at any large N; the sweep is flat down to ~32 (profiles/r01_direct_variants_ab.log:
+// 24 -> 388.6 ms, 48 -> 386.6, 64 -> 387.3, 128 -> 386.2 per 1 Mi step), which halves the slots.
+static int chunks_per_tile(int n_itiles, int UJ, long long ctas) {
+  long long per_cta = 32;
+  if (const char* e = getenv("NB_DIRECT_CHUNKS")) {  // tuning knob: chunks per CTA
     const long long v = atoll(e);
     if (v > 0) per_cta = v;
   }
-  const double share = (double)n_itiles * (double)UJ / (double)ctas;  // source tiles x target tiles per CTA
-  long long min_len = (long long)(share / (double)per_cta);
-  if (min_len < 1) min_len = 1;
-  int k = 0, at = 0;
-  tab.start[0] = 0;
-  if (const char* e = getenv("NB_DIRECT_PLAN")) {  // A/B knob: 0 = equal chunks (per_cta of them per CTA), as in round 1
-    if (atoi(e) == 0) {
-      long long c = (per_cta * ctas + n_itiles - 1) / n_itiles;
-      if (c > UJ) c = UJ;
-      if (c > NB_MAX_ROW_CHUNKS) c = NB_MAX_ROW_CHUNKS;
-      if (c < 1) c = 1;
-      for (long long q = 1; q <= c; q++) tab.start[q] = (int)((long long)UJ * q / c);
-      for (int q = (int)c + 1; q <= NB_MAX_ROW_CHUNKS; q++) tab.start[q] = UJ;
-      return (int)c;
-    }
-  }
-  while (at < UJ) {
-    const long long rest = UJ - at;
-    long long len = (rest + 2) / 3;
-    if (len < min_len) {  // the short end of the row: what is left in equal parts of about min_len
-      long long parts = (rest + min_len / 2) / min_len;
-      if (parts < 1) parts = 1;
-      if (parts > NB_MAX_ROW_CHUNKS - k) parts = NB_MAX_ROW_CHUNKS - k;
-      for (long long q = 1; q <= parts; q++) tab.start[++k] = at + (int)(rest * q / parts);
-      at = UJ;
-      break;
-    }
-    if (k == NB_MAX_ROW_CHUNKS - 1) len = rest;
-    at += (int)len;
-    tab.start[++k] = at;
-  }
-  for (int q = k + 1; q <= NB_MAX_ROW_CHUNKS; q++) tab.start[q] = UJ;
-  return k;
+  long long c = (per_cta * ctas + n_itiles - 1) / n_itiles;
+  if (c > UJ) c = UJ;
+  if (c < 1) c = 1;
+  return (int)c;
 }
 
 // Launch one pass.  Source tiles [ja0, ja0+na) then [jb0, jb0+nbt) of `src` (tile = JT bodies) against
@@ -508,7 +470,7 @@ int launch_direct_pass(nb_context* ctx, const DirectCfg& cfg, const float4* src,
     if (v > 0 && v < occ) use_occ = v;
   }
   const long long ctas = (long long)use_occ * ctx->sm_count;
-  ps.C = plan_row_chunks(n_itiles, UJ, ctas, ps.tab);
+  ps.C = chunks_per_tile(n_itiles, UJ, ctas);
   ps.chunks = (long long)n_itiles * ps.C;
   if (ps.chunks > 0x7fffffffll - 65536) {
     set_error("direct N^2: %lld work chunks exceed the kernel's 32-bit chunk counter", ps.chunks);
@@ -518,16 +480,14 @@ int launch_direct_pass(nb_context* ctx, const DirectCfg& cfg, const float4* src,
   // pass 0 reserves room for the remote-source pass of a sharded step too ((R-1) x as many source tiles,
   // planned here the way that pass will be): the buffer must not move while pass 0 runs
   size_t slots = ps.slot_base + (size_t)ps.chunks;
-  if (pass_index == 0 && ctx->mg_nranks > 1) {
-    nb_chunk_tab remote;
-    slots += (size_t)n_itiles * (size_t)plan_row_chunks(n_itiles, UJ * (ctx->mg_nranks - 1), ctas, remote);
-  }
+  if (pass_index == 0 && ctx->mg_nranks > 1)
+    slots += (size_t)n_itiles * (size_t)chunks_per_tile(n_itiles, UJ * (ctx->mg_nranks - 1), ctas);
   if (int rc = ctx->partial.ensure(slots * 3 * cfg.IT() * sizeof(float))) return rc;
   float* part = ctx->partial.as<float>();
   unsigned* work = ctx->direct_work.as<unsigned>() + 2 * pass_index;
 #define NB_LAUNCH_DIRECT(T_, I_, JT_, E_)                                                                     \
-  direct_force_kernel<T_, I_, JT_, E_><<<ps.G, T_, 0, st>>>(src, tgt, part, work, (int)ps.chunks, n_itiles, ps.tab,   \
-                                                            ja0, na, jb0, eps2, (unsigned long long)ps.slot_base)
+  direct_force_kernel<T_, I_, JT_, E_><<<ps.G, T_, 0, st>>>(src, tgt, part, work, (int)ps.chunks, ps.C, UJ, ja0, na, \
+                                                            jb0, eps2, (unsigned long long)ps.slot_base)
   ProfScope prof(ctx, st);
   if (big) {
     if (eps0) NB_LAUNCH_DIRECT(NB_DIRECT_BIG_T, NB_DIRECT_BIG_I, NB_DIRECT_BIG_JT, true);

@@ -127,7 +127,10 @@ constexpr uint32_t RS_FLAG_AGG = 1u << 30, RS_FLAG_INC = 2u << 30, RS_VAL_MASK =
 constexpr int RS_MAX_PASSES = 3;   // ceil(32 / 11)
 constexpr int RS_MAX_BITS = 11;
 constexpr int RS_MAX_BINS = 1 << RS_MAX_BITS;
-constexpr int RS_LOOK = 4;         // predecessors examined per look-back round trip
+#ifndef NB_RS_LOOK
+#define NB_RS_LOOK 4  // build-time knob
+#endif
+constexpr int RS_LOOK = NB_RS_LOOK;  // predecessors examined per look-back round trip
 
 struct RsPlan {
   int passes;
