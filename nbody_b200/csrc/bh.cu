@@ -190,6 +190,18 @@ __device__ __forceinline__ int bh_delta_adj(const uint32_t* __restrict__ keys, i
   return __clz(a ^ b);
 }
 
+#ifndef NB_BH_SEPARATE_GATHER
+#define NB_BH_SEPARATE_GATHER 0  // build-time knob: 1 = the leaves are gathered by a kernel of their own before the tile pass
+#endif
+// leaves of the tree = bodies in sorted order, packed {x,y,z,m}: one random 16-B read per body
+__global__ void __launch_bounds__(256) bh_gather_kernel(const float4* __restrict__ packed, size_t n,
+                                                        const int32_t* __restrict__ perm,
+                                                        float4* __restrict__ leaves) {
+  const size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  leaves[k] = __ldg(packed + perm[k]);
+}
+
 struct TreeOut {
   float4* node_com;  // [2n-1]: internal nodes 0..n-2, leaf k of the sorted order at n-1+k
   int4* meta;        // [n-1] {left, right, prefix, 0}
@@ -353,15 +365,20 @@ __global__ void __launch_bounds__(TB_THREADS, 1024 / TB_THREADS) bh_tree_kernel(
 #pragma unroll
     for (int i = 0; i < TB_K; i++) {
       const int q = tid + i * TB_THREADS;
-      idx[i] = (q < tcount) ? perm[t0 + q] : -1;
+      idx[i] = (q < tcount && !NB_BH_SEPARATE_GATHER) ? perm[t0 + q] : -1;
     }
 #pragma unroll
     for (int i = 0; i < TB_K; i++) {
       const int q = tid + i * TB_THREADS;
       if (q < tcount) {
+#if NB_BH_SEPARATE_GATHER
+        const float4 v = o.node_com[o.leaf0 + t0 + q];
+        s_com[tb_pad(q)] = v;
+#else
         const float4 v = __ldg(packed + idx[i]);
         s_com[tb_pad(q)] = v;
         o.node_com[o.leaf0 + t0 + q] = v;
+#endif
         s_lo[tb_pad(q)] = (short)q;
         s_hi[tb_pad(q)] = (short)q;
         s_d[tb_pad(q + 1)] = bh_delta_adj(keys, n, t0 + q);
@@ -898,6 +915,10 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
     o.supers = b->supers.as<int4>();
     o.nsupers = reinterpret_cast<int*>(misc) + 48;
     const unsigned tiles = (unsigned)((n + TB_TILE - 1) / TB_TILE);
+#if NB_BH_SEPARATE_GATHER
+    bh_gather_kernel<<<gn, 256, 0, st>>>(b->packed.as<float4>(), n, b->perm_sorted, o.node_com + o.leaf0);
+    NB_LAUNCH_CHECK(ctx);
+#endif
     bh_tree_kernel<<<tiles, TB_THREADS, kTreeSmem, st>>>(b->keys_sorted, b->perm_sorted, b->packed.as<float4>(), o);
     NB_LAUNCH_CHECK(ctx);
     if (tiles > 1) {  // the subtrees the tiles left over (at most 2 x 62 each: one per level of each spine)

@@ -128,7 +128,7 @@ constexpr int RS_MAX_PASSES = 3;   // ceil(32 / 11)
 constexpr int RS_MAX_BITS = 11;
 constexpr int RS_MAX_BINS = 1 << RS_MAX_BITS;
 #ifndef NB_RS_LOOK
-#define NB_RS_LOOK 4  // build-time knob
+#define NB_RS_LOOK 1  // build-time knob: 1 -> 0.463 ms, 2 -> 0.470, 4 -> 0.485 for the 16 Mi Morton sort (profiles/r02_bh_tree_tile_shapes_ab_v2.jsonl)
 #endif
 constexpr int RS_LOOK = NB_RS_LOOK;  // predecessors examined per look-back round trip
 
