@@ -550,6 +550,7 @@ __global__ void __launch_bounds__(256) bh_parent_kernel(int n, const int4* __res
 #define NB_BH_PRAGMA_UNROLL(n) NB_BH_PRAGMA_(unroll n)
 constexpr int BH_WARPS = 4;
 constexpr int BH_LIST = 64;
+constexpr int BH_STAGE = 32 * 32;  // bytes per warp: one {centre of mass, node record} per lane
 
 // SHARDED (multi-GPU, mgpu.cu): every rank holds the same tree; this rank traverses only the groups it
 // is dealt (by the group's first sorted body, so the deal is identical on every rank although the
@@ -576,9 +577,11 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   if (threadIdx.x < 32) size2_tab[threadIdx.x] = misc[threadIdx.x];
   __syncthreads();
-  const size_t smem_per_warp = (size_t)stack_cap * 4 + BH_LIST * 16;
+  const size_t smem_per_warp = (size_t)stack_cap * 4 + BH_LIST * 16 + BH_STAGE;
   float4* list = reinterpret_cast<float4*>(bh_smem + (size_t)w * smem_per_warp);
-  int* stack = reinterpret_cast<int*>(bh_smem + (size_t)w * smem_per_warp + BH_LIST * 16);
+  float4* stage_c = list + BH_LIST;                              // next round's nodes, one per lane (cp.async)
+  int4* stage_m = reinterpret_cast<int4*>(stage_c + 32);
+  int* stack = reinterpret_cast<int*>(bh_smem + (size_t)w * smem_per_warp + BH_LIST * 16 + BH_STAGE);
   int deepest = 0;
   const int leaf0 = n - 1;
   const unsigned lt = (1u << lane) - 1u;
@@ -624,27 +627,31 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
   unsigned visits = 0;
   if (lane == 0) stack[0] = 0;
   __syncwarp();
-  // The node fetches are software-pipelined: the next round's nodes are popped and their loads issued BEFORE the
+  // The node fetches are software-pipelined: the next round's nodes are popped and their fetches issued BEFORE the
   // current interaction list is evaluated, so the (L2 / DRAM) latency of the walk hides under the pair arithmetic.
+  // The fetches are cp.async copies into a per-lane staging slot in shared memory: no destination registers, hence
+  // no scoreboard wait until the data is needed.  (With plain loads ptxas put a MOV of the node's mass right behind
+  // the load -- the wait for the data BEFORE the evaluation: 11.5 % of the kernel's stall samples on that one MOV.)
   int ni;
   bool have;
-  float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
-  int4 mt = make_int4(0, 0, 31, 0);
+  float4 c;
+  int4 mt;
   auto pop_and_fetch = [&]() {
     const int m = min(sp, 32);
     have = lane < m;
-    ni = have ? stack[sp - m + lane] : 0;
+    ni = have ? stack[sp - m + lane] : 0;  // lanes without a node fetch the root (ignored)
     sp -= m;
     __syncwarp();
-    c = make_float4(0.f, 0.f, 0.f, 0.f);
-    mt = make_int4(0, 0, 31, 0);
-    if (have) {  // both fetches issue together (no dependence of the second on the first's data)
-      c = node_com[ni];
-      if (ni < leaf0) mt = meta[ni];
-    }
+    const int mi = max(min(ni, leaf0 - 1), 0);  // leaves have no record: some internal node's is fetched and ignored
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(smem_u32(stage_c + lane)), "l"(node_com + ni) : "memory");
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(smem_u32(stage_m + lane)), "l"(meta + mi) : "memory");
+    asm volatile("cp.async.commit_group;" ::: "memory");
   };
   pop_and_fetch();
   for (;;) {
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    c = stage_c[lane];
+    mt = stage_m[lane];
     const bool leaf = ni >= leaf0;
     const bool valid = have && c.w != 0.f;  // total_mass == 0 -> skipped (:157-158)
     bool acc = leaf;
@@ -861,7 +868,7 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
     b->group = g;
     if (const char* ce = getenv("NB_BH_STACK")) {
       int c = atoi(ce);
-      c = c < 512 ? 512 : (c > 2816 ? 2816 : c);  // 4 warps x (cap x 4 + 1 KiB) <= 48 KiB
+      c = c < 512 ? 512 : (c > 2560 ? 2560 : c);  // 4 warps x (cap x 4 + 2 KiB) <= 48 KiB
       if (c != b->stack_cap) b->occ = 0;
       b->stack_cap = c;
     }
@@ -973,7 +980,7 @@ int bh_forces(nb_context* ctx, const nb_particles* d, float theta, float G, floa
   float* misc = b->misc.as<float>();
   int* cursor = reinterpret_cast<int*>(misc) + 45;
   NB_CUDA(cudaMemsetAsync(cursor, 0, sizeof(int), st));
-  const size_t smem = (size_t)BH_WARPS * ((size_t)b->stack_cap * 4 + BH_LIST * 16);
+  const size_t smem = (size_t)BH_WARPS * ((size_t)b->stack_cap * 4 + BH_LIST * 16 + BH_STAGE);
   const float eps2 = eps * eps;
   const bool eps0 = !(eps2 >= NB_EPS2_GUARD);
   if (!b->occ) {

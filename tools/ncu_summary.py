@@ -1,6 +1,8 @@
 #!/usr/bin/env python
 """Extract the metrics we cite from an .ncu-rep into a small text summary (profiles/*.txt).
-usage: tools/ncu_summary.py report.ncu-rep [kernel-substring] > profiles/xxx.txt"""
+usage: tools/ncu_summary.py report.ncu-rep [kernel-substring] > profiles/xxx.txt
+       tools/ncu_summary.py report.ncu-rep direct_force_kernel --traffic-json BODIES profiles/direct_traffic.json
+         (DRAM bytes of one force-kernel launch, read by bench.py for roofline.traffic)"""
 import csv
 import subprocess
 import sys
@@ -41,6 +43,25 @@ def main():
     rows = list(csv.reader(out.splitlines()))
     hdr, units, data = rows[0], rows[1], rows[2:]
     kcol = hdr.index("Kernel Name")
+    if "--traffic-json" in sys.argv:
+        import json
+        k = sys.argv.index("--traffic-json")
+        bodies, dst = int(sys.argv[k + 1]), sys.argv[k + 2]
+        for r in data:
+            if sub in r[kcol]:
+                def val(name):
+                    i = hdr.index(name)
+                    mult = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[units[i]]
+                    return float(r[i].replace(",", "")) * mult
+                rd, wr = val("dram__bytes_read.sum"), val("dram__bytes_write.sum")
+                with open(dst, "w") as f:
+                    json.dump({"bodies": bodies, "dram_bytes_per_launch": int(rd + wr), "dram_bytes_read": int(rd),
+                               "dram_bytes_written": int(wr), "kernel": r[kcol][:80],
+                               "source": f"ncu --set full capture {rep.split('/')[-1]} (tools/ncu_summary.py --traffic-json)"}, f)
+                    f.write("\n")
+                print(open(dst).read())
+                return
+        raise SystemExit("kernel not found")
     print(f"# {rep}")
     for r in data:
         if sub and sub not in r[kcol]:
