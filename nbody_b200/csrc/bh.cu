@@ -53,7 +53,8 @@ struct BH {
   int group = 64;         // max bodies per traversal group / warp (32 or 64; NB_BH_GROUP overrides)
   int super = 512;        // max leaves of the subtree a group is cut from (NB_BH_SUPER overrides; >= group)
   int occ = 0;
-  int stack_cap = 2048;   // entries per warp traversal stack (NB_BH_STACK overrides)
+  int stack_cap = 1280;   // entries per warp traversal stack (NB_BH_STACK overrides): deepest seen 440 (16 Mi Plummer);
+                          // 2048 -> 5 CTAs per SM and 32.2 ms for that traversal, 1024 -> 8 CTAs and 31.65 ms
   bool built = false;
 };
 

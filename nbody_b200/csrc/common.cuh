@@ -174,8 +174,7 @@ struct nb_pass {
   long long U;       // work units = n_itiles * UJ
   long long chunks;  // n_itiles * C
   int UJ;            // source tiles per target tile
-  int C;             // chunks per target tile, rows [0, T1)
-  int C2, T1;        // ... and of the last rows [T1, n_itiles): finer chunks for the tail of the launch
+  int C;             // chunks per target tile
   int G;             // gridDim.x of that launch
   int n_itiles;
   size_t slot_base;  // first partial slot of this pass

@@ -180,18 +180,23 @@ __device__ unsigned long long nb_direct_trace_buf[3 * 4096];
 // most of it.  Which CTA computes a chunk does not affect its result, and chunk c always lands in
 // partial slot c, so the sums stay reproducible.  The last CTA to leave re-arms the counters (work[1]
 // counts leavers), which keeps the launch replayable from a CUDA graph.
-// Round 2: two chunk lengths per launch, long ones for most rows and short ones for the last rows (plan_chunks below).
-// Tried in round 2 and dropped (profiles/r02_direct_chunk_plans_ab.jsonl): rows cut into chunks of DESCENDING length
-// claimed class by class (all rows' long chunks first, the short ones last), which needs a third of the partial slots
-// for the same tail: 394.1 ms per 1 Mi step against 387.9; the same equal chunks claimed class-major instead of
-// row-major: 391.0 ms.  With row-major claiming the CTAs in flight cover ~32 target tiles x ALL source ranges, so the
-// whole packed source array stays in use at once; class-major makes all 888 CTAs stream the same few source tiles.
+// Round 2 tried to cut the per-chunk partial slots (6 KB each, 350 MB at any large N with 64 chunks per CTA) without
+// lengthening the tail of the launch; all measured on one box against this kernel (profiles/r02_direct_same_box_ab.jsonl,
+// r02_direct_chunk_plans_ab.jsonl; ms per 1 Mi step, this kernel: 387.0):
+//   * 32 equal chunks per CTA (half the slots): 389.0 -- the tail is one chunk long;
+//   * rows cut into chunks of descending length, claimed class by class (long chunks of all rows first): 394.1, and
+//     equal chunks in that order 391.0 -- with row-major claiming the CTAs in flight cover ~32 target tiles x ALL source
+//     ranges, the whole packed source array in use at once; class-major makes all 888 CTAs stream the same few tiles;
+//   * long chunks for most rows and short ones for the last rows, row-major (a third of the slots, same tail): 392.4 --
+//     and 391.0 / 390.2 with twice / four times as many chunks, i.e. not the schedule but the kernel: the extra
+//     chunk-to-range arithmetic changed ptxas' schedule of the one-mass pair loop (the general loop stayed at 428-430).
+// Kept: this kernel and 64 chunks per CTA; NB_DIRECT_CHUNKS=32 halves the scratch for +0.5 %.
 template <int T, int I, int JT, bool EPS0>
 __global__ void __launch_bounds__(T, NB_DIRECT_THREADS_PER_SM / T) direct_force_kernel(const float4* __restrict__ src,
                                                           const float4* __restrict__ tgt,
                                                           float* __restrict__ partial, unsigned* __restrict__ work,
-                                                          int n_chunks, int C1, int C2, int T1, int UJ, int ja0, int na,
-                                                          int jb0, float eps2, unsigned long long slot_base) {
+                                                          int n_chunks, int C, int UJ, int ja0, int na, int jb0,
+                                                          float eps2, unsigned long long slot_base) {
   constexpr int P = I / 2;
   constexpr int IT = T * I;
   constexpr uint32_t TILE_BYTES = JT * sizeof(float4);
@@ -206,28 +211,7 @@ __global__ void __launch_bounds__(T, NB_DIRECT_THREADS_PER_SM / T) direct_force_
     const int g = (j < na) ? (ja0 + j) : (jb0 + (j - na));
     return src + (size_t)g * JT;
   };
-  // chunk c -> target tile and source-tile range: rows [0, T1) are cut into C1 chunks each, the last rows into C2
-  const int coarse = T1 * C1;
-  auto chunk_range = [&](int c, int& itile, int& j0, int& j1) {
-    int C, jc;
-    if (c < coarse) {
-      C = C1;
-      itile = c / C1;
-      jc = c - itile * C1;
-    } else {
-      C = C2;
-      const int cf = c - coarse, r = cf / C2;
-      itile = T1 + r;
-      jc = cf - r * C2;
-    }
-    j0 = (int)(((long long)jc * UJ) / C);
-    j1 = (int)(((long long)(jc + 1) * UJ) / C);
-  };
-  auto first_jtile = [&](int c) -> int {
-    int it, j0, j1;
-    chunk_range(c, it, j0, j1);
-    return j0;
-  };
+  auto first_jtile = [&](int c) -> int { return (int)(((long long)(c % C) * UJ) / C); };
   if (tid == 0) {
     mbar_init(&full[0], 1);
     mbar_init(&full[1], 1);
@@ -260,8 +244,9 @@ __global__ void __launch_bounds__(T, NB_DIRECT_THREADS_PER_SM / T) direct_force_
   int chunk = claimed[0];
   unsigned n = 0;  // tiles this CTA has consumed: buffer and mbarrier parity
   for (unsigned k = 0; chunk < n_chunks; k++) {
-    int itile, j, jend;
-    chunk_range(chunk, itile, j, jend);
+    const int itile = chunk / C, jc = chunk - itile * C;
+    int j = (int)(((long long)jc * UJ) / C);
+    const int jend = (int)(((long long)(jc + 1) * UJ) / C);
     {
       const float4* base = tgt + (size_t)itile * IT + tid;
 #pragma unroll
@@ -410,10 +395,8 @@ __global__ void __launch_bounds__(256) reduce_kernel(const float* __restrict__ p
   // chunk sums of this body's target tile in chunk order, compensated (each chunk sum already is)
   float ax = 0.f, ay = 0.f, az = 0.f, ex = 0.f, ey = 0.f, ez = 0.f;
   for (int ps = 0; ps < ra.npass; ps++) {
-    const int T1 = ra.pass[ps].T1, C1 = ra.pass[ps].C;
-    const int C = t < T1 ? C1 : ra.pass[ps].C2;
-    const size_t first = t < T1 ? (size_t)t * C1 : (size_t)T1 * C1 + (size_t)(t - T1) * C;
-    const float* p = partial + (ra.pass[ps].slot_base + first) * (size_t)(3 * IT) + r;
+    const int C = ra.pass[ps].C;
+    const float* p = partial + (ra.pass[ps].slot_base + (size_t)t * C) * (size_t)(3 * IT) + r;
     for (int c = 0; c < C; c++, p += 3 * IT) {
       float y, s;
       y = __fsub_rn(p[0], ex); s = __fadd_rn(ax, y); ex = __fsub_rn(__fsub_rn(s, ax), y); ax = s;
@@ -451,41 +434,18 @@ static int occupancy(bool eps0) {
   return occ > 0 ? occ : 1;
 }
 
-// Chunks per target tile (row): enough that every CTA claims about `per_cta` of them, never more than one chunk per
-// source tile.
-static int chunks_per_tile(int n_itiles, int UJ, long long ctas, long long per_cta) {
+// Chunks per target tile: enough chunks that every CTA claims about `per_cta` of them (the tail of a
+// launch is at most one chunk long), never more than one chunk per source tile.
+static int chunks_per_tile(int n_itiles, int UJ, long long ctas) {
+  long long per_cta = 64;
+  if (const char* e = getenv("NB_DIRECT_CHUNKS")) {  // tuning knob: chunks per CTA
+    const long long v = atoll(e);
+    if (v > 0) per_cta = v;
+  }
   long long c = (per_cta * ctas + n_itiles - 1) / n_itiles;
   if (c > UJ) c = UJ;
   if (c < 1) c = 1;
   return (int)c;
-}
-
-// Two chunk sizes per launch.  The tail of a launch is one chunk long, which wants short chunks (64 per CTA measured
-// best in round 1), but every chunk owns a 6 KB partial slot (350 MB at any large N).  So most rows get LONG chunks
-// (16 per CTA) and only the last rows -- claimed last, chunk indices being row-major -- get short ones (64 per CTA):
-// enough of them to keep every CTA busy for one long chunk, i.e. ctas / C1 rows, x 1.5.  1 Mi bodies: 1858 rows x 7 +
-// 190 rows x 28 chunks = 18 326 slots = 113 MB (round 1: 56 832 = 350 MB).  The claiming order stays row-major: the
-// CTAs in flight then cover ~32 target tiles x ALL source ranges, the whole packed source array in use at once
-// (claiming all rows' long chunks first and short ones last -- a guided schedule with a third of the slots -- ran
-// 1.6 % slower, and equal chunks in that order 0.8 %: profiles/r02_direct_chunk_plans_ab.jsonl).
-static void plan_chunks(int n_itiles, int UJ, long long ctas, int& C1, int& C2, int& T1) {
-  long long fine = 64, coarse = 16;
-  if (const char* e = getenv("NB_DIRECT_CHUNKS")) {  // tuning knob: short chunks per CTA (long ones: a quarter)
-    const long long v = atoll(e);
-    if (v > 0) {
-      fine = v;
-      coarse = v >= 4 ? v / 4 : v;
-    }
-  }
-  C1 = chunks_per_tile(n_itiles, UJ, ctas, coarse);
-  C2 = chunks_per_tile(n_itiles, UJ, ctas, fine);
-  long long fine_rows = (3 * ctas / 2 + C1 - 1) / C1;
-  if (C2 <= C1 || fine_rows >= n_itiles) {  // small launches: one chunk size
-    C1 = C2;
-    T1 = n_itiles;
-    return;
-  }
-  T1 = n_itiles - (int)fine_rows;
 }
 
 // Launch one pass.  Source tiles [ja0, ja0+na) then [jb0, jb0+nbt) of `src` (tile = JT bodies) against
@@ -500,7 +460,7 @@ int launch_direct_pass(nb_context* ctx, const DirectCfg& cfg, const float4* src,
   ps.slot_base = (pass_index == 0) ? 0 : ctx->pass[0].slot_base + (size_t)ctx->pass[0].chunks;
   if (ps.U == 0) {
     ps.G = 0;
-    ps.C = ps.C2 = ps.T1 = 0;
+    ps.C = 0;
     ps.chunks = 0;
     return NB_OK;
   }
@@ -514,27 +474,23 @@ int launch_direct_pass(nb_context* ctx, const DirectCfg& cfg, const float4* src,
     if (v > 0 && v < occ) use_occ = v;
   }
   const long long ctas = (long long)use_occ * ctx->sm_count;
-  plan_chunks(n_itiles, UJ, ctas, ps.C, ps.C2, ps.T1);
-  ps.chunks = (long long)ps.T1 * ps.C + (long long)(n_itiles - ps.T1) * ps.C2;
+  ps.C = chunks_per_tile(n_itiles, UJ, ctas);
+  ps.chunks = (long long)n_itiles * ps.C;
   if (ps.chunks > 0x7fffffffll - 65536) {
     set_error("direct N^2: %lld work chunks exceed the kernel's 32-bit chunk counter", ps.chunks);
     return NB_ERR_INVALID;
   }
   ps.G = (int)(ctas < ps.chunks ? ctas : ps.chunks);
   // pass 0 reserves room for the remote-source pass of a sharded step too ((R-1) x as many source tiles,
-  // planned here the way that pass will be): the buffer must not move while pass 0 runs
+  // hence at most (R-1) x as many chunks): the buffer must not move while pass 0 runs
   size_t slots = ps.slot_base + (size_t)ps.chunks;
-  if (pass_index == 0 && ctx->mg_nranks > 1) {
-    int c1, c2, t1;
-    plan_chunks(n_itiles, UJ * (ctx->mg_nranks - 1), ctas, c1, c2, t1);
-    slots += (size_t)t1 * (size_t)c1 + (size_t)(n_itiles - t1) * (size_t)c2;
-  }
+  if (pass_index == 0 && ctx->mg_nranks > 1) slots += (size_t)ps.chunks * (size_t)(ctx->mg_nranks - 1);
   if (int rc = ctx->partial.ensure(slots * 3 * cfg.IT() * sizeof(float))) return rc;
   float* part = ctx->partial.as<float>();
   unsigned* work = ctx->direct_work.as<unsigned>() + 2 * pass_index;
 #define NB_LAUNCH_DIRECT(T_, I_, JT_, E_)                                                                     \
-  direct_force_kernel<T_, I_, JT_, E_><<<ps.G, T_, 0, st>>>(src, tgt, part, work, (int)ps.chunks, ps.C, ps.C2, ps.T1, \
-                                                            UJ, ja0, na, jb0, eps2, (unsigned long long)ps.slot_base)
+  direct_force_kernel<T_, I_, JT_, E_><<<ps.G, T_, 0, st>>>(src, tgt, part, work, (int)ps.chunks, ps.C, UJ, ja0, na, \
+                                                            jb0, eps2, (unsigned long long)ps.slot_base)
   ProfScope prof(ctx, st);
   if (big) {
     if (eps0) NB_LAUNCH_DIRECT(NB_DIRECT_BIG_T, NB_DIRECT_BIG_I, NB_DIRECT_BIG_JT, true);

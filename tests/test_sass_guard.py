@@ -13,7 +13,7 @@ import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "nbody_b200", "libnbody_b200.so")
-KERNEL = "_ZN2nb19direct_force_kernelILi256ELi2ELi1024ELb0EEEvPK6float4S3_PfPjiiiiiiiify"
+KERNEL = "_ZN2nb19direct_force_kernelILi256ELi2ELi1024ELb0EEEvPK6float4S3_PfPjiiiiiify"
 
 pytestmark = pytest.mark.skipif(shutil.which("cuobjdump") is None or not os.path.exists(LIB),
                                 reason="needs cuobjdump and the built library")
