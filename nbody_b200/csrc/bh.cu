@@ -44,6 +44,7 @@ struct BH {
   int pipeline = 1;   // NB_BH_PIPELINE=0: fetch the next round's nodes after the list evaluation (A/B)
   nb::DevBuf slot;    // int per split position: meeting point of the two children of a node that spans tiles
   nb::DevBuf parent;  // filled on export only
+  nb::DevBuf inv;     // inverse sort permutation (sharded finish only)
   nb::DevBuf groups;  // int2 {first,count} per traversal group
   uint32_t* keys_sorted = nullptr;  // where the last build's sorted keys / permutation live
   int32_t* perm_sorted = nullptr;
@@ -345,7 +346,10 @@ __device__ __forceinline__ float4 tb_form(int l, int g, int r, int dL, int dR, i
   return c;
 }
 
-__global__ void __launch_bounds__(TB_THREADS, 1024 / TB_THREADS) bh_tree_kernel(const uint32_t* __restrict__ keys,
+#ifndef NB_TB_MIN_BLOCKS
+#define NB_TB_MIN_BLOCKS (1024 / NB_TB_THREADS)  // build-time knob: resident tiles per SM asked of ptxas (register cap)
+#endif
+__global__ void __launch_bounds__(TB_THREADS, NB_TB_MIN_BLOCKS) bh_tree_kernel(const uint32_t* __restrict__ keys,
                                                                  const int32_t* __restrict__ perm,
                                                                  const float4* __restrict__ packed, TreeOut o) {
   extern __shared__ __align__(16) unsigned char tb_smem[];
@@ -624,7 +628,7 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
   const f2 xi2 = pk(me[0].x, me[BPL - 1].x), yi2 = pk(me[0].y, me[BPL - 1].y), zi2 = pk(me[0].z, me[BPL - 1].z);
   f2 sx2 = pk(0.f, 0.f), sy2 = sx2, sz2 = sx2;
 
-  int sp = 1, nl = 0;
+  int sp = 1, nl = 0, lbase = 0;
   unsigned visits = 0;
   if (lane == 0) stack[0] = 0;
   __syncwarp();
@@ -665,7 +669,8 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
     }
     const bool is_acc = valid && acc, is_rej = valid && !acc;
     const unsigned amask = __ballot_sync(0xffffffffu, is_acc), rmask = __ballot_sync(0xffffffffu, is_rej);
-    if (is_acc) list[nl + __popc(amask & lt)] = make_float4(c.x, c.y, c.z, G * c.w);  // G*M once per node
+    // the list is a ring of two 32-entry halves: a batch is one half, what is left over already sits in the other
+    if (is_acc) list[(lbase + nl + __popc(amask & lt)) & (BH_LIST - 1)] = make_float4(c.x, c.y, c.z, G * c.w);  // G*M once per node
     const int npush = 2 * __popc(rmask);
     deepest = max(deepest, sp + npush);
     if (sp + npush > stack_cap) {  // never silently drop subtrees (the reference does, :186-194)
@@ -684,8 +689,9 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
     if (!done && pipeline) pop_and_fetch();  // in flight while the list is evaluated
     while (nl >= 32 || (done && nl > 0)) {
       const int ne = min(nl, 32);
+      const float4* lcur = list + lbase;
       auto body = [&](int e) {
-        const float4 p = list[e];  // warp-broadcast LDS.128; p.w = G * M
+        const float4 p = lcur[e];  // warp-broadcast LDS.128; p.w = G * M
         const float gm = p.w;
         if constexpr (BPL == 2) {
           // the lane's two bodies as one packed fp32x2 pair (FADD2/FFMA2/FMUL2, as in direct.cu)
@@ -724,14 +730,9 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
         for (int e = 0; e < ne; e++) body(e);
       }
       visits += ne;
-      __syncwarp();
-      const int rest = nl - ne;  // < 32
-      float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (lane < rest) t = list[ne + lane];
-      __syncwarp();
-      if (lane < rest) list[lane] = t;
-      __syncwarp();
-      nl = rest;
+      __syncwarp();  // every lane has read the batch before later entries wrap into its half
+      if (ne == 32) lbase ^= 32;  // what is left (< 32 entries) already sits at the start of the other half
+      nl -= ne;
     }
     if (done) break;
     if (!pipeline) pop_and_fetch();
@@ -782,15 +783,22 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
 }
 
 // accelerations arrive in sorted order; hand them back to body order, optionally with the kick
-// (src/cuda/integrator.cu:24-36, same rounding sequence as integrate.cu)
+// (src/cuda/integrator.cu:24-36, same rounding sequence as integrate.cu).  One thread per BODY: its arrays (acc,
+// vel, acc_old: nine of them) are read and written coalesced, and the acceleration is ONE random 16-B read through the
+// inverse permutation.  Round 1 ran one thread per sorted slot and scattered through perm: twelve random 4-B accesses
+// per body, ~4.5 ms for 16 Mi bodies on every rank of a sharded step.
+__global__ void __launch_bounds__(256) bh_inverse_perm_kernel(const int32_t* __restrict__ perm, size_t n,
+                                                              int32_t* __restrict__ inv) {
+  const size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < n) inv[perm[k]] = (int32_t)k;
+}
 template <bool KICK>
 __global__ void __launch_bounds__(256) bh_shard_finish_kernel(const float4* __restrict__ acc_sorted,
-                                                              const int32_t* __restrict__ perm, nb_particles d,
+                                                              const int32_t* __restrict__ inv, nb_particles d,
                                                               size_t n, float dt) {
-  const size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (k >= n) return;
-  const int i = perm[k];
-  const float4 a = acc_sorted[k];
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float4 a = __ldg(acc_sorted + inv[i]);
   d.acc_x[i] = a.x;
   d.acc_y[i] = a.y;
   d.acc_z[i] = a.z;
@@ -822,6 +830,7 @@ void bh_destroy(nb_context* ctx) {
   b->keys.release(); b->perm.release(); b->keys_alt.release(); b->perm_alt.release(); b->packed.release();
   b->node_com.release(); b->meta.release(); b->parent.release(); b->slot.release(); b->misc.release();
   b->roots.release();
+  b->inv.release();
   b->supers.release();
   b->glen.release();
   b->gtiles.release();
@@ -1029,6 +1038,21 @@ int bh_shard_wait(nb_context* ctx, const unsigned* flags, int flag_base, unsigne
   return launch_peer_wait(ctx, flags, flag_base, step, nranks, self, timeout_flag, st);
 }
 
+// inverse of the sort permutation of the tree just built (enqueued behind this rank's traversal, i.e. before the
+// wait for the peers' accelerations)
+int bh_shard_inverse(nb_context* ctx, cudaStream_t st) {
+  BH* b = bh_get(ctx);
+  if (!b || !b->built) {
+    set_error("Barnes-Hut: no tree built");
+    return NB_ERR_INVALID;
+  }
+  const size_t n = b->n;
+  if (int rc = b->inv.ensure(n * 4)) return rc;
+  bh_inverse_perm_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(b->perm_sorted, n, b->inv.as<int32_t>());
+  NB_LAUNCH_CHECK(ctx);
+  return NB_OK;
+}
+
 int bh_shard_finish(nb_context* ctx, const float4* acc_sorted, const nb_particles* d, float dt, bool kick,
                     cudaStream_t st) {
   BH* b = bh_get(ctx);
@@ -1043,8 +1067,8 @@ int bh_shard_finish(nb_context* ctx, const float4* acc_sorted, const nb_particle
     return NB_ERR_INVALID;
   }
   const unsigned gn = (unsigned)((n + 255) / 256);
-  if (kick) bh_shard_finish_kernel<true><<<gn, 256, 0, st>>>(acc_sorted, b->perm_sorted, *d, n, dt);
-  else bh_shard_finish_kernel<false><<<gn, 256, 0, st>>>(acc_sorted, b->perm_sorted, *d, n, dt);
+  if (kick) bh_shard_finish_kernel<true><<<gn, 256, 0, st>>>(acc_sorted, b->inv.as<int32_t>(), *d, n, dt);
+  else bh_shard_finish_kernel<false><<<gn, 256, 0, st>>>(acc_sorted, b->inv.as<int32_t>(), *d, n, dt);
   NB_LAUNCH_CHECK(ctx);
   return NB_OK;
 }

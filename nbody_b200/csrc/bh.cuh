@@ -18,6 +18,7 @@ int bh_forces(nb_context* ctx, const nb_particles* d, float theta, float G, floa
               const BhShard* shard);
 int bh_shard_wait(nb_context* ctx, const unsigned* flags, int flag_base, unsigned step, int nranks, int self,
                   int* timeout_flag, cudaStream_t st);
+int bh_shard_inverse(nb_context* ctx, cudaStream_t st);
 int bh_shard_finish(nb_context* ctx, const float4* acc_sorted, const nb_particles* d, float dt, bool kick,
                     cudaStream_t st);
 

@@ -456,7 +456,8 @@ int nb_mgpu_bh_traverse(nb_context* ctx, const nb_particles* d_all, float dt, fl
   sh.flag_index = parity * NB_MAX_PEERS + ctx->bhs_rank;
   sh.step = step;
   sh.done_counter = ps->done_counter;
-  return bh_forces(ctx, d_all, theta, G, eps, st, &sh);
+  if (int rc = bh_forces(ctx, d_all, theta, G, eps, st, &sh)) return rc;
+  return bh_shard_inverse(ctx, st);
 }
 
 // second half: wait for every peer's share, scatter to body order [+ kick all bodies]
