@@ -118,6 +118,8 @@ float orc_lbvh_cell_size(int L, const float bbox[6]) {
 /* Groups of a supergroup, as nbody_b200/csrc/bh.cu tb_emit forms them (mode bit 0; mode 0 = equal runs only, kept for
  * the comparison): follow the tree split whenever that costs no extra warp
  * (ceil(a / group) + ceil(b / group) == ceil(c / group)), else cut equal runs. */
+static int g_hybrid_slack_from = 0; /* experiment knob (orc_set_hybrid_slack): allow ONE extra group when need >= this */
+void orc_set_hybrid_slack(int from) { g_hybrid_slack_from = from; }
 static void hybrid_groups(int ni, int leaf0, int group, const int32_t* left, const int32_t* right,
                           const int32_t* range_first, const int32_t* range_last, int32_t* gfirst, int32_t* gcount,
                           int* ngroups) {
@@ -135,7 +137,8 @@ static void hybrid_groups(int ni, int leaf0, int group, const int32_t* left, con
   const int l = left[ni], r = right[ni];
   const int a = l >= leaf0 ? 1 : range_last[l] - range_first[l] + 1, b = c - a;
   const int need = (c + group - 1) / group;
-  if ((a + group - 1) / group + (b + group - 1) / group == need) {
+  const int slack = (g_hybrid_slack_from > 0 && need >= g_hybrid_slack_from) ? 1 : 0;
+  if ((a + group - 1) / group + (b + group - 1) / group <= need + slack) {
     hybrid_groups(l, leaf0, group, left, right, range_first, range_last, gfirst, gcount, ngroups);
     hybrid_groups(r, leaf0, group, left, right, range_first, range_last, gfirst, gcount, ngroups);
     return;

@@ -120,6 +120,7 @@ float orc_lbvh_cell_size(int prefix_len, const float bbox[6]);
  * box; accepted nodes are evaluated 32 at a time in list order (monopole,
  * src/cuda/force_barnes_hut.cu:175-181).  Outputs in SORTED order. *interactions = node-body
  * force evaluations. */
+void orc_set_hybrid_slack(int from);
 void orc_lbvh_forces_ex(int n, const int32_t* left, const int32_t* right, const int32_t* prefix,
                         const int32_t* range_first, const int32_t* range_last, const float* node_com,
                         const float* sx, const float* sy, const float* sz, const float bbox[6], float theta, float G,
