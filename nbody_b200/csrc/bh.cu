@@ -216,6 +216,7 @@ struct TreeOut {
   int* nroots;
   int4* supers;  // supergroups {node, first leaf, last leaf, -}: cut into traversal groups by bh_groups_kernel
   int* nsupers;
+  int* err;      // host-mapped: a capacity of the build or the traversal was exceeded (reported, never dropped)
 };
 
 // Traversal groups of a supergroup (a maximal subtree of <= smax leaves, node `id` with leaves [cl, cr]).
@@ -476,7 +477,9 @@ __global__ void __launch_bounds__(TB_THREADS, NB_TB_MIN_BLOCKS) bh_tree_kernel(c
   // ---- the subtrees left over (the tile's two spines: their siblings lie in other tiles) go to the top pass -----
   if (tid == 0) {
     int nr = 0;
-    for (int q = 0; q < tcount && nr < TB_MAX_ROOTS; q = s_hi[tb_pad(q)] + 1) s_roots[nr++] = q;
+    int q = 0;
+    for (; q < tcount && nr < TB_MAX_ROOTS; q = s_hi[tb_pad(q)] + 1) s_roots[nr++] = q;
+    if (q < tcount) *o.err = 2;  // more left-over subtrees than two spines of 62 levels can have: cannot happen
     s_nroots = nr;
     s_base = atomicAdd(o.nroots, nr);
   }
@@ -854,6 +857,11 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
     return NB_ERR_INVALID;
   }
   b->n = n;
+  if (!b->h_flag) {
+    NB_CUDA(cudaHostAlloc(&b->h_flag, sizeof(int), cudaHostAllocMapped));
+    *b->h_flag = 0;
+    NB_CUDA(cudaHostGetDevicePointer(&b->d_flag, b->h_flag, 0));
+  }
   if (int rc = b->keys.ensure(n * 4)) return rc;
   if (int rc = b->perm.ensure(n * 4)) return rc;
   if (int rc = b->keys_alt.ensure(n * 4)) return rc;
@@ -929,6 +937,7 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
     o.nroots = reinterpret_cast<int*>(misc) + 47;
     o.glen = b->glen.as<unsigned char>();
     NB_CUDA(cudaMemsetAsync(o.glen, 0, gc_tiles * GC_TILE, st));
+    o.err = b->d_flag;
     o.supers = b->supers.as<int4>();
     o.nsupers = reinterpret_cast<int*>(misc) + 48;
     const unsigned tiles = (unsigned)((n + TB_TILE - 1) / TB_TILE);
@@ -958,8 +967,10 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
 
 static int bh_check_overflow(BH* b) {
   if (b->h_flag && *b->h_flag) {
+    const int what = *b->h_flag;
     *b->h_flag = 0;
-    set_error("Barnes-Hut traversal stack overflow (tree deeper than the %d-entry warp stack allows)", b->stack_cap);
+    if (what == 2) set_error("Barnes-Hut tree build: a tile left more subtrees than its list holds");
+    else set_error("Barnes-Hut traversal stack overflow (tree deeper than the %d-entry warp stack allows; NB_BH_STACK raises it)", b->stack_cap);
     return NB_ERR_INTERNAL;
   }
   return NB_OK;

@@ -21,7 +21,10 @@ def _run(state, cell=1.0, cutoff=2.0, eps=0.01, G=1.0):
 
 
 @pytest.mark.parametrize("n,cell,kind", [(1, 1.0, "box"), (2, 1.0, "box"), (1000, 1.0, "box"), (5000, 2.0, "sphere"),
-                                         (50000, 0.5, "box"), (200000, 1.0, "box"), (30000, 0.37, "plummer")])
+                                         (50000, 0.5, "box"), (200000, 1.0, "box"), (30000, 0.37, "plummer"),
+                                         # few bodies on a fine grid: 9.3 M cells, almost all empty -- long runs of empty
+                                         # cells between occupied ones (the gap list of sh_ranges_gather / sh_fill_gaps)
+                                         (300, 0.095, "box"), (3, 0.1, "box")])
 def test_grid_bit_exact(orc, n, cell, kind):
     from nbody_b200 import ics
     if kind == "sphere":

@@ -70,7 +70,13 @@ def _build(state, theta=0.5, eps=0.01):
 
 
 @pytest.mark.parametrize("n,kind", [(1, "box"), (2, "box"), (3, "box"), (100, "plummer"), (5000, "sphere"),
-                                    (65536, "plummer"), (200000, "dups")])
+                                    (65536, "plummer"), (200000, "dups"),
+                                    # around the tree kernel's 512-leaf tiles and 4-leaf thread blocks
+                                    (4, "box"), (5, "box"), (511, "box"), (512, "box"), (513, "box"), (1023, "plummer"),
+                                    (1025, "plummer"), (4097, "sphere"),
+                                    # every key equal (one point): the tree is decided by the index tie-break alone,
+                                    # across tiles; and two points
+                                    (3000, "coincident"), (2049, "two_points")])
 def test_morton_sort_lbvh_bit_exact(orc, n, kind):
     from nbody_b200 import ics
     if kind == "plummer":
@@ -83,6 +89,15 @@ def test_morton_sort_lbvh_bit_exact(orc, n, kind):
             st[k] *= 1e-3
             st[k][:8] = [50, -50, 50, -50, 50, -50, 50, -50]
             st[k][100:200] = st[k][100]
+    elif kind == "coincident":
+        st = ics.uniform_box(n, -1, 1, seed=5)
+        for k in ("pos_x", "pos_y", "pos_z"):
+            st[k][:] = np.float32(0.25)
+    elif kind == "two_points":
+        st = ics.uniform_box(n, -1, 1, seed=5)
+        for k, (a, b) in zip(("pos_x", "pos_y", "pos_z"), ((-1.0, 2.0), (0.5, 0.5), (3.0, -4.0))):
+            st[k][0::2] = np.float32(a)
+            st[k][1::2] = np.float32(b)
     else:
         st = ics.uniform_box(n, -1, 1, seed=5)
     d, calc = _build(st)
