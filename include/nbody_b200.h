@@ -120,6 +120,19 @@ int nb_particles_download(nb_context* ctx, nb_particles* h, const nb_particles* 
 /* ---- direct N^2: DirectForceCalculator::computeForces -> launchDirectForceKernel
  *      (src/cuda/force_direct.cu:103-106, 88-98, 10-85).  Overwrites acc_x/y/z only. --------- */
 int nb_direct_forces(nb_context* ctx, const nb_particles* d, float G, float eps2, nb_stream s);
+/* nb_direct_forces with NO device allocation at call time.  It has no counterpart in the reference and was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it).  Same kernels, arguments and result as nb_direct_forces; the
+ * scratch (chunk counters, packed sources, per-chunk partial sums) lives in a file-scope static __device__ array
+ * of 17 MiB + 256 B that every GPU loading the library holds until exit.  Limit: d->count <=
+ * NB_DIRECT_STATIC_MAX_BODIES, beyond it NB_ERR_INVALID with a message and nothing launched.  Calls no cudaMalloc,
+ * cudaFree or allocating library routine (the first call per device resolves the array's device address with
+ * cudaGetSymbolAddress and queries kernel occupancy; nothing is allocated).  All calls share the array: calls that
+ * overlap on the GPU race -- keep them on one stream, or order them.  Results: bit-identical to nb_direct_forces
+ * for count <= 16384; above that the partial sums of a target tile are grouped into fewer chunks to fit the array,
+ * so results agree to summation rounding (same pair terms). */
+#define NB_DIRECT_STATIC_MAX_BODIES 65536
+int nb_direct_forces_static(nb_context* ctx, const nb_particles* d, float G, float eps2, nb_stream s);
 
 /* ---- Integrator (src/cuda/integrator.cu) --------------------------------------------------- */
 int nb_store_accelerations(nb_context* ctx, const nb_particles* d, nb_stream s);   /* :248-250, :39-48 */

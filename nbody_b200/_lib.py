@@ -82,6 +82,7 @@ SYMBOLS = {
     "nb_particles_upload": (_i, [_vp, _pp, _pp, _vp]),
     "nb_particles_download": (_i, [_vp, _pp, _pp, _vp]),
     "nb_direct_forces": (_i, [_vp, _pp, _f, _f, _vp]),
+    "nb_direct_forces_static": (_i, [_vp, _pp, _f, _f, _vp]),
     "nb_store_accelerations": (_i, [_vp, _pp, _vp]),
     "nb_update_positions": (_i, [_vp, _pp, _f, _vp]),
     "nb_update_velocities": (_i, [_vp, _pp, _f, _vp]),

@@ -17,7 +17,9 @@
 //     tiles of a chunk and across the chunks of a target tile.
 #include "direct.cuh"
 
+#include <cstdint>
 #include <cstdlib>
+#include <mutex>
 #include <type_traits>
 
 namespace nb {
@@ -561,3 +563,145 @@ int direct_run(nb_context* ctx, const nb_particles* d, float dt, float G, float 
 }
 
 }  // namespace nb
+
+// ---------------------------------------------------------------------------------------------
+// nb_direct_forces_static: direct N^2 forces with NO device allocation at call time.
+//
+// No counterpart in the reference; added for callers that cannot
+// call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The same
+// three kernels as nb_direct_forces -- pack, direct_force_kernel, reduce -- run with their scratch (chunk
+// counters, packed sources, per-chunk partial sums) in ONE file-scope __device__ array instead of the
+// context's growable buffers.  Every GPU that loads the library holds the array until the process exits.
+// All calls share it: calls that overlap on the GPU (two streams, two contexts, two host threads on the same
+// device) race.  The array keeps the previous call's contents; the only part that has to start at zero, the
+// chunk counters, is cleared on the caller's stream at the top of every call.
+// ---------------------------------------------------------------------------------------------
+constexpr size_t kStaticMaxBodies = NB_DIRECT_STATIC_MAX_BODIES;
+constexpr size_t kStaticHeadBytes = 256;                                  // chunk counters {claimed, leavers}
+constexpr size_t kStaticSrcBytes = kStaticMaxBodies * sizeof(float4);     // packed {x, y, z, G m}: 1 MiB
+constexpr size_t kStaticPartialBytes = (size_t)16 << 20;                  // per-chunk partial sums: 16 MiB
+constexpr size_t kStaticBytes = kStaticHeadBytes + kStaticSrcBytes + kStaticPartialBytes;
+static __device__ __align__(256) unsigned char nb_direct_static_scratch[kStaticBytes];
+
+
+namespace nb {
+namespace {
+struct StaticSetup {
+  bool ready = false;
+  unsigned char* base = nullptr;  // DEVICE address of nb_direct_static_scratch on this device
+  int occ[4] = {0, 0, 0, 0};      // resident CTAs per SM: {big, big eps0, small, small eps0}
+};
+constexpr int kMaxDevices = 64;
+StaticSetup g_static_setup[kMaxDevices];
+std::mutex g_static_mutex;
+
+// once per device, with that device current: in host code the array's name is a host-side stand-in, the
+// kernels need the address cudaGetSymbolAddress returns for THIS device
+int static_setup(int device, StaticSetup** out) {
+  if (device < 0 || device >= kMaxDevices) {
+    set_error("nb_direct_forces_static: device ordinal %d out of range", device);
+    return NB_ERR_INVALID;
+  }
+  std::lock_guard<std::mutex> lock(g_static_mutex);
+  StaticSetup& s = g_static_setup[device];
+  if (!s.ready) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, nb_direct_static_scratch);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(nb_direct_static_scratch)", __FILE__, __LINE__);
+    if (!p || (reinterpret_cast<uintptr_t>(p) & 255u)) {
+      set_error("nb_direct_forces_static: static scratch address %p is null or not 256-byte aligned", p);
+      return NB_ERR_INTERNAL;
+    }
+    s.base = static_cast<unsigned char*>(p);
+    s.occ[0] = occupancy<NB_DIRECT_BIG_T, NB_DIRECT_BIG_I, NB_DIRECT_BIG_JT>(false);
+    s.occ[1] = occupancy<NB_DIRECT_BIG_T, NB_DIRECT_BIG_I, NB_DIRECT_BIG_JT>(true);
+    s.occ[2] = occupancy<128, 2, 256>(false);
+    s.occ[3] = occupancy<128, 2, 256>(true);
+    s.ready = true;
+  }
+  *out = &s;
+  return NB_OK;
+}
+}  // namespace
+
+}  // namespace nb
+
+extern "C" int nb_direct_forces_static(nb_context* ctx, const nb_particles* d, float G, float eps2, nb_stream s) {
+  using namespace nb;
+  if (!ctx) {
+    set_error("null context");
+    return NB_ERR_INVALID;
+  }
+  if (!d) {
+    set_error("null particle data");
+    return NB_ERR_INVALID;
+  }
+  const size_t n = d->count;
+  if (n == 0) return NB_OK;
+  if (n > kStaticMaxBodies) {
+    set_error("nb_direct_forces_static: %zu bodies exceed the static scratch's maximum of %zu "
+              "(NB_DIRECT_STATIC_MAX_BODIES); use nb_direct_forces, which allocates",
+              n, kStaticMaxBodies);
+    return NB_ERR_INVALID;
+  }
+  if (!d->pos_x || !d->pos_y || !d->pos_z || !d->mass || !d->acc_x || !d->acc_y || !d->acc_z) {
+    set_error("particle data has null position/mass/acceleration arrays");
+    return NB_ERR_INVALID;
+  }
+  NB_CUDA(cudaSetDevice(ctx->device));
+  StaticSetup* su = nullptr;
+  if (int rc = static_setup(ctx->device, &su)) return rc;
+  cudaStream_t st = (cudaStream_t)s;
+
+  unsigned* work = reinterpret_cast<unsigned*>(su->base);
+  float4* src = reinterpret_cast<float4*>(su->base + kStaticHeadBytes);
+  float* part = reinterpret_cast<float*>(su->base + kStaticHeadBytes + kStaticSrcBytes);
+
+  // same configuration, padding and chunk plan as direct_run / launch_direct_pass ...
+  const DirectCfg& cfg = direct_cfg(n);
+  const bool big = (&cfg == &kCfgBig);
+  const bool eps0 = !(eps2 >= NB_EPS2_GUARD);
+  const size_t n_pad = padded_count(n, cfg);  // <= kStaticMaxBodies: the maximum is a multiple of every tile size
+  const int n_itiles = (int)((n + cfg.IT() - 1) / cfg.IT());
+  const int UJ = (int)((n + cfg.JT - 1) / cfg.JT);
+  const long long ctas = (long long)su->occ[(big ? 0 : 2) + (eps0 ? 1 : 0)] * ctx->sm_count;
+  int C = chunks_per_tile(n_itiles, UJ, ctas);
+  // ... except that the partial slots have to fit the fixed array: fewer, longer chunks per target tile when they
+  // would not (n > 16384).  Chunk sums are then added in a different grouping than nb_direct_forces' -- the same
+  // pair terms, equal to rounding; at n <= 16384 the plan, and so every bit of the result, is the same.
+  const size_t slot_bytes = (size_t)3 * cfg.IT() * sizeof(float);
+  const long long c_fit = (long long)(kStaticPartialBytes / slot_bytes) / n_itiles;
+  if (C > c_fit) C = (int)c_fit;
+  if (C < 1 || n_pad * sizeof(float4) > kStaticSrcBytes) {
+    set_error("nb_direct_forces_static: internal sizing error (n=%zu, n_pad=%zu, C=%d)", n, n_pad, C);
+    return NB_ERR_INTERNAL;
+  }
+  const long long chunks = (long long)n_itiles * C;
+  const int grid = (int)(ctas < chunks ? ctas : chunks);
+
+  // the chunk counters must start at zero (a launch re-arms them on its way out, but an earlier call that failed
+  // part-way would leave them set); a memset node on the caller's stream, no allocation
+  NB_CUDA(cudaMemsetAsync(work, 0, kStaticHeadBytes, st));
+  if (int rc = launch_pack(ctx, d, src, n, n_pad, G, 0.f, false, st)) return rc;
+#define NB_LAUNCH_DIRECT_STATIC(T_, I_, JT_, E_)                                                                \
+  direct_force_kernel<T_, I_, JT_, E_><<<grid, T_, 0, st>>>(src, src, part, work, (int)chunks, C, UJ, 0, UJ, 0, eps2, 0ull)
+  if (big) {
+    if (eps0) NB_LAUNCH_DIRECT_STATIC(NB_DIRECT_BIG_T, NB_DIRECT_BIG_I, NB_DIRECT_BIG_JT, true);
+    else NB_LAUNCH_DIRECT_STATIC(NB_DIRECT_BIG_T, NB_DIRECT_BIG_I, NB_DIRECT_BIG_JT, false);
+  } else {
+    if (eps0) NB_LAUNCH_DIRECT_STATIC(128, 2, 256, true);
+    else NB_LAUNCH_DIRECT_STATIC(128, 2, 256, false);
+  }
+#undef NB_LAUNCH_DIRECT_STATIC
+  NB_LAUNCH_CHECK(ctx);
+  ReduceArgs ra;
+  ra.npass = 1;
+  ra.pass[0] = nb_pass{};
+  ra.pass[0].C = C;
+  ra.pass[0].slot_base = 0;
+  const unsigned rgrid = (unsigned)((n + 255) / 256);
+  if (big) reduce_kernel<NB_DIRECT_BIG_I * NB_DIRECT_BIG_T, false><<<rgrid, 256, 0, st>>>(part, ra, *d, n, 0.f);
+  else reduce_kernel<256, false><<<rgrid, 256, 0, st>>>(part, ra, *d, n, 0.f);
+  NB_LAUNCH_CHECK(ctx);
+  return NB_OK;
+}
