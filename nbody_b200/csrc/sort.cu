@@ -131,6 +131,14 @@ constexpr int RS_MAX_BINS = 1 << RS_MAX_BITS;
 #define NB_RS_LOOK 1  // build-time knob: 1 -> 0.463 ms, 2 -> 0.470, 4 -> 0.485 for the 16 Mi Morton sort (profiles/r02_bh_tree_tile_shapes_ab_v2.jsonl)
 #endif
 constexpr int RS_LOOK = NB_RS_LOOK;  // predecessors examined per look-back round trip
+#ifndef NB_RS_MIN_BLOCKS
+#define NB_RS_MIN_BLOCKS 2  // build-time knob: resident CTAs per SM the pass kernel is compiled for (3 = 40 registers with spills: 0.507 ms against 0.488)
+#endif
+#ifndef NB_RS_BATCH
+#define NB_RS_BATCH 16  // build-time knob: keys a thread holds in registers at a time while ranking / staging (8: 0.488 ms, 16: 0.483 for 16 Mi x 30 bits in place)
+#endif
+constexpr int RS_BATCH = NB_RS_BATCH;
+static_assert(RS_ITEMS % RS_BATCH == 0, "the batch must divide the keys per thread");
 
 struct RsPlan {
   int passes;
@@ -238,7 +246,7 @@ __device__ __forceinline__ void st_status2(uint32_t* p, uint32_t lo, uint32_t hi
 // ballots of the unused high bits see zeros and change nothing).  gexcl: global exclusive digit offsets; status: tiles x 2^bits words,
 // zeroed; ticket: zeroed.  IDENT: the values are the identity permutation (value = index) and not read.
 template <int RB, bool IDENT>
-__global__ void __launch_bounds__(RS_THREADS, 2) rs_pass_kernel(const uint32_t* __restrict__ keys_in,
+__global__ void __launch_bounds__(RS_THREADS, NB_RS_MIN_BLOCKS) rs_pass_kernel(const uint32_t* __restrict__ keys_in,
                                                                  const int32_t* __restrict__ vals_in,
                                                                  uint32_t* __restrict__ keys_out,
                                                                  int32_t* __restrict__ vals_out, size_t n, int shift,
@@ -273,53 +281,58 @@ __global__ void __launch_bounds__(RS_THREADS, 2) rs_pass_kernel(const uint32_t* 
 
   // ---- load + rank inside the warp's 512 consecutive keys -----------------------------------------
   const uint32_t wofs = (uint32_t)w * RS_WARP_KEYS + lane;  // offset of this lane's first key inside the tile
-  uint32_t key[RS_ITEMS];
-  uint32_t pos[RS_ITEMS];  // rank among the warp's keys of the same digit; later the key's slot in the tile
+  // Registers: a thread never holds its 16 keys at once.  It ranks them RS_BATCH at a time and keeps, per key, only
+  // pd = (digit << 16) | rank (rank < 512, later the slot < 8192: the low half never carries into the digit); the
+  // keys are read again (from L2: this CTA loaded them microseconds ago) when they move to the staging buffer.
+  // 16 live registers across the look-back instead of 32.
+  uint32_t pd[RS_ITEMS];
   const uint32_t lt = (1u << lane) - 1u;
   uint32_t* mycnt = cntw + w * CW;
   const bool full = (uint32_t)w * RS_WARP_KEYS + RS_WARP_KEYS <= tcount;  // warp-uniform
-  {
-    const uint32_t* kin = keys_in + tbase + wofs;
-    if (full) {
-#pragma unroll
-      for (int k = 0; k < RS_ITEMS; k++) key[k] = kin[k * 32];
-    } else {
-#pragma unroll
-      for (int k = 0; k < RS_ITEMS; k++) key[k] = (wofs + k * 32 < tcount) ? kin[k * 32] : 0xffffffffu;
-    }
-  }
+  const uint32_t* kin = keys_in + tbase + wofs;
   // ranking runs at the top level of the kernel (no enclosing branch: the ballots need no divergence checks);
   // a partial last tile is handled by one extra ballot per key (padding lanes are nobody's peer)
 #pragma unroll
-  for (int k = 0; k < RS_ITEMS; k++) {
-    const bool ok = wofs + k * 32 < tcount;
-    const uint32_t dgt = (key[k] >> shift) & mask;
-    uint32_t peers = __ballot_sync(0xffffffffu, ok);
+  for (int h = 0; h < RS_ITEMS; h += RS_BATCH) {
+    uint32_t key[RS_BATCH];
+    if (full) {
 #pragma unroll
-    for (int b = 0; b < RB; b++) {
-      // v = lanes whose bit b is set, x = 0 if mine is set else ~0: peers &= ~(v ^ x) ... written as v ^ ~x below.
-      // PTX on purpose: the compiler's own sequence tests the bit twice and shifts first (6 instructions per bit).
-      uint32_t v, x;
-      asm volatile(
-          "{\n"
-          ".reg .pred p;\n"
-          ".reg .b32 t;\n"
-          "and.b32 t, %2, %3;\n"
-          "setp.ne.u32 p, t, 0;\n"
-          "vote.sync.ballot.b32 %0, p, 0xffffffff;\n"
-          "selp.b32 %1, 0, 0xffffffff, p;\n"
-          "}"
-          : "=r"(v), "=r"(x)
-          : "r"(dgt), "r"(1u << b));
-      peers &= v ^ x;
+      for (int k = 0; k < RS_BATCH; k++) key[k] = kin[(h + k) * 32];
+    } else {
+#pragma unroll
+      for (int k = 0; k < RS_BATCH; k++) key[k] = (wofs + (h + k) * 32 < tcount) ? kin[(h + k) * 32] : 0xffffffffu;
     }
-    const int leader = max(__ffs(peers) - 1, 0);
-    const uint32_t sh16 = (dgt & 1u) * 16u;
-    uint32_t old = 0;
-    // a warp's shared-memory atomics retire in issue order: key k sees the counts of keys < k
-    if (ok && lane == leader) old = atomicAdd(&mycnt[dgt >> 1], (uint32_t)__popc(peers) << sh16);
-    old = __shfl_sync(0xffffffffu, old, leader);
-    pos[k] = ((old >> sh16) & 0xffffu) + __popc(peers & lt);
+#pragma unroll
+    for (int k = 0; k < RS_BATCH; k++) {
+      const bool ok = wofs + (h + k) * 32 < tcount;
+      const uint32_t dgt = (key[k] >> shift) & mask;
+      uint32_t peers = __ballot_sync(0xffffffffu, ok);
+#pragma unroll
+      for (int b = 0; b < RB; b++) {
+        // v = lanes whose bit b is set, x = 0 if mine is set else ~0: peers &= ~(v ^ x) ... written as v ^ ~x below.
+        // PTX on purpose: the compiler's own sequence tests the bit twice and shifts first (6 instructions per bit).
+        uint32_t v, x;
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            ".reg .b32 t;\n"
+            "and.b32 t, %2, %3;\n"
+            "setp.ne.u32 p, t, 0;\n"
+            "vote.sync.ballot.b32 %0, p, 0xffffffff;\n"
+            "selp.b32 %1, 0, 0xffffffff, p;\n"
+            "}"
+            : "=r"(v), "=r"(x)
+            : "r"(dgt), "r"(1u << b));
+        peers &= v ^ x;
+      }
+      const int leader = max(__ffs(peers) - 1, 0);
+      const uint32_t sh16 = (dgt & 1u) * 16u;
+      uint32_t old = 0;
+      // a warp's shared-memory atomics retire in issue order: key k sees the counts of keys < k
+      if (ok && lane == leader) old = atomicAdd(&mycnt[dgt >> 1], (uint32_t)__popc(peers) << sh16);
+      old = __shfl_sync(0xffffffffu, old, leader);
+      pd[h + k] = (dgt << 16) | (((old >> sh16) & 0xffffu) + __popc(peers & lt));
+    }
   }
   __syncthreads();
 
@@ -418,31 +431,31 @@ __global__ void __launch_bounds__(RS_THREADS, 2) rs_pass_kernel(const uint32_t* 
   // every key's slot in the digit-ordered staging buffer (the last use of the per-warp counters)
 #pragma unroll
   for (int k = 0; k < RS_ITEMS; k++) {
-    const uint32_t dgt = (key[k] >> shift) & mask;
-    pos[k] += ((mycnt[dgt >> 1] >> ((dgt & 1u) * 16u)) & 0xffffu);
+    const uint32_t dgt = pd[k] >> 16;
+    pd[k] += ((mycnt[dgt >> 1] >> ((dgt & 1u) * 16u)) & 0xffffu);
   }
   __syncthreads();  // lstart complete, counters dead: the staging buffer may overwrite them
 #pragma unroll
-  for (int k = 0; k < RS_ITEMS; k++) pos[k] += lstart[(key[k] >> shift) & mask];
-  // ---- registers -> staging buffer (digit order) -> global (runs of consecutive addresses) -----------
-  if (IDENT) {
+  for (int k = 0; k < RS_ITEMS; k++) pd[k] = lstart[pd[k] >> 16] + (pd[k] & 0xffffu);
+  // ---- global (again) -> staging buffer (digit order) -> global (runs of consecutive addresses) ------
+  {
+    const int32_t* vin = IDENT ? nullptr : vals_in + tbase + wofs;
 #pragma unroll
-    for (int k = 0; k < RS_ITEMS; k++) {
-      if (full || wofs + k * 32 < tcount) {
-        buf_k[pos[k]] = key[k];
-        buf_v[pos[k]] = (uint32_t)(tbase + wofs + k * 32);
+    for (int h = 0; h < RS_ITEMS; h += RS_BATCH) {
+      uint32_t key[RS_BATCH], val[RS_BATCH];
+#pragma unroll
+      for (int k = 0; k < RS_BATCH; k++) {
+        const bool ok = full || wofs + (h + k) * 32 < tcount;
+        key[k] = ok ? kin[(h + k) * 32] : 0u;
+        if (IDENT) val[k] = (uint32_t)(tbase + wofs + (h + k) * 32);
+        else val[k] = ok ? (uint32_t)vin[(h + k) * 32] : 0u;
       }
-    }
-  } else {
-    const int32_t* vin = vals_in + tbase + wofs;
-    uint32_t val[RS_ITEMS];
 #pragma unroll
-    for (int k = 0; k < RS_ITEMS; k++) val[k] = (full || wofs + k * 32 < tcount) ? (uint32_t)vin[k * 32] : 0u;
-#pragma unroll
-    for (int k = 0; k < RS_ITEMS; k++) {
-      if (full || wofs + k * 32 < tcount) {
-        buf_k[pos[k]] = key[k];
-        buf_v[pos[k]] = val[k];
+      for (int k = 0; k < RS_BATCH; k++) {
+        if (full || wofs + (h + k) * 32 < tcount) {
+          buf_k[pd[h + k]] = key[k];
+          buf_v[pd[h + k]] = val[k];
+        }
       }
     }
   }
