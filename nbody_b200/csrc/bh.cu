@@ -46,6 +46,8 @@ struct BH {
   nb::DevBuf parent;  // filled on export only
   nb::DevBuf inv;     // inverse sort permutation (sharded finish only)
   nb::DevBuf groups;  // int2 {first,count} per traversal group
+  nb::DevBuf pairs;   // 3 x 16 B per internal node: both children's {centre of mass, mass}, {ids, size^2}; + 1 for the root
+  int walk_pairs = 1; // NB_BH_WALK=nodes: round-1/2 walk, one node per stack entry (A/B)
   uint32_t* keys_sorted = nullptr;  // where the last build's sorted keys / permutation live
   int32_t* perm_sorted = nullptr;
   float h_bbox[6] = {0, 0, 0, 0, 0, 0};
@@ -541,6 +543,38 @@ __global__ void __launch_bounds__(256) bh_parent_kernel(int n, const int4* __res
   parent[m.y] = i;
 }
 
+// ---- child-pair records for the traversal ---------------------------------------------------------------
+// The walk (bh_force_pairs_kernel) keeps only nodes that have to be OPENED on its stack and tests both children of an
+// opened node in one go; for that it wants both children's centres of mass, ids and cell sizes in one 48-byte record
+// per internal node, instead of one 32-byte fetch per child after a trip through the stack:
+//   rec[3 i + 0] = centre of mass + mass of the left child, rec[3 i + 1] = of the right child,
+//   rec[3 i + 2] = {left id, right id, size^2 of the left child's cell, of the right child's} (a leaf's is 0).
+// Record n - 1 (one past the internal nodes) is a virtual parent of the root -- {root, a massless dummy} -- where
+// every walk starts, so the root needs no special case (n == 1: the root is the only leaf).
+__global__ void __launch_bounds__(256) bh_pairs_kernel(int n, const float4* __restrict__ node_com,
+                                                       const int4* __restrict__ meta, const float* __restrict__ misc,
+                                                       float4* __restrict__ rec) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int leaf0 = n - 1;
+  if (i > leaf0) return;
+  float4 a, b = make_float4(0.f, 0.f, 0.f, 0.f);
+  int4 m;
+  if (i == leaf0) {  // virtual parent of the root
+    a = __ldg(node_com);
+    m = make_int4(0, 0, __float_as_int(n > 1 ? misc[__ldg(&meta[0].z)] : 0.f), 0);
+  } else {
+    const int4 me = __ldg(meta + i);
+    a = __ldg(node_com + me.x);
+    b = __ldg(node_com + me.y);
+    const float sa = me.x >= leaf0 ? 0.f : misc[__ldg(&meta[me.x].z)];
+    const float sb = me.y >= leaf0 ? 0.f : misc[__ldg(&meta[me.y].z)];
+    m = make_int4(me.x, me.y, __float_as_int(sa), __float_as_int(sb));
+  }
+  rec[3 * (size_t)i] = a;
+  rec[3 * (size_t)i + 1] = b;
+  rec[3 * (size_t)i + 2] = make_float4(__int_as_float(m.x), __int_as_float(m.y), __int_as_float(m.z), __int_as_float(m.w));
+}
+
 // ---- traversal ---------------------------------------------------------------------------------------
 // One warp owns 32*BPL Morton-consecutive bodies and a stack of node indices in shared memory.
 // Each round the warp pops up to 32 nodes, ONE PER LANE: every lane fetches its node and tests it
@@ -556,6 +590,9 @@ __global__ void __launch_bounds__(256) bh_parent_kernel(int n, const int4* __res
 #endif
 #define NB_BH_PRAGMA_(x) _Pragma(#x)
 #define NB_BH_PRAGMA_UNROLL(n) NB_BH_PRAGMA_(unroll n)
+#ifndef NB_BH_MIN_BLOCKS
+#define NB_BH_MIN_BLOCKS 6  // build-time knob: resident CTAs per SM the pair-record traversal is compiled for (register cap)
+#endif
 constexpr int BH_WARPS = 4;
 constexpr int BH_LIST = 64;
 constexpr int BH_STAGE = 32 * 32;  // bytes per warp: one {centre of mass, node record} per lane
@@ -785,6 +822,224 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
   }
 }
 
+// ---- traversal over child-pair records (the default) ----------------------------------------------------------
+// Same groups, same acceptance test per node, hence the same interaction SET as bh_force_kernel; what changes is the
+// bookkeeping.  bh_force_kernel pushes every child of an opened node and pops it again just to test it: two pops, two
+// 32-byte fetches and two trips through the ballot/compaction code per accepted entry.  The kernel is bound by
+// instruction issue (FFMA2 holds the issue port for both its cycles and every integer instruction of the walk adds to
+// it: profiles/r02_issue_slots_ubench.jsonl), so the walk's instructions are paid in full.  Here the stack holds only
+// nodes that must be OPENED; a lane pops one, fetches its 48-byte pair record (bh_pairs_kernel) and tests BOTH
+// children: accepted ones go to the interaction list, rejected internal ones onto the stack.  Half the pops and
+// rounds, four ballots per round instead of two per child.  The list is a ring of four 32-entry batches (a round adds
+// up to 64 entries to fewer than 32 left over).  List order: lane order, a lane's left child before its right one;
+// oracle/lbvh.c restates it step for step.
+constexpr int BH_PLIST = 128;
+constexpr int BH_PSTAGE = 32 * 48;  // bytes per warp: one pair record per lane
+
+template <int BPL, bool EPS0, bool SHARDED>
+__global__ void __launch_bounds__(BH_WARPS * 32, NB_BH_MIN_BLOCKS)
+    bh_force_pairs_kernel(int n, const float4* __restrict__ node_com, const float4* __restrict__ rec,
+                          const int32_t* __restrict__ perm, float theta2, float G, float eps2, float* __restrict__ ax,
+                          float* __restrict__ ay, float* __restrict__ az, unsigned long long* __restrict__ counter,
+                          int* __restrict__ overflow, const int2* __restrict__ groups, const int* __restrict__ ngroups,
+                          int* __restrict__ cursor, int stack_cap, int* __restrict__ max_stack, BhShard sh) {
+  extern __shared__ __align__(16) unsigned char bh_smem[];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const size_t smem_per_warp = (size_t)stack_cap * 4 + BH_PLIST * 16 + BH_PSTAGE;
+  float4* list = reinterpret_cast<float4*>(bh_smem + (size_t)w * smem_per_warp);
+  float4* stage_a = list + BH_PLIST;  // next round's records, one per lane (cp.async): left child, right child, ids
+  float4* stage_b = stage_a + 32;
+  float4* stage_m = stage_b + 32;
+  int* stack = reinterpret_cast<int*>(stage_m + 32);
+  int deepest = 0;
+  const int leaf0 = n - 1;
+  const unsigned lt = (1u << lane) - 1u;
+  const int total_groups = *ngroups;
+  unsigned long long visits_bodies = 0;
+
+  for (;;) {  // persistent warp: pull traversal groups from a work queue until it is empty
+  int g = 0;
+  if (lane == 0) g = atomicAdd(cursor, 1);
+  g = __shfl_sync(0xffffffffu, g, 0);
+  if (g >= total_groups) break;
+  const int2 grp = groups[g];
+  const int k0 = grp.x, gcnt = grp.y;
+  if (SHARDED && (((unsigned)k0 * 2654435761u) >> 20) % (unsigned)sh.nranks != (unsigned)sh.rank) continue;  // dealt to another rank
+
+  struct { float x, y, z; } me[BPL];  // scalar loads on purpose, see bh_force_kernel
+  float sx[BPL], sy[BPL], sz[BPL];
+  float lo[3] = {3.0e38f, 3.0e38f, 3.0e38f}, hi[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
+#pragma unroll
+  for (int b = 0; b < BPL; b++) {
+    me[b].x = me[b].y = me[b].z = 0.f;
+    if (b * 32 + lane < gcnt) {
+      const float* q = reinterpret_cast<const float*>(node_com + leaf0 + k0 + b * 32 + lane);
+      me[b].x = __ldg(q); me[b].y = __ldg(q + 1); me[b].z = __ldg(q + 2);
+      lo[0] = fminf(lo[0], me[b].x); hi[0] = fmaxf(hi[0], me[b].x);
+      lo[1] = fminf(lo[1], me[b].y); hi[1] = fmaxf(hi[1], me[b].y);
+      lo[2] = fminf(lo[2], me[b].z); hi[2] = fmaxf(hi[2], me[b].z);
+    }
+    sx[b] = sy[b] = sz[b] = 0.f;
+  }
+#pragma unroll
+  for (int a = 0; a < 3; a++) {
+    lo[a] = warp_min(lo[a]);
+    hi[a] = warp_max(hi[a]);
+  }
+  const f2 e2 = pk(eps2, eps2);
+  const f2 xi2 = pk(me[0].x, me[BPL - 1].x), yi2 = pk(me[0].y, me[BPL - 1].y), zi2 = pk(me[0].z, me[BPL - 1].z);
+  f2 sx2 = pk(0.f, 0.f), sy2 = sx2, sz2 = sx2;
+
+  int sp = 1, nl = 0, lbase = 0;
+  unsigned visits = 0;
+  if (lane == 0) stack[0] = leaf0;  // the virtual parent of the root
+  __syncwarp();
+  int popped = 0;
+  auto pop_and_fetch = [&]() {
+    const int m = min(sp, 32);
+    popped = m;
+    const int ni = (lane < m) ? stack[sp - m + lane] : leaf0;  // lanes without a node fetch the virtual record (ignored)
+    sp -= m;
+    __syncwarp();
+    const float4* r = rec + 3 * (size_t)ni;
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(smem_u32(stage_a + lane)), "l"(r) : "memory");
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(smem_u32(stage_b + lane)), "l"(r + 1) : "memory");
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(smem_u32(stage_m + lane)), "l"(r + 2) : "memory");
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  // distance^2 from a centre of mass to the group's box, softened: the denominator of the acceptance test
+  auto box_d2 = [&](const float4& c) {
+    const float ddx = fmaxf(fmaxf(lo[0] - c.x, c.x - hi[0]), 0.f);
+    const float ddy = fmaxf(fmaxf(lo[1] - c.y, c.y - hi[1]), 0.f);
+    const float ddz = fmaxf(fmaxf(lo[2] - c.z, c.z - hi[2]), 0.f);
+    return fmaf(ddz, ddz, fmaf(ddy, ddy, fmaf(ddx, ddx, eps2)));
+  };
+  pop_and_fetch();
+  for (;;) {
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    const float4 ca = stage_a[lane], cb = stage_b[lane];
+    const float4 mf = stage_m[lane];
+    const int ia = __float_as_int(mf.x), ib = __float_as_int(mf.y);
+    const bool have = lane < popped;
+    // a child is used for the whole group iff it is a leaf or size^2 < theta^2 * d^2 (:167); total mass 0 -> skipped
+    // (:157-158).  Both tests run unconditionally: no branches around them.
+    const bool va = have && ca.w != 0.f, vb = have && cb.w != 0.f;
+    const bool ta = (ia >= leaf0) | (mf.z < theta2 * box_d2(ca));
+    const bool tb = (ib >= leaf0) | (mf.w < theta2 * box_d2(cb));
+    const bool acc_a = va && ta, acc_b = vb && tb, rej_a = va && !ta, rej_b = vb && !tb;
+    const unsigned ma = __ballot_sync(0xffffffffu, acc_a), mb = __ballot_sync(0xffffffffu, acc_b);
+    const unsigned ra = __ballot_sync(0xffffffffu, rej_a), rb = __ballot_sync(0xffffffffu, rej_b);
+    const int lpos = lbase + nl + __popc(ma & lt) + __popc(mb & lt);
+    if (acc_a) list[lpos & (BH_PLIST - 1)] = make_float4(ca.x, ca.y, ca.z, G * ca.w);  // G*M once per node
+    if (acc_b) list[(lpos + (acc_a ? 1 : 0)) & (BH_PLIST - 1)] = make_float4(cb.x, cb.y, cb.z, G * cb.w);
+    const int npush = __popc(ra) + __popc(rb);
+    deepest = max(deepest, sp + npush);
+    if (sp + npush > stack_cap) {  // never silently drop subtrees (the reference does, :186-194)
+      if (lane == 0) *overflow = 1;
+      break;
+    }
+    const int spos = sp + __popc(ra & lt) + __popc(rb & lt);
+    if (rej_a) stack[spos] = ia;
+    if (rej_b) stack[spos + (rej_a ? 1 : 0)] = ib;
+    nl += __popc(ma) + __popc(mb);
+    sp += npush;
+    __syncwarp();
+    const bool done = (sp == 0);
+    if (!done) pop_and_fetch();  // in flight while the list is evaluated
+    while (nl >= 32 || (done && nl > 0)) {
+      const int ne = min(nl, 32);
+      const float4* lcur = list + lbase;
+      auto body = [&](int e) {
+        const float4 p = lcur[e];  // warp-broadcast LDS.128; p.w = G * M
+        const float gm = p.w;
+        if constexpr (BPL == 2) {
+          // the lane's two bodies as one packed fp32x2 pair (FADD2/FFMA2/FMUL2, as in direct.cu)
+          const f2 dx = sub2(pk(p.x, p.x), xi2), dy = sub2(pk(p.y, p.y), yi2), dz = sub2(pk(p.z, p.z), zi2);
+          const f2 d2 = fma2(dz, dz, fma2(dy, dy, fma2(dx, dx, e2)));
+          float r0, r1;
+          upk(d2, r0, r1);
+          float i0 = rsq(r0), i1 = rsq(r1);
+          if (EPS0) {  // own leaf / exact coincidence at eps ~ 0
+            i0 = (r0 > eps2) ? i0 : 0.f;
+            i1 = (r1 > eps2) ? i1 : 0.f;
+          }
+          const f2 ri = pk(i0, i1);
+          const f2 f = mul2(pk(gm, gm), mul2(mul2(ri, ri), ri));
+          sx2 = fma2(f, dx, sx2);
+          sy2 = fma2(f, dy, sy2);
+          sz2 = fma2(f, dz, sz2);
+        } else {
+#pragma unroll
+          for (int b = 0; b < BPL; b++) {
+            const float dx = p.x - me[b].x, dy = p.y - me[b].y, dz = p.z - me[b].z;
+            const float d2 = fmaf(dz, dz, fmaf(dy, dy, fmaf(dx, dx, eps2)));
+            float inv = rsq(d2);
+            if (EPS0) inv = (d2 > eps2) ? inv : 0.f;  // own leaf / exact coincidence at eps ~ 0
+            const float f = gm * (inv * inv * inv);
+            sx[b] = fmaf(f, dx, sx[b]);
+            sy[b] = fmaf(f, dy, sy[b]);
+            sz[b] = fmaf(f, dz, sz[b]);
+          }
+        }
+      };
+      if (ne == 32) {
+        NB_BH_PRAGMA_UNROLL(NB_BH_UNROLL)
+        for (int e = 0; e < 32; e++) body(e);
+      } else {
+        for (int e = 0; e < ne; e++) body(e);
+      }
+      visits += ne;
+      __syncwarp();  // every lane has read the batch before later entries wrap into it
+      if (ne == 32) lbase = (lbase + 32) & (BH_PLIST - 1);
+      nl -= ne;
+    }
+    if (done) break;
+  }
+  if constexpr (BPL == 2) {
+    upk(sx2, sx[0], sx[1]);
+    upk(sy2, sy[0], sy[1]);
+    upk(sz2, sz[0], sz[1]);
+  }
+#pragma unroll
+  for (int b = 0; b < BPL; b++) {
+    if (b * 32 + lane < gcnt) {
+      if (SHARDED) {
+        const float4 v = make_float4(sx[b], sy[b], sz[b], 0.f);
+#pragma unroll
+        for (int r = 0; r < 8; r++)
+          if (r < sh.nranks) sh.out[r][k0 + b * 32 + lane] = v;
+      } else {
+        const int i = perm[k0 + b * 32 + lane];
+        ax[i] = sx[b];
+        ay[i] = sy[b];
+        az[i] = sz[b];
+      }
+    }
+  }
+  visits_bodies += (unsigned long long)visits * (unsigned long long)gcnt;
+  __syncwarp();
+  }  // next group
+  if (lane == 0 && visits_bodies) {
+    atomicAdd(counter, visits_bodies);
+    atomicMax(max_stack, deepest);
+  }
+  if (SHARDED) {
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const unsigned prev = atomicAdd(sh.done_counter, 1u);
+      if (prev == gridDim.x - 1) {  // every CTA's peer stores are fenced: publish
+        *sh.done_counter = 0;
+        __threadfence_system();
+        for (int r = 0; r < sh.nranks; r++)
+          if (r != sh.rank)
+            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(sh.flags[r] + sh.flag_index), "r"(sh.step)
+                         : "memory");
+      }
+    }
+  }
+}
+
 // accelerations arrive in sorted order; hand them back to body order, optionally with the kick
 // (src/cuda/integrator.cu:24-36, same rounding sequence as integrate.cu).  One thread per BODY: its arrays (acc,
 // vel, acc_old: nine of them) are read and written coalesced, and the acceleration is ONE random 16-B read through the
@@ -838,6 +1093,7 @@ void bh_destroy(nb_context* ctx) {
   b->glen.release();
   b->gtiles.release();
   b->groups.release();
+  b->pairs.release();
   if (b->h_flag) cudaFreeHost(b->h_flag);
   delete b;
   ctx->bh = nullptr;
@@ -890,6 +1146,11 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
       if (c != b->stack_cap) b->occ = 0;
       b->stack_cap = c;
     }
+    if (const char* we = getenv("NB_BH_WALK")) {
+      const int wp = strcmp(we, "nodes") != 0;
+      if (wp != b->walk_pairs) b->occ = 0;
+      b->walk_pairs = wp;
+    }
     if (const char* he = getenv("NB_BH_HYBRID")) b->hybrid = atoi(he) != 0;
     if (const char* pe = getenv("NB_BH_PIPELINE")) b->pipeline = atoi(pe) != 0;
     const char* se = getenv("NB_BH_SUPER");
@@ -897,6 +1158,8 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
     if (sg < g) sg = g;
     b->super = sg;
   }
+  if (b->walk_pairs)
+    if (int rc = b->pairs.ensure(n * 3 * sizeof(float4))) return rc;
   if (int rc = b->supers.ensure((4 * n / ((size_t)b->super + 1) + 16) * sizeof(int4))) return rc;
   const size_t gc_tiles = (n + GC_TILE - 1) / GC_TILE;
   if (int rc = b->glen.ensure(gc_tiles * GC_TILE)) return rc;
@@ -961,6 +1224,12 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
     bh_group_fill_kernel<<<(unsigned)gc_tiles, 256, 0, st>>>(o.glen, gt, gtotal, o.groups, o.ngroups);
     NB_LAUNCH_CHECK(ctx);
   }
+  if (b->walk_pairs) {
+    NB_STAGE(ctx, st, "bh.pairs");
+    bh_pairs_kernel<<<gn, 256, 0, st>>>((int)n, b->node_com.as<float4>(), b->meta.as<int4>(), misc,
+                                        b->pairs.as<float4>());
+    NB_LAUNCH_CHECK(ctx);
+  }
   b->built = true;
   return NB_OK;
 }
@@ -1001,12 +1270,18 @@ int bh_forces(nb_context* ctx, const nb_particles* d, float theta, float G, floa
   float* misc = b->misc.as<float>();
   int* cursor = reinterpret_cast<int*>(misc) + 45;
   NB_CUDA(cudaMemsetAsync(cursor, 0, sizeof(int), st));
-  const size_t smem = (size_t)BH_WARPS * ((size_t)b->stack_cap * 4 + BH_LIST * 16 + BH_STAGE);
+  const size_t smem = b->walk_pairs
+                          ? (size_t)BH_WARPS * ((size_t)b->stack_cap * 4 + BH_PLIST * 16 + BH_PSTAGE)
+                          : (size_t)BH_WARPS * ((size_t)b->stack_cap * 4 + BH_LIST * 16 + BH_STAGE);
   const float eps2 = eps * eps;
   const bool eps0 = !(eps2 >= NB_EPS2_GUARD);
   if (!b->occ) {
     int o = 0;
-    if (b->group == 64)
+    if (b->walk_pairs && b->group == 64)
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, bh_force_pairs_kernel<2, false, false>, BH_WARPS * 32, smem);
+    else if (b->walk_pairs)
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, bh_force_pairs_kernel<1, false, false>, BH_WARPS * 32, smem);
+    else if (b->group == 64)
       cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, bh_force_kernel<2, false, false>, BH_WARPS * 32, smem);
     else
       cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, bh_force_kernel<1, false, false>, BH_WARPS * 32, smem);
@@ -1026,10 +1301,18 @@ int bh_forces(nb_context* ctx, const nb_particles* d, float theta, float G, floa
       d->acc_x, d->acc_y, d->acc_z, reinterpret_cast<unsigned long long*>(misc + 40), b->d_flag,                   \
       b->groups.as<int2>(), reinterpret_cast<const int*>(misc) + 44, cursor, b->stack_cap,                        \
       reinterpret_cast<int*>(misc) + 46, b->pipeline, shv)
-#define NB_BH_LAUNCH(BPL_, E_)               \
-  do {                                       \
-    if (shard) NB_BH_LAUNCH_S(BPL_, E_, true); \
-    else NB_BH_LAUNCH_S(BPL_, E_, false);    \
+#define NB_BH_LAUNCH_P(BPL_, E_, S_)                                                                               \
+  bh_force_pairs_kernel<BPL_, E_, S_><<<grid, BH_WARPS * 32, smem, st>>>(                                          \
+      (int)n, b->node_com.as<float4>(), b->pairs.as<float4>(), b->perm_sorted, theta * theta, G, eps2, d->acc_x,   \
+      d->acc_y, d->acc_z, reinterpret_cast<unsigned long long*>(misc + 40), b->d_flag, b->groups.as<int2>(),       \
+      reinterpret_cast<const int*>(misc) + 44, cursor, b->stack_cap, reinterpret_cast<int*>(misc) + 46, shv)
+#define NB_BH_LAUNCH(BPL_, E_)                                  \
+  do {                                                          \
+    if (b->walk_pairs) {                                        \
+      if (shard) NB_BH_LAUNCH_P(BPL_, E_, true);                \
+      else NB_BH_LAUNCH_P(BPL_, E_, false);                     \
+    } else if (shard) NB_BH_LAUNCH_S(BPL_, E_, true);           \
+    else NB_BH_LAUNCH_S(BPL_, E_, false);                       \
   } while (0)
   if (b->group == 64) {
     if (eps0) NB_BH_LAUNCH(2, true);
@@ -1039,6 +1322,7 @@ int bh_forces(nb_context* ctx, const nb_particles* d, float theta, float G, floa
     else NB_BH_LAUNCH(1, false);
   }
 #undef NB_BH_LAUNCH_S
+#undef NB_BH_LAUNCH_P
 #undef NB_BH_LAUNCH
   NB_LAUNCH_CHECK(ctx);
   return NB_OK;

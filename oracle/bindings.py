@@ -275,6 +275,11 @@ def lbvh_cell_size(L, bb):
     return lib().orc_lbvh_cell_size(int(L), _f32(bb))
 
 
+def set_walk_pairs(on):
+    """1 (default): lbvh_forces restates bh_force_pairs_kernel; 0: bh_force_kernel (NB_BH_WALK=nodes)."""
+    lib().orc_set_walk_pairs(1 if on else 0)
+
+
 def lbvh_forces(tree, com, sx, sy, sz, bb, theta, G, eps, group=32, super_=None):
     n = sx.size
     ax, ay, az = (np.zeros(n, np.float32) for _ in range(3))

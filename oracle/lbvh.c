@@ -120,6 +120,13 @@ float orc_lbvh_cell_size(int L, const float bbox[6]) {
  * (ceil(a / group) + ceil(b / group) == ceil(c / group)), else cut equal runs. */
 static int g_hybrid_slack_from = 0; /* experiment knob (orc_set_hybrid_slack): allow ONE extra group when need >= this */
 void orc_set_hybrid_slack(int from) { g_hybrid_slack_from = from; }
+/* experiment knobs / counters of the walk (tools/ and tests/measure_* only) */
+static int g_leaf_bucket = 0;      /* a rejected node with at most this many leaves hands over all its leaves */
+static uint64_t g_walk_pops = 0;   /* nodes popped by the last orc_lbvh_forces_ex call */
+void orc_set_leaf_bucket(int b) { g_leaf_bucket = b; }
+static int g_walk_pairs = 1;       /* 1: restate bh_force_pairs_kernel (the default walk), 0: bh_force_kernel (NB_BH_WALK=nodes) */
+void orc_set_walk_pairs(int on) { g_walk_pairs = on; }
+uint64_t orc_get_walk_pops(void) { return g_walk_pops; }
 static void hybrid_groups(int ni, int leaf0, int group, const int32_t* left, const int32_t* right,
                           const int32_t* range_first, const int32_t* range_last, int32_t* gfirst, int32_t* gcount,
                           int* ngroups) {
@@ -165,13 +172,20 @@ void orc_lbvh_forces_ex(int n, const int32_t* left, const int32_t* right, const 
                         const float* sx, const float* sy, const float* sz, const float bbox[6], float theta, float G,
                         float eps, int group, int super, int mode, float alpha, float* ax, float* ay, float* az,
                         uint64_t* interactions, uint64_t* stats) {
-  /* Sequential restatement of nbody_b200/csrc/bh.cu: bh_groups_kernel + bh_force_kernel.  A
+  /* Sequential restatement of nbody_b200/csrc/bh.cu: bh_groups_kernel + bh_force_pairs_kernel / bh_force_kernel.  A
    * supergroup is a maximal subtree with at most `super` (>= group) leaves (a lone leaf whose parent
    * is larger is a supergroup of one); its c bodies are cut into ceil(c / group) runs of consecutive
    * bodies, run i starting at floor(i * c / runs): those runs are the traversal groups (with
    * super == group they are the subtrees themselves).
-   * A group (one warp) owns a stack of node indices.  Each round pops the top
-   * min(32, size) entries (one per lane, bottom-to-top = lane 0..m-1).  A node is used for the whole
+   * A group (one warp) owns a stack of node indices.  Two walks, same acceptance test per node and so the same
+   * interaction set, different order (orc_set_walk_pairs):
+   *  - pairs (default, bh_force_pairs_kernel): the stack holds nodes to OPEN, starting with a virtual parent of the
+   *    root.  Each round pops the top min(32, size) entries (lane 0..m-1 = bottom to top); lane l tests the left
+   *    and then the right child of its node; accepted children are appended to the interaction list and rejected
+   *    ones pushed, both in lane order, a lane's left child first.
+   *  - nodes (bh_force_kernel, NB_BH_WALK=nodes): the stack holds nodes to TEST; each round pops up to 32, accepted
+   *    ones join the list in lane order, the children (left, right) of rejected ones are pushed in lane order.
+   * A node is used for the whole
    * group iff it is a leaf or size^2 < theta^2 * (dmin^2 + eps^2), dmin = distance from the node's
    * centre of mass to the group's bounding box (<= every body's own distance, so every body of the
    * group would also accept it under the reference's per-body test,
@@ -189,7 +203,8 @@ void orc_lbvh_forces_ex(int n, const int32_t* left, const int32_t* right, const 
     size2_of[L] = s * s;
   }
   size2_of[31] = 0.0f;
-  uint64_t total = 0, entries = 0;
+  uint64_t total = 0, entries = 0, pops = 0;
+  const int bucket = g_leaf_bucket;
   /* groups: top-down, a node whose leaf range fits becomes a group */
   int32_t* gfirst = (int32_t*)malloc(sizeof(int32_t) * (size_t)n);
   int32_t* gcount = (int32_t*)malloc(sizeof(int32_t) * (size_t)n);
@@ -220,7 +235,7 @@ void orc_lbvh_forces_ex(int n, const int32_t* left, const int32_t* right, const 
     }
     free(st);
   }
-#pragma omp parallel for schedule(dynamic, 16) reduction(+ : total, entries)
+#pragma omp parallel for schedule(dynamic, 16) reduction(+ : total, entries, pops)
   for (int g = 0; g < ngroups; g++) {
     const int k0 = gfirst[g], cnt = gcount[g];
     float accx[64], accy[64], accz[64];
@@ -232,17 +247,42 @@ void orc_lbvh_forces_ex(int n, const int32_t* left, const int32_t* right, const 
       lo[2] = fminf(lo[2], sz[k0 + t]); hi[2] = fmaxf(hi[2], sz[k0 + t]);
     }
     int32_t* stack = (int32_t*)malloc(sizeof(int32_t) * 8192);
-    int32_t list[96];
+    int32_t* list = (int32_t*)malloc(sizeof(int32_t) * (size_t)(96 + 32 * (bucket > 0 ? bucket : 0)));
     int sp = 0, nl = 0;
     stack[sp++] = 0;
+    const int walk_pairs = g_walk_pairs && alpha == 0.0f && bucket == 0; /* the experiment knobs belong to the node walk */
+    if (walk_pairs) stack[0] = -1; /* the virtual parent of the root (record n - 1 of bh_pairs_kernel) */
     for (;;) {
       const int m = sp < 32 ? sp : 32;
       int32_t popped[32];
       for (int l = 0; l < m; l++) popped[l] = stack[sp - m + l];
       sp -= m;
+      pops += (uint64_t)m;
       int32_t push[64];
       int np = 0;
-      for (int l = 0; l < m; l++) {
+      /* pair walk (bh_force_pairs_kernel): the stack holds nodes to OPEN; lane l tests both children of its node,
+       * left before right; accepted children join the list and rejected ones the stack, both in lane order */
+      for (int l = 0; walk_pairs && l < m; l++) {
+        const int pn = popped[l];
+        const int kids[2] = {pn < 0 ? 0 : left[pn], pn < 0 ? -1 : right[pn]};
+        for (int q = 0; q < 2; q++) {
+          const int ni = kids[q];
+          if (ni < 0) continue;
+          const float* c = node_com + 4 * (size_t)ni;
+          if (c[3] == 0.0f) continue; /* src/cuda/force_barnes_hut.cu:157-158 */
+          int accept = 1;
+          if (ni < leaf0) {
+            float ddx = fmaxf(fmaxf(lo[0] - c[0], c[0] - hi[0]), 0.0f);
+            float ddy = fmaxf(fmaxf(lo[1] - c[1], c[1] - hi[1]), 0.0f);
+            float ddz = fmaxf(fmaxf(lo[2] - c[2], c[2] - hi[2]), 0.0f);
+            float d2 = fmaf(ddz, ddz, fmaf(ddy, ddy, fmaf(ddx, ddx, eps2)));
+            accept = size2_of[prefix[ni]] < theta2 * d2;
+          }
+          if (accept) list[nl++] = ni;
+          else push[np++] = ni;
+        }
+      }
+      for (int l = 0; !walk_pairs && l < m; l++) {
         const int ni = popped[l];
         const float* c = node_com + 4 * (size_t)ni;
         if (c[3] == 0.0f) continue; /* src/cuda/force_barnes_hut.cu:157-158 */
@@ -262,6 +302,9 @@ void orc_lbvh_forces_ex(int n, const int32_t* left, const int32_t* right, const 
         }
         if (accept) {
           list[nl++] = ni;
+        } else if (bucket > 0 && range_last[ni] - range_first[ni] + 1 <= bucket) {
+          for (int k = range_first[ni]; k <= range_last[ni]; k++)
+            if (node_com[4 * (size_t)(leaf0 + k) + 3] != 0.0f) list[nl++] = leaf0 + k;
         } else {
           push[np++] = left[ni];
           push[np++] = right[ni];
@@ -294,6 +337,7 @@ void orc_lbvh_forces_ex(int n, const int32_t* left, const int32_t* right, const 
       if (done) break;
     }
     free(stack);
+    free(list);
     for (int t = 0; t < cnt; t++) {
       ax[k0 + t] = accx[t]; ay[k0 + t] = accy[t]; az[k0 + t] = accz[t];
     }
@@ -301,6 +345,7 @@ void orc_lbvh_forces_ex(int n, const int32_t* left, const int32_t* right, const 
   free(gfirst);
   free(gcount);
   if (interactions) *interactions = total;
+  g_walk_pops = pops;
   if (stats) {
     stats[0] = (uint64_t)ngroups;
     stats[1] = entries;

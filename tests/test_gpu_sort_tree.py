@@ -121,10 +121,21 @@ def test_morton_sort_lbvh_bit_exact(orc, n, kind):
         assert abs(t["node_com"][0, 3] - st["mass"].sum(dtype=np.float64)) <= 1e-3 * st["mass"].sum()
 
 
+@pytest.fixture
+def walk(request, orc, monkeypatch):
+    """the traversal's two walks (NB_BH_WALK: pair records, the default, or one node per stack entry) with the
+    oracle set to restate the same one"""
+    monkeypatch.setenv("NB_BH_WALK", request.param)
+    orc.set_walk_pairs(request.param == "pairs")
+    yield request.param
+    orc.set_walk_pairs(True)
+
+
+@pytest.mark.parametrize("walk", ["pairs", "nodes"], indirect=True)
 @pytest.mark.parametrize("group,sup", [(64, None), (32, None), (64, 64), (32, 100)])
 @pytest.mark.parametrize("n,theta", [(1, 0.5), (2, 0.5), (30, 0.1), (1000, 0.5), (20000, 0.5), (20000, 0.8),
                                      (100000, 0.5)])
-def test_bh_forces_vs_lbvh_oracle(orc, n, theta, group, sup, monkeypatch):
+def test_bh_forces_vs_lbvh_oracle(orc, n, theta, group, sup, walk, monkeypatch):
     """Same tree, same traversal groups, same operation order: only rsqrt differs (<= 1e-5).
     sup = leaves of the subtrees the groups are cut from (default 8 x group; == group: the subtrees)."""
     from nbody_b200 import ics

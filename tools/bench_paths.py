@@ -28,6 +28,8 @@ ALGO_BYTES = {
     "bh.morton": 16 + 4 + 16,  # x,y,z,m read; key and packed {x,y,z,m} written (the sort generates the identity values)
     # keys + perm read, packed float4 gathered, leaf record written; per internal node {left,right,prefix} + centre of mass
     "bh.tree": 4 + 4 + 16 + 16 + 16 + 16,
+    # node record + both children's centres of mass + their levels read, one 48-byte pair record written per node
+    "bh.pairs": 16 + 32 + 8 + 48,
     "sh.bbox": 12,
     "sh.assign": 16 + 4 + 4 + 4 + 16,  # x,y,z,m read; particle_cell, key, identity value and packed written
     "sh.ranges_gather": 4 + 4 + 16 + 16,  # sorted key + index read, packed gathered, cell-ordered float4 written (+ cell ranges)
