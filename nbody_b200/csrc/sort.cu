@@ -134,6 +134,9 @@ constexpr int RS_LOOK = NB_RS_LOOK;  // predecessors examined per look-back roun
 #ifndef NB_RS_MIN_BLOCKS
 #define NB_RS_MIN_BLOCKS 2  // build-time knob: resident CTAs per SM the pass kernel is compiled for (3 = 40 registers with spills: 0.507 ms against 0.488)
 #endif
+#ifndef NB_RS_MATCH
+#define NB_RS_MATCH 0  // build-time knob: rank with match.any.sync instead of one ballot per digit bit
+#endif
 #ifndef NB_RS_BATCH
 #define NB_RS_BATCH 16  // build-time knob: keys a thread holds in registers at a time while ranking / staging (8: 0.488 ms, 16: 0.483 for 16 Mi x 30 bits in place)
 #endif
@@ -307,6 +310,9 @@ __global__ void __launch_bounds__(RS_THREADS, NB_RS_MIN_BLOCKS) rs_pass_kernel(c
       const bool ok = wofs + (h + k) * 32 < tcount;
       const uint32_t dgt = (key[k] >> shift) & mask;
       uint32_t peers = __ballot_sync(0xffffffffu, ok);
+#if NB_RS_MATCH
+      peers &= __match_any_sync(0xffffffffu, dgt);  // experiment: MATCH.ANY instead of one ballot per digit bit
+#else
 #pragma unroll
       for (int b = 0; b < RB; b++) {
         // v = lanes whose bit b is set, x = 0 if mine is set else ~0: peers &= ~(v ^ x) ... written as v ^ ~x below.
@@ -325,6 +331,7 @@ __global__ void __launch_bounds__(RS_THREADS, NB_RS_MIN_BLOCKS) rs_pass_kernel(c
             : "r"(dgt), "r"(1u << b));
         peers &= v ^ x;
       }
+#endif
       const int leader = max(__ffs(peers) - 1, 0);
       const uint32_t sh16 = (dgt & 1u) * 16u;
       uint32_t old = 0;
