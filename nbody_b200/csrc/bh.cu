@@ -597,6 +597,150 @@ constexpr int BH_WARPS = 4;
 constexpr int BH_LIST = 64;
 constexpr int BH_STAGE = 32 * 32;  // bytes per warp: one {centre of mass, node record} per lane
 
+// What a warp holds for its traversal group, shared by both walks: the lane's BPL bodies (as one packed fp32x2 pair when
+// BPL == 2), their running sums, and the group's bounding box.
+template <int BPL, bool EPS0>
+struct BhGroup {
+  struct { float x, y, z; } me[BPL];
+  float sx[BPL], sy[BPL], sz[BPL];
+  float lo[3], hi[3];
+  f2 xi2, yi2, zi2, sx2, sy2, sz2, e2;
+  float eps2;
+
+  // scalar loads on purpose: a float4 load pins x,y,z to one aligned register quad, and ptxas then re-packs the
+  // (body 0, body 1) pairs with MOVs for every list entry (4.5 MOVs per entry measured)
+  __device__ __forceinline__ void load(const float4* __restrict__ leaves, int k0, int gcnt, int lane, float eps2_) {
+    eps2 = eps2_;
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+      lo[a] = 3.0e38f;
+      hi[a] = -3.0e38f;
+    }
+#pragma unroll
+    for (int b = 0; b < BPL; b++) {
+      me[b].x = me[b].y = me[b].z = 0.f;
+      if (b * 32 + lane < gcnt) {
+        const float* q = reinterpret_cast<const float*>(leaves + k0 + b * 32 + lane);
+        me[b].x = __ldg(q); me[b].y = __ldg(q + 1); me[b].z = __ldg(q + 2);
+        lo[0] = fminf(lo[0], me[b].x); hi[0] = fmaxf(hi[0], me[b].x);
+        lo[1] = fminf(lo[1], me[b].y); hi[1] = fmaxf(hi[1], me[b].y);
+        lo[2] = fminf(lo[2], me[b].z); hi[2] = fmaxf(hi[2], me[b].z);
+      }
+      sx[b] = sy[b] = sz[b] = 0.f;
+    }
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+      lo[a] = warp_min(lo[a]);
+      hi[a] = warp_max(hi[a]);
+    }
+    e2 = pk(eps2, eps2);
+    xi2 = pk(me[0].x, me[BPL - 1].x);
+    yi2 = pk(me[0].y, me[BPL - 1].y);
+    zi2 = pk(me[0].z, me[BPL - 1].z);
+    sx2 = sy2 = sz2 = pk(0.f, 0.f);
+  }
+
+  // distance^2 from a centre of mass to the group's box, softened: the denominator of the acceptance test.  dmin <=
+  // every body's own distance, so a node the group accepts is a node every body would accept with the reference's
+  // per-body test (:160-172).
+  __device__ __forceinline__ float box_d2(const float4& c) const {
+    const float ddx = fmaxf(fmaxf(lo[0] - c.x, c.x - hi[0]), 0.f);
+    const float ddy = fmaxf(fmaxf(lo[1] - c.y, c.y - hi[1]), 0.f);
+    const float ddz = fmaxf(fmaxf(lo[2] - c.z, c.z - hi[2]), 0.f);
+    return fmaf(ddz, ddz, fmaf(ddy, ddy, fmaf(ddx, ddx, eps2)));
+  }
+
+  // the monopole term (:175-181) of one list entry {x, y, z, G * M} for the lane's bodies
+  __device__ __forceinline__ void add(const float4 p) {
+    const float gm = p.w;
+    if constexpr (BPL == 2) {
+      // the lane's two bodies as one packed fp32x2 pair (FADD2/FFMA2/FMUL2, as in direct.cu)
+      const f2 dx = sub2(pk(p.x, p.x), xi2), dy = sub2(pk(p.y, p.y), yi2), dz = sub2(pk(p.z, p.z), zi2);
+      const f2 d2 = fma2(dz, dz, fma2(dy, dy, fma2(dx, dx, e2)));
+      float r0, r1;
+      upk(d2, r0, r1);
+      float i0 = rsq(r0), i1 = rsq(r1);
+      if (EPS0) {  // own leaf / exact coincidence at eps ~ 0
+        i0 = (r0 > eps2) ? i0 : 0.f;
+        i1 = (r1 > eps2) ? i1 : 0.f;
+      }
+      const f2 ri = pk(i0, i1);
+      const f2 f = mul2(pk(gm, gm), mul2(mul2(ri, ri), ri));
+      sx2 = fma2(f, dx, sx2);
+      sy2 = fma2(f, dy, sy2);
+      sz2 = fma2(f, dz, sz2);
+    } else {
+#pragma unroll
+      for (int b = 0; b < BPL; b++) {
+        const float dx = p.x - me[b].x, dy = p.y - me[b].y, dz = p.z - me[b].z;
+        const float d2 = fmaf(dz, dz, fmaf(dy, dy, fmaf(dx, dx, eps2)));
+        float inv = rsq(d2);
+        if (EPS0) inv = (d2 > eps2) ? inv : 0.f;  // own leaf / exact coincidence at eps ~ 0
+        const float f = gm * (inv * inv * inv);
+        sx[b] = fmaf(f, dx, sx[b]);
+        sy[b] = fmaf(f, dy, sy[b]);
+        sz[b] = fmaf(f, dz, sz[b]);
+      }
+    }
+  }
+
+  // ne <= 32 list entries, each a warp-broadcast LDS.128
+  __device__ __forceinline__ void evaluate(const float4* lcur, int ne) {
+    if (ne == 32) {
+      NB_BH_PRAGMA_UNROLL(NB_BH_UNROLL)
+      for (int e = 0; e < 32; e++) add(lcur[e]);
+    } else {
+      for (int e = 0; e < ne; e++) add(lcur[e]);
+    }
+  }
+
+  // accelerations out: body order through the sort permutation, or (SHARDED) sorted order into every rank's
+  // exchange buffer
+  template <bool SHARDED>
+  __device__ __forceinline__ void store(int k0, int gcnt, int lane, const int32_t* __restrict__ perm,
+                                        float* __restrict__ ax, float* __restrict__ ay, float* __restrict__ az,
+                                        const BhShard& sh) {
+    if constexpr (BPL == 2) {
+      upk(sx2, sx[0], sx[1]);
+      upk(sy2, sy[0], sy[1]);
+      upk(sz2, sz[0], sz[1]);
+    }
+#pragma unroll
+    for (int b = 0; b < BPL; b++) {
+      if (b * 32 + lane < gcnt) {
+        if (SHARDED) {
+          const float4 v = make_float4(sx[b], sy[b], sz[b], 0.f);
+#pragma unroll
+          for (int r = 0; r < 8; r++)
+            if (r < sh.nranks) sh.out[r][k0 + b * 32 + lane] = v;
+        } else {
+          const int i = perm[k0 + b * 32 + lane];
+          ax[i] = sx[b];
+          ay[i] = sy[b];
+          az[i] = sz[b];
+        }
+      }
+    }
+  }
+};
+
+// SHARDED epilogue of a traversal kernel: the last CTA to finish raises this rank's step flag on every peer
+__device__ __forceinline__ void bh_shard_publish(const BhShard& sh) {
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned prev = atomicAdd(sh.done_counter, 1u);
+    if (prev == gridDim.x - 1) {  // every CTA's peer stores are fenced: publish
+      *sh.done_counter = 0;
+      __threadfence_system();
+      for (int r = 0; r < sh.nranks; r++)
+        if (r != sh.rank)
+          asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(sh.flags[r] + sh.flag_index), "r"(sh.step)
+                       : "memory");
+    }
+  }
+}
+
 // SHARDED (multi-GPU, mgpu.cu): every rank holds the same tree; this rank traverses only the groups it
 // is dealt (by the group's first sorted body, so the deal is identical on every rank although the
 // order of the group array is not) and stores each body's acceleration, in SORTED order, into the
@@ -642,31 +786,8 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
   const int k0 = grp.x, gcnt = grp.y;
   if (SHARDED && (((unsigned)k0 * 2654435761u) >> 20) % (unsigned)sh.nranks != (unsigned)sh.rank) continue;  // dealt to another rank
 
-  // scalar loads on purpose: a float4 load pins x,y,z to one aligned register quad, and ptxas then
-  // re-packs the (body 0, body 1) pairs with MOVs for every list entry (4.5 MOVs per entry measured)
-  struct { float x, y, z; } me[BPL];
-  float sx[BPL], sy[BPL], sz[BPL];
-  float lo[3] = {3.0e38f, 3.0e38f, 3.0e38f}, hi[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
-#pragma unroll
-  for (int b = 0; b < BPL; b++) {
-    me[b].x = me[b].y = me[b].z = 0.f;
-    if (b * 32 + lane < gcnt) {
-      const float* q = reinterpret_cast<const float*>(node_com + leaf0 + k0 + b * 32 + lane);
-      me[b].x = __ldg(q); me[b].y = __ldg(q + 1); me[b].z = __ldg(q + 2);
-      lo[0] = fminf(lo[0], me[b].x); hi[0] = fmaxf(hi[0], me[b].x);
-      lo[1] = fminf(lo[1], me[b].y); hi[1] = fmaxf(hi[1], me[b].y);
-      lo[2] = fminf(lo[2], me[b].z); hi[2] = fmaxf(hi[2], me[b].z);
-    }
-    sx[b] = sy[b] = sz[b] = 0.f;
-  }
-#pragma unroll
-  for (int a = 0; a < 3; a++) {
-    lo[a] = warp_min(lo[a]);
-    hi[a] = warp_max(hi[a]);
-  }
-  const f2 e2 = pk(eps2, eps2);
-  const f2 xi2 = pk(me[0].x, me[BPL - 1].x), yi2 = pk(me[0].y, me[BPL - 1].y), zi2 = pk(me[0].z, me[BPL - 1].z);
-  f2 sx2 = pk(0.f, 0.f), sy2 = sx2, sz2 = sx2;
+  BhGroup<BPL, EPS0> bodies;
+  bodies.load(node_com + leaf0, k0, gcnt, lane, eps2);
 
   int sp = 1, nl = 0, lbase = 0;
   unsigned visits = 0;
@@ -700,13 +821,7 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
     const bool leaf = ni >= leaf0;
     const bool valid = have && c.w != 0.f;  // total_mass == 0 -> skipped (:157-158)
     bool acc = leaf;
-    if (valid && !leaf) {
-      const float ddx = fmaxf(fmaxf(lo[0] - c.x, c.x - hi[0]), 0.f);
-      const float ddy = fmaxf(fmaxf(lo[1] - c.y, c.y - hi[1]), 0.f);
-      const float ddz = fmaxf(fmaxf(lo[2] - c.z, c.z - hi[2]), 0.f);
-      const float d2 = fmaf(ddz, ddz, fmaf(ddy, ddy, fmaf(ddx, ddx, eps2)));
-      acc = size2_tab[mt.z] < theta2 * d2;  // size2 / dist2 < theta2 (:167)
-    }
+    if (valid && !leaf) acc = size2_tab[mt.z] < theta2 * bodies.box_d2(c);  // size2 / dist2 < theta2 (:167)
     const bool is_acc = valid && acc, is_rej = valid && !acc;
     const unsigned amask = __ballot_sync(0xffffffffu, is_acc), rmask = __ballot_sync(0xffffffffu, is_rej);
     // the list is a ring of two 32-entry halves: a batch is one half, what is left over already sits in the other
@@ -729,46 +844,7 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
     if (!done && pipeline) pop_and_fetch();  // in flight while the list is evaluated
     while (nl >= 32 || (done && nl > 0)) {
       const int ne = min(nl, 32);
-      const float4* lcur = list + lbase;
-      auto body = [&](int e) {
-        const float4 p = lcur[e];  // warp-broadcast LDS.128; p.w = G * M
-        const float gm = p.w;
-        if constexpr (BPL == 2) {
-          // the lane's two bodies as one packed fp32x2 pair (FADD2/FFMA2/FMUL2, as in direct.cu)
-          const f2 dx = sub2(pk(p.x, p.x), xi2), dy = sub2(pk(p.y, p.y), yi2), dz = sub2(pk(p.z, p.z), zi2);
-          const f2 d2 = fma2(dz, dz, fma2(dy, dy, fma2(dx, dx, e2)));
-          float r0, r1;
-          upk(d2, r0, r1);
-          float i0 = rsq(r0), i1 = rsq(r1);
-          if (EPS0) {  // own leaf / exact coincidence at eps ~ 0
-            i0 = (r0 > eps2) ? i0 : 0.f;
-            i1 = (r1 > eps2) ? i1 : 0.f;
-          }
-          const f2 ri = pk(i0, i1);
-          const f2 f = mul2(pk(gm, gm), mul2(mul2(ri, ri), ri));
-          sx2 = fma2(f, dx, sx2);
-          sy2 = fma2(f, dy, sy2);
-          sz2 = fma2(f, dz, sz2);
-        } else {
-#pragma unroll
-          for (int b = 0; b < BPL; b++) {
-            const float dx = p.x - me[b].x, dy = p.y - me[b].y, dz = p.z - me[b].z;
-            const float d2 = fmaf(dz, dz, fmaf(dy, dy, fmaf(dx, dx, eps2)));
-            float inv = rsq(d2);
-            if (EPS0) inv = (d2 > eps2) ? inv : 0.f;  // own leaf / exact coincidence at eps ~ 0
-            const float f = gm * (inv * inv * inv);
-            sx[b] = fmaf(f, dx, sx[b]);
-            sy[b] = fmaf(f, dy, sy[b]);
-            sz[b] = fmaf(f, dz, sz[b]);
-          }
-        }
-      };
-      if (ne == 32) {
-        NB_BH_PRAGMA_UNROLL(NB_BH_UNROLL)
-        for (int e = 0; e < 32; e++) body(e);
-      } else {
-        for (int e = 0; e < ne; e++) body(e);
-      }
+      bodies.evaluate(list + lbase, ne);
       visits += ne;
       __syncwarp();  // every lane has read the batch before later entries wrap into its half
       if (ne == 32) lbase ^= 32;  // what is left (< 32 entries) already sits at the start of the other half
@@ -777,27 +853,7 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
     if (done) break;
     if (!pipeline) pop_and_fetch();
   }
-  if constexpr (BPL == 2) {
-    upk(sx2, sx[0], sx[1]);
-    upk(sy2, sy[0], sy[1]);
-    upk(sz2, sz[0], sz[1]);
-  }
-#pragma unroll
-  for (int b = 0; b < BPL; b++) {
-    if (b * 32 + lane < gcnt) {
-      if (SHARDED) {
-        const float4 v = make_float4(sx[b], sy[b], sz[b], 0.f);
-#pragma unroll
-        for (int r = 0; r < 8; r++)
-          if (r < sh.nranks) sh.out[r][k0 + b * 32 + lane] = v;
-      } else {
-        const int i = perm[k0 + b * 32 + lane];
-        ax[i] = sx[b];
-        ay[i] = sy[b];
-        az[i] = sz[b];
-      }
-    }
-  }
+  bodies.template store<SHARDED>(k0, gcnt, lane, perm, ax, ay, az, sh);
   visits_bodies += (unsigned long long)visits * (unsigned long long)gcnt;
   __syncwarp();
   }  // next group
@@ -805,21 +861,7 @@ __global__ void __launch_bounds__(BH_WARPS * 32) bh_force_kernel(int n, const fl
     atomicAdd(counter, visits_bodies);
     atomicMax(max_stack, deepest);
   }
-  if (SHARDED) {
-    __threadfence_system();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      const unsigned prev = atomicAdd(sh.done_counter, 1u);
-      if (prev == gridDim.x - 1) {  // every CTA's peer stores are fenced: publish
-        *sh.done_counter = 0;
-        __threadfence_system();
-        for (int r = 0; r < sh.nranks; r++)
-          if (r != sh.rank)
-            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(sh.flags[r] + sh.flag_index), "r"(sh.step)
-                         : "memory");
-      }
-    }
-  }
+  if (SHARDED) bh_shard_publish(sh);
 }
 
 // ---- traversal over child-pair records (the default) ----------------------------------------------------------
@@ -866,29 +908,8 @@ __global__ void __launch_bounds__(BH_WARPS * 32, NB_BH_MIN_BLOCKS)
   const int k0 = grp.x, gcnt = grp.y;
   if (SHARDED && (((unsigned)k0 * 2654435761u) >> 20) % (unsigned)sh.nranks != (unsigned)sh.rank) continue;  // dealt to another rank
 
-  struct { float x, y, z; } me[BPL];  // scalar loads on purpose, see bh_force_kernel
-  float sx[BPL], sy[BPL], sz[BPL];
-  float lo[3] = {3.0e38f, 3.0e38f, 3.0e38f}, hi[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
-#pragma unroll
-  for (int b = 0; b < BPL; b++) {
-    me[b].x = me[b].y = me[b].z = 0.f;
-    if (b * 32 + lane < gcnt) {
-      const float* q = reinterpret_cast<const float*>(node_com + leaf0 + k0 + b * 32 + lane);
-      me[b].x = __ldg(q); me[b].y = __ldg(q + 1); me[b].z = __ldg(q + 2);
-      lo[0] = fminf(lo[0], me[b].x); hi[0] = fmaxf(hi[0], me[b].x);
-      lo[1] = fminf(lo[1], me[b].y); hi[1] = fmaxf(hi[1], me[b].y);
-      lo[2] = fminf(lo[2], me[b].z); hi[2] = fmaxf(hi[2], me[b].z);
-    }
-    sx[b] = sy[b] = sz[b] = 0.f;
-  }
-#pragma unroll
-  for (int a = 0; a < 3; a++) {
-    lo[a] = warp_min(lo[a]);
-    hi[a] = warp_max(hi[a]);
-  }
-  const f2 e2 = pk(eps2, eps2);
-  const f2 xi2 = pk(me[0].x, me[BPL - 1].x), yi2 = pk(me[0].y, me[BPL - 1].y), zi2 = pk(me[0].z, me[BPL - 1].z);
-  f2 sx2 = pk(0.f, 0.f), sy2 = sx2, sz2 = sx2;
+  BhGroup<BPL, EPS0> bodies;
+  bodies.load(node_com + leaf0, k0, gcnt, lane, eps2);
 
   int sp = 1, nl = 0, lbase = 0;
   unsigned visits = 0;
@@ -907,13 +928,6 @@ __global__ void __launch_bounds__(BH_WARPS * 32, NB_BH_MIN_BLOCKS)
     asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(smem_u32(stage_m + lane)), "l"(r + 2) : "memory");
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
-  // distance^2 from a centre of mass to the group's box, softened: the denominator of the acceptance test
-  auto box_d2 = [&](const float4& c) {
-    const float ddx = fmaxf(fmaxf(lo[0] - c.x, c.x - hi[0]), 0.f);
-    const float ddy = fmaxf(fmaxf(lo[1] - c.y, c.y - hi[1]), 0.f);
-    const float ddz = fmaxf(fmaxf(lo[2] - c.z, c.z - hi[2]), 0.f);
-    return fmaf(ddz, ddz, fmaf(ddy, ddy, fmaf(ddx, ddx, eps2)));
-  };
   pop_and_fetch();
   for (;;) {
     asm volatile("cp.async.wait_group 0;" ::: "memory");
@@ -924,8 +938,8 @@ __global__ void __launch_bounds__(BH_WARPS * 32, NB_BH_MIN_BLOCKS)
     // a child is used for the whole group iff it is a leaf or size^2 < theta^2 * d^2 (:167); total mass 0 -> skipped
     // (:157-158).  Both tests run unconditionally: no branches around them.
     const bool va = have && ca.w != 0.f, vb = have && cb.w != 0.f;
-    const bool ta = (ia >= leaf0) | (mf.z < theta2 * box_d2(ca));
-    const bool tb = (ib >= leaf0) | (mf.w < theta2 * box_d2(cb));
+    const bool ta = (ia >= leaf0) | (mf.z < theta2 * bodies.box_d2(ca));
+    const bool tb = (ib >= leaf0) | (mf.w < theta2 * bodies.box_d2(cb));
     const bool acc_a = va && ta, acc_b = vb && tb, rej_a = va && !ta, rej_b = vb && !tb;
     const unsigned ma = __ballot_sync(0xffffffffu, acc_a), mb = __ballot_sync(0xffffffffu, acc_b);
     const unsigned ra = __ballot_sync(0xffffffffu, rej_a), rb = __ballot_sync(0xffffffffu, rej_b);
@@ -948,46 +962,7 @@ __global__ void __launch_bounds__(BH_WARPS * 32, NB_BH_MIN_BLOCKS)
     if (!done) pop_and_fetch();  // in flight while the list is evaluated
     while (nl >= 32 || (done && nl > 0)) {
       const int ne = min(nl, 32);
-      const float4* lcur = list + lbase;
-      auto body = [&](int e) {
-        const float4 p = lcur[e];  // warp-broadcast LDS.128; p.w = G * M
-        const float gm = p.w;
-        if constexpr (BPL == 2) {
-          // the lane's two bodies as one packed fp32x2 pair (FADD2/FFMA2/FMUL2, as in direct.cu)
-          const f2 dx = sub2(pk(p.x, p.x), xi2), dy = sub2(pk(p.y, p.y), yi2), dz = sub2(pk(p.z, p.z), zi2);
-          const f2 d2 = fma2(dz, dz, fma2(dy, dy, fma2(dx, dx, e2)));
-          float r0, r1;
-          upk(d2, r0, r1);
-          float i0 = rsq(r0), i1 = rsq(r1);
-          if (EPS0) {  // own leaf / exact coincidence at eps ~ 0
-            i0 = (r0 > eps2) ? i0 : 0.f;
-            i1 = (r1 > eps2) ? i1 : 0.f;
-          }
-          const f2 ri = pk(i0, i1);
-          const f2 f = mul2(pk(gm, gm), mul2(mul2(ri, ri), ri));
-          sx2 = fma2(f, dx, sx2);
-          sy2 = fma2(f, dy, sy2);
-          sz2 = fma2(f, dz, sz2);
-        } else {
-#pragma unroll
-          for (int b = 0; b < BPL; b++) {
-            const float dx = p.x - me[b].x, dy = p.y - me[b].y, dz = p.z - me[b].z;
-            const float d2 = fmaf(dz, dz, fmaf(dy, dy, fmaf(dx, dx, eps2)));
-            float inv = rsq(d2);
-            if (EPS0) inv = (d2 > eps2) ? inv : 0.f;  // own leaf / exact coincidence at eps ~ 0
-            const float f = gm * (inv * inv * inv);
-            sx[b] = fmaf(f, dx, sx[b]);
-            sy[b] = fmaf(f, dy, sy[b]);
-            sz[b] = fmaf(f, dz, sz[b]);
-          }
-        }
-      };
-      if (ne == 32) {
-        NB_BH_PRAGMA_UNROLL(NB_BH_UNROLL)
-        for (int e = 0; e < 32; e++) body(e);
-      } else {
-        for (int e = 0; e < ne; e++) body(e);
-      }
+      bodies.evaluate(list + lbase, ne);
       visits += ne;
       __syncwarp();  // every lane has read the batch before later entries wrap into it
       if (ne == 32) lbase = (lbase + 32) & (BH_PLIST - 1);
@@ -995,27 +970,7 @@ __global__ void __launch_bounds__(BH_WARPS * 32, NB_BH_MIN_BLOCKS)
     }
     if (done) break;
   }
-  if constexpr (BPL == 2) {
-    upk(sx2, sx[0], sx[1]);
-    upk(sy2, sy[0], sy[1]);
-    upk(sz2, sz[0], sz[1]);
-  }
-#pragma unroll
-  for (int b = 0; b < BPL; b++) {
-    if (b * 32 + lane < gcnt) {
-      if (SHARDED) {
-        const float4 v = make_float4(sx[b], sy[b], sz[b], 0.f);
-#pragma unroll
-        for (int r = 0; r < 8; r++)
-          if (r < sh.nranks) sh.out[r][k0 + b * 32 + lane] = v;
-      } else {
-        const int i = perm[k0 + b * 32 + lane];
-        ax[i] = sx[b];
-        ay[i] = sy[b];
-        az[i] = sz[b];
-      }
-    }
-  }
+  bodies.template store<SHARDED>(k0, gcnt, lane, perm, ax, ay, az, sh);
   visits_bodies += (unsigned long long)visits * (unsigned long long)gcnt;
   __syncwarp();
   }  // next group
@@ -1023,21 +978,7 @@ __global__ void __launch_bounds__(BH_WARPS * 32, NB_BH_MIN_BLOCKS)
     atomicAdd(counter, visits_bodies);
     atomicMax(max_stack, deepest);
   }
-  if (SHARDED) {
-    __threadfence_system();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      const unsigned prev = atomicAdd(sh.done_counter, 1u);
-      if (prev == gridDim.x - 1) {  // every CTA's peer stores are fenced: publish
-        *sh.done_counter = 0;
-        __threadfence_system();
-        for (int r = 0; r < sh.nranks; r++)
-          if (r != sh.rank)
-            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(sh.flags[r] + sh.flag_index), "r"(sh.step)
-                         : "memory");
-      }
-    }
-  }
+  if (SHARDED) bh_shard_publish(sh);
 }
 
 // accelerations arrive in sorted order; hand them back to body order, optionally with the kick
