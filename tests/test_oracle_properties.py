@@ -1,5 +1,6 @@
 """CPU: internal consistency of the oracle itself (so a bug in it cannot hide a bug in the kernels)."""
 import numpy as np
+import pytest
 
 from tests.conftest import rel_err
 
@@ -89,6 +90,37 @@ def test_lbvh_com_and_forces_consistency(orc):
     # cell size table: level 0 = largest extent, three prefix bits halve it
     s0, s3 = orc.lbvh_cell_size(0, bb), orc.lbvh_cell_size(3, bb)
     assert abs(s0 - (bb[3:] - bb[:3] + np.float32(0.001)).max()) < 1e-6 and abs(s3 - s0 / 2) < 1e-6
+
+
+@pytest.mark.parametrize("n,theta,group", [(1, 0.5, 64), (2, 0.5, 64), (777, 0.5, 64), (5000, 0.5, 64),
+                                           (5000, 0.8, 32), (5000, 0.0, 64)])
+def test_lbvh_walks_accept_the_same_nodes(orc, n, theta, group):
+    """The two walks of the traversal (child-pair records / one node per stack entry) apply the same acceptance test to
+    the same nodes: identical interaction counts, sums equal to the rounding of a different order."""
+    from nbody_b200 import ics
+    st = ics.plummer(n, seed=9) if n > 2 else ics.uniform_box(n, -1, 1, seed=9)
+    bb = orc.bbox(st["pos_x"], st["pos_y"], st["pos_z"])
+    keys, idx = orc.morton_keys(st["pos_x"], st["pos_y"], st["pos_z"], bb)
+    sk, sp = orc.sort_pairs(keys, idx)
+    if n > 1:
+        t = orc.lbvh_build(sk)
+    else:
+        z = np.zeros(1, np.int32)
+        t = dict(left=z, right=z, prefix=z, first=z, last=z)
+    sx, sy, sz, sm = (st[k][sp] for k in ("pos_x", "pos_y", "pos_z", "mass"))
+    com = orc.lbvh_com(t, sx, sy, sz, sm) if n > 1 else np.array([[sx[0], sy[0], sz[0], sm[0]]], np.float32)
+    try:
+        orc.set_walk_pairs(True)
+        a = orc.lbvh_forces(t, com, sx, sy, sz, bb, theta, 1.0, 0.01, group)
+        orc.set_walk_pairs(False)
+        b = orc.lbvh_forces(t, com, sx, sy, sz, bb, theta, 1.0, 0.01, group)
+    finally:
+        orc.set_walk_pairs(True)
+    assert a[3] == b[3]
+    if theta == 0.0:
+        assert a[3] == n * n
+    if n > 1:
+        assert rel_err(a[:3], b[:3]).max() < 1e-5
 
 
 def test_octree_as_written_vs_intended(orc):
