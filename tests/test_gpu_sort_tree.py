@@ -161,6 +161,42 @@ def test_bh_forces_vs_lbvh_oracle(orc, n, theta, group, sup, walk, monkeypatch):
     assert calc.getTree().interactions() == inter
 
 
+@pytest.mark.parametrize("walk", ["pairs", "nodes"], indirect=True)
+@pytest.mark.parametrize("kind", ["zero_mass_runs", "coincident", "two_points"])
+def test_bh_forces_degenerate_inputs_vs_lbvh_oracle(orc, kind, walk):
+    """Massless bodies -- singly and in runs long enough that whole subtrees have total mass 0 and are skipped
+    (src/cuda/force_barnes_hut.cu:157-158) -- and trees decided by the index tie-break alone (every key equal, two
+    distinct points), for both walks: interaction counts exact, forces <= 1e-5 against the step-for-step oracle."""
+    from nbody_b200 import ics
+    n = 6000
+    st = ics.plummer(n, seed=21)
+    if kind == "zero_mass_runs":
+        st["mass"][::3] = 0.0
+        order = np.argsort(st["pos_x"], kind="stable")
+        st["mass"][order[:700]] = 0.0   # a spatially compact massless region: whole subtrees with mass 0
+    elif kind == "coincident":
+        for k in ("pos_x", "pos_y", "pos_z"):
+            st[k][:] = np.float32(0.25)
+    else:
+        for k, (a, b) in zip(("pos_x", "pos_y", "pos_z"), ((0.1, 0.9), (0.2, 0.7), (-0.3, 0.4))):
+            st[k][0::2] = np.float32(a)
+            st[k][1::2] = np.float32(b)
+    d, calc = _build(st, 0.5)
+    out = d.numpy()
+    t = calc.getTree().export()
+    sp = t["perm"]
+    sx, sy, sz = (st[k][sp] for k in ("pos_x", "pos_y", "pos_z"))
+    tree = orc.lbvh_build(t["keys"])
+    ax, ay, az, inter = orc.lbvh_forces(tree, t["node_com"], sx, sy, sz, t["bbox"], 0.5, 1.0, 0.01, 64, None)
+    assert calc.getTree().interactions() == inter
+    got = (out["acc_x"][sp], out["acc_y"][sp], out["acc_z"][sp])
+    assert all(np.isfinite(g).all() for g in got)
+    ref = np.sqrt(np.asarray(ax, np.float64) ** 2 + np.asarray(ay, np.float64) ** 2 + np.asarray(az, np.float64) ** 2)
+    err = np.sqrt(sum((np.asarray(g, np.float64) - np.asarray(r, np.float64)) ** 2 for g, r in zip(got, (ax, ay, az))))
+    # relative to the largest acceleration: bodies whose pulls cancel exactly (coincident points) have |a| = 0
+    assert err.max() <= 1e-5 * max(ref.max(), 1e-30)
+
+
 def test_bh_vs_octree_oracle_and_direct(orc):
     """Stated tolerance: at equal theta the LBVH forces agree with the reference's
     intended octree algorithm within the Barnes-Hut error itself, and are no less accurate."""
