@@ -1081,12 +1081,6 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
     const int g = (e && atoi(e) == 32) ? 32 : 64;
     if (g != b->group) b->occ = 0;
     b->group = g;
-    if (const char* ce = getenv("NB_BH_STACK")) {
-      int c = atoi(ce);
-      c = c < 512 ? 512 : (c > 2560 ? 2560 : c);  // 4 warps x (cap x 4 + 2 KiB) <= 48 KiB
-      if (c != b->stack_cap) b->occ = 0;
-      b->stack_cap = c;
-    }
     {
       // One walk for single-GPU and sharded steps alike: a sharded step stays bit-identical to the single-GPU one.
       // (On 8 ranks the 0.24 ms record pass per 16 Mi bodies, paid by every rank, slightly exceeds the ~4 % it saves
@@ -1095,6 +1089,15 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
       if (const char* we = getenv("NB_BH_WALK")) wp = strcmp(we, "nodes") != 0;
       if (wp != b->walk_pairs) b->occ = 0;
       b->walk_pairs = wp;
+    }
+    if (const char* ce = getenv("NB_BH_STACK")) {
+      // 48 KiB of dynamic shared memory without opt-in: 4 warps x (cap x 4 B + list and staging: 2 KiB node walk,
+      // 3.5 KiB pair walk)
+      const int cmax = b->walk_pairs ? 2176 : 2560;
+      int c = atoi(ce);
+      c = c < 512 ? 512 : (c > cmax ? cmax : c);
+      if (c != b->stack_cap) b->occ = 0;
+      b->stack_cap = c;
     }
     if (const char* he = getenv("NB_BH_HYBRID")) b->hybrid = atoi(he) != 0;
     if (const char* pe = getenv("NB_BH_PIPELINE")) b->pipeline = atoi(pe) != 0;
