@@ -1090,11 +1090,12 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
       if (wp != b->walk_pairs) b->occ = 0;
       b->walk_pairs = wp;
     }
-    if (const char* ce = getenv("NB_BH_STACK")) {
+    {
       // 48 KiB of dynamic shared memory without opt-in: 4 warps x (cap x 4 B + list and staging: 2 KiB node walk,
       // 3.5 KiB pair walk)
       const int cmax = b->walk_pairs ? 2176 : 2560;
-      int c = atoi(ce);
+      int c = b->stack_cap;
+      if (const char* ce = getenv("NB_BH_STACK")) c = atoi(ce);
       c = c < 512 ? 512 : (c > cmax ? cmax : c);
       if (c != b->stack_cap) b->occ = 0;
       b->stack_cap = c;
