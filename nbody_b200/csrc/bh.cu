@@ -1093,7 +1093,7 @@ int bh_build(nb_context* ctx, const nb_particles* d, cudaStream_t st) {
     {
       // 48 KiB of dynamic shared memory without opt-in: 4 warps x (cap x 4 B + list and staging: 2 KiB node walk,
       // 3.5 KiB pair walk)
-      const int cmax = b->walk_pairs ? 2176 : 2560;
+      const int cmax = b->walk_pairs ? 2176 : 2528;  // the node walk also holds a 128-byte static table
       int c = b->stack_cap;
       if (const char* ce = getenv("NB_BH_STACK")) c = atoi(ce);
       c = c < 512 ? 512 : (c > cmax ? cmax : c);

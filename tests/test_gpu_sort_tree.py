@@ -197,6 +197,30 @@ def test_bh_forces_degenerate_inputs_vs_lbvh_oracle(orc, kind, walk):
     assert err.max() <= 1e-5 * max(ref.max(), 1e-30)
 
 
+@pytest.mark.parametrize("walk", ["pairs", "nodes"], indirect=True)
+@pytest.mark.parametrize("cap", ["100", "100000"])
+def test_bh_stack_capacity_knob_is_clamped(orc, walk, cap, monkeypatch):
+    """NB_BH_STACK outside the supported range (the warp stacks, list and staging of a CTA must fit 48 KiB of shared
+    memory) is clamped, not passed on to a launch that would fail; the forces do not depend on the capacity."""
+    from nbody_b200 import ics
+    st = ics.plummer(20000, seed=12)
+    d0, calc0 = _build(st, 0.5)
+    a0 = d0.numpy()
+    monkeypatch.setenv("NB_BH_STACK", cap)
+    d1, calc1 = _build(st, 0.5)
+    a1 = d1.numpy()
+    for k in ("acc_x", "acc_y", "acc_z"):
+        assert np.array_equal(a0[k].view(np.uint32), a1[k].view(np.uint32)), k
+    import ctypes as C
+    import nbody_b200 as nb
+    from nbody_b200 import _lib
+    deep, capacity = C.c_int(0), C.c_int(0)
+    _lib.check(_lib.lib().nb_bh_max_stack(nb.get_context().handle, C.byref(deep), C.byref(capacity)))
+    assert 512 <= capacity.value <= 2560 and 0 < deep.value <= capacity.value
+    monkeypatch.setenv("NB_BH_STACK", "1280")
+    _build(st, 0.5)   # back to the default capacity for the tests that follow (the library keeps the last setting)
+
+
 def test_bh_vs_octree_oracle_and_direct(orc):
     """Stated tolerance: at equal theta the LBVH forces agree with the reference's
     intended octree algorithm within the Barnes-Hut error itself, and are no less accurate."""
