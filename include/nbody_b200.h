@@ -189,7 +189,9 @@ int nb_sh_forces(nb_context* ctx, const nb_particles* d, float cutoff, float G, 
 int nb_sh_export(nb_context* ctx, int32_t dims[3], float bbox_padded[6], int32_t* particle_cell,
                  int32_t* cell_start, int32_t* cell_end, int32_t* sorted_indices);
 int nb_sh_total_cells(nb_context* ctx, int* total_cells);
-/* body-body pairs inside the cutoff evaluated by the last nb_sh_forces (ordered pairs, self excluded) */
+/* body-body pairs inside the cutoff evaluated by the last nb_sh_forces (ordered pairs, self excluded).  A measurement
+ * hook: counted on demand by a second sweep over the grid of the last nb_sh_build (same loop and test as the force
+ * evaluation, no force arithmetic), so the timed force kernel carries no counters; synchronises the device. */
 int nb_sh_stats(nb_context* ctx, uint64_t* pairs);
 
 /* ---- stand-alone primitives (exported for tests and reuse) ---------------------------------- */

@@ -55,6 +55,8 @@ struct SH {
   int32_t* idx_sorted = nullptr;
   SHMisc* h_misc = nullptr;
   bool built = false;
+  float stats_cutoff2 = -1.f;  // cutoff^2 of the last force evaluation (< 0: none yet)
+  bool stats_valid = false;    // misc->pairs holds the count of that evaluation
 };
 
 namespace nb {
@@ -231,7 +233,10 @@ __global__ void __launch_bounds__(256) sh_pair_fill_kernel(const uint32_t* __res
 #else
 #define NB_SH_BOUNDS __launch_bounds__(128)
 #endif
-template <bool EPS0>
+// FORCE / COUNT: the timed force evaluation does not count the in-cutoff pairs (four integer instructions per
+// candidate, each paid at FP32-pipe rates on this SM: DESIGN.md 3.5); nb_sh_stats counts them on demand with the
+// COUNT-only instantiation, same loop, same test.
+template <bool EPS0, bool FORCE, bool COUNT>
 __global__ void NB_SH_BOUNDS sh_force_kernel(size_t n, const float4* __restrict__ spos,
                                                        const uint32_t* __restrict__ keys,
                                                        const int32_t* __restrict__ sidx,
@@ -277,41 +282,49 @@ __global__ void NB_SH_BOUNDS sh_force_kernel(size_t n, const float4* __restrict_
         for (int jj = j0; jj < j1; jj++) {
           const float4 c = __ldg(spos + jj);
           const f2 ddx = sub2(pk(c.x, c.x), xi), ddy = sub2(pk(c.y, c.y), yi), ddz = sub2(pk(c.z, c.z), zi);
-          const f2 d2 = add2(add2(mul2(ddx, ddx), mul2(ddy, ddy)), mul2(ddz, ddz));
+          // dx*dx + dy*dy + dz*dz (:131) as the reference's binary evaluates it (nvcc contracts it to
+          // FMUL dy*dy, FFMA dx*dx + ., FFMA dz*dz + . -- SASS of oracle/_ref): the cutoff decision below is
+          // bit-identical to the reference's
+          const f2 d2 = fma2(ddz, ddz, fma2(ddx, ddx, mul2(ddy, ddy)));
           float r0, r1;
           upk(d2, r0, r1);
           const bool in0 = (r0 < cutoff2), in1 = (r1 < cutoff2);  // un-softened test (:131-135)
-          cnt += (in0 ? 1u : 0u) + ((in1 && two) ? 1u : 0u);
-          upk(add2(d2, e2), r0, r1);
-          float i0 = rsq(r0), i1 = rsq(r1);
-          if (EPS0) {
-            i0 = (r0 > eps2) ? i0 : 0.f;
-            i1 = (r1 > eps2) ? i1 : 0.f;
+          if (COUNT) cnt += (in0 ? 1u : 0u) + ((in1 && two) ? 1u : 0u);
+          if (FORCE) {
+            upk(add2(d2, e2), r0, r1);
+            float i0 = rsq(r0), i1 = rsq(r1);
+            if (EPS0) {
+              i0 = (r0 > eps2) ? i0 : 0.f;
+              i1 = (r1 > eps2) ? i1 : 0.f;
+            }
+            i0 = in0 ? i0 : 0.f;
+            i1 = in1 ? i1 : 0.f;
+            const f2 inv = pk(i0, i1);
+            const float gm = G * c.w;
+            const f2 f = mul2(pk(gm, gm), mul2(mul2(inv, inv), inv));
+            sx = fma2(f, ddx, sx);
+            sy = fma2(f, ddy, sy);
+            sz = fma2(f, ddz, sz);
           }
-          i0 = in0 ? i0 : 0.f;
-          i1 = in1 ? i1 : 0.f;
-          const f2 inv = pk(i0, i1);
-          const float gm = G * c.w;
-          const f2 f = mul2(pk(gm, gm), mul2(mul2(inv, inv), inv));
-          sx = fma2(f, ddx, sx);
-          sy = fma2(f, ddy, sy);
-          sz = fma2(f, ddz, sz);
         }
       }
     }
-    float a, b;
-    const int i = sidx[k0];
-    const int i2 = two ? sidx[k0 + 1] : i;
-    upk(sx, a, b); ax[i] = a; if (two) ax[i2] = b;
-    upk(sy, a, b); ay[i] = a; if (two) ay[i2] = b;
-    upk(sz, a, b); az[i] = a; if (two) az[i2] = b;
-    if (cutoff2 > 0.f) cnt -= two ? 2u : 1u;  // the bodies themselves (inside their own run; r = 0 passes the test unless cutoff = 0)
+    if (FORCE) {
+      float a, b;
+      const int i = sidx[k0];
+      const int i2 = two ? sidx[k0 + 1] : i;
+      upk(sx, a, b); ax[i] = a; if (two) ax[i2] = b;
+      upk(sy, a, b); ay[i] = a; if (two) ay[i2] = b;
+      upk(sz, a, b); az[i] = a; if (two) az[i2] = b;
+    }
+    if (COUNT && cutoff2 > 0.f) cnt -= two ? 2u : 1u;  // the bodies themselves (inside their own run; r = 0 passes the test unless cutoff = 0)
   }
-  // one atomic per warp
-  unsigned long long c = cnt;
+  if (COUNT) {  // one atomic per warp
+    unsigned long long c = cnt;
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
-  if ((threadIdx.x & 31) == 0 && c) atomicAdd(pairs, c);
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(pairs, c);
+  }
 }
 
 static SH* sh_get(nb_context* ctx) {
@@ -338,6 +351,8 @@ int sh_build(nb_context* ctx, const nb_particles* d, float cell, cudaStream_t st
   }
   const size_t n = d->count;
   s->built = false;
+  s->stats_valid = false;
+  s->stats_cutoff2 = -1.f;
   if (!(cell > 0.f) || std::isnan(cell) || std::isinf(cell)) {
     set_error("Spatial hash cell size must be positive and finite");
     return NB_ERR_INVALID;
@@ -436,7 +451,8 @@ int sh_forces(nb_context* ctx, const nb_particles* d, float cutoff, float G, flo
     return NB_ERR_INVALID;
   }
   SHMisc* misc = s->misc.as<SHMisc>();
-  NB_CUDA(cudaMemsetAsync(&misc->pairs, 0, sizeof(unsigned long long), st));
+  s->stats_cutoff2 = cutoff * cutoff;  // nb_sh_stats counts the pairs of this evaluation on demand
+  s->stats_valid = false;
   const float eps2 = eps * eps;
   ProfScope prof(ctx, st);
   NB_STAGE(ctx, st, "sh.force");
@@ -445,7 +461,7 @@ int sh_forces(nb_context* ctx, const nb_particles* d, float cutoff, float G, flo
   if ((size_t)s->total_cells < nonempty_bound) nonempty_bound = (size_t)s->total_cells;
   const size_t threads = (n + nonempty_bound + 1) / 2;
 #define NB_SH_LAUNCH(E_)                                                                                             \
-  sh_force_kernel<E_><<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(                                            \
+  sh_force_kernel<E_, true, false><<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(                              \
       n, s->spos.as<float4>(), s->keys_sorted, s->idx_sorted, s->pair_slot.as<int32_t>(),                            \
       s->cell_start.as<int32_t>(), s->cell_end.as<int32_t>(), misc, s->cell_size, cutoff * cutoff, G, eps2,         \
       d->acc_x, d->acc_y, d->acc_z, &misc->pairs)
@@ -487,7 +503,29 @@ int nb_sh_stats(nb_context* ctx, uint64_t* pairs) {
   }
   NB_CUDA(cudaSetDevice(ctx->device));
   NB_CUDA(cudaDeviceSynchronize());
-  NB_CUDA(cudaMemcpy(pairs, &ctx->sh->misc.as<SHMisc>()->pairs, 8, cudaMemcpyDeviceToHost));
+  SH* s = ctx->sh;
+  SHMisc* misc = s->misc.as<SHMisc>();
+  if (s->stats_cutoff2 < 0.f) {  // no force evaluation on this grid yet
+    *pairs = 0;
+    return NB_OK;
+  }
+  if (!s->stats_valid) {
+    // counted on demand: the same sweep and the same test as the force evaluation, without the force arithmetic
+    // (the cell-ordered bodies of the last build are still in place)
+    const size_t n = s->n;
+    NB_CUDA(cudaMemset(&misc->pairs, 0, sizeof(unsigned long long)));
+    size_t nonempty_bound = n;
+    if ((size_t)s->total_cells < nonempty_bound) nonempty_bound = (size_t)s->total_cells;
+    const size_t threads = (n + nonempty_bound + 1) / 2;
+    sh_force_kernel<false, false, true><<<(unsigned)((threads + 127) / 128), 128>>>(
+        n, s->spos.as<float4>(), s->keys_sorted, s->idx_sorted, s->pair_slot.as<int32_t>(),
+        s->cell_start.as<int32_t>(), s->cell_end.as<int32_t>(), misc, s->cell_size, s->stats_cutoff2, 0.f, 0.f,
+        nullptr, nullptr, nullptr, &misc->pairs);
+    NB_LAUNCH_CHECK(ctx);
+    NB_CUDA(cudaDeviceSynchronize());
+    s->stats_valid = true;
+  }
+  NB_CUDA(cudaMemcpy(pairs, &misc->pairs, 8, cudaMemcpyDeviceToHost));
   return NB_OK;
 }
 

@@ -85,7 +85,10 @@ void orc_spatial_forces(int n, const float* px, const float* py, const float* pz
             int j = sorted_indices[k];
             if (j == i) continue;
             float ddx = px[j] - xi, ddy = py[j] - yi, ddz = pz[j] - zi;
-            float dist2 = ddx * ddx + ddy * ddy + ddz * ddz;
+            /* :131 as the reference's BINARY evaluates it: nvcc (default -fmad=true) contracts dx*dx + dy*dy + dz*dz
+             * to FMUL dy*dy, FFMA dx*dx + ., FFMA dz*dz + . (SASS of oracle/_ref/libnbody_ref.so,
+             * spatialHashForceKernel); the in-cutoff decision follows that rounding */
+            float dist2 = fmaf(ddz, ddz, fmaf(ddx, ddx, ddy * ddy));
             if (dist2 < cutoff2) {
               dist2 += eps2;
               float inv = 1.0f / sqrtf(dist2);

@@ -67,6 +67,15 @@ def test_grid_forces_vs_oracle(orc, n, cell, cutoff):
     ratio = err / np.maximum(np.maximum(mag, rms), 1e-30)
     assert ratio.max() <= 1e-5, f"max err ratio {ratio.max():.3e} (plain relative {np.max(err / np.maximum(mag, 1e-30)):.3e})"
     assert np.isfinite(out["acc_x"]).all()
+    # in-cutoff pairs, counted on demand by nb_sh_stats with the force sweep's own test: exact (the oracle evaluates
+    # r^2 with the contraction of the reference's binary, as the kernel does), and stable when asked twice
+    import ctypes as C
+    import nbody_b200 as nb
+    from nbody_b200 import _lib
+    got = C.c_uint64(0)
+    for _ in range(2):
+        _lib.check(_lib.lib().nb_sh_stats(nb.get_context().handle, C.byref(got)))
+        assert got.value == pairs
 
 
 def test_cell_index_anchor(orc):
