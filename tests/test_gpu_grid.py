@@ -78,6 +78,33 @@ def test_grid_forces_vs_oracle(orc, n, cell, cutoff):
         assert got.value == pairs
 
 
+def test_pair_count_follows_the_last_force_evaluation(orc):
+    """nb_sh_stats counts on demand: 0 on a grid no forces were evaluated on, the count of the LAST evaluation's
+    cutoff afterwards, and a rebuild forgets it."""
+    import ctypes as C
+    import nbody_b200 as nb
+    from nbody_b200 import _lib, ics
+    L, ctx = _lib.lib(), nb.get_context()
+    st = ics.uniform_box(5000, -4, 4, seed=3)
+    h = nb.ParticleDataManager.fromState(st)
+    d = nb.ParticleData()
+    nb.ParticleDataManager.allocateDevice(d, h.count)
+    nb.ParticleDataManager.copyToDevice(d, h)
+    got = C.c_uint64(123)
+    _lib.check(L.nb_sh_build(ctx.handle, C.byref(d.c), 1.0, None))
+    _lib.check(L.nb_sh_stats(ctx.handle, C.byref(got)))
+    assert got.value == 0
+    grid = orc.grid_build(st["pos_x"], st["pos_y"], st["pos_z"], 1.0)
+    for cutoff in (2.0, 0.7, 0.0):
+        _lib.check(L.nb_sh_forces(ctx.handle, C.byref(d.c), cutoff, 1.0, 0.05, None))
+        _lib.check(L.nb_sh_stats(ctx.handle, C.byref(got)))
+        want = orc.spatial_forces(st["pos_x"], st["pos_y"], st["pos_z"], st["mass"], grid, cutoff, 1.0, 0.05)[3]
+        assert got.value == want, cutoff
+    _lib.check(L.nb_sh_build(ctx.handle, C.byref(d.c), 1.0, None))
+    _lib.check(L.nb_sh_stats(ctx.handle, C.byref(got)))
+    assert got.value == 0
+
+
 def test_cell_index_anchor(orc):
     """tests/test_spatial_hash.cpp:38-51"""
     assert orc.cell_index(0.5, 0.5, 0.5, 2.0) == (0, 0, 0)
