@@ -26,6 +26,9 @@ int launch_scan_tiles(nb_context* ctx, unsigned long long* tile_sum, int ntiles,
                       cudaStream_t st);  // render.cu
 }  // namespace nb
 
+#ifndef NB_SH_SATMASK
+#define NB_SH_SATMASK 0  // build-time knob (experiment): cutoff applied as a saturated FFMA mask instead of compare + select
+#endif
 #ifndef NB_SH_UNROLL
 #define NB_SH_UNROLL 4  // candidates per trip of the sweep (build-time tuning knob)
 #endif
@@ -267,6 +270,9 @@ __global__ void NB_SH_BOUNDS sh_force_kernel(size_t n, const float4* __restrict_
     const int cz = (int)floorf(__fdiv_rn(__fsub_rn(mez, m->bbox[2]), cell));
     const f2 e2 = pk(eps2, eps2);
     f2 sx = pk(0.f, 0.f), sy = sx, sz = sx;
+#if NB_SH_SATMASK
+    const float sat_big = __fdividef(1.2676506e30f, fmaxf(cutoff2, 1e-30f)), sat_c = sat_big * cutoff2;
+#endif
     for (int dz = -1; dz <= 1; dz++) {
       const int z = cz + dz;
       if (z < 0 || z >= nz) continue;
@@ -289,6 +295,9 @@ __global__ void NB_SH_BOUNDS sh_force_kernel(size_t n, const float4* __restrict_
           float r0, r1;
           upk(d2, r0, r1);
           const bool in0 = (r0 < cutoff2), in1 = (r1 < cutoff2);  // un-softened test (:131-135)
+#if NB_SH_SATMASK
+          const float r2a = r0, r2b = r1;
+#endif
           if (COUNT) cnt += (in0 ? 1u : 0u) + ((in1 && two) ? 1u : 0u);
           if (FORCE) {
             upk(add2(d2, e2), r0, r1);
@@ -297,9 +306,17 @@ __global__ void NB_SH_BOUNDS sh_force_kernel(size_t n, const float4* __restrict_
               i0 = (r0 > eps2) ? i0 : 0.f;
               i1 = (r1 > eps2) ? i1 : 0.f;
             }
+#if NB_SH_SATMASK
+            // experiment: the cutoff as a saturated multiply-add on the FP32 pipe (mask = 1 inside, 0 outside or on
+            // the cutoff; BIG = 2^100 / cutoff^2, so one ulp of r^2 below the cutoff already saturates) instead of
+            // two compares and two selects on the integer pipe
+            const float k0_ = __saturatef(fmaf(-sat_big, r2a, sat_c)), k1_ = __saturatef(fmaf(-sat_big, r2b, sat_c));
+            const f2 inv = mul2(pk(i0, i1), pk(k0_, k1_));
+#else
             i0 = in0 ? i0 : 0.f;
             i1 = in1 ? i1 : 0.f;
             const f2 inv = pk(i0, i1);
+#endif
             const float gm = G * c.w;
             const f2 f = mul2(pk(gm, gm), mul2(mul2(inv, inv), inv));
             sx = fma2(f, ddx, sx);
