@@ -172,13 +172,23 @@ constexpr int TB_MAX_ROOTS = 128;               // subtrees left per tile: two s
 // thread j's leaf i sits at (TB_K + 1) j + i: an odd stride, no shared-memory bank conflicts in phase 1
 __device__ __forceinline__ int tb_pad(int q) { return q + q / TB_K; }
 
+#ifndef NB_BH_COM_RCP
+#define NB_BH_COM_RCP 0  // build-time knob (experiment, changes the last bit of the centres of mass: not the oracle's formula)
+#endif
 __device__ __forceinline__ float4 bh_combine(const float4& a, const float4& b) {
   const float ms = __fadd_rn(a.w, b.w);
   float4 c;
   if (ms > 0.f) {
+#if NB_BH_COM_RCP
+    const float inv = __frcp_rn(ms);  // experiment: one IEEE reciprocal and three multiplies instead of three divides
+    c.x = __fmul_rn(__fadd_rn(__fmul_rn(a.x, a.w), __fmul_rn(b.x, b.w)), inv);
+    c.y = __fmul_rn(__fadd_rn(__fmul_rn(a.y, a.w), __fmul_rn(b.y, b.w)), inv);
+    c.z = __fmul_rn(__fadd_rn(__fmul_rn(a.z, a.w), __fmul_rn(b.z, b.w)), inv);
+#else
     c.x = __fdiv_rn(__fadd_rn(__fmul_rn(a.x, a.w), __fmul_rn(b.x, b.w)), ms);
     c.y = __fdiv_rn(__fadd_rn(__fmul_rn(a.y, a.w), __fmul_rn(b.y, b.w)), ms);
     c.z = __fdiv_rn(__fadd_rn(__fmul_rn(a.z, a.w), __fmul_rn(b.z, b.w)), ms);
+#endif
   } else {
     c.x = a.x; c.y = a.y; c.z = a.z;
   }
