@@ -172,6 +172,9 @@ constexpr int TB_MAX_ROOTS = 128;               // subtrees left per tile: two s
 // thread j's leaf i sits at (TB_K + 1) j + i: an odd stride, no shared-memory bank conflicts in phase 1
 __device__ __forceinline__ int tb_pad(int q) { return q + q / TB_K; }
 
+#ifndef NB_BH_SCALAR
+#define NB_BH_SCALAR 0  // build-time knob (experiment): scalar FFMA pair body for two bodies per lane instead of packed fp32x2
+#endif
 #ifndef NB_BH_COM_RCP
 #define NB_BH_COM_RCP 0  // build-time knob (experiment, changes the last bit of the centres of mass: not the oracle's formula)
 #endif
@@ -663,7 +666,7 @@ struct BhGroup {
   // the monopole term (:175-181) of one list entry {x, y, z, G * M} for the lane's bodies
   __device__ __forceinline__ void add(const float4 p) {
     const float gm = p.w;
-    if constexpr (BPL == 2) {
+    if constexpr (BPL == 2 && !NB_BH_SCALAR) {
       // the lane's two bodies as one packed fp32x2 pair (FADD2/FFMA2/FMUL2, as in direct.cu)
       const f2 dx = sub2(pk(p.x, p.x), xi2), dy = sub2(pk(p.y, p.y), yi2), dz = sub2(pk(p.z, p.z), zi2);
       const f2 d2 = fma2(dz, dz, fma2(dy, dy, fma2(dx, dx, e2)));
@@ -710,7 +713,7 @@ struct BhGroup {
   __device__ __forceinline__ void store(int k0, int gcnt, int lane, const int32_t* __restrict__ perm,
                                         float* __restrict__ ax, float* __restrict__ ay, float* __restrict__ az,
                                         const BhShard& sh) {
-    if constexpr (BPL == 2) {
+    if constexpr (BPL == 2 && !NB_BH_SCALAR) {
       upk(sx2, sx[0], sx[1]);
       upk(sy2, sy[0], sy[1]);
       upk(sz2, sz[0], sz[1]);
