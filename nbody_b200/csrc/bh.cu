@@ -1248,6 +1248,10 @@ int bh_forces(nb_context* ctx, const nb_particles* d, float theta, float G, floa
     else
       cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, bh_force_kernel<1, false, false>, BH_WARPS * 32, smem);
     b->occ = o > 0 ? o : 1;
+    if (const char* oe = getenv("NB_BH_OCC")) {  // tuning knob: resident CTAs per SM of the traversal
+      const int v = atoi(oe);
+      if (v > 0 && v < b->occ) b->occ = v;
+    }
   }
   long long max_groups = (long long)n;  // upper bound (the real count lives on the device)
   long long want = (max_groups + BH_WARPS - 1) / BH_WARPS;
