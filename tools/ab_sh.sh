@@ -1,3 +1,6 @@
+#!/bin/bash
+# same-box A/B of spatial-hash builds at 10 M bodies, after the grid tests on the default build:
+#   TAGS="default <tag> ..." OUT=name.jsonl tools/ab_sh.sh      (<tag> = a tools/build_variant.sh library)
 out=gpurun_out/${OUT:-r02_sh_force_ab.jsonl}; : > $out
 python -m pytest tests/test_gpu_grid.py tests/test_gpu_full_size_parity.py tests/test_gpu_vs_reference.py tests/test_gpu_reference_suite.py -m gpu -x -q -k "sh or grid or spatial or hash" 2>&1 | tail -4
 for tag in ${TAGS:-default shold default shold}; do

@@ -1,3 +1,5 @@
+#!/bin/bash
+# ncu launch list of the 16 Mi Barnes-Hut step and one --set full capture of the pair-walk traversal (gpurun, 1 GPU)
 export PYTHONPATH=$PWD
 M=gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum
 ncu --metrics $M --clock-control none -c 400 --csv --log-file gpurun_out/r02_bh16_launches_v8.csv python tools/bench_paths.py bh 16777216 plummer > /dev/null 2>&1
