@@ -127,7 +127,8 @@ int nb_direct_forces(nb_context* ctx, const nb_particles* d, float G, float eps2
  * of 17 MiB + 256 B that every GPU loading the library holds until exit.  Limit: d->count <=
  * NB_DIRECT_STATIC_MAX_BODIES, beyond it NB_ERR_INVALID with a message and nothing launched.  Calls no cudaMalloc,
  * cudaFree or allocating library routine (the first call per device resolves the array's device address with
- * cudaGetSymbolAddress and queries kernel occupancy; nothing is allocated).  All calls share the array: calls that
+ * cudaGetSymbolAddress and queries kernel occupancy; nothing is allocated -- make that first call outside stream
+ * capture).  All calls share the array: calls that
  * overlap on the GPU race -- keep them on one stream, or order them.  Results: bit-identical to nb_direct_forces
  * for count <= 16384; above that the partial sums of a target tile are grouped into fewer chunks to fit the array,
  * so results agree to summation rounding (same pair terms). */
