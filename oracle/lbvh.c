@@ -123,10 +123,12 @@ void orc_set_hybrid_slack(int from) { g_hybrid_slack_from = from; }
 /* experiment knobs / counters of the walk (tools/ and tests/measure_* only) */
 static int g_leaf_bucket = 0;      /* a rejected node with at most this many leaves hands over all its leaves */
 static uint64_t g_walk_pops = 0;   /* nodes popped by the last orc_lbvh_forces_ex call */
+static uint64_t g_walk_rounds = 0; /* rounds (pops of up to 32 entries) of that call */
 void orc_set_leaf_bucket(int b) { g_leaf_bucket = b; }
 static int g_walk_pairs = 1;       /* 1: restate bh_force_pairs_kernel (the default walk), 0: bh_force_kernel (NB_BH_WALK=nodes) */
 void orc_set_walk_pairs(int on) { g_walk_pairs = on; }
 uint64_t orc_get_walk_pops(void) { return g_walk_pops; }
+uint64_t orc_get_walk_rounds(void) { return g_walk_rounds; }
 static void hybrid_groups(int ni, int leaf0, int group, const int32_t* left, const int32_t* right,
                           const int32_t* range_first, const int32_t* range_last, int32_t* gfirst, int32_t* gcount,
                           int* ngroups) {
@@ -203,7 +205,7 @@ void orc_lbvh_forces_ex(int n, const int32_t* left, const int32_t* right, const 
     size2_of[L] = s * s;
   }
   size2_of[31] = 0.0f;
-  uint64_t total = 0, entries = 0, pops = 0;
+  uint64_t total = 0, entries = 0, pops = 0, rounds = 0;
   const int bucket = g_leaf_bucket;
   /* groups: top-down, a node whose leaf range fits becomes a group */
   int32_t* gfirst = (int32_t*)malloc(sizeof(int32_t) * (size_t)n);
@@ -235,7 +237,7 @@ void orc_lbvh_forces_ex(int n, const int32_t* left, const int32_t* right, const 
     }
     free(st);
   }
-#pragma omp parallel for schedule(dynamic, 16) reduction(+ : total, entries, pops)
+#pragma omp parallel for schedule(dynamic, 16) reduction(+ : total, entries, pops, rounds)
   for (int g = 0; g < ngroups; g++) {
     const int k0 = gfirst[g], cnt = gcount[g];
     float accx[64], accy[64], accz[64];
@@ -258,6 +260,7 @@ void orc_lbvh_forces_ex(int n, const int32_t* left, const int32_t* right, const 
       for (int l = 0; l < m; l++) popped[l] = stack[sp - m + l];
       sp -= m;
       pops += (uint64_t)m;
+      rounds++;
       int32_t push[64];
       int np = 0;
       /* pair walk (bh_force_pairs_kernel): the stack holds nodes to OPEN; lane l tests both children of its node,
@@ -346,6 +349,7 @@ void orc_lbvh_forces_ex(int n, const int32_t* left, const int32_t* right, const 
   free(gcount);
   if (interactions) *interactions = total;
   g_walk_pops = pops;
+  g_walk_rounds = rounds;
   if (stats) {
     stats[0] = (uint64_t)ngroups;
     stats[1] = entries;

@@ -123,6 +123,7 @@ float orc_lbvh_cell_size(int prefix_len, const float bbox[6]);
 void orc_set_hybrid_slack(int from);
 void orc_set_leaf_bucket(int b);   /* experiment knob of the walk, see lbvh.c */
 uint64_t orc_get_walk_pops(void);
+uint64_t orc_get_walk_rounds(void);
 void orc_set_walk_pairs(int on);  /* 1 (default): restate bh_force_pairs_kernel; 0: bh_force_kernel (NB_BH_WALK=nodes) */
 void orc_lbvh_forces_ex(int n, const int32_t* left, const int32_t* right, const int32_t* prefix,
                         const int32_t* range_first, const int32_t* range_last, const float* node_com,
